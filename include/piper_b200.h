@@ -1,0 +1,177 @@
+/*
+ * piper_b200.h - C ABI of the B200-native Piper-VITS inference runtime.
+ *
+ * This is the drop-in boundary for the reference's hot path: everything under
+ * PiperMetalRuntime.synthesize (Sources/PiperMetal/PiperMetalRuntime.swift:62-80) ->
+ * GraphExecutor.executeOutput (Sources/PiperMetal/Execution/GraphExecutor.swift:156-327)
+ * -> 2755 x executeNode -> MetalBackend -> the .metal kernels.  A Swift (or C++/Python)
+ * host binds these symbols instead of constructing a GraphExecutor; see INTEGRATION.md
+ * for the SwiftPM module and the PiperCUDARuntime wrapper that keeps the
+ * synthesize(phonemeIDs:noiseScale:lengthScale:noiseW:) signature.
+ *
+ * Plain C: pointers and sizes only.  No exceptions cross this boundary; every call
+ * returns a status code and piper_b200_last_error() gives the message (the reference
+ * throws ExecutionError / NSError, CPUBackend.swift:3-17, PiperMetalRuntime.swift:74-78).
+ *
+ * Threading: one context per GPU; calls on one context must be serialised by the caller
+ * (the reference's runtime is likewise single-caller, GraphExecutor.swift:27,33).
+ */
+#ifndef PIPER_B200_H
+#define PIPER_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PIPER_B200_ABI_VERSION 1
+
+/* status codes */
+#define PIPER_B200_OK 0
+#define PIPER_B200_ERR_INVALID_ARGUMENT 1  /* ~ ExecutionError.shapeMismatch / typeMismatch */
+#define PIPER_B200_ERR_IO 2                /* file unreadable */
+#define PIPER_B200_ERR_DECODE 3            /* ~ ONNXDecodingError (ONNXLoader.swift:3-21) */
+#define PIPER_B200_ERR_UNSUPPORTED 4       /* ~ ExecutionError.unsupportedOp: graph is not a Piper VITS export */
+#define PIPER_B200_ERR_CUDA 5              /* ~ ExecutionError.metalUnavailable / MetalBackend NSError */
+#define PIPER_B200_ERR_STATE 6             /* call order (not finalized, ...) */
+#define PIPER_B200_ERR_CAPACITY 7          /* durations exploded past the frame capacity */
+
+/* ONNX TensorProto.data_type values accepted by piper_b200_set_weight
+ * (the three dtypes of TensorValue.swift:4-8 plus int32, which widens to int64, :84-100) */
+#define PIPER_B200_DTYPE_F32 1
+#define PIPER_B200_DTYPE_I32 6
+#define PIPER_B200_DTYPE_I64 7
+#define PIPER_B200_DTYPE_BOOL 9
+
+/* arithmetic of the flow + HiFi-GAN convolutions (text encoder, duration predictor and
+ * length regulator always run in fp32 so that ceil() decisions match the fp32 oracle) */
+#define PIPER_B200_PRECISION_FP32 0        /* CUDA-core fp32 everywhere (parity mode) */
+#define PIPER_B200_PRECISION_BF16 1        /* tcgen05 kind::f16, bf16 operands, fp32 accumulate in TMEM */
+#define PIPER_B200_PRECISION_F16 2         /* tcgen05 kind::f16, fp16 operands, fp32 accumulate in TMEM */
+
+/* request flags */
+#define PIPER_B200_FLAG_IDS_ON_DEVICE 1u   /* phoneme_ids is a device pointer (lengths, speaker_ids stay host) */
+#define PIPER_B200_FLAG_KEEP_ON_DEVICE 2u  /* leave audio in HBM: result.audio is a device pointer */
+#define PIPER_B200_FLAG_KEEP_STAGES 4u     /* retain stage tensors for piper_b200_get_stage */
+#define PIPER_B200_FLAG_PCM16 8u           /* also produce int16 PCM (WavFileWriter.swift:20-30 rule) */
+
+typedef struct piper_b200_ctx piper_b200_ctx;
+
+/* Replaces PiperConfig (PiperConfig.swift:3-46) + what GraphExecutor learns from the graph. */
+typedef struct piper_b200_voice_info {
+  int32_t sample_rate;      /* audio.sample_rate */
+  int32_t num_symbols;      /* rows of enc_p.emb.weight */
+  int32_t num_speakers;     /* 1 for single-speaker voices */
+  int32_t hidden;           /* 192 */
+  int32_t hop;              /* samples per frame (256) */
+  int32_t dec_channels0;    /* upsample_initial_channel (256 medium / 512 high) */
+  int32_t resblock;         /* 1 or 2 */
+  int32_t n_ups;
+  float noise_scale;        /* inference.noise_scale  (PiperConfig.swift:16-20) */
+  float length_scale;       /* inference.length_scale */
+  float noise_w;            /* inference.noise_w */
+  int64_t n_params;         /* scalar count over all bound initializers */
+  double dec_flops_per_frame;   /* algorithmic FLOPs of the HiFi-GAN generator per frame */
+  double flow_flops_per_frame;
+  double enc_flops_per_id;      /* text encoder + duration predictor dense FLOPs per phoneme id */
+} piper_b200_voice_info;
+
+/* Replaces ExecutionInputs (GraphExecutor.swift:5-15), widened to a ragged batch.
+ * Utterance b owns ids[id_off_b .. id_off_b+lengths[b]) with id_off the running sum. */
+typedef struct piper_b200_request {
+  const int64_t* phoneme_ids;   /* concatenated over the batch */
+  const int64_t* lengths;       /* [batch]  (graph feed input_lengths) */
+  const int64_t* speaker_ids;   /* [batch] or NULL (graph feed sid) */
+  int32_t batch;
+  uint32_t flags;
+  float noise_scale;            /* scales[0]; NaN -> voice default (PiperMetalRuntime.swift:63-65) */
+  float length_scale;           /* scales[1] */
+  float noise_w;                /* scales[2] */
+  /* Determinism hook = the reference's `overrides` of the two RandomNormalLike outputs
+   * (GraphExecutor.swift:190-193, 2647-2651).  NULL -> generated on the device with the
+   * reference's own generator (elementwise.metal:132-163) seeded with `seed`. */
+  const float* noise_dp;        /* host, per utterance [2, lengths[b]] concatenated */
+  const float* noise_main;      /* host, per utterance [hidden, noise_main_stride] */
+  int64_t noise_main_stride;    /* frames available per utterance in noise_main */
+  uint64_t seed;                /* Options.seed (PiperMetalRuntime.swift:12-15); only low 32 bits used */
+} piper_b200_request;
+
+/* Replaces the [Float] return value (PiperMetalRuntime.swift:73-79).  Pointers stay valid
+ * until the next synthesize/destroy on the same context. */
+typedef struct piper_b200_result {
+  const float* audio;           /* concatenated utterances; pinned host memory (or device, see flags) */
+  const int16_t* pcm16;         /* only with PIPER_B200_FLAG_PCM16, same offsets */
+  const int64_t* sample_offsets;/* [batch+1] */
+  const int64_t* frame_lengths; /* [batch] y_lengths of the length regulator */
+  const int32_t* durations;     /* [sum lengths] ceil(w) per phoneme id, host */
+  int64_t total_samples;
+  int64_t total_frames;
+} piper_b200_result;
+
+/* Replaces GraphExecutor.RunTimings (GraphExecutor.swift:29-38). */
+typedef struct piper_b200_timings {
+  double wall_ms;               /* host wall clock of the call */
+  double gpu_ms;                /* CUDA events around all device work of the call */
+  double front_ms;              /* text encoder + duration predictor + length regulator */
+  double flow_ms;
+  double decoder_ms;
+  double h2d_ms, d2h_ms;
+  int64_t kernel_launches;      /* kernels launched by the call */
+  int64_t h2d_bytes, d2h_bytes;
+  double dec_flops, flow_flops; /* algorithmic FLOPs executed by the call */
+} piper_b200_timings;
+
+int piper_b200_abi_version(void);
+const char* piper_b200_last_error(const piper_b200_ctx* ctx);   /* ctx may be NULL */
+
+/* MetalContext.init (MetalContext.swift:11-32): device + stream + kernel module */
+int piper_b200_create(int device, piper_b200_ctx** out);
+void piper_b200_destroy(piper_b200_ctx* ctx);
+
+/* Route A - C++ twin of PiperMetalRuntime.init(modelURL:configURL:) (PiperMetalRuntime.swift:37-41):
+ * parses the .onnx (ONNXLoader.swift:25-61) and .onnx.json (PiperConfig.swift:41-45), binds, finalizes. */
+int piper_b200_load_voice(piper_b200_ctx* ctx, const char* model_path, const char* config_path);
+
+/* Route B - a host that already parsed the model (Swift PiperONNX) pushes initializers
+ * (ONNXIR.swift:23-93 tensors) and the Conv/ConvTranspose attributes, then finalizes. */
+int piper_b200_set_weight(piper_b200_ctx* ctx, const char* name, int32_t dtype, const int64_t* dims,
+                          int32_t rank, const void* data, size_t bytes);
+int piper_b200_set_conv_attr(piper_b200_ctx* ctx, const char* weight_name, int32_t stride,
+                             int32_t dilation, int32_t group, int32_t pad_begin, int32_t pad_end);
+int piper_b200_set_config(piper_b200_ctx* ctx, int32_t sample_rate, int32_t num_speakers,
+                          float noise_scale, float length_scale, float noise_w);
+int piper_b200_finalize(piper_b200_ctx* ctx);   /* recognise the VITS graph, repack to kernel layouts */
+
+int piper_b200_get_voice_info(const piper_b200_ctx* ctx, piper_b200_voice_info* out);
+int piper_b200_set_precision(piper_b200_ctx* ctx, int32_t precision);
+int piper_b200_set_stream(piper_b200_ctx* ctx, void* cuda_stream);   /* NULL -> the context's own stream */
+
+/* GraphExecutor.executeOutput (GraphExecutor.swift:156) for a ragged batch. */
+int piper_b200_synthesize(piper_b200_ctx* ctx, const piper_b200_request* req, piper_b200_result* res);
+int piper_b200_get_timings(const piper_b200_ctx* ctx, piper_b200_timings* out);
+
+/* Parity hooks = GraphExecutor.execute(inputs:maxNodeIndex:overrides:) (GraphExecutor.swift:75-152),
+ * which returns intermediates for node-by-node diffing.  After a synthesize with
+ * PIPER_B200_FLAG_KEEP_STAGES, copies stage `name` of utterance `utt` to dst in the graph's
+ * [channels, length] layout.  Names: "x","m_p","logs_p","logw","z_p","z".
+ * dst==NULL queries the shape only. */
+int piper_b200_get_stage(piper_b200_ctx* ctx, const char* name, int32_t utt, float* dst,
+                         int64_t capacity, int64_t* channels, int64_t* length);
+
+/* The integer-exact part on its own: Exp, Mul, Ceil, ReduceSum, Clip, Cast,
+ * CumSum, Range/Less path -> frame-to-phoneme index.  logw is host memory, concatenated
+ * over the batch.  frame_index is written per utterance at frame_capacity stride, -1 marks
+ * frames no phoneme covers. */
+int piper_b200_length_regulate(piper_b200_ctx* ctx, const float* logw, const int64_t* lengths,
+                               int32_t batch, float length_scale, int32_t* durations,
+                               int64_t* frame_lengths, int32_t* frame_index, int64_t frame_capacity);
+
+/* RandomNormalLike with the reference's generator (elementwise.metal:132-163). */
+int piper_b200_random_normal(piper_b200_ctx* ctx, uint64_t seed, int64_t count, float* dst_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PIPER_B200_H */

@@ -1,0 +1,120 @@
+// Launch interface of the sm_100a kernels (definitions in kernels_f32.cu / conv_tc.cu).
+// Activations are "packed rows": all utterances of a batch lie one after another along
+// the time axis, separated by zero gap rows; a buffer is [rows][channels] fp32
+// (channels contiguous).  Every producer writes ALL rows [0,R) (zeros on gap rows), so a
+// convolution's "same" zero padding and the graph's x*x_mask multiplications both fall out
+// of the layout.  Rows outside [0,R) are never read (guarded).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+namespace piper {
+
+struct Exec {
+  cudaStream_t st = nullptr;
+  int64_t launches = 0;
+};
+
+// out[orow][co] = epi( bias[co] + uttbias[utt][co] + sum_{tap,ci} act(in[q+in_off+tap*tap_step][ci]) * w[tap][ci][co] )
+//   orow = q*out_mul + out_add;  phases>1 => transposed conv, one polyphase sub-filter per blockIdx.z
+struct ConvArgs {
+  const float* in = nullptr;  int ldin = 0;
+  const float* w = nullptr;   int ldw = 0;       // [phases][taps][cin][ldw]
+  const float* bias = nullptr;
+  float* out = nullptr;       int ldout = 0;
+  const float* res = nullptr; int ldres = 0;     // added after activation (may alias out)
+  const float* uttbias = nullptr; int ldub = 0;  // [batch][ldub] per-utterance bias (speaker conditioning)
+  const int* row_utt = nullptr;                  // utterance id (>=0) or -1 per base row
+  int valid_div = 1;                             // out row r is valid iff row_utt[r / valid_div] >= 0
+  int R_in = 0, Q = 0;                           // input rows; number of q positions
+  int cin = 0, cout = 0, taps = 1;
+  int tap_step = 1, in_off = 0;
+  int out_mul = 1, out_add = 0;
+  int phases = 1, ct_pad = 0;                    // transposed conv: stride = phases
+  int in_act = 0; float in_slope = 0.f;          // leaky-relu on the input operand
+  int relu = 0;                                  // relu on (acc + bias)
+  int accum = 0;                                 // out += value
+  float div = 0.f;                               // if != 0: out = value / div (after accum)
+};
+void launch_conv_f32(Exec& ex, const ConvArgs& a);
+
+struct LNArgs {
+  const float* x = nullptr;   // [R][C]
+  const float* y = nullptr;   // optional addend before the norm (x + y)
+  const float* gamma = nullptr; const float* beta = nullptr;
+  float* out = nullptr;       // [R][C]
+  const float* res = nullptr; // optional: out = res + f(LN(.)) (DDSConv residual)
+  const int* row_utt = nullptr;
+  int R = 0, C = 0;
+  int gelu = 0;
+};
+void launch_layernorm(Exec& ex, const LNArgs& a);
+
+void launch_embed(Exec& ex, const int64_t* ids_packed, const float* emb, float* x, int R, int H,
+                  int n_vocab, float scale);
+
+// relative-position multi-head attention over qkv [R][3H] (q|k|v), per utterance
+void launch_attention(Exec& ex, const float* qkv, const float* rel_k, const float* rel_v, float* out,
+                      const int* utt_start, const int* utt_len, int batch, int max_len, int H,
+                      int n_heads, int window);
+
+// depthwise conv (k taps, dilation d) + channel LayerNorm + GELU, DDSConv first half
+void launch_dds_sep_ln_gelu(Exec& ex, const float* x, const float* w_sep /*[k][C]*/, const float* b_sep,
+                            const float* gamma, const float* beta, float* out, const int* row_utt,
+                            int R, int C, int k, int dil);
+
+// h[r][c] = w[c]*z[r] + b[c] + cond[r][c]   (ConvFlow.pre on one channel + DDSConv's `x + g`)
+void launch_convflow_pre(Exec& ex, const float* z, const float* w, const float* b, const float* cond,
+                         float* h, const int* row_utt, int R, int C);
+
+// inverse rational-quadratic spline with linear tails on one channel; params [R][ldp] (3*bins-1 used)
+void launch_spline_inverse(Exec& ex, float* z_target, const float* params, int ldp, const int* row_utt,
+                           int R, int bins, float tail_bound, float inv_sqrt_filter);
+
+// reference RandomNormalLike (elementwise.metal:132-163): per utterance gid = c*len + t
+void launch_noise_dp(Exec& ex, float* z /*[2][R]*/, const float* ext /*ragged [2,T_b] or null*/,
+                     const int* utt_start, const int* utt_len, const int64_t* ext_off, int batch, int R,
+                     uint32_t seed, float noise_w);
+
+// durations: logw = (z0 - m)*exp(-logs); w = exp(logw)*length_scale; ceil; cumsum; y_len
+void launch_durations(Exec& ex, const float* z0, float ea_m, float ea_logs, float length_scale,
+                      const int* utt_start, const int* utt_len, int batch, float* logw_out,
+                      int* dur /*[R]*/, int* cum /*[R]*/, int64_t* y_len /*[batch]*/);
+// logw given directly (parity entry point)
+void launch_durations_from_logw(Exec& ex, const float* logw, float length_scale, const int* utt_start,
+                                const int* utt_len, int batch, int* dur, int* cum, int64_t* y_len);
+// frame layout: fstart[b] = exclusive scan of (y_len + gap); total rows -> fstart[batch]
+void launch_frame_layout(Exec& ex, const int64_t* y_len, int batch, int gap, int64_t* fstart);
+// per frame row: utterance id (or -1) and source phoneme row (or -1)
+void launch_frame_map(Exec& ex, const int64_t* fstart, const int64_t* y_len, const int* cum,
+                      const int* utt_start, const int* utt_len, int batch, int Rf, int* frow_utt,
+                      int* frow_src);
+// z_p[r][c] = m_p[src][c] + noise * exp(logs_p[src][c]) * noise_scale
+void launch_expand_prior(Exec& ex, const float* stats /*[Rp][2H]*/, const int* frow_utt,
+                         const int* frow_src, const int64_t* fstart, const int64_t* y_len,
+                         const float* ext_noise, int64_t ext_stride, uint32_t seed, float noise_scale,
+                         float* zp, int Rf, int H);
+
+// acts = tanh(xin[:, :H] + g) * sigmoid(xin[:, H:] + g)
+void launch_wn_gate(Exec& ex, const float* xin /*[R][2H]*/, const float* cond /*[B][ldc] or null*/,
+                    int ldc, const int* row_utt, float* acts, int R, int H);
+
+// out[r] = tanh(sum_{tap,c} lrelu(in[r+tap-pad][c], slope) * w[tap][c]) and optional pcm16
+void launch_conv_post_tanh(Exec& ex, const float* in, int C, const float* w, int k, float slope,
+                           const int* row_utt, int valid_div, float* out, int R);
+
+// speaker conditioning: out[b][co] = bias[co] + sum_ci W[co][ci] * emb_g[sid[b]][ci]
+void launch_cond_gemv(Exec& ex, const float* emb_g, const int64_t* sids, const float* W, const float* bias,
+                      float* out, int ldo, int batch, int gin, int cout, int n_speakers);
+
+// gather per-utterance audio out of the packed sample rows into a dense concatenation
+void launch_gather_audio(Exec& ex, const float* packed, const int64_t* fstart, const int64_t* y_len,
+                         const int64_t* sample_off, int batch, int hop, float* dense, int16_t* pcm16,
+                         int64_t total_samples);
+
+void launch_pack_ids(Exec& ex, const int64_t* ids, const int64_t* id_off, const int* utt_start,
+                     const int* utt_len, int batch, int64_t* ids_packed, int* row_utt, int n_vocab);
+void launch_random_normal(Exec& ex, float* out, int64_t count, uint32_t seed);
+void launch_fill_i32(Exec& ex, int* p, int v, int64_t n);
+
+}  // namespace piper

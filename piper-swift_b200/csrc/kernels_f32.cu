@@ -1,0 +1,897 @@
+// fp32 CUDA-core kernels of the Piper-VITS pipeline (sm_100a).
+// These cover the stages whose results feed discrete decisions (text encoder, stochastic
+// duration predictor, length regulator: SURVEY 8a4-a9) and serve as the parity-mode
+// implementation of the flow and HiFi-GAN stages (8a10-a12); the tensor-core versions of
+// the latter live in conv_tc.cu.  Each kernel names the ONNX ops / reference kernels it
+// replaces; none of them is a translation of the one-thread-per-output Metal kernels.
+#include "kernels.h"
+
+#include <cfloat>
+#include <cmath>
+#include <cstdio>
+
+namespace piper {
+
+#define KLAUNCH(ex) (++(ex).launches)
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float gelu_erf(float x) {
+  // exact-erf GELU (ONNX Erf; the ORT-CPU target, not elementwise.metal:292-312's approximation)
+  return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
+}
+
+// ------------------------------------------------------------------------------------------
+// Generic fp32 implicit-GEMM convolution (replaces conv1d_f32 / convtranspose1d_f32,
+// conv1d.metal:28-71,97-142, and matmul_f32 for 1x1 convs).  64x64 output tile per CTA,
+// K chunks of 16 input channels per tap staged through shared memory, 4x4 register
+// micro-tile per thread.  Transposed convs run as `phases` polyphase sub-filters
+// (blockIdx.z), which removes the `% stride` tap skipping of conv1d.metal:128-137.
+// ------------------------------------------------------------------------------------------
+constexpr int CBM = 64, CBN = 64, CBK = 16;
+
+__global__ void __launch_bounds__(256) conv_f32_kernel(ConvArgs a) {
+  __shared__ __align__(16) float As[CBK][CBM];
+  __shared__ __align__(16) float Bs[CBK][CBN];
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int q0 = blockIdx.x * CBM;
+  const int n0 = blockIdx.y * CBN;
+  int in_off = a.in_off, out_add = a.out_add;
+  const float* wbase = a.w;
+  if (a.phases > 1) {
+    const int ph = blockIdx.z;
+    out_add = ph;
+    in_off = (ph + a.ct_pad) / a.phases;
+    wbase += (size_t)ph * a.taps * a.cin * a.ldw;
+  }
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  const int arow = tid & 63, akq = tid >> 6;   // A loader: row, float4 index inside the K chunk
+  const int bk = tid >> 4, bn4 = tid & 15;     // B loader
+  for (int tap = 0; tap < a.taps; ++tap) {
+    const int srow = q0 + arow + in_off + tap * a.tap_step;
+    const bool row_ok = (q0 + arow) < a.Q && srow >= 0 && srow < a.R_in;
+    const float* arow_ptr = a.in + (size_t)(row_ok ? srow : 0) * a.ldin;
+    for (int ci0 = 0; ci0 < a.cin; ci0 += CBK) {
+      float4 av = make_float4(0.f, 0.f, 0.f, 0.f);
+      const int ci = ci0 + akq * 4;
+      if (row_ok && ci < a.cin) av = *reinterpret_cast<const float4*>(arow_ptr + ci);
+      if (a.in_act) {
+        av.x = av.x >= 0.f ? av.x : av.x * a.in_slope;
+        av.y = av.y >= 0.f ? av.y : av.y * a.in_slope;
+        av.z = av.z >= 0.f ? av.z : av.z * a.in_slope;
+        av.w = av.w >= 0.f ? av.w : av.w * a.in_slope;
+      }
+      float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (ci0 + bk < a.cin)
+        bv = *reinterpret_cast<const float4*>(wbase + ((size_t)tap * a.cin + ci0 + bk) * a.ldw + n0 + bn4 * 4);
+      __syncthreads();
+      As[akq * 4 + 0][arow] = av.x;
+      As[akq * 4 + 1][arow] = av.y;
+      As[akq * 4 + 2][arow] = av.z;
+      As[akq * 4 + 3][arow] = av.w;
+      *reinterpret_cast<float4*>(&Bs[bk][bn4 * 4]) = bv;
+      __syncthreads();
+#pragma unroll
+      for (int k = 0; k < CBK; ++k) {
+        const float4 a4 = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
+        const float4 b4 = *reinterpret_cast<const float4*>(&Bs[k][tx * 4]);
+        const float ar[4] = {a4.x, a4.y, a4.z, a4.w};
+        const float br[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(ar[i], br[j], acc[i][j]);
+      }
+    }
+  }
+  // epilogue
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int q = q0 + ty * 4 + i;
+    if (q >= a.Q) continue;
+    const int orow = q * a.out_mul + out_add;
+    int utt = 0;
+    if (a.row_utt) utt = a.row_utt[orow / a.valid_div];
+    const bool valid = utt >= 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int co = n0 + tx * 4 + j;
+      if (co >= a.cout) continue;
+      float v = acc[i][j];
+      if (a.bias) v += a.bias[co];
+      if (a.uttbias && valid) v += a.uttbias[(size_t)utt * a.ldub + co];
+      if (a.relu) v = fmaxf(v, 0.f);
+      if (a.res) v += a.res[(size_t)orow * a.ldres + co];
+      float* o = a.out + (size_t)orow * a.ldout + co;
+      if (a.accum) v += *o;
+      if (a.div != 0.f) v = v / a.div;
+      *o = valid ? v : 0.f;
+    }
+  }
+}
+
+void launch_conv_f32(Exec& ex, const ConvArgs& a) {
+  if (a.Q <= 0) return;
+  dim3 grid((a.Q + CBM - 1) / CBM, (a.cout + CBN - 1) / CBN, a.phases);
+  conv_f32_kernel<<<grid, 256, 0, ex.st>>>(a);
+  KLAUNCH(ex);
+}
+
+// ------------------------------------------------------------------------------------------
+// Channel LayerNorm (the decomposed ReduceMean/Sub/Pow/ReduceMean/Add/Sqrt/Div/Mul/Add chain,
+// GraphExecutor.swift:2104-2125 -> reduce.metal:12-25), fused with the preceding residual
+// add (x + y), optional exact GELU and the DDSConv residual.  One warp per row, two-pass
+// mean / variance with warp shuffles, values kept in registers.
+// ------------------------------------------------------------------------------------------
+constexpr int LN_MAXV = 8;   // channels <= 256
+
+__global__ void __launch_bounds__(256) layernorm_kernel(LNArgs a) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= a.R) return;
+  const size_t base = (size_t)warp * a.C;
+  const bool valid = !a.row_utt || a.row_utt[warp] >= 0;
+  if (!valid) {
+    for (int c = lane; c < a.C; c += 32) a.out[base + c] = 0.f;
+    return;
+  }
+  float v[LN_MAXV];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i) {
+    const int c = lane + 32 * i;
+    v[i] = 0.f;
+    if (c < a.C) {
+      v[i] = a.x[base + c];
+      if (a.y) v[i] += a.y[base + c];
+      s += v[i];
+    }
+  }
+  const float mean = warp_sum(s) / (float)a.C;
+  float sq = 0.f;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i) {
+    const int c = lane + 32 * i;
+    if (c < a.C) {
+      v[i] -= mean;
+      sq += v[i] * v[i];
+    }
+  }
+  const float var = warp_sum(sq) / (float)a.C;
+  const float denom = sqrtf(var + 1e-5f);
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i) {
+    const int c = lane + 32 * i;
+    if (c < a.C) {
+      float o = v[i] / denom * a.gamma[c] + a.beta[c];
+      if (a.gelu) o = gelu_erf(o);
+      if (a.res) o += a.res[base + c];
+      a.out[base + c] = o;
+    }
+  }
+}
+
+void launch_layernorm(Exec& ex, const LNArgs& a) {
+  if (a.R <= 0) return;
+  const int warps_per_block = 8;
+  layernorm_kernel<<<(a.R + warps_per_block - 1) / warps_per_block, 256, 0, ex.st>>>(a);
+  KLAUNCH(ex);
+}
+
+// ------------------------------------------------------------------------------------------
+// Embedding lookup * sqrt(H) (Gather axis 0 + Mul, GraphExecutor.swift:661-666;
+// gather.metal:43-58).  ids_packed holds -1 on gap rows.  Out-of-range ids give a zero row,
+// the reference's OOB rule.
+// ------------------------------------------------------------------------------------------
+__global__ void embed_kernel(const int64_t* __restrict__ ids, const float* __restrict__ emb,
+                             float* __restrict__ x, int R, int H, int n_vocab, float scale) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)R * H) return;
+  const int r = (int)(i / H), c = (int)(i % H);
+  int64_t id = ids[r];
+  float v = 0.f;
+  if (id >= 0 && id < n_vocab) v = emb[id * H + c] * scale;
+  x[i] = v;
+}
+
+void launch_embed(Exec& ex, const int64_t* ids_packed, const float* emb, float* x, int R, int H,
+                  int n_vocab, float scale) {
+  const int64_t n = (int64_t)R * H;
+  if (n <= 0) return;
+  embed_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ex.st>>>(ids_packed, emb, x, R, H, n_vocab, scale);
+  KLAUNCH(ex);
+}
+
+// ------------------------------------------------------------------------------------------
+// Relative-position multi-head attention: replaces MatMul QK^T, the
+// pad/reshape/slice "skew" of the relative logits, Softmax, MatMul PV and the relative-value
+// term.  The relative embeddings are banded (|j-i| <= window), so they are added inside the
+// key loop: O(T*9) instead of the exported O(T*(2T-1)) matmuls.  One warp per query row,
+// keys streamed through shared memory 32 at a time, online softmax in fp32.
+// ------------------------------------------------------------------------------------------
+constexpr int ATT_WARPS = 8;
+constexpr int ATT_KT = 32;
+constexpr int ATT_MAXD = 4;   // head dim <= 128
+
+__global__ void __launch_bounds__(ATT_WARPS * 32) attention_kernel(
+    const float* __restrict__ qkv, const float* __restrict__ rel_k, const float* __restrict__ rel_v,
+    float* __restrict__ out, const int* __restrict__ utt_start, const int* __restrict__ utt_len,
+    int H, int n_heads, int window) {
+  extern __shared__ float sm[];
+  const int kc = H / n_heads;
+  const int ldk = kc + 1;
+  float* Ks = sm;                              // [ATT_KT][ldk]
+  float* Vs = Ks + ATT_KT * ldk;               // [ATT_KT][ldk]
+  float* Qs = Vs + ATT_KT * ldk;               // [ATT_WARPS][kc]
+  float* RK = Qs + ATT_WARPS * kc;             // [2w+1][kc]
+  float* RV = RK + (2 * window + 1) * kc;      // [2w+1][kc]
+  float* QR = RV + (2 * window + 1) * kc;      // [ATT_WARPS][2w+1]
+  const int b = blockIdx.z, head = blockIdx.y;
+  const int T = utt_len[b];
+  const int row0 = utt_start[b];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int i = blockIdx.x * ATT_WARPS + warp;   // query index inside the utterance
+  if (blockIdx.x * ATT_WARPS >= T) return;
+  const int nrel = 2 * window + 1;
+  const int ld = 3 * H;
+  for (int t = threadIdx.x; t < nrel * kc; t += blockDim.x) {
+    RK[t] = rel_k[t];
+    RV[t] = rel_v[t];
+  }
+  const bool active = i < T;
+  const float inv_sqrt = 1.0f / sqrtf((float)kc);
+  if (active) {
+    const float* q = qkv + (size_t)(row0 + i) * ld + head * kc;
+    for (int d = lane; d < kc; d += 32) Qs[warp * kc + d] = q[d] / sqrtf((float)kc);
+  }
+  (void)inv_sqrt;
+  __syncthreads();
+  if (active) {
+    for (int m = 0; m < nrel; ++m) {
+      float s = 0.f;
+      for (int d = lane; d < kc; d += 32) s += Qs[warp * kc + d] * RK[m * kc + d];
+      s = warp_sum(s);
+      if (lane == 0) QR[warp * nrel + m] = s;
+    }
+  }
+  __syncwarp();
+  float mrun = -FLT_MAX, lrun = 0.f;
+  float acc[ATT_MAXD];
+#pragma unroll
+  for (int d = 0; d < ATT_MAXD; ++d) acc[d] = 0.f;
+  for (int j0 = 0; j0 < T; j0 += ATT_KT) {
+    __syncthreads();
+    for (int t = threadIdx.x; t < ATT_KT * kc; t += blockDim.x) {
+      const int jj = t / kc, d = t % kc;
+      float kv = 0.f, vv = 0.f;
+      if (j0 + jj < T) {
+        const float* rowp = qkv + (size_t)(row0 + j0 + jj) * ld + head * kc + d;
+        kv = rowp[H];
+        vv = rowp[2 * H];
+      }
+      Ks[jj * ldk + d] = kv;
+      Vs[jj * ldk + d] = vv;
+    }
+    __syncthreads();
+    if (!active) continue;
+    const int j = j0 + lane;
+    float s = -FLT_MAX;
+    if (j < T) {
+      s = 0.f;
+      const float* qv = Qs + warp * kc;
+      const float* kr = Ks + lane * ldk;
+      for (int d = 0; d < kc; ++d) s = fmaf(qv[d], kr[d], s);
+      const int rel = j - i;
+      if (rel >= -window && rel <= window) s += QR[warp * nrel + rel + window];
+    }
+    const float mnew = fmaxf(mrun, warp_max(s));
+    const float p = (j < T) ? expf(s - mnew) : 0.f;
+    const float corr = expf(mrun - mnew);
+    lrun = lrun * corr + warp_sum(p);
+#pragma unroll
+    for (int d = 0; d < ATT_MAXD; ++d) acc[d] *= corr;
+    mrun = mnew;
+    const int jn = min(ATT_KT, T - j0);
+    for (int jj = 0; jj < jn; ++jj) {
+      const float pj = __shfl_sync(0xffffffffu, p, jj);
+      const int rel = j0 + jj - i;
+      const bool inwin = rel >= -window && rel <= window;
+#pragma unroll
+      for (int dd = 0; dd < ATT_MAXD; ++dd) {
+        const int d = lane + 32 * dd;
+        if (d < kc) {
+          float vv = Vs[jj * ldk + d];
+          if (inwin) vv += RV[(rel + window) * kc + d];
+          acc[dd] = fmaf(pj, vv, acc[dd]);
+        }
+      }
+    }
+  }
+  if (active) {
+    float* o = out + (size_t)(row0 + i) * H + head * kc;
+#pragma unroll
+    for (int dd = 0; dd < ATT_MAXD; ++dd) {
+      const int d = lane + 32 * dd;
+      if (d < kc) o[d] = acc[dd] / lrun;
+    }
+  }
+}
+
+void launch_attention(Exec& ex, const float* qkv, const float* rel_k, const float* rel_v, float* out,
+                      const int* utt_start, const int* utt_len, int batch, int max_len, int H,
+                      int n_heads, int window) {
+  if (batch <= 0 || max_len <= 0) return;
+  const int kc = H / n_heads;
+  const int nrel = 2 * window + 1;
+  const size_t smem = sizeof(float) * (2 * ATT_KT * (kc + 1) + ATT_WARPS * kc + 2 * nrel * kc + ATT_WARPS * nrel);
+  dim3 grid((max_len + ATT_WARPS - 1) / ATT_WARPS, n_heads, batch);
+  attention_kernel<<<grid, ATT_WARPS * 32, smem, ex.st>>>(qkv, rel_k, rel_v, out, utt_start, utt_len, H,
+                                                         n_heads, window);
+  KLAUNCH(ex);
+}
+
+// ------------------------------------------------------------------------------------------
+// DDSConv first half: depthwise Conv (groups=C, dilation d) + LayerNorm + GELU.
+// w_sep is tap-major [k][C] so that a warp reads consecutive channels.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) dds_sep_ln_gelu_kernel(
+    const float* __restrict__ x, const float* __restrict__ w_sep, const float* __restrict__ b_sep,
+    const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ out,
+    const int* __restrict__ row_utt, int R, int C, int k, int dil) {
+  const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (r >= R) return;
+  const size_t base = (size_t)r * C;
+  if (row_utt && row_utt[r] < 0) {
+    for (int c = lane; c < C; c += 32) out[base + c] = 0.f;
+    return;
+  }
+  const int pad = (k * dil - dil) / 2;
+  float v[LN_MAXV];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i) {
+    const int c = lane + 32 * i;
+    v[i] = 0.f;
+    if (c < C) {
+      float a = b_sep[c];
+      for (int t = 0; t < k; ++t) {
+        const int rr = r + t * dil - pad;
+        if (rr >= 0 && rr < R) a = fmaf(w_sep[t * C + c], x[(size_t)rr * C + c], a);
+      }
+      v[i] = a;
+      s += a;
+    }
+  }
+  const float mean = warp_sum(s) / (float)C;
+  float sq = 0.f;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i)
+    if (lane + 32 * i < C) {
+      v[i] -= mean;
+      sq += v[i] * v[i];
+    }
+  const float denom = sqrtf(warp_sum(sq) / (float)C + 1e-5f);
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i) {
+    const int c = lane + 32 * i;
+    if (c < C) out[base + c] = gelu_erf(v[i] / denom * gamma[c] + beta[c]);
+  }
+}
+
+void launch_dds_sep_ln_gelu(Exec& ex, const float* x, const float* w_sep, const float* b_sep,
+                            const float* gamma, const float* beta, float* out, const int* row_utt,
+                            int R, int C, int k, int dil) {
+  if (R <= 0) return;
+  dds_sep_ln_gelu_kernel<<<(R + 7) / 8, 256, 0, ex.st>>>(x, w_sep, b_sep, gamma, beta, out, row_utt, R, C, k, dil);
+  KLAUNCH(ex);
+}
+
+// ConvFlow.pre (1 -> C channels, k=1) fused with DDSConv's `x + g` conditioning add.
+__global__ void convflow_pre_kernel(const float* __restrict__ z, const float* __restrict__ w,
+                                    const float* __restrict__ b, const float* __restrict__ cond,
+                                    float* __restrict__ h, const int* __restrict__ row_utt, int R, int C) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)R * C) return;
+  const int r = (int)(i / C), c = (int)(i % C);
+  float v = 0.f;
+  if (!row_utt || row_utt[r] >= 0) v = fmaf(w[c], z[r], b[c]) + cond[i];
+  h[i] = v;
+}
+
+void launch_convflow_pre(Exec& ex, const float* z, const float* w, const float* b, const float* cond,
+                         float* h, const int* row_utt, int R, int C) {
+  const int64_t n = (int64_t)R * C;
+  if (n <= 0) return;
+  convflow_pre_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ex.st>>>(z, w, b, cond, h, row_utt, R, C);
+  KLAUNCH(ex);
+}
+
+// ------------------------------------------------------------------------------------------
+// Inverse rational-quadratic spline with linear tails: replaces the
+// Softmax/Softplus/CumSum/Pad/GreaterOrEqual+ReduceSum (searchsorted)/GatherElements/
+// Sqrt/Div chain and the NonZero/GatherND/ScatterND masked assignment
+// (GraphExecutor.swift:2379-2602; nonzero.metal's atomic compaction is not needed because
+// every element is evaluated in place).  One thread per (utterance position); op order
+// follows the oracle so that the discrete bin choice matches.
+// ------------------------------------------------------------------------------------------
+constexpr int SPL_MAXB = 16;
+
+__global__ void spline_inverse_kernel(float* __restrict__ zt, const float* __restrict__ params, int ldp,
+                                      const int* __restrict__ row_utt, int R, int nb, float tb,
+                                      float inv_sqrt_fc) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= R) return;
+  if (row_utt && row_utt[r] < 0) {
+    zt[r] = 0.f;
+    return;
+  }
+  const float x = zt[r];
+  if (!(x >= -tb && x <= tb)) return;   // linear tails: identity
+  const float* p = params + (size_t)r * ldp;
+  const float min_w = 1e-3f, min_h = 1e-3f, min_d = 1e-3f;
+  float cw[SPL_MAXB + 1], chh[SPL_MAXB + 1];
+  // widths
+  {
+    float u[SPL_MAXB];
+    float mx = -FLT_MAX;
+    for (int i = 0; i < nb; ++i) {
+      u[i] = p[i] * inv_sqrt_fc;
+      mx = fmaxf(mx, u[i]);
+    }
+    float sum = 0.f;
+    for (int i = 0; i < nb; ++i) {
+      u[i] = expf(u[i] - mx);
+      sum += u[i];
+    }
+    float run = 0.f;
+    cw[0] = -tb;
+    for (int i = 0; i < nb; ++i) {
+      const float wd = min_w + (1.f - min_w * nb) * (u[i] / sum);
+      run += wd;
+      cw[i + 1] = (2.f * tb) * run + (-tb);
+    }
+    cw[nb] = tb;
+  }
+  {
+    float u[SPL_MAXB];
+    float mx = -FLT_MAX;
+    for (int i = 0; i < nb; ++i) {
+      u[i] = p[nb + i] * inv_sqrt_fc;
+      mx = fmaxf(mx, u[i]);
+    }
+    float sum = 0.f;
+    for (int i = 0; i < nb; ++i) {
+      u[i] = expf(u[i] - mx);
+      sum += u[i];
+    }
+    float run = 0.f;
+    chh[0] = -tb;
+    for (int i = 0; i < nb; ++i) {
+      const float hd = min_h + (1.f - min_h * nb) * (u[i] / sum);
+      run += hd;
+      chh[i + 1] = (2.f * tb) * run + (-tb);
+    }
+    chh[nb] = tb;
+  }
+  // searchsorted over cumheights (last edge + eps)
+  int bin = -1;
+  for (int i = 0; i <= nb; ++i) {
+    const float edge = (i == nb) ? chh[i] + 1e-6f : chh[i];
+    bin += (x >= edge) ? 1 : 0;
+  }
+  bin = min(max(bin, 0), nb - 1);
+  const float in_cw = cw[bin], in_w = cw[bin + 1] - cw[bin];
+  const float in_ch = chh[bin], in_h = chh[bin + 1] - chh[bin];
+  const float delta = in_h / in_w;
+  // derivatives: padded with the constant so that the boundary derivative is 1
+  const float cst = logf(expf(1.f - min_d) - 1.f);
+  auto deriv = [&](int i) {
+    const float ud = (i == 0 || i == nb) ? cst : p[2 * nb + i - 1];
+    const float sp = (ud > 20.f) ? ud : log1pf(expf(ud));   // torch softplus (threshold 20)
+    return min_d + sp;
+  };
+  const float d0 = deriv(bin), d1 = deriv(bin + 1);
+  const float t = x - in_ch;
+  const float s2 = d0 + d1 - 2.f * delta;
+  const float a = t * s2 + in_h * (delta - d0);
+  const float b = in_h * d0 - t * s2;
+  const float c = -delta * t;
+  const float disc = b * b - 4.f * a * c;
+  const float root = (2.f * c) / (-b - sqrtf(disc));
+  zt[r] = root * in_w + in_cw;
+}
+
+void launch_spline_inverse(Exec& ex, float* z_target, const float* params, int ldp, const int* row_utt,
+                           int R, int bins, float tail_bound, float inv_sqrt_filter) {
+  if (R <= 0) return;
+  spline_inverse_kernel<<<(R + 127) / 128, 128, 0, ex.st>>>(z_target, params, ldp, row_utt, R, bins,
+                                                           tail_bound, inv_sqrt_filter);
+  KLAUNCH(ex);
+}
+
+// ------------------------------------------------------------------------------------------
+// RandomNormalLike with the reference's generator (elementwise.metal:132-163): xorshift32 x2
+// seeded by seedLo ^ (gid*747796405+2891336453), Box-Muller r*cos(theta).
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t xorshift32(uint32_t x) {
+  x ^= x << 13;
+  x ^= x >> 17;
+  x ^= x << 5;
+  return x;
+}
+__device__ __forceinline__ float ref_normal(uint32_t seed, uint32_t gid) {
+  uint32_t state = seed ^ (gid * 747796405u + 2891336453u);
+  state = xorshift32(state);
+  const uint32_t u0i = state;
+  state = xorshift32(state);
+  const uint32_t u1i = state;
+  const float u0 = ((float)u0i + 1.0f) / 4294967296.0f;
+  const float u1 = ((float)u1i + 1.0f) / 4294967296.0f;
+  const float r = sqrtf(-2.0f * logf(u0));
+  const float theta = 6.28318530718f * u1;
+  return r * cosf(theta);
+}
+
+__global__ void random_normal_kernel(float* out, int64_t count, uint32_t seed) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < count) out[i] = ref_normal(seed, (uint32_t)i);
+}
+void launch_random_normal(Exec& ex, float* out, int64_t count, uint32_t seed) {
+  if (count <= 0) return;
+  random_normal_kernel<<<(unsigned)((count + 255) / 256), 256, 0, ex.st>>>(out, count, seed);
+  KLAUNCH(ex);
+}
+
+__global__ void fill_i32_kernel(int* p, int v, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+void launch_fill_i32(Exec& ex, int* p, int v, int64_t n) {
+  if (n <= 0) return;
+  fill_i32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ex.st>>>(p, v, n);
+  KLAUNCH(ex);
+}
+
+// z[ch][r] = noise * noise_w for the duration predictor ([1,2,T] per utterance, gid = ch*T+t)
+__global__ void noise_dp_kernel(float* __restrict__ z, const float* __restrict__ ext,
+                                const int* __restrict__ utt_start, const int* __restrict__ utt_len,
+                                const int64_t* __restrict__ ext_off, int R, uint32_t seed, float noise_w) {
+  const int b = blockIdx.y;
+  const int T = utt_len[b], r0 = utt_start[b];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * T; i += gridDim.x * blockDim.x) {
+    const int ch = i / T, t = i % T;
+    const float n = ext ? ext[ext_off[b] * 2 + i] : ref_normal(seed, (uint32_t)i);
+    z[(size_t)ch * R + r0 + t] = n * noise_w;
+  }
+}
+void launch_noise_dp(Exec& ex, float* z, const float* ext, const int* utt_start, const int* utt_len,
+                     const int64_t* ext_off, int batch, int R, uint32_t seed, float noise_w) {
+  if (batch <= 0) return;
+  noise_dp_kernel<<<dim3(4, batch), 256, 0, ex.st>>>(z, ext, utt_start, utt_len, ext_off, R, seed, noise_w);
+  KLAUNCH(ex);
+}
+
+// ------------------------------------------------------------------------------------------
+// Length regulator, integer part: Exp, Mul(length_scale), Ceil, ReduceSum,
+// Clip(min 1), Cast f32->i64 (cast.metal:8-29: NaN -> 0, saturate, trunc), CumSum
+// (cumsum.metal's O(n^2) loop becomes a block scan).  One CTA per utterance.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ int dur_from_w(float w) {
+  const float c = ceilf(w);
+  if (isnan(c)) return 0;
+  if (c >= 1073741824.f) return 1 << 30;   // saturate (capacity check rejects this later)
+  if (c <= 0.f) return 0;
+  return (int)c;
+}
+
+template <bool FROM_LOGW>
+__global__ void __launch_bounds__(256) durations_kernel(const float* __restrict__ src, float ea_m,
+                                                        float ea_logs, float length_scale,
+                                                        const int* __restrict__ utt_start,
+                                                        const int* __restrict__ utt_len,
+                                                        float* __restrict__ logw_out, int* __restrict__ dur,
+                                                        int* __restrict__ cum, int64_t* __restrict__ y_len) {
+  __shared__ int warp_tot[8];
+  __shared__ int carry_s;
+  const int b = blockIdx.x;
+  const int T = utt_len[b], r0 = utt_start[b];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  for (int t0 = 0; t0 < T; t0 += 256) {
+    const int t = t0 + threadIdx.x;
+    int d = 0;
+    if (t < T) {
+      float lw = src[r0 + t];
+      if (!FROM_LOGW) {
+        lw = (lw - ea_m) * expf(-ea_logs);     // ElementwiseAffine reverse, channel 0
+        if (logw_out) logw_out[r0 + t] = lw;
+      }
+      const float w = expf(lw) * length_scale;   // x_mask == 1 inside the utterance
+      d = dur_from_w(w);
+      dur[r0 + t] = d;
+    }
+    int v = d;   // inclusive warp scan
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int n = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += n;
+    }
+    if (lane == 31) warp_tot[warp] = v;
+    __syncthreads();
+    int pre = carry_s;
+    for (int w = 0; w < warp; ++w) pre += warp_tot[w];
+    if (t < T) cum[r0 + t] = min(pre + v, 1 << 30);
+    __syncthreads();
+    if (threadIdx.x == 255) carry_s = min(pre + v, 1 << 30);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) y_len[b] = carry_s < 1 ? 1 : carry_s;
+}
+
+void launch_durations(Exec& ex, const float* z0, float ea_m, float ea_logs, float length_scale,
+                      const int* utt_start, const int* utt_len, int batch, float* logw_out, int* dur,
+                      int* cum, int64_t* y_len) {
+  if (batch <= 0) return;
+  durations_kernel<false><<<batch, 256, 0, ex.st>>>(z0, ea_m, ea_logs, length_scale, utt_start, utt_len,
+                                                    logw_out, dur, cum, y_len);
+  KLAUNCH(ex);
+}
+void launch_durations_from_logw(Exec& ex, const float* logw, float length_scale, const int* utt_start,
+                                const int* utt_len, int batch, int* dur, int* cum, int64_t* y_len) {
+  if (batch <= 0) return;
+  durations_kernel<true><<<batch, 256, 0, ex.st>>>(logw, 0.f, 0.f, length_scale, utt_start, utt_len,
+                                                   nullptr, dur, cum, y_len);
+  KLAUNCH(ex);
+}
+
+// frame rows: fstart[b] = sum_{b'<b} (y_len[b'] + gap); fstart[batch] = total rows
+__global__ void frame_layout_kernel(const int64_t* __restrict__ y_len, int batch, int gap,
+                                    int64_t* __restrict__ fstart) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    int64_t acc = 0;
+    for (int b = 0; b < batch; ++b) {
+      fstart[b] = acc;
+      acc += y_len[b] + gap;
+    }
+    fstart[batch] = acc;
+  }
+}
+void launch_frame_layout(Exec& ex, const int64_t* y_len, int batch, int gap, int64_t* fstart) {
+  frame_layout_kernel<<<1, 32, 0, ex.st>>>(y_len, batch, gap, fstart);
+  KLAUNCH(ex);
+}
+
+// Range/Less/CumSum path (generate_path) as an index: frame f of utterance b belongs to the
+// first phoneme t with cum[t] > f.  Frames nobody covers (sum of durations 0) get -1.
+__global__ void frame_map_kernel(const int64_t* __restrict__ fstart, const int64_t* __restrict__ y_len,
+                                 const int* __restrict__ cum, const int* __restrict__ utt_start,
+                                 const int* __restrict__ utt_len, int batch, int Rf,
+                                 int* __restrict__ frow_utt, int* __restrict__ frow_src) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= Rf) return;
+  int lo = 0, hi = batch - 1;   // last b with fstart[b] <= r
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (fstart[mid] <= r) lo = mid; else hi = mid - 1;
+  }
+  const int b = lo;
+  const int64_t f = r - fstart[b];
+  int utt = -1, src = -1;
+  if (f < y_len[b]) {
+    utt = b;
+    const int T = utt_len[b], r0 = utt_start[b];
+    int l = 0, h = T;   // first t with cum[t] > f
+    while (l < h) {
+      const int mid = (l + h) >> 1;
+      if (cum[r0 + mid] > f) h = mid; else l = mid + 1;
+    }
+    src = l < T ? r0 + l : -1;
+  }
+  frow_utt[r] = utt;
+  frow_src[r] = src;
+}
+void launch_frame_map(Exec& ex, const int64_t* fstart, const int64_t* y_len, const int* cum,
+                      const int* utt_start, const int* utt_len, int batch, int Rf, int* frow_utt,
+                      int* frow_src) {
+  if (Rf <= 0) return;
+  frame_map_kernel<<<(Rf + 255) / 256, 256, 0, ex.st>>>(fstart, y_len, cum, utt_start, utt_len, batch, Rf,
+                                                       frow_utt, frow_src);
+  KLAUNCH(ex);
+}
+
+// ------------------------------------------------------------------------------------------
+// Expansion + prior sample: the exported MatMul path x (m_p, logs_p) is a
+// gather by frame index (0 FLOP); z_p = m_p + eps * exp(logs_p) * noise_scale.
+// eps is either injected ([hidden, stride] per utterance) or the reference generator with
+// gid = c*F_b + f (a [1,192,F] tensor per utterance).
+// ------------------------------------------------------------------------------------------
+__global__ void expand_prior_kernel(const float* __restrict__ stats, const int* __restrict__ frow_utt,
+                                    const int* __restrict__ frow_src, const int64_t* __restrict__ fstart,
+                                    const int64_t* __restrict__ y_len, const float* __restrict__ ext,
+                                    int64_t ext_stride, uint32_t seed, float noise_scale,
+                                    float* __restrict__ zp, int Rf, int H) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)Rf * H) return;
+  const int r = (int)(i / H), c = (int)(i % H);
+  const int b = frow_utt[r];
+  float v = 0.f;
+  if (b >= 0) {
+    const int src = frow_src[r];
+    float m = 0.f, logs = 0.f;
+    if (src >= 0) {
+      m = stats[(size_t)src * 2 * H + c];
+      logs = stats[(size_t)src * 2 * H + H + c];
+    }
+    const int64_t f = r - fstart[b];
+    const int64_t F = y_len[b];
+    const float eps = ext ? ext[((size_t)b * H + c) * ext_stride + f]
+                          : ref_normal(seed, (uint32_t)((int64_t)c * F + f));
+    v = m + eps * expf(logs) * noise_scale;
+  }
+  zp[i] = v;
+}
+void launch_expand_prior(Exec& ex, const float* stats, const int* frow_utt, const int* frow_src,
+                         const int64_t* fstart, const int64_t* y_len, const float* ext_noise,
+                         int64_t ext_stride, uint32_t seed, float noise_scale, float* zp, int Rf, int H) {
+  const int64_t n = (int64_t)Rf * H;
+  if (n <= 0) return;
+  expand_prior_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ex.st>>>(
+      stats, frow_utt, frow_src, fstart, y_len, ext_noise, ext_stride, seed, noise_scale, zp, Rf, H);
+  KLAUNCH(ex);
+}
+
+// WN gate (fused_add_tanh_sigmoid_multiply): Add cond, Split, Tanh, Sigmoid, Mul
+__global__ void wn_gate_kernel(const float* __restrict__ xin, const float* __restrict__ cond, int ldc,
+                               const int* __restrict__ row_utt, float* __restrict__ acts, int R, int H) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)R * H) return;
+  const int r = (int)(i / H), c = (int)(i % H);
+  const int b = row_utt ? row_utt[r] : 0;
+  float v = 0.f;
+  if (b >= 0) {
+    float ta = xin[(size_t)r * 2 * H + c], sa = xin[(size_t)r * 2 * H + H + c];
+    if (cond) {
+      ta += cond[(size_t)b * ldc + c];
+      sa += cond[(size_t)b * ldc + H + c];
+    }
+    v = tanhf(ta) * (1.0f / (1.0f + expf(-sa)));
+  }
+  acts[i] = v;
+}
+void launch_wn_gate(Exec& ex, const float* xin, const float* cond, int ldc, const int* row_utt,
+                    float* acts, int R, int H) {
+  const int64_t n = (int64_t)R * H;
+  if (n <= 0) return;
+  wn_gate_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ex.st>>>(xin, cond, ldc, row_utt, acts, R, H);
+  KLAUNCH(ex);
+}
+
+// conv_post (C -> 1 channel, no bias) with its preceding LeakyRelu and the final Tanh.
+__global__ void conv_post_tanh_kernel(const float* __restrict__ in, int C, const float* __restrict__ w,
+                                      int k, float slope, const int* __restrict__ row_utt, int valid_div,
+                                      float* __restrict__ out, int R) {
+  extern __shared__ float ws[];   // [k][C]
+  for (int i = threadIdx.x; i < k * C; i += blockDim.x) ws[i] = w[i];
+  __syncthreads();
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= R) return;
+  if (row_utt && row_utt[r / valid_div] < 0) {
+    out[r] = 0.f;
+    return;
+  }
+  const int pad = (k - 1) / 2;
+  float acc = 0.f;
+  for (int t = 0; t < k; ++t) {
+    const int rr = r + t - pad;
+    if (rr < 0 || rr >= R) continue;
+    const float4* p = reinterpret_cast<const float4*>(in + (size_t)rr * C);
+    for (int c4 = 0; c4 < C / 4; ++c4) {
+      float4 v = p[c4];
+      v.x = v.x >= 0.f ? v.x : v.x * slope;
+      v.y = v.y >= 0.f ? v.y : v.y * slope;
+      v.z = v.z >= 0.f ? v.z : v.z * slope;
+      v.w = v.w >= 0.f ? v.w : v.w * slope;
+      const float* wp = ws + t * C + c4 * 4;
+      acc = fmaf(v.x, wp[0], acc);
+      acc = fmaf(v.y, wp[1], acc);
+      acc = fmaf(v.z, wp[2], acc);
+      acc = fmaf(v.w, wp[3], acc);
+    }
+  }
+  out[r] = tanhf(acc);
+}
+void launch_conv_post_tanh(Exec& ex, const float* in, int C, const float* w, int k, float slope,
+                           const int* row_utt, int valid_div, float* out, int R) {
+  if (R <= 0) return;
+  conv_post_tanh_kernel<<<(R + 127) / 128, 128, sizeof(float) * k * C, ex.st>>>(in, C, w, k, slope, row_utt,
+                                                                             valid_div, out, R);
+  KLAUNCH(ex);
+}
+
+// speaker conditioning: Gather(emb_g, sid) + 1x1 Conv on a single column; one warp per output
+__global__ void cond_gemv_kernel(const float* __restrict__ emb_g, const int64_t* __restrict__ sids,
+                                 const float* __restrict__ W, const float* __restrict__ bias,
+                                 float* __restrict__ out, int ldo, int gin, int cout, int n_speakers) {
+  const int b = blockIdx.y;
+  const int co = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (co >= cout) return;
+  int64_t sid = sids ? sids[b] : 0;
+  if (sid < 0) sid += n_speakers;
+  float s = 0.f;
+  if (sid >= 0 && sid < n_speakers)
+    for (int ci = lane; ci < gin; ci += 32) s = fmaf(W[(size_t)co * gin + ci], emb_g[sid * gin + ci], s);
+  s = warp_sum(s);
+  if (lane == 0) out[(size_t)b * ldo + co] = s + (bias ? bias[co] : 0.f);
+}
+void launch_cond_gemv(Exec& ex, const float* emb_g, const int64_t* sids, const float* W, const float* bias,
+                      float* out, int ldo, int batch, int gin, int cout, int n_speakers) {
+  if (batch <= 0 || cout <= 0) return;
+  cond_gemv_kernel<<<dim3((cout + 7) / 8, batch), 256, 0, ex.st>>>(emb_g, sids, W, bias, out, ldo, gin, cout,
+                                                                n_speakers);
+  KLAUNCH(ex);
+}
+
+// packed sample rows -> dense per-utterance concatenation (+ PCM16 by WavFileWriter.swift:20-30:
+// Int(clamp(x,-1,1)*32767), truncation toward zero)
+__global__ void gather_audio_kernel(const float* __restrict__ packed, const int64_t* __restrict__ fstart,
+                                    const int64_t* __restrict__ y_len, const int64_t* __restrict__ sample_off,
+                                    int hop, float* __restrict__ dense, int16_t* __restrict__ pcm16) {
+  const int b = blockIdx.y;
+  const int64_t n = y_len[b] * hop;
+  const float* src = packed + fstart[b] * hop;
+  const int64_t o = sample_off[b];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float v = src[i];
+    dense[o + i] = v;
+    if (pcm16) pcm16[o + i] = (int16_t)(int)(fminf(fmaxf(v, -1.f), 1.f) * 32767.f);
+  }
+}
+void launch_gather_audio(Exec& ex, const float* packed, const int64_t* fstart, const int64_t* y_len,
+                         const int64_t* sample_off, int batch, int hop, float* dense, int16_t* pcm16,
+                         int64_t total_samples) {
+  if (batch <= 0 || total_samples <= 0) return;
+  int gx = (int)((total_samples / batch + 1023) / 1024);
+  gx = gx < 1 ? 1 : (gx > 256 ? 256 : gx);
+  gather_audio_kernel<<<dim3(gx, batch), 256, 0, ex.st>>>(packed, fstart, y_len, sample_off, hop, dense, pcm16);
+  KLAUNCH(ex);
+}
+
+// concatenated ids -> packed rows (-1 on gap rows) + per-row utterance id
+__global__ void pack_ids_kernel(const int64_t* __restrict__ ids, const int64_t* __restrict__ id_off,
+                                const int* __restrict__ utt_start, const int* __restrict__ utt_len,
+                                int64_t* __restrict__ ids_packed, int* __restrict__ row_utt, int n_vocab) {
+  const int b = blockIdx.y;
+  const int T = utt_len[b], r0 = utt_start[b];
+  const int64_t o = id_off[b];
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < T; t += gridDim.x * blockDim.x) {
+    int64_t id = ids[o + t];
+    if (id < 0) id = (id >= -(int64_t)n_vocab) ? id + n_vocab : INT64_MIN;   // negative-index wrap (gather.metal); -1 stays the gap marker
+    ids_packed[r0 + t] = id;
+    row_utt[r0 + t] = b;
+  }
+}
+void launch_pack_ids(Exec& ex, const int64_t* ids, const int64_t* id_off, const int* utt_start,
+                     const int* utt_len, int batch, int64_t* ids_packed, int* row_utt, int n_vocab) {
+  if (batch <= 0) return;
+  pack_ids_kernel<<<dim3(4, batch), 256, 0, ex.st>>>(ids, id_off, utt_start, utt_len, ids_packed, row_utt, n_vocab);
+  KLAUNCH(ex);
+}
+
+}  // namespace piper

@@ -1,0 +1,93 @@
+// Runtime context and the fixed stage pipeline that replaces GraphExecutor.executeOutput
+// (GraphExecutor.swift:156-327): no node interpretation, no per-call initializer decode, no
+// value table - ~150 fused launches over packed rows, one host sync (after the length
+// regulator publishes the frame counts).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/piper_b200.h"
+#include "kernels.h"
+#include "piper_config.h"
+#include "voice.h"
+
+namespace piper {
+
+// grow-only device arena with bump allocation per call
+struct Arena {
+  char* base = nullptr;
+  size_t cap = 0, off = 0;
+  void reset() { off = 0; }
+  void reserve(size_t bytes);   // may free + reallocate (contents are dead at that point)
+  template <typename T>
+  T* alloc(size_t n) {
+    const size_t bytes = (n * sizeof(T) + 255) & ~size_t(255);
+    if (off + bytes > cap) return nullptr;
+    T* p = reinterpret_cast<T*>(base + off);
+    off += bytes;
+    return p;
+  }
+  void release();
+};
+
+struct PinnedBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  void reserve(size_t bytes);
+  void release();
+};
+
+struct StageDump {
+  std::vector<float> x, stats, logw, zp, z;   // packed-row layouts
+  std::vector<int> utt_start, utt_len;
+  std::vector<int64_t> fstart, y_len;
+  int H = 0;
+  bool valid = false;
+};
+
+struct Context {
+  int device = 0;
+  cudaStream_t own_stream = nullptr;
+  cudaStream_t stream = nullptr;
+  Voice voice;
+  PiperConfig config;
+  bool have_config = false;
+  int precision = PIPER_B200_PRECISION_FP32;
+  std::string last_error;
+
+  Arena front, back;
+  PinnedBuf h_in, h_meta, h_audio, h_pcm;
+  std::vector<int64_t> sample_offsets, frame_lengths;
+  std::vector<int32_t> durations;
+  piper_b200_timings timings{};
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  StageDump dump;
+  float* d_audio_dense = nullptr;   // inside `back`
+
+  int gap_p = 0, gap_f = 0;         // zero rows between utterances (phoneme / frame level)
+
+  void init(int dev);
+  void destroy();
+  void finalize_voice();            // voice.finalize() + derived layout constants
+  int synthesize(const piper_b200_request& rq, piper_b200_result& rs);
+  int length_regulate(const float* logw, const int64_t* lengths, int batch, float length_scale,
+                      int32_t* durations, int64_t* frame_lengths, int32_t* frame_index, int64_t frame_capacity);
+};
+
+// fp32 CUDA-core implementation of flow + HiFi-GAN on packed rows (pipeline_back_f32.cpp)
+struct BackInputs {
+  const float* zp = nullptr;        // [Rf][H] fp32, gap rows zero
+  const int* frow_utt = nullptr;    // [Rf]
+  int Rf = 0, batch = 0;
+  const float* cond_flow = nullptr; // [n_flows][batch][2H*layers] or null
+  const float* cond_dec = nullptr;  // [batch][C0] or null
+};
+// returns packed audio [Rf*hop] (device, inside ctx.back); z_out (if non-null) receives the flow output
+float* run_back_f32(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep);
+size_t back_f32_bytes(const Context& ctx, int Rf, int batch);
+
+}  // namespace piper

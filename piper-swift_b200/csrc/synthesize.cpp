@@ -1,0 +1,379 @@
+// Context::synthesize - the hot path behind PiperMetalRuntime.synthesize
+// (PiperMetalRuntime.swift:62-80 -> GraphExecutor.executeOutput, GraphExecutor.swift:156-327).
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <stdexcept>
+
+#include "pipeline.h"
+
+namespace piper {
+
+#define CUDA_OK(x)                                                                         \
+  do {                                                                                     \
+    cudaError_t e_ = (x);                                                                  \
+    if (e_ != cudaSuccess)                                                                 \
+      throw std::runtime_error(std::string("cuda: ") + cudaGetErrorString(e_) + " at " #x); \
+  } while (0)
+
+namespace {
+
+ConvArgs conv_args(const ConvW& w, const float* in, int ldin, float* out, int ldout, int R, const int* row_utt) {
+  ConvArgs a;
+  a.in = in; a.ldin = ldin;
+  a.w = w.w; a.ldw = w.ldw; a.bias = w.b;
+  a.out = out; a.ldout = ldout;
+  a.row_utt = row_utt; a.valid_div = 1;
+  a.R_in = R; a.Q = R;
+  a.cin = w.cin; a.cout = w.cout; a.taps = w.taps;
+  a.tap_step = w.dil; a.in_off = -w.pad_l;
+  return a;
+}
+
+// DDSConv: per layer depthwise conv + LN + GELU, 1x1 conv, LN + GELU, residual
+void run_dds(Exec& ex, const std::vector<DDSLayerW>& layers, float* h, float* t1, float* t2, const int* row_utt,
+             int R, int C) {
+  for (const DDSLayerW& l : layers) {
+    launch_dds_sep_ln_gelu(ex, h, l.w_sep, l.b_sep, l.n1.gamma, l.n1.beta, t1, row_utt, R, C, l.k, l.dil);
+    launch_conv_f32(ex, conv_args(l.c1x1, t1, C, t2, C, R, row_utt));
+    LNArgs n;
+    n.x = t2; n.gamma = l.n2.gamma; n.beta = l.n2.beta; n.out = h; n.res = h; n.row_utt = row_utt;
+    n.R = R; n.C = C; n.gelu = 1;
+    launch_layernorm(ex, n);
+  }
+}
+
+double ms_between(cudaEvent_t a, cudaEvent_t b) {
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, a, b);
+  return ms;
+}
+
+}  // namespace
+
+int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
+  using clk = std::chrono::steady_clock;
+  const auto t_wall0 = clk::now();
+  if (!voice.finalized) { last_error = "state: voice not finalized"; return PIPER_B200_ERR_STATE; }
+  if (rq.batch <= 0 || !rq.phoneme_ids || !rq.lengths) {
+    last_error = "invalid argument: empty batch or null ids/lengths";
+    return PIPER_B200_ERR_INVALID_ARGUMENT;
+  }
+  if (precision != PIPER_B200_PRECISION_FP32) {
+    last_error = "unsupported: tensor-core precision modes are not built into this library yet";
+    return PIPER_B200_ERR_UNSUPPORTED;
+  }
+  const VoiceHParams& hp = voice.hp;
+  const int B = rq.batch, H = hp.hidden;
+  const bool ids_dev = rq.flags & PIPER_B200_FLAG_IDS_ON_DEVICE;
+  const bool keep_dev = rq.flags & PIPER_B200_FLAG_KEEP_ON_DEVICE;
+  const bool keep_stages = rq.flags & PIPER_B200_FLAG_KEEP_STAGES;
+  const bool want_pcm = rq.flags & PIPER_B200_FLAG_PCM16;
+  const float noise_scale = std::isnan(rq.noise_scale) ? config.noise_scale : rq.noise_scale;
+  const float length_scale = std::isnan(rq.length_scale) ? config.length_scale : rq.length_scale;
+  const float noise_w = std::isnan(rq.noise_w) ? config.noise_w : rq.noise_w;
+  const uint32_t seed = (uint32_t)(rq.seed & 0xffffffffu);
+
+  // ---- host-side layout of the phoneme rows ---------------------------------------------------
+  std::vector<int> utt_start(B), utt_len(B);
+  std::vector<int64_t> id_off(B + 1, 0);
+  int64_t rows = 0;
+  int max_len = 0;
+  for (int b = 0; b < B; ++b) {
+    const int64_t T = rq.lengths[b];
+    if (T <= 0 || T > (1 << 20)) {
+      last_error = "invalid argument: utterance " + std::to_string(b) + " has length " + std::to_string(T);
+      return PIPER_B200_ERR_INVALID_ARGUMENT;
+    }
+    utt_start[b] = (int)rows;
+    utt_len[b] = (int)T;
+    id_off[b + 1] = id_off[b] + T;
+    rows += T + (b + 1 < B ? gap_p : 0);
+    max_len = std::max(max_len, (int)T);
+  }
+  if (rows > (1 << 26)) { last_error = "capacity: too many phoneme rows"; return PIPER_B200_ERR_CAPACITY; }
+  const int Rp = (int)rows;
+  const int64_t n_ids = id_off[B];
+  if (hp.gin && !rq.speaker_ids) {
+    last_error = "invalid argument: multi-speaker voice needs speaker_ids";
+    return PIPER_B200_ERR_INVALID_ARGUMENT;
+  }
+
+  try {
+    CUDA_OK(cudaSetDevice(device));
+    Exec ex;
+    ex.st = stream;
+    timings = piper_b200_timings{};
+    const int L = hp.flow_wn_layers;
+    const int nflow = (int)voice.flows.size();
+    const int condw = hp.gin ? (H + nflow * 2 * H * L + hp.dec_c0) : 0;
+
+    // ---- front arena -------------------------------------------------------------------------
+    size_t fb = 0;
+    fb += (size_t)Rp * 4 * (H * 8 + 3 * H + hp.filter + 2 * H + 32 + 2 + 1) + (size_t)Rp * 4 * 4;
+    fb += (size_t)n_ids * 8 * 2 + (size_t)Rp * 8 + (size_t)B * (8 * 6 + 4 * 4) + (size_t)B * condw * 4;
+    if (rq.noise_dp) fb += (size_t)n_ids * 2 * 4;
+    fb += 64 * 256;
+    front.reserve(fb);
+    front.reset();
+    Arena& F = front;
+    int* d_utt_start = F.alloc<int>(B);
+    int* d_utt_len = F.alloc<int>(B);
+    int64_t* d_id_off = F.alloc<int64_t>(B + 1);
+    int64_t* d_sids = F.alloc<int64_t>(B);
+    int64_t* d_ids = F.alloc<int64_t>(n_ids);
+    int64_t* d_ids_packed = F.alloc<int64_t>(Rp);
+    int* p_utt = F.alloc<int>(Rp);
+    float* x = F.alloc<float>((size_t)Rp * H);
+    float* qkv = F.alloc<float>((size_t)Rp * 3 * H);
+    float* att = F.alloc<float>((size_t)Rp * H);
+    float* y = F.alloc<float>((size_t)Rp * H);
+    float* mid = F.alloc<float>((size_t)Rp * hp.filter);
+    float* stats = F.alloc<float>((size_t)Rp * 2 * H);
+    float* dph = F.alloc<float>((size_t)Rp * H);
+    float* dpc = F.alloc<float>((size_t)Rp * H);
+    float* hh = F.alloc<float>((size_t)Rp * H);
+    float* t1 = F.alloc<float>((size_t)Rp * H);
+    float* t2 = F.alloc<float>((size_t)Rp * H);
+    float* params = F.alloc<float>((size_t)Rp * 32);
+    float* zdp = F.alloc<float>((size_t)Rp * 2);
+    float* logw = F.alloc<float>(Rp);
+    int* dur = F.alloc<int>(Rp);
+    int* cum = F.alloc<int>(Rp);
+    int64_t* d_ylen = F.alloc<int64_t>(B);
+    int64_t* d_fstart = F.alloc<int64_t>(B + 1);
+    int64_t* d_soff = F.alloc<int64_t>(B + 1);
+    float* d_noise_dp = rq.noise_dp ? F.alloc<float>((size_t)n_ids * 2) : nullptr;
+    float* cond = condw ? F.alloc<float>((size_t)B * condw) : nullptr;
+    if (!d_soff || (rq.noise_dp && !d_noise_dp) || (condw && !cond))
+      throw std::runtime_error("capacity: front arena sizing bug");
+
+    // ---- H2D ------------------------------------------------------------------------------------
+    CUDA_OK(cudaEventRecord(ev[0], stream));
+    size_t h2d = 0;
+    {
+      const size_t meta = (size_t)B * 4 * 2 + (size_t)(B + 1) * 8 + (size_t)B * 8;
+      h_in.reserve(meta + (ids_dev ? 0 : (size_t)n_ids * 8) + 64);
+      char* hp_ = static_cast<char*>(h_in.p);
+      std::memcpy(hp_, utt_start.data(), (size_t)B * 4);
+      std::memcpy(hp_ + (size_t)B * 4, utt_len.data(), (size_t)B * 4);
+      std::memcpy(hp_ + (size_t)B * 8, id_off.data(), (size_t)(B + 1) * 8);
+      char* sid_h = hp_ + (size_t)B * 8 + (size_t)(B + 1) * 8;
+      if (rq.speaker_ids) std::memcpy(sid_h, rq.speaker_ids, (size_t)B * 8);
+      else std::memset(sid_h, 0, (size_t)B * 8);
+      CUDA_OK(cudaMemcpyAsync(d_utt_start, hp_, (size_t)B * 4, cudaMemcpyHostToDevice, stream));
+      CUDA_OK(cudaMemcpyAsync(d_utt_len, hp_ + (size_t)B * 4, (size_t)B * 4, cudaMemcpyHostToDevice, stream));
+      CUDA_OK(cudaMemcpyAsync(d_id_off, hp_ + (size_t)B * 8, (size_t)(B + 1) * 8, cudaMemcpyHostToDevice, stream));
+      CUDA_OK(cudaMemcpyAsync(d_sids, sid_h, (size_t)B * 8, cudaMemcpyHostToDevice, stream));
+      h2d += meta;
+      const int64_t* ids_src = rq.phoneme_ids;
+      if (!ids_dev) {
+        char* ids_h = sid_h + (size_t)B * 8;
+        std::memcpy(ids_h, rq.phoneme_ids, (size_t)n_ids * 8);
+        CUDA_OK(cudaMemcpyAsync(d_ids, ids_h, (size_t)n_ids * 8, cudaMemcpyHostToDevice, stream));
+        h2d += (size_t)n_ids * 8;
+        ids_src = d_ids;
+      }
+      if (rq.noise_dp) {
+        CUDA_OK(cudaMemcpyAsync(d_noise_dp, rq.noise_dp, (size_t)n_ids * 2 * 4, cudaMemcpyHostToDevice, stream));
+        h2d += (size_t)n_ids * 8;
+      }
+      CUDA_OK(cudaMemsetAsync(d_ids_packed, 0xff, (size_t)Rp * 8, stream));   // -1 on gap rows
+      CUDA_OK(cudaMemsetAsync(p_utt, 0xff, (size_t)Rp * 4, stream));
+      launch_pack_ids(ex, ids_src, d_id_off, d_utt_start, d_utt_len, B, d_ids_packed, p_utt, hp.n_vocab);
+    }
+    CUDA_OK(cudaEventRecord(ev[1], stream));
+
+    // ---- speaker conditioning vectors ----------------------------------------------------------------
+    float* cond_dp = nullptr;
+    float* cond_flow = nullptr;
+    float* cond_dec = nullptr;
+    if (condw) {
+      cond_dp = cond;
+      cond_flow = cond + (size_t)B * H;
+      cond_dec = cond_flow + (size_t)nflow * B * 2 * H * L;
+      launch_cond_gemv(ex, voice.emb_g, d_sids, voice.dp_cond_w, voice.dp_cond_b, cond_dp, H, B, hp.gin, H, hp.n_speakers);
+      for (int f = 0; f < nflow; ++f)
+        launch_cond_gemv(ex, voice.emb_g, d_sids, voice.flows[f].cond_w, voice.flows[f].cond_b,
+                         cond_flow + (size_t)f * B * 2 * H * L, 2 * H * L, B, hp.gin, 2 * H * L, hp.n_speakers);
+      launch_cond_gemv(ex, voice.emb_g, d_sids, voice.dec_cond_w, voice.dec_cond_b, cond_dec, hp.dec_c0, B, hp.gin,
+                       hp.dec_c0, hp.n_speakers);
+    }
+
+    // ---- text encoder ------------------------------------------------------------------
+    launch_embed(ex, d_ids_packed, voice.emb, x, Rp, H, hp.n_vocab, std::sqrt((float)H));
+    CUDA_OK(cudaMemsetAsync(att, 0, (size_t)Rp * H * 4, stream));
+    for (const EncLayerW& l : voice.enc) {
+      launch_conv_f32(ex, conv_args(l.qkv, x, H, qkv, 3 * H, Rp, p_utt));
+      launch_attention(ex, qkv, l.rel_k, l.rel_v, att, d_utt_start, d_utt_len, B, max_len, H, hp.n_heads, hp.window);
+      launch_conv_f32(ex, conv_args(l.o, att, H, y, H, Rp, p_utt));
+      LNArgs n1;
+      n1.x = x; n1.y = y; n1.gamma = l.n1.gamma; n1.beta = l.n1.beta; n1.out = x; n1.row_utt = p_utt; n1.R = Rp; n1.C = H;
+      launch_layernorm(ex, n1);
+      ConvArgs f1 = conv_args(l.ffn1, x, H, mid, hp.filter, Rp, p_utt);
+      f1.relu = 1;
+      launch_conv_f32(ex, f1);
+      launch_conv_f32(ex, conv_args(l.ffn2, mid, hp.filter, y, H, Rp, p_utt));
+      LNArgs n2 = n1;
+      n2.gamma = l.n2.gamma; n2.beta = l.n2.beta;
+      launch_layernorm(ex, n2);
+    }
+    launch_conv_f32(ex, conv_args(voice.enc_proj, x, H, stats, 2 * H, Rp, p_utt));
+
+    // ---- stochastic duration predictor, reverse ---------------------------------------------------
+    {
+      ConvArgs a = conv_args(voice.dp_pre, x, H, dph, H, Rp, p_utt);
+      a.uttbias = cond_dp; a.ldub = H;
+      launch_conv_f32(ex, a);
+      run_dds(ex, voice.dp_dds, dph, t1, t2, p_utt, Rp, H);
+      launch_conv_f32(ex, conv_args(voice.dp_proj, dph, H, dpc, H, Rp, p_utt));
+      CUDA_OK(cudaMemsetAsync(zdp, 0, (size_t)Rp * 2 * 4, stream));
+      launch_noise_dp(ex, zdp, d_noise_dp, d_utt_start, d_utt_len, d_id_off, B, Rp, seed, noise_w);
+      const float inv_sqrt_fc = 1.0f / std::sqrt((float)H);
+      for (const ConvFlowW& f : voice.dp_flows) {
+        launch_convflow_pre(ex, zdp + (size_t)(1 - f.target) * Rp, f.pre_w, f.pre_b, dpc, hh, p_utt, Rp, H);
+        run_dds(ex, f.dds, hh, t1, t2, p_utt, Rp, H);
+        launch_conv_f32(ex, conv_args(f.proj, hh, H, params, 32, Rp, p_utt));
+        launch_spline_inverse(ex, zdp + (size_t)f.target * Rp, params, 32, p_utt, Rp, hp.dp_bins, 5.0f, inv_sqrt_fc);
+      }
+    }
+
+    // ---- length regulator ----------------------------------------------------------------------
+    launch_durations(ex, zdp + (size_t)voice.dp_logw_channel * Rp, voice.ea_m, voice.ea_logs, length_scale,
+                     d_utt_start, d_utt_len, B, logw, dur, cum, d_ylen);
+    launch_frame_layout(ex, d_ylen, B, gap_f, d_fstart);
+    h_meta.reserve((size_t)(2 * B + 2) * 8 + (size_t)Rp * 4);
+    int64_t* h_ylen = static_cast<int64_t*>(h_meta.p);
+    int64_t* h_fstart = h_ylen + B;
+    int32_t* h_dur = reinterpret_cast<int32_t*>(h_fstart + B + 1);
+    CUDA_OK(cudaMemcpyAsync(h_ylen, d_ylen, (size_t)B * 8, cudaMemcpyDeviceToHost, stream));
+    CUDA_OK(cudaMemcpyAsync(h_fstart, d_fstart, (size_t)(B + 1) * 8, cudaMemcpyDeviceToHost, stream));
+    CUDA_OK(cudaMemcpyAsync(h_dur, dur, (size_t)Rp * 4, cudaMemcpyDeviceToHost, stream));
+    CUDA_OK(cudaEventRecord(ev[2], stream));
+    CUDA_OK(cudaStreamSynchronize(stream));   // the one data-dependent host sync: frame counts size the back end
+    size_t d2h = (size_t)(2 * B + 1) * 8 + (size_t)Rp * 4;
+
+    const int64_t Rf64 = h_fstart[B] - gap_f;
+    if (Rf64 <= 0 || Rf64 * hp.hop > (int64_t)2000000000) {
+      last_error = "capacity: predicted durations give " + std::to_string(Rf64) + " frame rows";
+      return PIPER_B200_ERR_CAPACITY;
+    }
+    const int Rf = (int)Rf64;
+    frame_lengths.assign(h_ylen, h_ylen + B);
+    sample_offsets.assign(B + 1, 0);
+    int64_t total_frames = 0;
+    for (int b = 0; b < B; ++b) {
+      if (rq.noise_main && h_ylen[b] > rq.noise_main_stride) {
+        last_error = "invalid argument: noise_main_stride " + std::to_string(rq.noise_main_stride) +
+                     " < frames of utterance " + std::to_string(b) + " (" + std::to_string(h_ylen[b]) + ")";
+        return PIPER_B200_ERR_INVALID_ARGUMENT;
+      }
+      total_frames += h_ylen[b];
+      sample_offsets[b + 1] = sample_offsets[b] + h_ylen[b] * hp.hop;
+    }
+    const int64_t total_samples = sample_offsets[B];
+    durations.resize(n_ids);
+    for (int b = 0; b < B; ++b)
+      std::memcpy(durations.data() + id_off[b], h_dur + utt_start[b], (size_t)utt_len[b] * 4);
+
+    // ---- back arena ---------------------------------------------------------------------------------------------
+    size_t bb = back_f32_bytes(*this, Rf, B);
+    bb += (size_t)Rf * H * 4 * 2 + (size_t)Rf * 4 * 2 + (size_t)total_samples * 6 + 64 * 256;
+    if (rq.noise_main) bb += (size_t)B * H * rq.noise_main_stride * 4;
+    back.reserve(bb);
+    back.reset();
+    Arena& K = back;
+    int* frow_utt = K.alloc<int>(Rf);
+    int* frow_src = K.alloc<int>(Rf);
+    float* zp = K.alloc<float>((size_t)Rf * H);
+    float* z_keep = keep_stages ? K.alloc<float>((size_t)Rf * H) : nullptr;
+    float* dense = K.alloc<float>(total_samples);
+    int16_t* pcm = want_pcm ? K.alloc<int16_t>(total_samples) : nullptr;
+    float* d_noise_main = nullptr;
+    if (rq.noise_main) {
+      d_noise_main = K.alloc<float>((size_t)B * H * rq.noise_main_stride);
+      if (!d_noise_main) throw std::runtime_error("capacity: back arena sizing bug (noise)");
+      CUDA_OK(cudaMemcpyAsync(d_noise_main, rq.noise_main, (size_t)B * H * rq.noise_main_stride * 4,
+                              cudaMemcpyHostToDevice, stream));
+      h2d += (size_t)B * H * rq.noise_main_stride * 4;
+    }
+    if (!dense) throw std::runtime_error("capacity: back arena sizing bug");
+    CUDA_OK(cudaMemcpyAsync(d_soff, sample_offsets.data(), (size_t)(B + 1) * 8, cudaMemcpyHostToDevice, stream));
+
+    launch_frame_map(ex, d_fstart, d_ylen, cum, d_utt_start, d_utt_len, B, Rf, frow_utt, frow_src);
+    launch_expand_prior(ex, stats, frow_utt, frow_src, d_fstart, d_ylen, d_noise_main, rq.noise_main_stride, seed,
+                        noise_scale, zp, Rf, H);
+    if (keep_stages) {
+      dump = StageDump{};
+      dump.H = H;
+      dump.utt_start = utt_start; dump.utt_len = utt_len;
+      dump.fstart.assign(h_fstart, h_fstart + B + 1);
+      dump.y_len.assign(h_ylen, h_ylen + B);
+      dump.x.resize((size_t)Rp * H); dump.stats.resize((size_t)Rp * 2 * H); dump.logw.resize(Rp);
+      dump.zp.resize((size_t)Rf * H); dump.z.resize((size_t)Rf * H);
+      CUDA_OK(cudaMemcpyAsync(dump.x.data(), x, dump.x.size() * 4, cudaMemcpyDeviceToHost, stream));
+      CUDA_OK(cudaMemcpyAsync(dump.stats.data(), stats, dump.stats.size() * 4, cudaMemcpyDeviceToHost, stream));
+      CUDA_OK(cudaMemcpyAsync(dump.logw.data(), logw, dump.logw.size() * 4, cudaMemcpyDeviceToHost, stream));
+      CUDA_OK(cudaMemcpyAsync(dump.zp.data(), zp, dump.zp.size() * 4, cudaMemcpyDeviceToHost, stream));
+    }
+    BackInputs bi;
+    bi.zp = zp; bi.frow_utt = frow_utt; bi.Rf = Rf; bi.batch = B;
+    bi.cond_flow = cond_flow; bi.cond_dec = cond_dec;
+    CUDA_OK(cudaEventRecord(ev[3], stream));
+    float* packed = run_back_f32(*this, ex, bi, z_keep);
+    launch_gather_audio(ex, packed, d_fstart, d_ylen, d_soff, B, hp.hop, dense, pcm, total_samples);
+    CUDA_OK(cudaEventRecord(ev[4], stream));
+    if (keep_stages) {
+      CUDA_OK(cudaMemcpyAsync(dump.z.data(), z_keep, dump.z.size() * 4, cudaMemcpyDeviceToHost, stream));
+      dump.valid = true;
+    }
+
+    // ---- D2H ---------------------------------------------------------------------------------------------------------
+    rs = piper_b200_result{};
+    if (keep_dev) {
+      rs.audio = dense;
+      rs.pcm16 = pcm;
+    } else {
+      h_audio.reserve((size_t)total_samples * 4);
+      CUDA_OK(cudaMemcpyAsync(h_audio.p, dense, (size_t)total_samples * 4, cudaMemcpyDeviceToHost, stream));
+      d2h += (size_t)total_samples * 4;
+      rs.audio = static_cast<const float*>(h_audio.p);
+      if (want_pcm) {
+        h_pcm.reserve((size_t)total_samples * 2);
+        CUDA_OK(cudaMemcpyAsync(h_pcm.p, pcm, (size_t)total_samples * 2, cudaMemcpyDeviceToHost, stream));
+        d2h += (size_t)total_samples * 2;
+        rs.pcm16 = static_cast<const int16_t*>(h_pcm.p);
+      }
+    }
+    CUDA_OK(cudaEventRecord(ev[5], stream));
+    CUDA_OK(cudaStreamSynchronize(stream));
+    CUDA_OK(cudaGetLastError());
+    d_audio_dense = dense;
+    rs.sample_offsets = sample_offsets.data();
+    rs.frame_lengths = frame_lengths.data();
+    rs.durations = durations.data();
+    rs.total_samples = total_samples;
+    rs.total_frames = total_frames;
+
+    timings.h2d_ms = ms_between(ev[0], ev[1]);
+    timings.front_ms = ms_between(ev[1], ev[2]);
+    timings.decoder_ms = ms_between(ev[3], ev[4]);   // flow + decoder; split refined by the tc back end
+    timings.flow_ms = 0;
+    timings.d2h_ms = ms_between(ev[4], ev[5]);
+    timings.gpu_ms = ms_between(ev[0], ev[5]);
+    timings.kernel_launches = ex.launches;
+    timings.h2d_bytes = (int64_t)h2d;
+    timings.d2h_bytes = (int64_t)d2h;
+    timings.dec_flops = hp.dec_flops_per_frame * (double)total_frames;
+    timings.flow_flops = hp.flow_flops_per_frame * (double)total_frames;
+    timings.wall_ms = std::chrono::duration<double, std::milli>(clk::now() - t_wall0).count();
+    return PIPER_B200_OK;
+  } catch (const std::exception& e) {
+    last_error = e.what();
+    cudaGetLastError();
+    return last_error.rfind("capacity", 0) == 0 ? PIPER_B200_ERR_CAPACITY : PIPER_B200_ERR_CUDA;
+  }
+}
+
+}  // namespace piper

@@ -1,0 +1,129 @@
+// Voice binding: recognises the Piper-VITS graph from initializer names/shapes plus the
+// Conv/ConvTranspose node attributes (the reference interprets the nodes one by one,
+// GraphExecutor.swift:227-264; this runtime binds them into a fixed stage pipeline) and
+// repacks every weight once into the layout its kernel reads (the reference re-decodes all
+// 401 initializers on every call, GraphExecutor.swift:187-189).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "onnx_reader.h"
+
+namespace piper {
+
+struct ConvAttr {
+  int stride = 1, dilation = 1, group = 1, pad_begin = -1, pad_end = -1;
+};
+
+struct HostTensor {
+  std::vector<int64_t> dims;
+  std::vector<float> f32;
+};
+
+// fp32 SIMT conv weights: [phases][taps][cin][ldw] (+ bias[ldw]); see kernels.h ConvArgs
+struct ConvW {
+  float* w = nullptr;
+  float* b = nullptr;
+  int cin = 0, cout = 0, k = 1, dil = 1, ldw = 0;
+  int taps = 1, phases = 1, ct_pad = 0;   // transposed conv: taps = k/stride, phases = stride
+  int pad_l = 0;
+};
+struct LNW {
+  float* gamma = nullptr;
+  float* beta = nullptr;
+  int c = 0;
+};
+struct DDSLayerW {
+  float* w_sep = nullptr;   // [k][C]
+  float* b_sep = nullptr;
+  LNW n1, n2;
+  ConvW c1x1;
+  int k = 3, dil = 1;
+};
+struct EncLayerW {
+  ConvW qkv, o, ffn1, ffn2;
+  float* rel_k = nullptr;   // [2w+1][kc]
+  float* rel_v = nullptr;
+  LNW n1, n2;
+};
+struct ConvFlowW {
+  float* pre_w = nullptr;   // [C]
+  float* pre_b = nullptr;
+  std::vector<DDSLayerW> dds;
+  ConvW proj;               // C -> 3*bins-1
+  int target = 0;           // which of the two z channels the spline transforms
+};
+struct CouplingW {
+  ConvW pre;                // half -> H (input channels permuted when the layer sits behind a Flip)
+  std::vector<ConvW> in_layers;
+  std::vector<ConvW> res;   // res part of res_skip (cols [0,H)); empty cout for the last layer
+  std::vector<ConvW> skip;  // skip part
+  ConvW post;               // H -> half, NEGATED so that x1 - m is an add
+  float* cond_w = nullptr;  // [2H*layers][gin] original layout for the speaker GEMV
+  float* cond_b = nullptr;
+  int in_off = 0, out_off = 0;   // channel offsets of the conditioning / updated half
+};
+struct ResBlockW {
+  std::vector<ConvW> c1, c2;   // ResBlock1: pairs; ResBlock2: c1 only
+};
+struct StageW {
+  ConvW up;                 // transposed conv, polyphase packed
+  std::vector<ResBlockW> rbs;
+  int ch = 0, stride = 1;
+};
+
+struct VoiceHParams {
+  int n_vocab = 0, hidden = 0, filter = 0, n_heads = 0, n_layers = 0, ffn_kernel = 0, window = 0;
+  int dp_layers = 0, dp_kernel = 0, dp_bins = 0;
+  std::vector<int> dp_flow_ids, flow_ids;
+  int flow_kernel = 0, flow_wn_layers = 0;
+  int resblock = 2, dec_c0 = 0;
+  std::vector<std::pair<int, int>> ups;   // (kernel, stride)
+  std::vector<int> rb_kernels;
+  std::vector<std::vector<int>> rb_dil;
+  int gin = 0, n_speakers = 1;
+  int hop = 1;
+  int64_t n_params = 0;
+  double dec_flops_per_frame = 0, flow_flops_per_frame = 0, enc_flops_per_id = 0;
+};
+
+struct Voice {
+  VoiceHParams hp;
+  // host-side staging (route A fills it from the ONNX file, route B from set_weight calls)
+  std::map<std::string, HostTensor> tensors;
+  std::map<std::string, ConvAttr> conv_attrs;
+  bool finalized = false;
+
+  // device weights
+  float* emb = nullptr;
+  std::vector<EncLayerW> enc;
+  ConvW enc_proj;
+  float* emb_g = nullptr;
+  ConvW dp_pre, dp_proj;
+  std::vector<DDSLayerW> dp_dds;
+  float* dp_cond_w = nullptr;
+  float* dp_cond_b = nullptr;
+  std::vector<ConvFlowW> dp_flows;   // execution order
+  int dp_logw_channel = 0;           // which physical z channel holds logw after the flips
+  float ea_m = 0.f, ea_logs = 0.f;
+  std::vector<CouplingW> flows;      // execution order
+  ConvW dec_pre;
+  float* dec_cond_w = nullptr;
+  float* dec_cond_b = nullptr;
+  std::vector<StageW> stages;
+  float* post_w = nullptr;           // [k][C]
+  int post_k = 7;
+
+  std::vector<void*> allocs;
+
+  void add_onnx(const OnnxModel& m);   // copies initializers + conv attributes
+  void finalize();                     // throws std::runtime_error on an unrecognised graph
+  void release();
+  ~Voice() { release(); }
+};
+
+}  // namespace piper

@@ -1,0 +1,339 @@
+"""Host-side mirror of the reference's `PiperMetalRuntime` (PiperMetalRuntime.swift:10-122)
+over the C ABI of include/piper_b200.h (ctypes; the Swift twin is in swift/).
+
+Same method names, argument meaning and error behaviour:
+  PiperCUDARuntime(model_path, config_path, options)      ~ init(modelURL:configURL:options:) :37
+  .synthesize(phoneme_ids, noise_scale=None, ...)         ~ synthesize(phonemeIDs:...) -> [Float] :62
+  .synthesize_stream(..., chunk_size=2048)                ~ synthesizeStream(...) :84 (PiperAudioChunk)
+  .last_run_timings                                       ~ lastRunTimings :33
+plus the additive batch / speaker / injected-noise forms the B200 configs need.
+There is NO CPU fallback: if the CUDA library is missing or no GPU is present the
+constructor raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+import os
+from dataclasses import dataclass
+from typing import Iterator, List, Optional, Sequence
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "libpiper_b200.so")
+
+OK = 0
+PRECISION = {"fp32": 0, "bf16": 1, "f16": 2}
+FLAG_IDS_ON_DEVICE, FLAG_KEEP_ON_DEVICE, FLAG_KEEP_STAGES, FLAG_PCM16 = 1, 2, 4, 8
+ERR_NAMES = {1: "invalid_argument", 2: "io", 3: "decode", 4: "unsupported", 5: "cuda", 6: "state", 7: "capacity"}
+
+
+class PiperB200Error(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"[{ERR_NAMES.get(code, code)}] {message}")
+        self.code = code
+
+
+class VoiceInfo(C.Structure):
+    _fields_ = [("sample_rate", C.c_int32), ("num_symbols", C.c_int32), ("num_speakers", C.c_int32),
+                ("hidden", C.c_int32), ("hop", C.c_int32), ("dec_channels0", C.c_int32),
+                ("resblock", C.c_int32), ("n_ups", C.c_int32),
+                ("noise_scale", C.c_float), ("length_scale", C.c_float), ("noise_w", C.c_float),
+                ("n_params", C.c_int64), ("dec_flops_per_frame", C.c_double),
+                ("flow_flops_per_frame", C.c_double), ("enc_flops_per_id", C.c_double)]
+
+
+class Request(C.Structure):
+    _fields_ = [("phoneme_ids", C.c_void_p), ("lengths", C.c_void_p), ("speaker_ids", C.c_void_p),
+                ("batch", C.c_int32), ("flags", C.c_uint32),
+                ("noise_scale", C.c_float), ("length_scale", C.c_float), ("noise_w", C.c_float),
+                ("noise_dp", C.c_void_p), ("noise_main", C.c_void_p), ("noise_main_stride", C.c_int64),
+                ("seed", C.c_uint64)]
+
+
+class Result(C.Structure):
+    _fields_ = [("audio", C.c_void_p), ("pcm16", C.c_void_p), ("sample_offsets", C.POINTER(C.c_int64)),
+                ("frame_lengths", C.POINTER(C.c_int64)), ("durations", C.POINTER(C.c_int32)),
+                ("total_samples", C.c_int64), ("total_frames", C.c_int64)]
+
+
+class Timings(C.Structure):
+    _fields_ = [("wall_ms", C.c_double), ("gpu_ms", C.c_double), ("front_ms", C.c_double),
+                ("flow_ms", C.c_double), ("decoder_ms", C.c_double), ("h2d_ms", C.c_double),
+                ("d2h_ms", C.c_double), ("kernel_launches", C.c_int64), ("h2d_bytes", C.c_int64),
+                ("d2h_bytes", C.c_int64), ("dec_flops", C.c_double), ("flow_flops", C.c_double)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+_lib = None
+
+
+def load_library(path: str = LIB_PATH):
+    """dlopen the C-ABI library and declare every prototype of include/piper_b200.h."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(path):
+        raise PiperB200Error(5, f"CUDA library not built: {path} (run __graft_entry__.build())")
+    lib = C.CDLL(path)
+    P = C.c_void_p
+    sig = {
+        "piper_b200_abi_version": (C.c_int, []),
+        "piper_b200_last_error": (C.c_char_p, [P]),
+        "piper_b200_create": (C.c_int, [C.c_int, C.POINTER(P)]),
+        "piper_b200_destroy": (None, [P]),
+        "piper_b200_load_voice": (C.c_int, [P, C.c_char_p, C.c_char_p]),
+        "piper_b200_set_weight": (C.c_int, [P, C.c_char_p, C.c_int32, C.POINTER(C.c_int64), C.c_int32, P, C.c_size_t]),
+        "piper_b200_set_conv_attr": (C.c_int, [P, C.c_char_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32]),
+        "piper_b200_set_config": (C.c_int, [P, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_float]),
+        "piper_b200_finalize": (C.c_int, [P]),
+        "piper_b200_get_voice_info": (C.c_int, [P, C.POINTER(VoiceInfo)]),
+        "piper_b200_set_precision": (C.c_int, [P, C.c_int32]),
+        "piper_b200_set_stream": (C.c_int, [P, P]),
+        "piper_b200_synthesize": (C.c_int, [P, C.POINTER(Request), C.POINTER(Result)]),
+        "piper_b200_get_timings": (C.c_int, [P, C.POINTER(Timings)]),
+        "piper_b200_get_stage": (C.c_int, [P, C.c_char_p, C.c_int32, P, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+        "piper_b200_length_regulate": (C.c_int, [P, P, P, C.c_int32, C.c_float, P, P, P, C.c_int64]),
+        "piper_b200_random_normal": (C.c_int, [P, C.c_uint64, C.c_int64, P]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+EXPORTED_SYMBOLS = [
+    "piper_b200_abi_version", "piper_b200_last_error", "piper_b200_create", "piper_b200_destroy",
+    "piper_b200_load_voice", "piper_b200_set_weight", "piper_b200_set_conv_attr", "piper_b200_set_config",
+    "piper_b200_finalize", "piper_b200_get_voice_info", "piper_b200_set_precision", "piper_b200_set_stream",
+    "piper_b200_synthesize", "piper_b200_get_timings", "piper_b200_get_stage", "piper_b200_length_regulate",
+    "piper_b200_random_normal",
+]
+
+
+@dataclass
+class Options:
+    """PiperMetalRuntime.Options (PiperMetalRuntime.swift:11-26).  preferCPU* have no meaning
+    here (there is no CPU path) and are accepted only for source compatibility."""
+    seed: int = 1234
+    prefer_cpu_conv: bool = False
+    prefer_cpu_elementwise: bool = False
+    device: int = 0
+    precision: str = "fp32"
+
+
+@dataclass
+class PiperAudioFormat:          # PiperAudio.swift:3-11
+    sample_rate: int
+    channels: int = 1
+
+
+@dataclass
+class PiperAudioChunk:           # PiperAudio.swift:13-25
+    format: PiperAudioFormat
+    start_sample_index: int
+    samples: np.ndarray
+    is_final: bool
+
+
+@dataclass
+class BatchResult:
+    audio: List[np.ndarray]
+    frame_lengths: np.ndarray
+    durations: List[np.ndarray]
+    total_samples: int
+    total_frames: int
+    pcm16: Optional[List[np.ndarray]] = None
+    device_ptr: Optional[int] = None
+
+
+class PiperCUDARuntime:
+    """B200 drop-in for PiperMetalRuntime (PiperMetalRuntime.swift:10)."""
+
+    def __init__(self, model_path: str, config_path: str, options: Optional[Options] = None):
+        self.options = options or Options()
+        self._lib = load_library()
+        self._ctx = C.c_void_p()
+        rc = self._lib.piper_b200_create(self.options.device, C.byref(self._ctx))
+        if rc != OK:
+            raise PiperB200Error(rc, self._lib.piper_b200_last_error(None).decode())
+        try:
+            self._check(self._lib.piper_b200_load_voice(self._ctx, model_path.encode(), config_path.encode()))
+            self.set_precision(self.options.precision)
+            info = VoiceInfo()
+            self._check(self._lib.piper_b200_get_voice_info(self._ctx, C.byref(info)))
+            self.info = info
+        except Exception:
+            self.close()
+            raise
+        self.model_path, self.config_path = model_path, config_path
+
+    # ---- plumbing ---------------------------------------------------------------------
+    def _check(self, rc: int):
+        if rc != OK:
+            raise PiperB200Error(rc, self._lib.piper_b200_last_error(self._ctx).decode())
+
+    def close(self):
+        if getattr(self, "_ctx", None) is not None and self._ctx:
+            self._lib.piper_b200_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_precision(self, precision: str):
+        self._check(self._lib.piper_b200_set_precision(self._ctx, PRECISION[precision]))
+        self.precision = precision
+
+    def set_stream(self, cuda_stream_ptr: Optional[int]):
+        self._check(self._lib.piper_b200_set_stream(self._ctx, C.c_void_p(cuda_stream_ptr or 0)))
+
+    @property
+    def sample_rate(self) -> int:
+        return int(self.info.sample_rate)
+
+    @property
+    def last_run_timings(self) -> dict:
+        t = Timings()
+        self._check(self._lib.piper_b200_get_timings(self._ctx, C.byref(t)))
+        return t.as_dict()
+
+    # ---- the reference's API --------------------------------------------------------------
+    def synthesize(self, phoneme_ids: Sequence[int], noise_scale: Optional[float] = None,
+                   length_scale: Optional[float] = None, noise_w: Optional[float] = None,
+                   speaker_id: Optional[int] = None) -> np.ndarray:
+        """Returns raw float32 samples (mono), like PiperMetalRuntime.synthesize (:62-80)."""
+        r = self.synthesize_batch([phoneme_ids], noise_scale, length_scale, noise_w,
+                                  speaker_ids=None if speaker_id is None else [speaker_id])
+        return r.audio[0]
+
+    def synthesize_stream(self, phoneme_ids: Sequence[int], noise_scale: Optional[float] = None,
+                          length_scale: Optional[float] = None, noise_w: Optional[float] = None,
+                          chunk_size: int = 2048) -> Iterator[PiperAudioChunk]:
+        """synthesizeStream (:84-121): chunks the finished waveform, as the reference does today."""
+        assert chunk_size > 0
+        fmt = PiperAudioFormat(self.sample_rate, 1)
+        samples = self.synthesize(phoneme_ids, noise_scale, length_scale, noise_w)
+        idx = 0
+        while idx < len(samples):
+            end = min(len(samples), idx + chunk_size)
+            yield PiperAudioChunk(fmt, idx, samples[idx:end].copy(), end == len(samples))
+            idx = end
+
+    # ---- additive: ragged batch, speakers, injected noise, device-resident inputs ---------------
+    def synthesize_batch(self, utterances: Sequence[Sequence[int]], noise_scale: Optional[float] = None,
+                         length_scale: Optional[float] = None, noise_w: Optional[float] = None,
+                         speaker_ids: Optional[Sequence[int]] = None,
+                         noise_dp: Optional[Sequence[np.ndarray]] = None,
+                         noise_main: Optional[Sequence[np.ndarray]] = None,
+                         seed: Optional[int] = None, keep_stages: bool = False, pcm16: bool = False,
+                         copy: bool = True) -> BatchResult:
+        B = len(utterances)
+        lengths = np.array([len(u) for u in utterances], dtype=np.int64)
+        ids = np.concatenate([np.asarray(u, dtype=np.int64) for u in utterances]) if B else np.zeros(0, np.int64)
+        return self.synthesize_packed(ids, lengths, noise_scale, length_scale, noise_w, speaker_ids, noise_dp,
+                                      noise_main, seed, keep_stages, pcm16, copy)
+
+    def synthesize_packed(self, ids: np.ndarray, lengths: np.ndarray, noise_scale=None, length_scale=None,
+                          noise_w=None, speaker_ids=None, noise_dp=None, noise_main=None, seed=None,
+                          keep_stages=False, pcm16=False, copy=True, ids_device_ptr: Optional[int] = None,
+                          keep_on_device: bool = False) -> BatchResult:
+        B = int(len(lengths))
+        lengths = np.ascontiguousarray(lengths, dtype=np.int64)
+        rq = Request()
+        keep = []   # keep numpy buffers alive across the call
+        if ids_device_ptr is not None:
+            rq.phoneme_ids = ids_device_ptr
+        else:
+            ids = np.ascontiguousarray(ids, dtype=np.int64)
+            keep.append(ids)
+            rq.phoneme_ids = ids.ctypes.data
+        rq.lengths = lengths.ctypes.data
+        if speaker_ids is not None:
+            sids = np.ascontiguousarray(speaker_ids, dtype=np.int64)
+            keep.append(sids)
+            rq.speaker_ids = sids.ctypes.data
+        rq.batch = B
+        nan = float("nan")
+        rq.noise_scale = nan if noise_scale is None else noise_scale
+        rq.length_scale = nan if length_scale is None else length_scale
+        rq.noise_w = nan if noise_w is None else noise_w
+        if noise_dp is not None:
+            nd = np.ascontiguousarray(np.concatenate([np.asarray(n, np.float32).reshape(-1) for n in noise_dp]))
+            if nd.size != 2 * int(lengths.sum()):
+                raise PiperB200Error(1, "noise_dp must be [2, T_b] per utterance")
+            keep.append(nd)
+            rq.noise_dp = nd.ctypes.data
+        if noise_main is not None:
+            H = int(self.info.hidden)
+            stride = max(int(n.shape[1]) for n in noise_main)
+            nm = np.zeros((B, H, stride), np.float32)
+            for b, n in enumerate(noise_main):
+                nm[b, :, :n.shape[1]] = n
+            keep.append(nm)
+            rq.noise_main = nm.ctypes.data
+            rq.noise_main_stride = stride
+        rq.seed = self.options.seed if seed is None else seed
+        rq.flags = ((FLAG_KEEP_STAGES if keep_stages else 0) | (FLAG_PCM16 if pcm16 else 0) |
+                    (FLAG_IDS_ON_DEVICE if ids_device_ptr is not None else 0) |
+                    (FLAG_KEEP_ON_DEVICE if keep_on_device else 0))
+        rs = Result()
+        self._check(self._lib.piper_b200_synthesize(self._ctx, C.byref(rq), C.byref(rs)))
+        offs = np.ctypeslib.as_array(rs.sample_offsets, shape=(B + 1,)).copy()
+        fl = np.ctypeslib.as_array(rs.frame_lengths, shape=(B,)).copy()
+        n_ids = int(lengths.sum())
+        dur_all = np.ctypeslib.as_array(rs.durations, shape=(n_ids,)).copy()
+        id_off = np.concatenate([[0], np.cumsum(lengths)])
+        durs = [dur_all[id_off[b]:id_off[b + 1]] for b in range(B)]
+        out = BatchResult([], fl, durs, int(rs.total_samples), int(rs.total_frames))
+        if keep_on_device:
+            out.device_ptr = int(rs.audio)
+            return out
+        total = int(rs.total_samples)
+        flat = np.ctypeslib.as_array(C.cast(rs.audio, C.POINTER(C.c_float)), shape=(total,))
+        if copy:
+            flat = flat.copy()
+        out.audio = [flat[offs[b]:offs[b + 1]] for b in range(B)]
+        if pcm16:
+            p = np.ctypeslib.as_array(C.cast(rs.pcm16, C.POINTER(C.c_int16)), shape=(total,)).copy()
+            out.pcm16 = [p[offs[b]:offs[b + 1]] for b in range(B)]
+        return out
+
+    # ---- parity hooks -------------------------------------------------------------------------------
+    def get_stage(self, name: str, utt: int = 0) -> np.ndarray:
+        ch, ln = C.c_int64(), C.c_int64()
+        self._check(self._lib.piper_b200_get_stage(self._ctx, name.encode(), utt, None, 0, C.byref(ch), C.byref(ln)))
+        out = np.zeros((ch.value, ln.value), np.float32)
+        self._check(self._lib.piper_b200_get_stage(self._ctx, name.encode(), utt, out.ctypes.data, out.size,
+                                                   C.byref(ch), C.byref(ln)))
+        return out
+
+    def length_regulate(self, logw: Sequence[np.ndarray], length_scale: float):
+        """(durations per utterance, frame_lengths, frame->phoneme index per utterance)"""
+        B = len(logw)
+        lengths = np.array([len(l) for l in logw], dtype=np.int64)
+        flat = np.ascontiguousarray(np.concatenate([np.asarray(l, np.float32) for l in logw]))
+        dur = np.zeros(int(lengths.sum()), np.int32)
+        fl = np.zeros(B, np.int64)
+        self._check(self._lib.piper_b200_length_regulate(self._ctx, flat.ctypes.data, lengths.ctypes.data, B,
+                                                         length_scale, dur.ctypes.data, fl.ctypes.data, None, 0))
+        cap = int(fl.max())
+        idx = np.full((B, cap), -2, np.int32)
+        self._check(self._lib.piper_b200_length_regulate(self._ctx, flat.ctypes.data, lengths.ctypes.data, B,
+                                                         length_scale, dur.ctypes.data, fl.ctypes.data,
+                                                         idx.ctypes.data, cap))
+        off = np.concatenate([[0], np.cumsum(lengths)])
+        return ([dur[off[b]:off[b + 1]] for b in range(B)], fl, [idx[b, :fl[b]] for b in range(B)])
+
+    def random_normal(self, count: int, seed: int = 1234) -> np.ndarray:
+        out = np.zeros(count, np.float32)
+        self._check(self._lib.piper_b200_random_normal(self._ctx, seed, count, out.ctypes.data))
+        return out
