@@ -1,0 +1,252 @@
+#!/usr/bin/env python
+"""bench.py - audio-seconds synthesized per second (BASELINE.json metric) on N B200s.
+
+A step = one pass of the hot path (phoneme ids -> waveforms) over one batch of synthetic
+utterances.  Workload at every N: BASELINE config 3 - the medium voice, a batch of 256
+utterances of ~100 phoneme ids PER GPU (weak scaling: independent utterances sharded
+across ranks, no data-path collective, final host gather of lengths only).
+`value`  : inputs (ids) already in HBM, audio left in HBM, CUDA-event timed.
+`e2e`    : the public API with HOST buffers - ids H2D and audio D2H inside the timed region.
+`--impl reference` : the reference's CPU path (the torch-CPU oracle of the same graph; ORT
+and the Swift reference are unavailable on this box) on a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "piper-swift_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np   # noqa: E402
+
+from piper_b200 import spec as S            # noqa: E402
+from piper_b200 import synth_voice          # noqa: E402
+
+VOICE_DIR = os.environ.get("PIPER_B200_VOICE_DIR", "/tmp/piper_b200_voices")
+METRIC = "audio_seconds_per_second"
+UNIT = "audio-s/s"
+
+
+def workload(args, rank):
+    spec = S.SPECS[args.voice]
+    utts = synth_voice.synthetic_utterances(args.batch, spec.n_vocab, args.t_lo, args.t_hi, seed=2024 + rank)
+    sids = None
+    if spec.n_speakers > 1:
+        sids = np.random.default_rng(5 + rank).integers(0, spec.n_speakers, args.batch).astype(np.int64)
+    return spec, utts, sids
+
+
+def config_dict(args, n_gpus):
+    return {"workload": f"BASELINE config 3: {args.voice} voice, batch of {args.batch} utterances "
+                        f"(T~U[{args.t_lo},{args.t_hi}] phoneme ids) per GPU, scales 0.667/1.0/0.8",
+            "voice": args.voice, "utterances_per_gpu": args.batch, "global_utterances": args.batch * n_gpus,
+            "precision": args.precision, "sharding": f"utterances x{n_gpus}, no collective",
+            "l2": "per-step activation working set > 1 GB >> 126 MB L2 (no explicit flush)"}
+
+
+class ClockSampler(threading.Thread):
+    def __init__(self, device):
+        super().__init__(daemon=True)
+        self.device, self.stop_flag, self.sm, self.reasons, self.sm_max = device, False, [], set(), None
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.device), f"--query-gpu={q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                self.sm.append(float(f[0]))
+                self.sm_max = float(f[1])
+                for n, v in zip(names, f[2:]):
+                    if v.lower().startswith("active"):
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def result(self):
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.sm_max,
+                "reasons": sorted(self.reasons), "samples": len(self.sm)}
+
+
+def cpu_oracle_rate(args, utts, sids, seconds_budget=20.0, max_utts=8):
+    """audio-s/s of the torch-CPU oracle on a bounded sample of the same workload."""
+    import torch
+    from oracle.vits_oracle import VitsOracle
+    from oracle import refrng
+    mp, _ = synth_voice.write_voice(S.SPECS[args.voice], VOICE_DIR)
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    orc = VitsOracle.from_file(mp)
+    ns, ls, nw = S.FIXTURE_SCALES
+    sr = S.SPECS[args.voice].sample_rate
+
+    def one(i):
+        u = utts[i]
+        o = orc.infer(u, ns, ls, nw, refrng.noise_dp(len(u)), noise_main_fn=refrng.noise_main,
+                      sid=None if sids is None else int(sids[i]))
+        return o["audio"].size / sr
+
+    one(0)   # warm-up
+    t0 = time.perf_counter()
+    audio_s, n = 0.0, 0
+    while n < min(max_utts, len(utts)) and (time.perf_counter() - t0) < seconds_budget:
+        audio_s += one(n)
+        n += 1
+    dt = time.perf_counter() - t0
+    return {"value": audio_s / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"first {n} utterances of the batch, B=1 sequential, torch {torch.__version__} CPU fp32 "
+                      f"({dt:.1f} s)", "ms_per_utterance": 1000 * dt / n}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    _, utts, sids = workload(args, 0)
+    per_step = []
+    base = None
+    for i in range(args.warmup + args.steps):
+        base = cpu_oracle_rate(args, utts, sids, seconds_budget=8.0, max_utts=2)
+        if i >= args.warmup:
+            per_step.append(base["value"])
+    v = float(np.mean(per_step))
+    base["value"] = v
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": config_dict(args, args.gpus), "cpu_baseline": base,
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--voice", default="medium")
+    ap.add_argument("--batch", type=int, default=256)
+    ap.add_argument("--t-lo", type=int, default=80)
+    ap.add_argument("--t-hi", type=int, default=120)
+    ap.add_argument("--precision", default=os.environ.get("PIPER_B200_PRECISION", "fp32"))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    from piper_b200.runtime import PiperCUDARuntime, Options
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    spec, utts, sids = workload(args, rank)
+    mp, cp = synth_voice.write_voice(spec, VOICE_DIR) if rank == 0 or world == 1 else (None, None)
+    if world > 1:
+        dist.barrier()
+        mp, cp = synth_voice.write_voice(spec, VOICE_DIR)
+    rt = PiperCUDARuntime(mp, cp, Options(device=local, precision=args.precision))
+    stream = torch.cuda.current_stream()
+    rt.set_stream(stream.cuda_stream)
+
+    lengths = np.array([len(u) for u in utts], dtype=np.int64)
+    ids = np.concatenate([np.asarray(u, np.int64) for u in utts])
+    ids_pinned = torch.from_numpy(ids).pin_memory()
+    ids_dev = ids_pinned.cuda(non_blocking=True)
+    ns, ls, nw = S.FIXTURE_SCALES
+
+    def step_resident():
+        return rt.synthesize_packed(None, lengths, ns, ls, nw, sids, ids_device_ptr=ids_dev.data_ptr(),
+                                    keep_on_device=True)
+
+    def step_e2e():
+        return rt.synthesize_packed(ids_pinned.numpy(), lengths, ns, ls, nw, sids, copy=False)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        samples, launches, tm = 0, 0, None
+        for _ in range(steps):
+            r = fn()
+            samples += r.total_samples
+            tm = rt.last_run_timings
+            launches += tm["kernel_launches"]
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        s = torch.tensor([float(samples)], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(s, op=dist.ReduceOp.SUM)
+        return float(t.item()), float(s.item()), launches, tm
+
+    for _ in range(args.warmup):
+        step_resident()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms, samples, launches, tm = timed(step_resident, args.steps)
+    sampler.stop_flag = True
+    sampler.join(2)
+    for _ in range(max(1, args.warmup // 2)):
+        step_e2e()
+    ms_e, samples_e, _, tm_e = timed(step_e2e, args.steps)
+
+    sr = spec.sample_rate
+    value = samples / sr / (ms / 1000.0)
+    e2e = samples_e / sr / (ms_e / 1000.0)
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = peaks.get("bf16_tflops_sustained", 1400.0)
+        back_tflops = (tm["dec_flops"] + tm["flow_flops"]) / (tm["decoder_ms"] / 1000.0) / 1e12
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": {"fp32": "f32", "bf16": "bf16", "f16": "f16"}[args.precision],
+            "data": "synthetic", "config": config_dict(args, world),
+            "ms_per_utterance": ms / args.steps / args.batch,
+            "stage_ms": {k: tm[k] for k in ("front_ms", "flow_ms", "decoder_ms", "h2d_ms", "d2h_ms", "gpu_ms")},
+            "roofline": {"bound": "tensor", "achieved": back_tflops, "peak": peak, "unit": "TFLOP/s",
+                         "frac": back_tflops / peak, "traffic": None,
+                         "kernel": "flow+HiFi-GAN conv kernels (aggregate of the back end, per step)",
+                         "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1.4 PF"},
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": tm_e["h2d_bytes"],
+                    "d2h_bytes_per_step": tm_e["d2h_bytes"], "ms_per_step": ms_e / args.steps},
+            "gpu_launches": launches, "clocks": sampler.result(),
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_oracle_rate(args, utts, sids)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    rt.close()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,65 @@
+"""CPU tests of the drop-in boundary: the C-ABI library loads, exports every symbol the header
+declares, and fails loudly (no CPU fallback) when there is no GPU."""
+import ctypes as C
+import os
+import re
+
+import pytest
+import torch
+
+from common import ROOT, voice_files
+from piper_b200 import runtime
+
+
+def _header_symbols():
+    text = open(os.path.join(ROOT, "include", "piper_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(piper_b200_[a-z_0-9]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = runtime.load_library()
+    syms = _header_symbols()
+    assert len(syms) >= 17
+    for s in syms:
+        assert hasattr(lib, s), f"{s} declared in include/piper_b200.h but not exported"
+    assert sorted(runtime.EXPORTED_SYMBOLS) == syms
+    assert lib.piper_b200_abi_version() == 1
+
+
+def test_struct_sizes_match_header():
+    # layout guard for the ctypes mirrors (x86-64 / aarch64 LP64)
+    assert C.sizeof(runtime.Request) == 80
+    assert C.sizeof(runtime.Result) == 56
+    assert C.sizeof(runtime.Timings) == 96
+    assert C.sizeof(runtime.VoiceInfo) == 80
+
+
+def test_null_arguments_are_rejected_without_touching_the_gpu():
+    lib = runtime.load_library()
+    assert lib.piper_b200_create(0, None) == 1
+    assert lib.piper_b200_synthesize(None, None, None) == 1
+    assert lib.piper_b200_load_voice(None, b"x", b"y") == 1
+    assert b"invalid argument" in lib.piper_b200_last_error(None)
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
+def test_no_gpu_fails_loudly():
+    lib = runtime.load_library()
+    ctx = C.c_void_p()
+    rc = lib.piper_b200_create(0, C.byref(ctx))
+    assert rc == 5 and not ctx.value           # PIPER_B200_ERR_CUDA, no context, no fallback
+    assert lib.piper_b200_last_error(None).startswith(b"cuda:")
+    mp, cp = voice_files("tiny")
+    with pytest.raises(runtime.PiperB200Error) as e:
+        runtime.PiperCUDARuntime(mp, cp)
+    assert e.value.code == 5
+
+
+def test_product_path_does_not_import_the_oracle():
+    pkg = os.path.join(ROOT, "piper-swift_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cpp", ".cu", ".h", ".swift")):
+                src = open(os.path.join(dirpath, f), errors="ignore").read()
+                assert "import oracle" not in src and "from oracle" not in src, f
