@@ -171,6 +171,15 @@ int piper_b200_length_regulate(piper_b200_ctx* ctx, const float* logw, const int
 /* RandomNormalLike with the reference's generator (elementwise.metal:132-163). */
 int piper_b200_random_normal(piper_b200_ctx* ctx, uint64_t seed, int64_t count, float* dst_host);
 
+/* Single-kernel self-test, the counterpart of PiperMetalMicrobench
+ * (Sources/PiperMetal/Microbench/PiperMetalMicrobench.swift:24-73): one convolution of the given
+ * shape on random data through the tcgen05 tensor-core kernel and through the fp32 CUDA-core
+ * kernel on identical operands.  mode 0 = Conv (+bias, +residual), 1 = WN gate (cout = 2*hidden),
+ * 2 = res|skip two-group GEMM, 3 = ConvTranspose (kernel k, stride).  precision = BF16 or F16.
+ * out4 = {max |tc - fp32|, max |fp32|, tc kernel ms, fp32 kernel ms}. */
+int piper_b200_selftest_conv(piper_b200_ctx* ctx, int32_t mode, int32_t cin, int32_t cout, int32_t k,
+                             int32_t dilation, int32_t stride, int32_t rows, int32_t precision, float* out4);
+
 #ifdef __cplusplus
 }
 #endif

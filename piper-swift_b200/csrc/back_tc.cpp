@@ -1,0 +1,295 @@
+// Residual-coupling flow (reverse) + HiFi-GAN generator on the tcgen05 implicit-GEMM kernel
+// (conv_tc.cu): the throughput back end.  Same dataflow as back_f32.cpp -
+// the graph's Slice/Split/Conv/Add/Tanh/Sigmoid/Mul/Sub/Concat and LeakyRelu/ConvTranspose/
+// Conv/Add/Div nodes (GraphExecutor.swift:1739-1860, 2017-2069) - but every dense convolution
+// runs on the tensor cores with 16-bit operands and fp32 accumulation, the WN gate is the
+// epilogue of the in_layer convolution, res|skip is one GEMM with two column groups, and
+// every producer also emits the 16-bit (leaky-relu'd) operand copy its consumer reads.
+// Residual streams, skip sums and the cross-resblock mean stay in fp32.
+#include <stdexcept>
+
+#include "conv_tc.h"
+#include "pipeline.h"
+
+namespace piper {
+
+namespace {
+
+#define CUDA_OK(x)                                                                         \
+  do {                                                                                     \
+    cudaError_t e_ = (x);                                                                  \
+    if (e_ != cudaSuccess)                                                                 \
+      throw std::runtime_error(std::string("cuda: ") + cudaGetErrorString(e_) + " at " #x); \
+  } while (0)
+
+int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+// columns per CTA: at most 128 so that two CTAs fit per SM
+int pick_nt(int cout) {
+  for (int nt : {128, 96, 64, 48, 32, 16})
+    if (cout % nt == 0) return nt;
+  return 16;
+}
+
+}  // namespace
+
+TcW make_tcw(Exec& ex, std::vector<void*>& allocs, const ConvW& a, const ConvW* b, int f16) {
+  TcW t;
+  t.cin = a.cin;
+  t.kb = a.cin >= 64 ? 64 : 32;
+  t.cin_pad = round_up(a.cin, t.kb);
+  t.cout = a.cout + (b ? b->cout : 0);
+  t.taps = a.taps; t.phases = a.phases; t.ct_pad = a.ct_pad; t.dil = a.dil; t.pad_l = a.pad_l;
+  t.bias = a.b;
+  if (!tc_conv_supported(a.cin, a.cout) || (b && (!tc_conv_supported(b->cin, b->cout) || b->cin != a.cin ||
+                                                   b->taps != a.taps || b->phases != a.phases)))
+    throw std::runtime_error("unsupported: convolution " + std::to_string(a.cin) + "->" + std::to_string(a.cout) +
+                             " does not fit the tensor-core tile constraints (use precision fp32)");
+  const size_t n = (size_t)t.phases * t.taps * t.cout * t.cin_pad;
+  CUDA_OK(cudaMalloc(&t.w, n * 2));
+  allocs.push_back(t.w);
+  launch_pack_tc_weights(ex, a.w, a.ldw, a.phases * a.taps, a.cin, a.cout, t.w, t.cout, 0, t.cin_pad, f16);
+  if (b) launch_pack_tc_weights(ex, b->w, b->ldw, b->phases * b->taps, b->cin, b->cout, t.w, t.cout, a.cout, t.cin_pad, f16);
+  return t;
+}
+
+void TcVoice::build(Exec& ex, const Voice& v, int f16_) {
+  release();
+  f16 = f16_;
+  for (const CouplingW& c : v.flows) {
+    TcCoupling t;
+    t.pre = make_tcw(ex, allocs, c.pre, nullptr, f16);
+    const int L = (int)c.in_layers.size();
+    for (int l = 0; l < L; ++l) {
+      t.in_layers.push_back(make_tcw(ex, allocs, c.in_layers[l], nullptr, f16));
+      if (l < L - 1) t.rs.push_back(make_tcw(ex, allocs, c.res[l], &c.skip[l], f16));
+      else t.rs.push_back(make_tcw(ex, allocs, c.skip[l], nullptr, f16));
+    }
+    t.post = make_tcw(ex, allocs, c.post, nullptr, f16);
+    flows.push_back(t);
+  }
+  dec_pre = make_tcw(ex, allocs, v.dec_pre, nullptr, f16);
+  for (const StageW& s : v.stages) {
+    TcStage t;
+    t.up = make_tcw(ex, allocs, s.up, nullptr, f16);
+    for (const ResBlockW& rb : s.rbs) {
+      if (rb.c2.empty() && rb.c1.size() > 2)
+        throw std::runtime_error("unsupported: ResBlock2 with more than two dilations");
+      TcResBlock r;
+      for (const ConvW& c : rb.c1) r.c1.push_back(make_tcw(ex, allocs, c, nullptr, f16));
+      for (const ConvW& c : rb.c2) r.c2.push_back(make_tcw(ex, allocs, c, nullptr, f16));
+      t.rbs.push_back(r);
+    }
+    stages.push_back(t);
+  }
+  CUDA_OK(cudaStreamSynchronize(ex.st));
+  built = true;
+}
+
+void TcVoice::release() {
+  for (void* p : allocs) cudaFree(p);
+  allocs.clear();
+  flows.clear();
+  stages.clear();
+  built = false;
+}
+
+namespace {
+
+size_t per_row_max_of(const Voice& v) {
+  size_t m = v.hp.dec_c0;
+  int U = 1;
+  for (auto& s : v.stages) {
+    U *= s.stride;
+    m = std::max(m, (size_t)U * s.ch);
+  }
+  return m;
+}
+
+// plain "same" convolution over R rows
+TcConvArgs tc_args(const TcW& w, const void* in, int ldin, int R, const int* row_utt, int valid_div, int f16) {
+  TcConvArgs a;
+  a.in = in; a.ldin = ldin; a.R_in = R; a.cin = w.cin;
+  a.w = &w;
+  a.Q = R;
+  a.tap_step = w.dil; a.in_off = -w.pad_l;
+  a.out_mul = 1;
+  a.n_groups = 1;
+  a.nt = pick_nt(w.cout);
+  a.n_tiles = w.cout / a.nt;
+  a.e[0].bias = w.bias;
+  a.row_utt = row_utt; a.valid_div = valid_div;
+  a.f16 = f16;
+  return a;
+}
+
+}  // namespace
+
+size_t back_tc_bytes(const Context& ctx, int Rf, int batch) {
+  const Voice& v = ctx.voice;
+  const int H = v.hp.hidden;
+  const size_t P = per_row_max_of(v);
+  size_t bytes = 0;
+  bytes += (size_t)Rf * H * (4 * 2 + 2 * 4);       // h, skip fp32; zb, hb, actsb, skipb 16-bit
+  bytes += (size_t)Rf * P * (4 * 3 + 2 * 5);       // xu, yb, xs fp32; actA, actB, xub, ybb, tbb 16-bit
+  bytes += (size_t)Rf * v.hp.hop * 4;              // packed audio
+  bytes += 32 * 256;
+  (void)batch;
+  return bytes;
+}
+
+float* run_back_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep) {
+  Voice& v = ctx.voice;
+  TcVoice& tv = ctx.tc;
+  Arena& A = ctx.back;
+  const int f16 = tv.f16;
+  const int H = v.hp.hidden, Rf = in.Rf;
+  const int L = v.hp.flow_wn_layers;
+  float* z = const_cast<float*>(in.zp);   // fp32, updated in place one half at a time
+  float* h = A.alloc<float>((size_t)Rf * H);
+  float* skip = A.alloc<float>((size_t)Rf * H);
+  uint16_t* zb = A.alloc<uint16_t>((size_t)Rf * H);
+  uint16_t* hb = A.alloc<uint16_t>((size_t)Rf * H);
+  uint16_t* actsb = A.alloc<uint16_t>((size_t)Rf * H);
+  uint16_t* skipb = A.alloc<uint16_t>((size_t)Rf * H);
+  if (!h || !skip || !zb || !hb || !actsb || !skipb) throw std::runtime_error("capacity: back arena too small (flow)");
+
+  // ---- flow ------------------------------------------------------------------------------
+  launch_to_act16(ex, z, zb, (int64_t)Rf * H, 1.f, f16);
+  for (size_t f = 0; f < v.flows.size(); ++f) {
+    const CouplingW& c = v.flows[f];
+    const TcCoupling& t = tv.flows[f];
+    const float* cond = in.cond_flow ? in.cond_flow + f * (size_t)in.batch * 2 * H * L : nullptr;
+    {
+      TcConvArgs a = tc_args(t.pre, zb + c.in_off, H, Rf, in.frow_utt, 1, f16);
+      a.e[0].out_f32 = h; a.e[0].ld_f32 = H;
+      a.e[0].out_act = hb; a.e[0].ld_act = H;
+      launch_conv_tc(ex, a);
+    }
+    for (int l = 0; l < L; ++l) {
+      {   // in_layer + (cond) + tanh*sigmoid gate
+        TcConvArgs a = tc_args(t.in_layers[l], hb, H, Rf, in.frow_utt, 1, f16);
+        a.gate = 1; a.n_groups = 2;
+        a.nt = pick_nt(H);
+        a.n_tiles = H / a.nt;
+        a.e[0].row0 = 0; a.e[0].bias = t.in_layers[l].bias;
+        a.e[1].row0 = H; a.e[1].bias = t.in_layers[l].bias + H;
+        a.e[0].out_act = actsb; a.e[0].ld_act = H;
+        if (cond) {
+          a.uttbias = cond; a.ldub = 2 * H * L;
+          a.e[0].ub_off = l * 2 * H; a.e[1].ub_off = l * 2 * H + H;
+        }
+        launch_conv_tc(ex, a);
+      }
+      {   // res | skip
+        const bool last = l == L - 1;
+        TcConvArgs a = tc_args(t.rs[l], actsb, H, Rf, in.frow_utt, 1, f16);
+        a.nt = pick_nt(H); a.n_tiles = H / a.nt;
+        if (!last) {
+          a.n_groups = 2;
+          a.e[0].row0 = 0; a.e[0].bias = c.res[l].b;
+          a.e[0].out_f32 = h; a.e[0].ld_f32 = H; a.e[0].res = h; a.e[0].ld_res = H;   // x = (x + res_acts) * mask
+          a.e[0].out_act = hb; a.e[0].ld_act = H;
+          a.e[1].row0 = H; a.e[1].bias = c.skip[l].b;
+          a.e[1].out_f32 = skip; a.e[1].ld_f32 = H; a.e[1].accum = l > 0;             // output += skip_acts
+        } else {
+          a.e[0].row0 = 0; a.e[0].bias = c.skip[l].b;
+          a.e[0].out_f32 = skip; a.e[0].ld_f32 = H; a.e[0].accum = l > 0;
+          a.e[0].out_act = skipb; a.e[0].ld_act = H;
+        }
+        launch_conv_tc(ex, a);
+      }
+    }
+    {   // post (weights negated): x1 + (-m), masked
+      TcConvArgs a = tc_args(t.post, skipb, H, Rf, in.frow_utt, 1, f16);
+      a.e[0].out_f32 = z + c.out_off; a.e[0].ld_f32 = H;
+      a.e[0].res = z + c.out_off; a.e[0].ld_res = H;
+      a.e[0].out_act = zb + c.out_off; a.e[0].ld_act = H;
+      launch_conv_tc(ex, a);
+    }
+  }
+  if (z_keep) CUDA_OK(cudaMemcpyAsync(z_keep, z, (size_t)Rf * H * 4, cudaMemcpyDeviceToDevice, ex.st));
+
+  // ---- HiFi-GAN ----------------------------------------------------------------------------
+  const size_t P = per_row_max_of(v);
+  float* xu = A.alloc<float>((size_t)Rf * P);
+  float* yb = A.alloc<float>((size_t)Rf * P);
+  float* xs = A.alloc<float>((size_t)Rf * P);
+  uint16_t* act[2] = {A.alloc<uint16_t>((size_t)Rf * P), A.alloc<uint16_t>((size_t)Rf * P)};
+  uint16_t* xub = A.alloc<uint16_t>((size_t)Rf * P);
+  uint16_t* ybb = A.alloc<uint16_t>((size_t)Rf * P);
+  uint16_t* tbb = A.alloc<uint16_t>((size_t)Rf * P);
+  float* audio = A.alloc<float>((size_t)Rf * v.hp.hop);
+  if (!xu || !yb || !xs || !act[0] || !act[1] || !xub || !ybb || !tbb || !audio)
+    throw std::runtime_error("capacity: back arena too small (decoder)");
+
+  int cur = 0;
+  {
+    TcConvArgs a = tc_args(tv.dec_pre, zb, H, Rf, in.frow_utt, 1, f16);
+    a.uttbias = in.cond_dec; a.ldub = v.hp.dec_c0;
+    a.e[0].out_act = act[cur]; a.e[0].ld_act = v.hp.dec_c0; a.e[0].act_slope = 0.1f;
+    launch_conv_tc(ex, a);
+  }
+  int R = Rf, U = 1;
+  const int nk = (int)v.stages[0].rbs.size();
+  for (size_t si = 0; si < v.stages.size(); ++si) {
+    const StageW& s = v.stages[si];
+    const TcStage& ts = tv.stages[si];
+    const bool last_stage = si + 1 == v.stages.size();
+    const int Rn = R * s.stride;
+    U *= s.stride;
+    const int C = s.ch;
+    {   // LeakyRelu(0.1) [already in the operand copy] + ConvTranspose, one polyphase GEMM per phase
+      TcConvArgs a;
+      a.in = act[cur]; a.ldin = ts.up.cin; a.R_in = R; a.cin = ts.up.cin;
+      a.w = &ts.up;
+      a.Q = R; a.tap_step = -1; a.out_mul = s.stride;
+      a.n_groups = 1; a.nt = pick_nt(C); a.n_tiles = C / a.nt;
+      a.e[0].bias = ts.up.bias;
+      a.e[0].out_f32 = xu; a.e[0].ld_f32 = C;
+      a.e[0].out_act = xub; a.e[0].ld_act = C; a.e[0].act_slope = 0.1f;
+      a.row_utt = in.frow_utt; a.valid_div = U;
+      a.f16 = f16;
+      launch_conv_tc(ex, a);
+    }
+    uint16_t* xsb = act[cur ^ 1];
+    for (int j = 0; j < nk; ++j) {
+      const TcResBlock& rb = ts.rbs[j];
+      const int M = (int)rb.c1.size();
+      const float* y = xu;
+      const uint16_t* y16 = xub;
+      for (int m = 0; m < M; ++m) {
+        const bool last = m == M - 1;
+        const uint16_t* src16 = y16;
+        if (!rb.c2.empty()) {   // ResBlock1: dilated conv -> lrelu -> plain conv
+          TcConvArgs a1 = tc_args(rb.c1[m], y16, C, Rn, in.frow_utt, U, f16);
+          a1.e[0].out_act = tbb; a1.e[0].ld_act = C; a1.e[0].act_slope = 0.1f;
+          launch_conv_tc(ex, a1);
+          src16 = tbb;
+        }
+        TcConvArgs a = tc_args(rb.c2.empty() ? rb.c1[m] : rb.c2[m], src16, C, Rn, in.frow_utt, U, f16);
+        a.e[0].res = y; a.e[0].ld_res = C;
+        if (!last) {
+          a.e[0].out_f32 = yb; a.e[0].ld_f32 = C;
+          a.e[0].out_act = ybb; a.e[0].ld_act = C; a.e[0].act_slope = 0.1f;
+        } else {
+          a.e[0].out_f32 = xs; a.e[0].ld_f32 = C;
+          a.e[0].accum = j > 0;
+          if (j == nk - 1) {
+            a.e[0].div = (float)nk;
+            if (!last_stage) { a.e[0].out_act = xsb; a.e[0].ld_act = C; a.e[0].act_slope = 0.1f; }
+          }
+        }
+        launch_conv_tc(ex, a);
+        y = yb;
+        y16 = ybb;
+      }
+    }
+    cur ^= 1;
+    R = Rn;
+  }
+  launch_conv_post_tanh(ex, xs, v.stages.back().ch, v.post_w, v.post_k, 0.01f, in.frow_utt, U, audio, R);
+  return audio;
+}
+
+}  // namespace piper

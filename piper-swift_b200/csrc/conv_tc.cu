@@ -1,0 +1,483 @@
+// tcgen05 / TMEM / TMA implicit-GEMM convolution (sm_100a).  See conv_tc.h for the contract.
+//
+// One CTA computes a 128-row (time) x nt-column (cout) output tile per column group:
+//   warp 0      : TMA producer - per pipeline stage one activation box (128 rows x kb channels,
+//                 rows shifted by the tap; out-of-range rows are zero-filled by TMA = the conv's
+//                 zero padding) and one weight box per group (nt rows x kb channels)
+//   warp 1      : TMEM allocation + the single thread issuing tcgen05.mma (M=128, N=nt, K=16)
+//   warps 2..5  : epilogue - tcgen05.ld of the fp32 accumulators (each warp its 32-lane quarter),
+//                 bias/residual/gate in registers, vectorised global stores
+// Pipeline: full[s]/empty[s] mbarriers between TMA and MMA, tmem_full between MMA and epilogue.
+#include "conv_tc.h"
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include <cstdio>
+#include <stdexcept>
+#include <string>
+
+namespace piper {
+
+namespace {
+
+constexpr int TC_BM = 128;
+constexpr int TC_STAGES = 4;
+constexpr int TC_THREADS = 192;
+
+// ---- PTX wrappers ------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ bool elect_one_unused() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P1;\n\t"
+      "LAB_WAIT:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+      "@P1 bra DONE;\n\t"
+      "bra LAB_WAIT;\n\t"
+      "DONE:\n\t"
+      "}\n" ::"r"(addr),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* bar, void* dst, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cta.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)),
+               "r"(cols)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_relinquish() {
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, 16-bit operands, fp32 accumulate
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                         uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}\n" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// K-major shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): rows of `kb` 16-bit
+// elements, 8-row swizzle atoms stacked every SBO bytes; version 1 (sm_100).
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, int kb) {
+  const uint64_t sbo = (kb == 64) ? 1024 : 512;       // 8 rows x (128 | 64) bytes
+  const uint64_t layout = (kb == 64) ? 2 : 4;         // SWIZZLE_128B | SWIZZLE_64B
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)1 << 16;                             // leading byte offset (unused for swizzled K-major)
+  d |= (sbo >> 4) << 32;
+  d |= (uint64_t)1 << 46;                             // descriptor version
+  d |= layout << 61;
+  return d;
+}
+// cute::UMMA::InstrDescriptor for kind::f16: fp32 accumulate, K-major A and B
+__device__ __forceinline__ uint32_t make_idesc(int n, int f16) {
+  const uint32_t fmt = f16 ? 0u : 1u;
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+}
+
+__device__ __forceinline__ uint32_t pack2(float a, float b, int f16) {
+  if (f16) {
+    const __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&h);
+  }
+  const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
+__device__ __forceinline__ float lrelu(float v, float s) { return v >= 0.f ? v : v * s; }
+
+struct TcKernelParams {
+  int Q, taps, tap_step, in_off, kblocks, kb;
+  int nt, n_groups, cout_rows;      // cout_rows = weight rows per (phase, tap)
+  int phases, ct_pad, out_mul;
+  int gate, f16;
+  TcEpi e[2];
+  const float* uttbias; int ldub;
+  const int* row_utt; int valid_div;
+  uint32_t tmem_cols;
+};
+
+}  // namespace
+
+namespace {
+
+__global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
+                                                             const __grid_constant__ CUtensorMap tmap_b,
+                                                             const TcKernelParams p, const int stages) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int a_bytes = TC_BM * p.kb * 2;
+  const int b_bytes = p.nt * p.kb * 2;                 // per group
+  const int stage_bytes = a_bytes + p.n_groups * b_bytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)stages * stage_bytes);
+  uint64_t* empty = full + TC_STAGES;
+  uint64_t* tmem_full = empty + TC_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * TC_BM;
+  const int ntile = blockIdx.y;
+  const int phase = blockIdx.z;
+  int in_off = p.in_off;
+  if (p.phases > 1) in_off = (phase + p.ct_pad) / p.phases;
+  const int n_it = p.taps * p.kblocks;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmap_a);
+    prefetch_tmap(&tmap_b);
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  } else if (warp == 1) {
+    tmem_alloc(tmem_slot, p.tmem_cols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      for (int it = 0; it < n_it; ++it) {
+        const int s = it % stages;
+        const uint32_t ph = (uint32_t)(it / stages) & 1u;
+        mbar_wait(&empty[s], ph ^ 1u);
+        const int tap = it / p.kblocks, kbi = it - tap * p.kblocks;
+        uint8_t* st = smem + (size_t)s * stage_bytes;
+        mbar_expect_tx(&full[s], (uint32_t)stage_bytes);
+        tma_load_2d(&tmap_a, &full[s], st, kbi * p.kb, m0 + in_off + tap * p.tap_step);
+        const int wrow = (phase * p.taps + tap) * p.cout_rows + ntile * p.nt;
+        for (int g = 0; g < p.n_groups; ++g)
+          tma_load_2d(&tmap_b, &full[s], st + a_bytes + g * b_bytes, kbi * p.kb, wrow + p.e[g].row0);
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
+    const uint32_t idesc = make_idesc(p.nt, p.f16);
+    for (int it = 0; it < n_it; ++it) {
+      const int s = it % stages;
+      const uint32_t ph = (uint32_t)(it / stages) & 1u;
+      mbar_wait(&full[s], ph);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
+        const uint64_t a_desc = make_smem_desc(a_addr, p.kb);
+        const int ksteps = p.kb / 16;
+        for (int g = 0; g < p.n_groups; ++g) {
+          const uint64_t b_desc = make_smem_desc(a_addr + a_bytes + g * b_bytes, p.kb);
+          for (int k = 0; k < ksteps; ++k)   // +32 bytes per K=16 step inside the swizzle atom
+            umma_f16(tmem_base + (uint32_t)(g * p.nt), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
+                     (it > 0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&empty[s]);                 // frees the smem slot when these MMAs retire
+        if (it == n_it - 1) umma_commit(tmem_full);
+      }
+      __syncwarp();
+    }
+  } else {
+    // ===== epilogue: warps 2..5, TMEM lane quarter = warp % 4 =====
+    const int quarter = warp & 3;
+    const int q = m0 + quarter * 32 + lane;
+    const bool active = q < p.Q;
+    const int orow = active ? q * p.out_mul + (p.phases > 1 ? phase : 0) : 0;
+    int utt = 0;
+    if (active && p.row_utt) utt = p.row_utt[orow / p.valid_div];
+    const bool valid = utt >= 0;
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+    const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    const int chunks = p.nt / 16;
+    if (p.gate) {
+      const TcEpi& e0 = p.e[0];
+      const TcEpi& e1 = p.e[1];
+      for (int c = 0; c < chunks; ++c) {
+        float va[16], vb[16];
+        __syncwarp();
+        tmem_ld16(lane_base + (uint32_t)(c * 16), va);
+        tmem_ld16(lane_base + (uint32_t)(p.nt + c * 16), vb);
+        if (!active) continue;
+        const int j = ntile * p.nt + c * 16;
+        uint32_t pk[8];
+#pragma unroll
+        for (int i = 0; i < 16; i += 2) {
+          float o[2];
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            float ta = va[i + h] + (e0.bias ? e0.bias[j + i + h] : 0.f);
+            float sa = vb[i + h] + (e1.bias ? e1.bias[j + i + h] : 0.f);
+            if (p.uttbias && valid) {
+              ta += p.uttbias[(size_t)utt * p.ldub + e0.ub_off + j + i + h];
+              sa += p.uttbias[(size_t)utt * p.ldub + e1.ub_off + j + i + h];
+            }
+            o[h] = valid ? tanhf(ta) * (1.0f / (1.0f + expf(-sa))) : 0.f;
+          }
+          pk[i / 2] = pack2(o[0], o[1], p.f16);
+        }
+        uint4* dst = reinterpret_cast<uint4*>(static_cast<uint16_t*>(e0.out_act) + (size_t)orow * e0.ld_act + e0.col0 + j);
+        dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+      }
+    } else {
+      for (int g = 0; g < p.n_groups; ++g) {
+        const TcEpi& e = p.e[g];
+        for (int c = 0; c < chunks; ++c) {
+          float v[16];
+          __syncwarp();
+          tmem_ld16(lane_base + (uint32_t)(g * p.nt + c * 16), v);
+          if (!active) continue;
+          const int j = ntile * p.nt + c * 16;
+          const size_t ocol = (size_t)e.col0 + j;
+          if (e.bias) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] += e.bias[j + i];
+          }
+          if (p.uttbias && valid) {
+            const float* ub = p.uttbias + (size_t)utt * p.ldub + e.ub_off + j;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] += ub[i];
+          }
+          if (e.res) {
+            const float4* r4 = reinterpret_cast<const float4*>(e.res + (size_t)orow * e.ld_res + ocol);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const float4 r = r4[i];
+              v[4 * i] += r.x; v[4 * i + 1] += r.y; v[4 * i + 2] += r.z; v[4 * i + 3] += r.w;
+            }
+          }
+          float4* o4 = e.out_f32 ? reinterpret_cast<float4*>(e.out_f32 + (size_t)orow * e.ld_f32 + ocol) : nullptr;
+          if (e.accum) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const float4 r = o4[i];
+              v[4 * i] += r.x; v[4 * i + 1] += r.y; v[4 * i + 2] += r.z; v[4 * i + 3] += r.w;
+            }
+          }
+          if (e.div != 0.f) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = v[i] / e.div;
+          }
+          if (!valid) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = 0.f;
+          }
+          if (o4) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+          }
+          if (e.out_act) {
+            uint32_t pk[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+              pk[i] = pack2(lrelu(v[2 * i], e.act_slope), lrelu(v[2 * i + 1], e.act_slope), p.f16);
+            uint4* dst = reinterpret_cast<uint4*>(static_cast<uint16_t*>(e.out_act) + (size_t)orow * e.ld_act + ocol);
+            dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, p.tmem_cols);
+}
+
+}  // namespace
+
+// ---- host side -----------------------------------------------------------------------------
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || !p ||
+        q != cudaDriverEntryPointSuccess)
+      throw std::runtime_error("cuda: cuTensorMapEncodeTiled entry point unavailable");
+    fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// 2-D K-major tensor map: inner dim = channels (16-bit), outer dim = rows
+CUtensorMap make_map(const void* base, uint64_t inner, uint64_t rows, uint64_t ld_elems, int box_inner,
+                     int box_rows, int f16) {
+  CUtensorMap m;
+  const cuuint64_t dims[2] = {inner, rows};
+  const cuuint64_t strides[1] = {ld_elems * 2};
+  const cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = encode_fn()(&m, f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                                 const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                 box_inner == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    throw std::runtime_error("cuda: cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
+  return m;
+}
+
+constexpr int TC_SMEM_MAX = 232448;   // 227 KB
+
+}  // namespace
+
+bool tc_conv_supported(int cin, int cout) { return cin % 32 == 0 && cout % 16 == 0 && cin >= 32 && cout >= 16; }
+
+void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
+  if (a.Q <= 0) return;
+  const TcW& w = *a.w;
+  if (a.nt % 16 || a.nt < 16 || a.nt > 256 || a.n_groups < 1 || a.n_groups > 2 || a.n_groups * a.nt > 512)
+    throw std::runtime_error("conv_tc: bad column tiling");
+  TcKernelParams p{};
+  p.Q = a.Q; p.taps = w.taps; p.tap_step = a.tap_step; p.in_off = a.in_off;
+  p.kb = w.kb; p.kblocks = w.cin_pad / w.kb;
+  p.nt = a.nt; p.n_groups = a.n_groups; p.cout_rows = w.cout;
+  p.phases = w.phases; p.ct_pad = w.ct_pad; p.out_mul = a.out_mul;
+  p.gate = a.gate; p.f16 = a.f16;
+  p.e[0] = a.e[0]; p.e[1] = a.e[1];
+  p.uttbias = a.uttbias; p.ldub = a.ldub;
+  p.row_utt = a.row_utt; p.valid_div = a.valid_div < 1 ? 1 : a.valid_div;
+  uint32_t cols = 32;
+  while ((int)cols < a.n_groups * a.nt) cols <<= 1;
+  p.tmem_cols = cols;
+
+  const CUtensorMap ta = make_map(a.in, (uint64_t)a.cin, (uint64_t)a.R_in, (uint64_t)a.ldin, w.kb, TC_BM, a.f16);
+  const CUtensorMap tb = make_map(w.w, (uint64_t)w.cin_pad, (uint64_t)w.phases * w.taps * w.cout, (uint64_t)w.cin_pad,
+                                  w.kb, a.nt, a.f16);
+  const int stage_bytes = TC_BM * w.kb * 2 + a.n_groups * a.nt * w.kb * 2;
+  int stages = TC_STAGES;
+  while (stages > 2 && stages * stage_bytes + 2048 > TC_SMEM_MAX) --stages;
+  // two CTAs per SM (one's epilogue under the other's main loop) beat a deeper pipeline
+  while (stages > 3 && 2 * (stages * stage_bytes + 2048) > TC_SMEM_MAX) --stages;
+  const int n_it = w.taps * p.kblocks;
+  if (stages > n_it) stages = n_it < 2 ? 2 : n_it;
+  const size_t smem = (size_t)stages * stage_bytes + 1024 + 256;
+  if (smem > (size_t)TC_SMEM_MAX) throw std::runtime_error("conv_tc: tile does not fit in shared memory");
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess)
+      throw std::runtime_error("cuda: cannot raise dynamic shared memory limit for conv_tc_kernel");
+    attr_set = true;
+  }
+  dim3 grid((a.Q + TC_BM - 1) / TC_BM, a.n_tiles, w.phases);
+  conv_tc_kernel<<<grid, TC_THREADS, smem, ex.st>>>(ta, tb, p, stages);
+  ++ex.launches;
+}
+
+// ---- weight repack + activation cast ---------------------------------------------------------
+namespace {
+__global__ void pack_tc_weights_kernel(const float* __restrict__ w, int ldw, int cin, int cout, uint16_t* __restrict__ dst,
+                                       int cout_total, int row_off, int cin_pad, int f16, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int ci = (int)(i % cin_pad);
+  const int co = (int)((i / cin_pad) % cout);
+  const int pt = (int)(i / ((int64_t)cin_pad * cout));
+  float v = 0.f;
+  if (ci < cin) v = w[((size_t)pt * cin + ci) * ldw + co];
+  uint16_t bits;
+  if (f16) {
+    const __half h = __float2half_rn(v);
+    bits = *reinterpret_cast<const uint16_t*>(&h);
+  } else {
+    const __nv_bfloat16 h = __float2bfloat16_rn(v);
+    bits = *reinterpret_cast<const uint16_t*>(&h);
+  }
+  dst[((size_t)pt * cout_total + row_off + co) * cin_pad + ci] = bits;
+}
+
+__global__ void to_act16_kernel(const float* __restrict__ src, uint32_t* __restrict__ dst, int64_t n2, float slope,
+                                int f16) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n2) return;
+  const float2 v = reinterpret_cast<const float2*>(src)[i];
+  dst[i] = pack2(lrelu(v.x, slope), lrelu(v.y, slope), f16);
+}
+}  // namespace
+
+void launch_pack_tc_weights(Exec& ex, const float* w_f32, int ldw, int phases_taps, int cin, int cout, void* dst,
+                            int cout_total, int row_off, int cin_pad, int f16) {
+  const int64_t n = (int64_t)phases_taps * cout * cin_pad;
+  if (n <= 0) return;
+  pack_tc_weights_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ex.st>>>(w_f32, ldw, cin, cout,
+                                                                        static_cast<uint16_t*>(dst), cout_total, row_off,
+                                                                        cin_pad, f16, n);
+  ++ex.launches;
+}
+
+void launch_to_act16(Exec& ex, const float* src, void* dst, int64_t n, float slope, int f16) {
+  const int64_t n2 = n / 2;
+  if (n2 <= 0) return;
+  to_act16_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, ex.st>>>(src, static_cast<uint32_t*>(dst), n2, slope, f16);
+  ++ex.launches;
+}
+
+}  // namespace piper

@@ -1,0 +1,72 @@
+// Tensor-core (tcgen05 / TMEM / TMA) implicit-GEMM convolution for sm_100a: launch interface.
+// Replaces conv1d_f32 / convtranspose1d_f32 (conv1d.metal:28-71, 97-142) and matmul_f32
+// (matmul.metal:22-49) for the dense convolutions of the flow and the HiFi-GAN generator
+//  when the context runs in a 16-bit operand precision mode.
+//
+// Operands are 16-bit (bf16 or fp16) "packed rows" [rows][channels] (channels contiguous, so
+// the GEMM A operand is K-major in shared memory exactly as TMA delivers it); weights are
+// repacked once to [phase][tap][cout][cin_pad] (K-major B operand).  Accumulation is fp32
+// in TMEM; the epilogue applies bias / per-utterance bias / residual / cross-resblock
+// accumulate / divide / gated tanh*sigmoid in fp32 and writes an fp32 tensor and/or the
+// 16-bit (optionally leaky-relu'd) operand copy the next convolution reads.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "kernels.h"
+
+namespace piper {
+
+// 16-bit weights of one convolution: [phases*taps][cout][cin_pad]
+struct TcW {
+  void* w = nullptr;        // bf16 or fp16
+  const float* bias = nullptr;   // fp32 [>=cout] (shared with the fp32 ConvW)
+  int cin = 0, cin_pad = 0, cout = 0;
+  int taps = 1, phases = 1, ct_pad = 0, dil = 1, pad_l = 0;
+  int kb = 64;              // K elements per pipeline stage (64 -> 128B swizzle, 32 -> 64B swizzle)
+};
+
+struct TcEpi {
+  // a column group: `nt * n_tiles` consecutive weight rows starting at row0 (per phase/tap)
+  int row0 = 0;                  // first weight row (cout index) of the group
+  const float* bias = nullptr;   // group-local: bias[j] belongs to weight row row0 + j (may be null)
+  int ub_off = 0;                // offset of the group's column 0 inside a uttbias row
+  int col0 = 0;                  // output column where the group's column 0 lands
+  float* out_f32 = nullptr; int ld_f32 = 0;
+  void* out_act = nullptr;  int ld_act = 0;     // 16-bit copy, leaky-relu(act_slope) applied
+  const float* res = nullptr; int ld_res = 0;   // fp32 residual added to the value (same col0)
+  int accum = 0;                 // value += out_f32 (previous contents)
+  float div = 0.f;               // if != 0: value /= div (after accum)
+  float act_slope = 1.f;
+};
+
+struct TcConvArgs {
+  const void* in = nullptr;      // 16-bit activations [R_in][ldin], view of `cin` channels
+  int ldin = 0, R_in = 0, cin = 0;
+  const TcW* w = nullptr;
+  int Q = 0;                     // output positions (per phase)
+  int tap_step = 1, in_off = 0;  // input row of tap t for position q: q + in_off + t*tap_step
+  int out_mul = 1;               // output row = q*out_mul + phase
+  int n_groups = 1;              // 1, or 2 = two independent column groups per CTA (res|skip, tanh|sigmoid)
+  int nt = 0;                    // columns per group handled by one CTA (UMMA N), multiple of 16, <= 256
+  int n_tiles = 1;               // CTAs along the column axis (each covers nt columns of every group)
+  int gate = 0;                  // 1: out_act = tanh(g0) * sigmoid(g1) (WN gate), only e[0] outputs used
+  TcEpi e[2];
+  const float* uttbias = nullptr; int ldub = 0;   // per-utterance bias [batch][ldub], indexed like bias
+  const int* row_utt = nullptr;  int valid_div = 1;
+  int f16 = 0;                   // 0 = bf16 operands, 1 = fp16 operands
+};
+
+// returns false (and sets err) when the shape cannot run on this kernel
+bool tc_conv_supported(int cin, int cout);
+void launch_conv_tc(Exec& ex, const TcConvArgs& a);
+
+// one-time weight repack from the fp32 SIMT layout [phases][taps][cin][ldw] (device) into dst rows
+// [ (ph*taps+t)*cout_total + row_off + co ][cin_pad]
+void launch_pack_tc_weights(Exec& ex, const float* w_f32, int ldw, int phases_taps, int cin, int cout,
+                            void* dst, int cout_total, int row_off, int cin_pad, int f16);
+// fp32 -> 16-bit copy of an activation tensor [R][C] (optional leaky-relu), used at stage boundaries
+void launch_to_act16(Exec& ex, const float* src, void* dst, int64_t n, float slope, int f16);
+
+}  // namespace piper

@@ -58,6 +58,7 @@ void Context::init(int dev) {
 void Context::destroy() {
   cudaSetDevice(device);
   if (stream) cudaStreamSynchronize(stream);
+  tc.release();
   voice.release();
   front.release();
   back.release();

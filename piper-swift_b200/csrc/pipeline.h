@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "../../include/piper_b200.h"
+#include "conv_tc.h"
 #include "kernels.h"
 #include "piper_config.h"
 #include "voice.h"
@@ -49,11 +50,38 @@ struct StageDump {
   bool valid = false;
 };
 
+// 16-bit tensor-core weights of the flow + HiFi-GAN convolutions (built on first use of a
+// 16-bit precision mode; back_tc.cpp)
+struct TcCoupling {
+  TcW pre, post;
+  std::vector<TcW> in_layers;
+  std::vector<TcW> rs;      // res|skip merged (last layer: skip only)
+};
+struct TcResBlock {
+  std::vector<TcW> c1, c2;
+};
+struct TcStage {
+  TcW up;
+  std::vector<TcResBlock> rbs;
+};
+struct TcVoice {
+  bool built = false;
+  int f16 = 0;
+  std::vector<TcCoupling> flows;
+  TcW dec_pre;
+  std::vector<TcStage> stages;
+  std::vector<void*> allocs;
+  void build(Exec& ex, const Voice& v, int f16);
+  void release();
+};
+TcW make_tcw(Exec& ex, std::vector<void*>& allocs, const ConvW& a, const ConvW* b, int f16);
+
 struct Context {
   int device = 0;
   cudaStream_t own_stream = nullptr;
   cudaStream_t stream = nullptr;
   Voice voice;
+  TcVoice tc;
   PiperConfig config;
   bool have_config = false;
   int precision = PIPER_B200_PRECISION_FP32;
@@ -74,6 +102,7 @@ struct Context {
   void destroy();
   void finalize_voice();            // voice.finalize() + derived layout constants
   int synthesize(const piper_b200_request& rq, piper_b200_result& rs);
+  int selftest_conv(int mode, int cin, int cout, int k, int dil, int stride, int rows, int prec, float* out4);
   int length_regulate(const float* logw, const int64_t* lengths, int batch, float length_scale,
                       int32_t* durations, int64_t* frame_lengths, int32_t* frame_index, int64_t frame_capacity);
 };
@@ -89,5 +118,8 @@ struct BackInputs {
 // returns packed audio [Rf*hop] (device, inside ctx.back); z_out (if non-null) receives the flow output
 float* run_back_f32(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep);
 size_t back_f32_bytes(const Context& ctx, int Rf, int batch);
+// tcgen05 implementation (back_tc.cpp); same contract
+float* run_back_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep);
+size_t back_tc_bytes(const Context& ctx, int Rf, int batch);
 
 }  // namespace piper

@@ -60,10 +60,8 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
     last_error = "invalid argument: empty batch or null ids/lengths";
     return PIPER_B200_ERR_INVALID_ARGUMENT;
   }
-  if (precision != PIPER_B200_PRECISION_FP32) {
-    last_error = "unsupported: tensor-core precision modes are not built into this library yet";
-    return PIPER_B200_ERR_UNSUPPORTED;
-  }
+  const bool use_tc = precision != PIPER_B200_PRECISION_FP32;
+  const int want_f16 = precision == PIPER_B200_PRECISION_F16 ? 1 : 0;
   const VoiceHParams& hp = voice.hp;
   const int B = rq.batch, H = hp.hidden;
   const bool ids_dev = rq.flags & PIPER_B200_FLAG_IDS_ON_DEVICE;
@@ -105,6 +103,16 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
     Exec ex;
     ex.st = stream;
     timings = piper_b200_timings{};
+    if (use_tc && (!tc.built || tc.f16 != want_f16)) {
+      try {
+        tc.build(ex, voice, want_f16);
+      } catch (const std::exception& e) {
+        tc.release();
+        last_error = e.what();
+        cudaGetLastError();
+        return last_error.rfind("unsupported", 0) == 0 ? PIPER_B200_ERR_UNSUPPORTED : PIPER_B200_ERR_CUDA;
+      }
+    }
     const int L = hp.flow_wn_layers;
     const int nflow = (int)voice.flows.size();
     const int condw = hp.gin ? (H + nflow * 2 * H * L + hp.dec_c0) : 0;
@@ -278,7 +286,7 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
       std::memcpy(durations.data() + id_off[b], h_dur + utt_start[b], (size_t)utt_len[b] * 4);
 
     // ---- back arena ---------------------------------------------------------------------------------------------
-    size_t bb = back_f32_bytes(*this, Rf, B);
+    size_t bb = use_tc ? back_tc_bytes(*this, Rf, B) : back_f32_bytes(*this, Rf, B);
     bb += (size_t)Rf * H * 4 * 2 + (size_t)Rf * 4 * 2 + (size_t)total_samples * 6 + 64 * 256;
     if (rq.noise_main) bb += (size_t)B * H * rq.noise_main_stride * 4;
     back.reserve(bb);
@@ -321,7 +329,7 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
     bi.zp = zp; bi.frow_utt = frow_utt; bi.Rf = Rf; bi.batch = B;
     bi.cond_flow = cond_flow; bi.cond_dec = cond_dec;
     CUDA_OK(cudaEventRecord(ev[3], stream));
-    float* packed = run_back_f32(*this, ex, bi, z_keep);
+    float* packed = use_tc ? run_back_tc(*this, ex, bi, z_keep) : run_back_f32(*this, ex, bi, z_keep);
     launch_gather_audio(ex, packed, d_fstart, d_ylen, d_soff, B, hp.hop, dense, pcm, total_samples);
     CUDA_OK(cudaEventRecord(ev[4], stream));
     if (keep_stages) {

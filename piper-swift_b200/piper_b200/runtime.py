@@ -98,6 +98,7 @@ def load_library(path: str = LIB_PATH):
         "piper_b200_get_stage": (C.c_int, [P, C.c_char_p, C.c_int32, P, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
         "piper_b200_length_regulate": (C.c_int, [P, P, P, C.c_int32, C.c_float, P, P, P, C.c_int64]),
         "piper_b200_random_normal": (C.c_int, [P, C.c_uint64, C.c_int64, P]),
+        "piper_b200_selftest_conv": (C.c_int, [P] + [C.c_int32] * 8 + [C.POINTER(C.c_float)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -112,7 +113,7 @@ EXPORTED_SYMBOLS = [
     "piper_b200_load_voice", "piper_b200_set_weight", "piper_b200_set_conv_attr", "piper_b200_set_config",
     "piper_b200_finalize", "piper_b200_get_voice_info", "piper_b200_set_precision", "piper_b200_set_stream",
     "piper_b200_synthesize", "piper_b200_get_timings", "piper_b200_get_stage", "piper_b200_length_regulate",
-    "piper_b200_random_normal",
+    "piper_b200_random_normal", "piper_b200_selftest_conv",
 ]
 
 
@@ -337,3 +338,11 @@ class PiperCUDARuntime:
         out = np.zeros(count, np.float32)
         self._check(self._lib.piper_b200_random_normal(self._ctx, seed, count, out.ctypes.data))
         return out
+
+    def selftest_conv(self, mode: int, cin: int, cout: int, k: int = 1, dilation: int = 1, stride: int = 1,
+                      rows: int = 1000, precision: str = "bf16") -> dict:
+        """piper_b200_selftest_conv: tcgen05 kernel vs fp32 CUDA-core kernel on identical operands."""
+        out = (C.c_float * 4)()
+        self._check(self._lib.piper_b200_selftest_conv(self._ctx, mode, cin, cout, k, dilation, stride, rows,
+                                                       PRECISION[precision], out))
+        return {"max_abs_diff": out[0], "max_abs_ref": out[1], "tc_ms": out[2], "f32_ms": out[3]}
