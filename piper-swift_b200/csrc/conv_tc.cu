@@ -15,6 +15,7 @@
 #include <cuda_fp16.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <stdexcept>
 #include <string>
 
@@ -149,7 +150,7 @@ struct TcKernelParams {
   int Q, taps, tap_step, in_off, kblocks, kb;
   int nt, n_groups, cout_rows;      // cout_rows = weight rows per (phase, tap)
   int phases, ct_pad, out_mul;
-  int gate, f16;
+  int gate, f16, window;
   TcEpi e[2];
   const float* uttbias; int ldub;
   const int* row_utt; int valid_div;
@@ -165,12 +166,19 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
                                                              const TcKernelParams p, const int stages) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const int a_bytes = TC_BM * p.kb * 2;
-  const int b_bytes = p.nt * p.kb * 2;                 // per group
-  const int stage_bytes = a_bytes + p.n_groups * b_bytes;
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)stages * stage_bytes);
+  const int row_bytes = p.kb * 2;
+  const int a_bytes = TC_BM * row_bytes;               // one 128-row activation box
+  const int b_bytes = p.nt * row_bytes;                // per group
+  // window mode: activations live in a 2-slot ring of 256-row windows (one per K block, shared by
+  // all taps through descriptor row offsets); the stage ring then holds weights only
+  const int a_ring_bytes = p.window ? 2 * 2 * a_bytes : 0;
+  const int stage_bytes = (p.window ? 0 : a_bytes) + p.n_groups * b_bytes;
+  uint8_t* stage_base = smem + a_ring_bytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(stage_base + (size_t)stages * stage_bytes);
   uint64_t* empty = full + TC_STAGES;
-  uint64_t* tmem_full = empty + TC_STAGES;
+  uint64_t* a_full = empty + TC_STAGES;
+  uint64_t* a_empty = a_full + 2;
+  uint64_t* tmem_full = a_empty + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -180,6 +188,8 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
   int in_off = p.in_off;
   if (p.phases > 1) in_off = (phase + p.ct_pad) / p.phases;
   const int n_it = p.taps * p.kblocks;
+  const int span = (p.taps - 1) * p.tap_step;          // row offset of the last tap (may be negative)
+  const int win_row0 = m0 + in_off + (span < 0 ? span : 0);
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_a);
@@ -187,6 +197,10 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
     for (int s = 0; s < stages; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&a_full[s], 1);
+      mbar_init(&a_empty[s], 1);
     }
     mbar_init(tmem_full, 1);
     fence_barrier_init();
@@ -205,14 +219,30 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
       for (int it = 0; it < n_it; ++it) {
         const int s = it % stages;
         const uint32_t ph = (uint32_t)(it / stages) & 1u;
+        int tap, kbi;
+        if (p.window) {                                 // K block outer, tap inner
+          kbi = it / p.taps; tap = it - kbi * p.taps;
+          if (tap == 0) {
+            const int slot = kbi & 1;
+            mbar_wait(&a_empty[slot], (((uint32_t)kbi >> 1) & 1u) ^ 1u);
+            uint8_t* aw = smem + (size_t)slot * 2 * a_bytes;
+            mbar_expect_tx(&a_full[slot], (uint32_t)(2 * a_bytes));
+            tma_load_2d(&tmap_a, &a_full[slot], aw, kbi * p.kb, win_row0);
+            tma_load_2d(&tmap_a, &a_full[slot], aw + a_bytes, kbi * p.kb, win_row0 + TC_BM);
+          }
+        } else {
+          tap = it / p.kblocks; kbi = it - tap * p.kblocks;
+        }
         mbar_wait(&empty[s], ph ^ 1u);
-        const int tap = it / p.kblocks, kbi = it - tap * p.kblocks;
-        uint8_t* st = smem + (size_t)s * stage_bytes;
+        uint8_t* st = stage_base + (size_t)s * stage_bytes;
         mbar_expect_tx(&full[s], (uint32_t)stage_bytes);
-        tma_load_2d(&tmap_a, &full[s], st, kbi * p.kb, m0 + in_off + tap * p.tap_step);
+        if (!p.window) {
+          tma_load_2d(&tmap_a, &full[s], st, kbi * p.kb, m0 + in_off + tap * p.tap_step);
+          st += a_bytes;
+        }
         const int wrow = (phase * p.taps + tap) * p.cout_rows + ntile * p.nt;
         for (int g = 0; g < p.n_groups; ++g)
-          tma_load_2d(&tmap_b, &full[s], st + a_bytes + g * b_bytes, kbi * p.kb, wrow + p.e[g].row0);
+          tma_load_2d(&tmap_b, &full[s], st + g * b_bytes, kbi * p.kb, wrow + p.e[g].row0);
       }
     }
   } else if (warp == 1) {
@@ -221,19 +251,32 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
     for (int it = 0; it < n_it; ++it) {
       const int s = it % stages;
       const uint32_t ph = (uint32_t)(it / stages) & 1u;
+      int tap = 0, kbi = 0;
+      if (p.window) {
+        kbi = it / p.taps; tap = it - kbi * p.taps;
+        if (tap == 0) mbar_wait(&a_full[kbi & 1], ((uint32_t)kbi >> 1) & 1u);
+      }
       mbar_wait(&full[s], ph);
       tc_fence_after();
       if (lane == 0) {
-        const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
+        uint32_t a_addr, b_addr = smem_u32(stage_base + (size_t)s * stage_bytes);
+        if (p.window) {   // tap shift = descriptor start address moved by whole rows inside the swizzled window
+          a_addr = smem_u32(smem + (size_t)(kbi & 1) * 2 * a_bytes) +
+                   (uint32_t)((tap * p.tap_step - (span < 0 ? span : 0)) * row_bytes);
+        } else {
+          a_addr = b_addr;
+          b_addr += a_bytes;
+        }
         const uint64_t a_desc = make_smem_desc(a_addr, p.kb);
         const int ksteps = p.kb / 16;
         for (int g = 0; g < p.n_groups; ++g) {
-          const uint64_t b_desc = make_smem_desc(a_addr + a_bytes + g * b_bytes, p.kb);
+          const uint64_t b_desc = make_smem_desc(b_addr + g * b_bytes, p.kb);
           for (int k = 0; k < ksteps; ++k)   // +32 bytes per K=16 step inside the swizzle atom
             umma_f16(tmem_base + (uint32_t)(g * p.nt), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
                      (it > 0 || k > 0) ? 1u : 0u);
         }
         umma_commit(&empty[s]);                 // frees the smem slot when these MMAs retire
+        if (p.window && tap == p.taps - 1) umma_commit(&a_empty[kbi & 1]);
         if (it == n_it - 1) umma_commit(tmem_full);
       }
       __syncwarp();
@@ -412,14 +455,18 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
   const CUtensorMap ta = make_map(a.in, (uint64_t)a.cin, (uint64_t)a.R_in, (uint64_t)a.ldin, w.kb, TC_BM, a.f16);
   const CUtensorMap tb = make_map(w.w, (uint64_t)w.cin_pad, (uint64_t)w.phases * w.taps * w.cout, (uint64_t)w.cin_pad,
                                   w.kb, a.nt, a.f16);
-  const int stage_bytes = TC_BM * w.kb * 2 + a.n_groups * a.nt * w.kb * 2;
+  const int span = (w.taps - 1) * (a.tap_step < 0 ? -a.tap_step : a.tap_step);
+  static const int window_env = [] { const char* e = getenv("PIPER_B200_TC_WINDOW"); return e ? atoi(e) : 1; }();
+  p.window = (a.window_mode != 0 && window_env != 0 && w.taps > 1 && span <= TC_BM) ? 1 : 0;
+  const int a_ring = p.window ? 4 * TC_BM * w.kb * 2 : 0;
+  const int stage_bytes = (p.window ? 0 : TC_BM * w.kb * 2) + a.n_groups * a.nt * w.kb * 2;
   int stages = TC_STAGES;
-  while (stages > 2 && stages * stage_bytes + 2048 > TC_SMEM_MAX) --stages;
+  while (stages > 2 && a_ring + stages * stage_bytes + 2048 > TC_SMEM_MAX) --stages;
   // two CTAs per SM (one's epilogue under the other's main loop) beat a deeper pipeline
-  while (stages > 3 && 2 * (stages * stage_bytes + 2048) > TC_SMEM_MAX) --stages;
+  while (stages > 3 && 2 * (a_ring + stages * stage_bytes + 2048) > TC_SMEM_MAX) --stages;
   const int n_it = w.taps * p.kblocks;
   if (stages > n_it) stages = n_it < 2 ? 2 : n_it;
-  const size_t smem = (size_t)stages * stage_bytes + 1024 + 256;
+  const size_t smem = (size_t)a_ring + (size_t)stages * stage_bytes + 1024 + 256;
   if (smem > (size_t)TC_SMEM_MAX) throw std::runtime_error("conv_tc: tile does not fit in shared memory");
   static bool attr_set = false;
   if (!attr_set) {

@@ -56,6 +56,7 @@ struct TcConvArgs {
   const float* uttbias = nullptr; int ldub = 0;   // per-utterance bias [batch][ldub], indexed like bias
   const int* row_utt = nullptr;  int valid_div = 1;
   int f16 = 0;                   // 0 = bf16 operands, 1 = fp16 operands
+  int window_mode = 1;           // 1: load each K block's activation window once and shift taps by descriptor offsets
 };
 
 // returns false (and sets err) when the shape cannot run on this kernel

@@ -783,44 +783,53 @@ void launch_wn_gate(Exec& ex, const float* xin, const float* cond, int ldc, cons
 }
 
 // conv_post (C -> 1 channel, no bias) with its preceding LeakyRelu and the final Tanh.
-__global__ void conv_post_tanh_kernel(const float* __restrict__ in, int C, const float* __restrict__ w,
-                                      int k, float slope, const int* __restrict__ row_utt, int valid_div,
-                                      float* __restrict__ out, int R) {
-  extern __shared__ float ws[];   // [k][C]
+constexpr int CP_ROWS = 128;
+__global__ void __launch_bounds__(CP_ROWS) conv_post_tanh_kernel(const float* __restrict__ in, int C,
+                                                                   const float* __restrict__ w, int k, float slope,
+                                                                   const int* __restrict__ row_utt, int valid_div,
+                                                                   float* __restrict__ out, int R) {
+  // a CTA stages CP_ROWS + k - 1 input rows (leaky-relu applied) in shared memory with coalesced
+  // loads, then every thread reduces one output row over taps x channels (row stride C+1: no bank conflicts)
+  extern __shared__ float sm[];
+  float* ws = sm;                 // [k][C]
+  float* xs = sm + k * C;         // [CP_ROWS + k - 1][C + 1]
+  const int pad = (k - 1) / 2;
+  const int r0 = blockIdx.x * CP_ROWS;
   for (int i = threadIdx.x; i < k * C; i += blockDim.x) ws[i] = w[i];
+  const int nrows = CP_ROWS + k - 1;
+  const int c4n = C / 4;
+  for (int i = threadIdx.x; i < nrows * c4n; i += blockDim.x) {
+    const int rr = i / c4n, c4 = i - rr * c4n;
+    const int gr = r0 + rr - pad;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (gr >= 0 && gr < R) v = *reinterpret_cast<const float4*>(in + (size_t)gr * C + c4 * 4);
+    float* d = xs + rr * (C + 1) + c4 * 4;
+    d[0] = v.x >= 0.f ? v.x : v.x * slope;
+    d[1] = v.y >= 0.f ? v.y : v.y * slope;
+    d[2] = v.z >= 0.f ? v.z : v.z * slope;
+    d[3] = v.w >= 0.f ? v.w : v.w * slope;
+  }
   __syncthreads();
-  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  const int r = r0 + threadIdx.x;
   if (r >= R) return;
   if (row_utt && row_utt[r / valid_div] < 0) {
     out[r] = 0.f;
     return;
   }
-  const int pad = (k - 1) / 2;
   float acc = 0.f;
   for (int t = 0; t < k; ++t) {
-    const int rr = r + t - pad;
-    if (rr < 0 || rr >= R) continue;
-    const float4* p = reinterpret_cast<const float4*>(in + (size_t)rr * C);
-    for (int c4 = 0; c4 < C / 4; ++c4) {
-      float4 v = p[c4];
-      v.x = v.x >= 0.f ? v.x : v.x * slope;
-      v.y = v.y >= 0.f ? v.y : v.y * slope;
-      v.z = v.z >= 0.f ? v.z : v.z * slope;
-      v.w = v.w >= 0.f ? v.w : v.w * slope;
-      const float* wp = ws + t * C + c4 * 4;
-      acc = fmaf(v.x, wp[0], acc);
-      acc = fmaf(v.y, wp[1], acc);
-      acc = fmaf(v.z, wp[2], acc);
-      acc = fmaf(v.w, wp[3], acc);
-    }
+    const float* xr = xs + (threadIdx.x + t) * (C + 1);
+    const float* wp = ws + t * C;
+    for (int c = 0; c < C; ++c) acc = fmaf(xr[c], wp[c], acc);
   }
   out[r] = tanhf(acc);
 }
 void launch_conv_post_tanh(Exec& ex, const float* in, int C, const float* w, int k, float slope,
                            const int* row_utt, int valid_div, float* out, int R) {
   if (R <= 0) return;
-  conv_post_tanh_kernel<<<(R + 127) / 128, 128, sizeof(float) * k * C, ex.st>>>(in, C, w, k, slope, row_utt,
-                                                                             valid_div, out, R);
+  const size_t smem = sizeof(float) * ((size_t)k * C + (size_t)(CP_ROWS + k - 1) * (C + 1));
+  conv_post_tanh_kernel<<<(R + CP_ROWS - 1) / CP_ROWS, CP_ROWS, smem, ex.st>>>(in, C, w, k, slope, row_utt,
+                                                                              valid_div, out, R);
   KLAUNCH(ex);
 }
 

@@ -1,0 +1,112 @@
+"""GPU tests of the tensor-core (tcgen05 / TMEM / TMA) back end through the C ABI.
+
+Kernel level : piper_b200_selftest_conv - the tcgen05 implicit-GEMM convolution against the fp32
+               CUDA-core kernel on identical, exactly representable operands.  Tolerance: 2e-3 * max|ref|
+               for the fp32 outputs (observed: bit-exact), 2e-2 for the 16-bit gate output.
+Graph level  : precision modes "f16" / "bf16" against the fp32 oracle.  The text encoder, duration
+               predictor and length regulator stay in fp32, so durations / y_len must be bit-exact;
+               waveform tolerance (stated, measured on B200, profiles/r01_tc_parity_vs_oracle.log):
+                 f16  : SNR >= 58 dB, max-abs <= 4e-3      (observed 63-65 dB, 1.2e-3)
+                 bf16 : SNR >= 40 dB, max-abs <= 3e-2      (observed 45-47 dB, 9.5e-3)
+"""
+import numpy as np
+import pytest
+
+from common import S, voice_files, oracle, snr_db, fixture_ids
+from oracle import refrng
+from piper_b200.runtime import PiperCUDARuntime, Options, PiperB200Error
+from piper_b200.synth_voice import synthetic_utterances
+
+pytestmark = pytest.mark.gpu
+
+_rt = {}
+
+
+def rt(name, precision):
+    key = (name, precision)
+    if key not in _rt:
+        mp, cp = voice_files(name)
+        _rt[key] = PiperCUDARuntime(mp, cp, Options(precision=precision))
+    return _rt[key]
+
+
+CASES = [  # mode, cin, cout, k, dil, stride, rows
+    (0, 64, 64, 1, 1, 1, 300), (0, 64, 64, 3, 1, 1, 1000), (0, 32, 32, 7, 3, 1, 5000), (0, 32, 32, 3, 1, 1, 129),
+    (0, 96, 192, 1, 1, 1, 700), (0, 192, 96, 1, 1, 1, 700), (0, 192, 256, 7, 1, 1, 515), (0, 128, 128, 5, 6, 1, 2000),
+    (0, 192, 512, 7, 1, 1, 400), (0, 256, 256, 11, 5, 1, 900), (0, 64, 64, 7, 12, 1, 4000), (0, 32, 32, 11, 5, 1, 1),
+    (1, 192, 384, 5, 1, 1, 1000), (2, 192, 384, 1, 1, 1, 1000),
+    (3, 256, 128, 16, 1, 8, 300), (3, 128, 64, 16, 1, 8, 1000), (3, 64, 32, 8, 1, 4, 3000), (3, 128, 64, 4, 1, 2, 500),
+]
+
+
+@pytest.mark.parametrize("prec", ["bf16", "f16"])
+@pytest.mark.parametrize("case", CASES, ids=lambda c: "m%d_%dto%d_k%d_d%d_s%d_r%d" % c)
+def test_tcgen05_conv_matches_fp32_kernel(case, prec):
+    r = rt("tiny", "fp32").selftest_conv(*case, precision=prec)
+    tol = (2e-2 if case[0] == 1 else 2e-3) * max(1.0, r["max_abs_ref"])
+    assert r["max_abs_ref"] > 0.5
+    assert r["max_abs_diff"] <= tol, r
+
+
+def test_selftest_rejects_bad_shapes():
+    with pytest.raises(PiperB200Error):
+        rt("tiny", "fp32").selftest_conv(0, 24, 64, 3, 1, 1, 100, precision="bf16")    # cin not a multiple of 32
+    with pytest.raises(PiperB200Error):
+        rt("tiny", "fp32").selftest_conv(0, 64, 64, 3, 1, 1, 100, precision="fp32")
+
+
+TOL = {"f16": (58.0, 4e-3), "bf16": (40.0, 3e-2)}
+
+
+@pytest.mark.parametrize("prec", ["f16", "bf16"])
+@pytest.mark.parametrize("name,factor,sid", [("medium", 1, None), ("medium", 8, None), ("high", 2, None),
+                                             ("medium-multispeaker", 2, 7)])
+def test_tc_modes_against_oracle(name, factor, sid, prec):
+    ids = fixture_ids(factor)
+    ns, ls, nw = S.FIXTURE_SCALES
+    o = oracle(name).infer(ids, ns, ls, nw, refrng.noise_dp(len(ids)), noise_main_fn=refrng.noise_main, sid=sid)
+    r = rt(name, prec).synthesize_batch([ids], ns, ls, nw, speaker_ids=None if sid is None else [sid], keep_stages=True)
+    assert np.array_equal(r.durations[0], o["w_ceil"].astype(np.int32))       # front end is fp32: bit-exact
+    assert int(r.frame_lengths[0]) == o["y_len"]
+    zp = rt(name, prec).get_stage("z_p", 0)
+    assert np.abs(zp - o["z_p"].reshape(zp.shape)).max() < 5e-5             # still fp32 up to here
+    snr_min, abs_max = TOL[prec]
+    a = r.audio[0]
+    assert a.shape == o["audio"].shape
+    assert snr_db(o["audio"], a) >= snr_min
+    assert np.abs(a - o["audio"]).max() <= abs_max
+    t = rt(name, prec).last_run_timings
+    assert t["kernel_launches"] > 50
+
+
+def test_tc_mode_unsupported_voice_fails_loudly():
+    """tiny has 16/8-channel convolutions that do not fit the tcgen05 tile: error, no silent fallback."""
+    with pytest.raises(PiperB200Error) as e:
+        rt("tiny", "f16").synthesize(S.FIXTURE_IDS)
+    assert e.value.code == 4
+
+
+def test_tc_batch_invariance_and_masks():
+    """Ragged batch in f16 mode: every utterance equals its B=1 result (gap rows stay zero)."""
+    utts = [fixture_ids(1), fixture_ids(3), [1, 5, 2], fixture_ids(2)[:-3]]
+    r = rt("medium", "f16")
+    batch = r.synthesize_batch(utts, *S.FIXTURE_SCALES)
+    for u, a, d in zip(utts, batch.audio, batch.durations):
+        s = r.synthesize_batch([u], *S.FIXTURE_SCALES)
+        assert np.array_equal(d, s.durations[0])
+        assert np.array_equal(a, s.audio[0])
+
+
+def test_tc_full_size_batch_properties():
+    """BASELINE config 3 shape in f16 mode: size-independent properties + oracle spot check."""
+    utts = synthetic_utterances(256, 256)
+    r = rt("medium", "f16")
+    out = r.synthesize_batch(utts, *S.FIXTURE_SCALES)
+    ref = rt("medium", "fp32").synthesize_batch(utts, *S.FIXTURE_SCALES)
+    assert np.array_equal(out.frame_lengths, ref.frame_lengths)
+    assert all(np.array_equal(x, y) for x, y in zip(out.durations, ref.durations))
+    allv = np.concatenate(out.audio)
+    assert np.isfinite(allv).all() and np.abs(allv).max() <= 1.0
+    assert snr_db(np.concatenate(ref.audio), allv) >= 58.0
+    again = r.synthesize_batch(utts, *S.FIXTURE_SCALES)
+    assert all(np.array_equal(x, y) for x, y in zip(out.audio, again.audio))
