@@ -6,6 +6,7 @@
 // epilogue of the in_layer convolution, res|skip is one GEMM with two column groups, and
 // every producer also emits the 16-bit (leaky-relu'd) operand copy its consumer reads.
 // Residual streams, skip sums and the cross-resblock mean stay in fp32.
+#include <cstdlib>
 #include <stdexcept>
 
 #include "conv_tc.h"
@@ -80,6 +81,34 @@ void TcVoice::build(Exec& ex, const Voice& v, int f16_) {
       for (const ConvW& c : rb.c2) r.c2.push_back(make_tcw(ex, allocs, c, nullptr, f16));
       t.rbs.push_back(r);
     }
+    {   // fused MRF stage when every resblock is a two-convolution ResBlock2 with 32 or 64 channels
+      const int nk = (int)s.rbs.size();
+      int kk[MRF_MAX_RB] = {0, 0, 0, 0}, d0[MRF_MAX_RB] = {0, 0, 0, 0}, d1[MRF_MAX_RB] = {0, 0, 0, 0};
+      bool ok = nk >= 1 && nk <= MRF_MAX_RB;
+      for (int j = 0; ok && j < nk; ++j) {
+        const ResBlockW& rb = s.rbs[j];
+        ok = rb.c2.empty() && rb.c1.size() == 2 && rb.c1[0].k == rb.c1[1].k && rb.c1[0].cin == s.ch &&
+             rb.c1[0].cout == s.ch && rb.c1[0].pad_l == rb.c1[0].dil * (rb.c1[0].k - 1) / 2 &&
+             rb.c1[1].pad_l == rb.c1[1].dil * (rb.c1[1].k - 1) / 2;
+        if (ok) { kk[j] = rb.c1[0].k; d0[j] = rb.c1[0].dil; d1[j] = rb.c1[1].dil; }
+      }
+      if (ok && mrf_tc_supported(s.ch, nk, kk, d0, d1)) {
+        int taps = 0;
+        for (int j = 0; j < nk; ++j)
+          for (int c = 0; c < 2; ++c) { t.tap_base[j][c] = taps; taps += kk[j]; }
+        const size_t tap_elems = (size_t)s.ch * s.ch;
+        CUDA_OK(cudaMalloc(&t.mrf_w, (size_t)taps * tap_elems * 2));
+        allocs.push_back(t.mrf_w);
+        for (int j = 0; j < nk; ++j)
+          for (int c = 0; c < 2; ++c) {
+            const ConvW& cw = s.rbs[j].c1[c];
+            launch_pack_tc_weights(ex, cw.w, cw.ldw, cw.taps, cw.cin, cw.cout,
+                                   static_cast<uint16_t*>(t.mrf_w) + (size_t)t.tap_base[j][c] * tap_elems, s.ch, 0, s.ch, f16);
+          }
+        t.mrf_taps = taps;
+        t.mrf = true;
+      }
+    }
     stages.push_back(t);
   }
   CUDA_OK(cudaStreamSynchronize(ex.st));
@@ -132,6 +161,7 @@ size_t back_tc_bytes(const Context& ctx, int Rf, int batch) {
   size_t bytes = 0;
   bytes += (size_t)Rf * H * (4 * 2 + 2 * 4);       // h, skip fp32; zb, hb, actsb, skipb 16-bit
   bytes += (size_t)Rf * P * (4 * 3 + 2 * 5);       // xu, yb, xs fp32; actA, actB, xub, ybb, tbb 16-bit
+  bytes += 64 * 1280 * 2 + 4096;                   // pad rows of the planar operand layout
   bytes += (size_t)Rf * v.hp.hop * 4;              // packed audio
   bytes += 32 * 256;
   (void)batch;
@@ -216,7 +246,7 @@ float* run_back_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep) 
   float* yb = A.alloc<float>((size_t)Rf * P);
   float* xs = A.alloc<float>((size_t)Rf * P);
   uint16_t* act[2] = {A.alloc<uint16_t>((size_t)Rf * P), A.alloc<uint16_t>((size_t)Rf * P)};
-  uint16_t* xub = A.alloc<uint16_t>((size_t)Rf * P);
+  uint16_t* xub = A.alloc<uint16_t>((size_t)Rf * P + 64 * 1280);   // + pad rows of the planar layout
   uint16_t* ybb = A.alloc<uint16_t>((size_t)Rf * P);
   uint16_t* tbb = A.alloc<uint16_t>((size_t)Rf * P);
   float* audio = A.alloc<float>((size_t)Rf * v.hp.hop);
@@ -239,6 +269,15 @@ float* run_back_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep) 
     const int Rn = R * s.stride;
     U *= s.stride;
     const int C = s.ch;
+    static const int mrf_env = [] { const char* e = getenv("PIPER_B200_MRF"); return e ? atoi(e) : 1; }();
+    const bool use_mrf = ts.mrf && mrf_env;
+    // fused stages read lrelu(x) as a group-planar tensor [C/8][act_rows][8] with zero pad rows around the signal
+    const int act_pad = 128;
+    const int64_t act_rows = (int64_t)Rn + act_pad + 1152;
+    if (use_mrf) {
+      CUDA_OK(cudaMemset2DAsync(xub, (size_t)act_rows * 16, 0, (size_t)act_pad * 16, C / 8, ex.st));
+      CUDA_OK(cudaMemset2DAsync(xub + ((size_t)act_pad + Rn) * 8, (size_t)act_rows * 16, 0, (size_t)1152 * 16, C / 8, ex.st));
+    }
     {   // LeakyRelu(0.1) [already in the operand copy] + ConvTranspose, one polyphase GEMM per phase
       TcConvArgs a;
       a.in = act[cur]; a.ldin = ts.up.cin; a.R_in = R; a.cin = ts.up.cin;
@@ -248,11 +287,28 @@ float* run_back_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep) 
       a.e[0].bias = ts.up.bias;
       a.e[0].out_f32 = xu; a.e[0].ld_f32 = C;
       a.e[0].out_act = xub; a.e[0].ld_act = C; a.e[0].act_slope = 0.1f;
+      if (use_mrf) { a.e[0].act_planar = 1; a.e[0].act_rows = act_rows; a.e[0].act_pad = act_pad; }
       a.row_utt = in.frow_utt; a.valid_div = U;
       a.f16 = f16;
       launch_conv_tc(ex, a);
     }
     uint16_t* xsb = act[cur ^ 1];
+    if (use_mrf) {   // whole MRF stage in one persistent kernel, intermediates on chip
+      MrfArgs a;
+      a.R = Rn; a.C = C; a.nk = nk;
+      for (int j = 0; j < nk; ++j) {
+        a.k[j] = s.rbs[j].c1[0].k; a.d0[j] = s.rbs[j].c1[0].dil; a.d1[j] = s.rbs[j].c1[1].dil;
+        a.tap_base[j][0] = ts.tap_base[j][0]; a.tap_base[j][1] = ts.tap_base[j][1];
+        a.b1[j] = s.rbs[j].c1[0].b; a.b2[j] = s.rbs[j].c1[1].b;
+      }
+      a.w = ts.mrf_w; a.total_taps = ts.mrf_taps;
+      a.x = xu; a.x_act = xub; a.act_rows = act_rows; a.act_pad = act_pad;
+      a.row_utt = in.frow_utt; a.valid_div = U;
+      if (last_stage) a.out_f32 = xs;
+      else { a.out_act = xsb; a.act_slope = 0.1f; }
+      a.f16 = f16;
+      launch_mrf_tc(ex, a);
+    } else
     for (int j = 0; j < nk; ++j) {
       const TcResBlock& rb = ts.rbs[j];
       const int M = (int)rb.c1.size();

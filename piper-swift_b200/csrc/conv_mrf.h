@@ -1,0 +1,47 @@
+// Fused multi-receptive-field stage of the HiFi-GAN generator on tcgen05 (sm_100a).
+// One persistent kernel computes, for a whole generator stage with ResBlock2 blocks,
+//     out = (1/nk) * sum_r  y2_r,   y1_r = x + conv_{k_r,d0_r}(lrelu(x)) + b1_r,
+//                                   y2_r = y1_r + conv_{k_r,d1_r}(lrelu(y1_r)) + b2_r
+// i.e. the graph's LeakyRelu/Conv/Add chains, the Add across kernels and the Div
+// (GraphExecutor.swift:1739-1810, 2047-2069; conv1d.metal:28-71) with every intermediate on
+// chip: operands in swizzled shared memory, the fp32 residual stream and the cross-resblock sum
+// in tensor memory.  HBM traffic per element: read x (fp32) + lrelu(x) (16-bit), write the
+// stage output once - instead of ~12 bytes per element per convolution.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "kernels.h"
+
+namespace piper {
+
+constexpr int MRF_MAX_RB = 4;
+
+struct MrfArgs {
+  int R = 0;                     // rows (time positions) of this stage
+  int C = 0;                     // channels (32 or 64)
+  int nk = 0;                    // resblocks
+  int k[MRF_MAX_RB] = {0, 0, 0, 0};
+  int d0[MRF_MAX_RB] = {0, 0, 0, 0}, d1[MRF_MAX_RB] = {0, 0, 0, 0};
+  int tap_base[MRF_MAX_RB][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}};   // first tap (row block of C rows) of conv (r, j) in `w`
+  const float* b1[MRF_MAX_RB] = {nullptr, nullptr, nullptr, nullptr};
+  const float* b2[MRF_MAX_RB] = {nullptr, nullptr, nullptr, nullptr};
+  const void* w = nullptr;       // 16-bit weights [total_taps][C cout][C cin]
+  int total_taps = 0;
+  const float* x = nullptr;      // fp32 stage input [R][C] (ConvTranspose output)
+  // 16-bit lrelu(x), group-planar [C/8][act_rows][8]; signal row r at plane row act_pad + r; the rows before
+  // act_pad and after act_pad + R must be zero (act_pad >= 128, act_rows >= R + act_pad + 1152)
+  const void* x_act = nullptr;
+  int64_t act_rows = 0; int act_pad = 0;
+  const int* row_utt = nullptr;  int valid_div = 1;
+  void* out_act = nullptr;       // optional 16-bit lrelu(out, act_slope) [R][C]
+  float act_slope = 1.f;
+  float* out_f32 = nullptr;      // optional fp32 out [R][C]
+  int f16 = 0;
+};
+
+bool mrf_tc_supported(int C, int nk, const int* k, const int* d0, const int* d1);
+void launch_mrf_tc(Exec& ex, const MrfArgs& a);
+
+}  // namespace piper

@@ -9,6 +9,7 @@
 //                 bias/residual/gate in registers, vectorised global stores
 // Pipeline: full[s]/empty[s] mbarriers between TMA and MMA, tmem_full between MMA and epilogue.
 #include "conv_tc.h"
+#include "tc_common.cuh"
 
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -21,130 +22,9 @@
 
 namespace piper {
 
+using namespace tc;
+
 namespace {
-
-constexpr int TC_BM = 128;
-constexpr int TC_STAGES = 4;
-constexpr int TC_THREADS = 192;
-
-// ---- PTX wrappers ------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
-}
-__device__ __forceinline__ bool elect_one_unused() {
-  uint32_t pred = 0;
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "elect.sync _|p, 0xffffffff;\n\t"
-      "selp.u32 %0, 1, 0, p;\n\t"
-      "}\n"
-      : "=r"(pred));
-  return pred != 0;
-}
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
-               : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  const uint32_t addr = smem_u32(bar);
-  asm volatile(
-      "{\n\t"
-      ".reg .pred P1;\n\t"
-      "LAB_WAIT:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
-      "@P1 bra DONE;\n\t"
-      "bra LAB_WAIT;\n\t"
-      "DONE:\n\t"
-      "}\n" ::"r"(addr),
-      "r"(parity)
-      : "memory");
-}
-__device__ __forceinline__ void fence_barrier_init() {
-  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* bar, void* dst, int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cta.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
-      : "memory");
-}
-__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
-  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
-}
-__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
-  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)),
-               "r"(cols)
-               : "memory");
-}
-__device__ __forceinline__ void tmem_relinquish() {
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
-  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
-               : "memory");
-}
-// D[tmem] (+)= A[smem] * B[smem]^T, 16-bit operands, fp32 accumulate
-__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
-                                         uint32_t accumulate) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
-      "}\n" ::"r"(tmem_d),
-      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
-  uint32_t r[16];
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-}
-
-// K-major shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): rows of `kb` 16-bit
-// elements, 8-row swizzle atoms stacked every SBO bytes; version 1 (sm_100).
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, int kb) {
-  const uint64_t sbo = (kb == 64) ? 1024 : 512;       // 8 rows x (128 | 64) bytes
-  const uint64_t layout = (kb == 64) ? 2 : 4;         // SWIZZLE_128B | SWIZZLE_64B
-  uint64_t d = 0;
-  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
-  d |= (uint64_t)1 << 16;                             // leading byte offset (unused for swizzled K-major)
-  d |= (sbo >> 4) << 32;
-  d |= (uint64_t)1 << 46;                             // descriptor version
-  d |= layout << 61;
-  return d;
-}
-// cute::UMMA::InstrDescriptor for kind::f16: fp32 accumulate, K-major A and B
-__device__ __forceinline__ uint32_t make_idesc(int n, int f16) {
-  const uint32_t fmt = f16 ? 0u : 1u;
-  return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
-}
-
-__device__ __forceinline__ uint32_t pack2(float a, float b, int f16) {
-  if (f16) {
-    const __half2 h = __floats2half2_rn(a, b);
-    return *reinterpret_cast<const uint32_t*>(&h);
-  }
-  const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-  return *reinterpret_cast<const uint32_t*>(&h);
-}
-__device__ __forceinline__ float lrelu(float v, float s) { return v >= 0.f ? v : v * s; }
 
 struct TcKernelParams {
   int Q, taps, tap_step, in_off, kblocks, kb;
@@ -163,6 +43,7 @@ namespace {
 
 __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
                                                              const __grid_constant__ CUtensorMap tmap_b,
+                                                             const __grid_constant__ CUtensorMap tmap_ans,
                                                              const TcKernelParams p, const int stages) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -227,8 +108,12 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
             mbar_wait(&a_empty[slot], (((uint32_t)kbi >> 1) & 1u) ^ 1u);
             uint8_t* aw = smem + (size_t)slot * 2 * a_bytes;
             mbar_expect_tx(&a_full[slot], (uint32_t)(2 * a_bytes));
-            tma_load_2d(&tmap_a, &a_full[slot], aw, kbi * p.kb, win_row0);
-            tma_load_2d(&tmap_a, &a_full[slot], aw + a_bytes, kbi * p.kb, win_row0 + TC_BM);
+            if (p.window == 2) {   // [channel group][row][8 channels], no swizzle
+              tma_load_3d(&tmap_ans, &a_full[slot], aw, 0, win_row0, kbi * (p.kb / 8));
+            } else {
+              tma_load_2d(&tmap_a, &a_full[slot], aw, kbi * p.kb, win_row0);
+              tma_load_2d(&tmap_a, &a_full[slot], aw + a_bytes, kbi * p.kb, win_row0 + TC_BM);
+            }
           }
         } else {
           tap = it / p.kblocks; kbi = it - tap * p.kblocks;
@@ -267,12 +152,19 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
           a_addr = b_addr;
           b_addr += a_bytes;
         }
-        const uint64_t a_desc = make_smem_desc(a_addr, p.kb);
+        uint64_t a_desc = make_smem_desc(a_addr, p.kb);
+        uint64_t a_kstep = 2;                   // +32 bytes per K=16 step inside the swizzle atom
+        if (p.window == 2) {                    // no-swizzle window: rows 16 B apart, channel groups 2*TC_BM*16 B apart
+          a_addr = smem_u32(smem + (size_t)(kbi & 1) * 2 * a_bytes) +
+                   (uint32_t)((tap * p.tap_step - (span < 0 ? span : 0)) * 16);
+          a_desc = make_smem_desc_ns(a_addr, 2 * TC_BM * 16, 128);
+          a_kstep = (uint64_t)(2 * 2 * TC_BM * 16) >> 4;
+        }
         const int ksteps = p.kb / 16;
         for (int g = 0; g < p.n_groups; ++g) {
           const uint64_t b_desc = make_smem_desc(b_addr + g * b_bytes, p.kb);
-          for (int k = 0; k < ksteps; ++k)   // +32 bytes per K=16 step inside the swizzle atom
-            umma_f16(tmem_base + (uint32_t)(g * p.nt), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
+          for (int k = 0; k < ksteps; ++k)
+            umma_f16(tmem_base + (uint32_t)(g * p.nt), a_desc + a_kstep * (uint64_t)k, b_desc + (uint64_t)(2 * k), idesc,
                      (it > 0 || k > 0) ? 1u : 0u);
         }
         umma_commit(&empty[s]);                 // frees the smem slot when these MMAs retire
@@ -376,9 +268,15 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
 #pragma unroll
             for (int i = 0; i < 8; ++i)
               pk[i] = pack2(lrelu(v[2 * i], e.act_slope), lrelu(v[2 * i + 1], e.act_slope), p.f16);
-            uint4* dst = reinterpret_cast<uint4*>(static_cast<uint16_t*>(e.out_act) + (size_t)orow * e.ld_act + ocol);
-            dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-            dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+            if (e.act_planar) {
+              uint16_t* base = static_cast<uint16_t*>(e.out_act) + ((size_t)(ocol >> 3) * e.act_rows + e.act_pad + orow) * 8;
+              *reinterpret_cast<uint4*>(base) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+              *reinterpret_cast<uint4*>(base + (size_t)e.act_rows * 8) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+            } else {
+              uint4* dst = reinterpret_cast<uint4*>(static_cast<uint16_t*>(e.out_act) + (size_t)orow * e.ld_act + ocol);
+              dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+              dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+            }
           }
         }
       }
@@ -393,42 +291,6 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
 
 // ---- host side -----------------------------------------------------------------------------
 namespace {
-
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  if (!fn) {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || !p ||
-        q != cudaDriverEntryPointSuccess)
-      throw std::runtime_error("cuda: cuTensorMapEncodeTiled entry point unavailable");
-    fn = reinterpret_cast<EncodeTiledFn>(p);
-  }
-  return fn;
-}
-
-// 2-D K-major tensor map: inner dim = channels (16-bit), outer dim = rows
-CUtensorMap make_map(const void* base, uint64_t inner, uint64_t rows, uint64_t ld_elems, int box_inner,
-                     int box_rows, int f16) {
-  CUtensorMap m;
-  const cuuint64_t dims[2] = {inner, rows};
-  const cuuint64_t strides[1] = {ld_elems * 2};
-  const cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_rows};
-  const cuuint32_t estr[2] = {1, 1};
-  const CUresult r = encode_fn()(&m, f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
-                                 const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                                 box_inner == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
-                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS)
-    throw std::runtime_error("cuda: cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
-  return m;
-}
-
-constexpr int TC_SMEM_MAX = 232448;   // 227 KB
 
 }  // namespace
 
@@ -457,7 +319,9 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
                                   w.kb, a.nt, a.f16);
   const int span = (w.taps - 1) * (a.tap_step < 0 ? -a.tap_step : a.tap_step);
   static const int window_env = [] { const char* e = getenv("PIPER_B200_TC_WINDOW"); return e ? atoi(e) : 1; }();
-  p.window = (a.window_mode != 0 && window_env != 0 && w.taps > 1 && span <= TC_BM) ? 1 : 0;
+  p.window = (a.window_mode != 0 && window_env != 0 && w.taps > 1 && span <= TC_BM) ? window_env : 0;
+  if (p.window == 1 && a.tap_step % 8 != 0) p.window = 0;   // swizzled windows: only atom-aligned shifts are fast
+  if (p.window == 2 && (a.ldin % 8 != 0 || a.cin % 8 != 0)) p.window = 0;
   const int a_ring = p.window ? 4 * TC_BM * w.kb * 2 : 0;
   const int stage_bytes = (p.window ? 0 : TC_BM * w.kb * 2) + a.n_groups * a.nt * w.kb * 2;
   int stages = TC_STAGES;
@@ -474,8 +338,10 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
       throw std::runtime_error("cuda: cannot raise dynamic shared memory limit for conv_tc_kernel");
     attr_set = true;
   }
+  CUtensorMap tans = ta;
+  if (p.window == 2) tans = make_map_ns(a.in, (uint64_t)a.cin, (uint64_t)a.R_in, (uint64_t)a.ldin, 2 * TC_BM, w.kb / 8, a.f16);
   dim3 grid((a.Q + TC_BM - 1) / TC_BM, a.n_tiles, w.phases);
-  conv_tc_kernel<<<grid, TC_THREADS, smem, ex.st>>>(ta, tb, p, stages);
+  conv_tc_kernel<<<grid, TC_THREADS, smem, ex.st>>>(ta, tb, tans, p, stages);
   ++ex.launches;
 }
 

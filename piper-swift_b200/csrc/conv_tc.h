@@ -35,6 +35,9 @@ struct TcEpi {
   int col0 = 0;                  // output column where the group's column 0 lands
   float* out_f32 = nullptr; int ld_f32 = 0;
   void* out_act = nullptr;  int ld_act = 0;     // 16-bit copy, leaky-relu(act_slope) applied
+  // act_planar: out_act is "group-planar" [C/8][act_rows][8] (8-channel groups as planes, each row 16 bytes;
+  // the layout conv_mrf.cu bulk-copies into its no-swizzle operand window); row r lives at plane row act_pad + r
+  int act_planar = 0; int64_t act_rows = 0; int act_pad = 0;
   const float* res = nullptr; int ld_res = 0;   // fp32 residual added to the value (same col0)
   int accum = 0;                 // value += out_f32 (previous contents)
   float div = 0.f;               // if != 0: value /= div (after accum)

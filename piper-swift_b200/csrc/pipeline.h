@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "../../include/piper_b200.h"
+#include "conv_mrf.h"
 #include "conv_tc.h"
 #include "kernels.h"
 #include "piper_config.h"
@@ -63,6 +64,11 @@ struct TcResBlock {
 struct TcStage {
   TcW up;
   std::vector<TcResBlock> rbs;
+  // fused MRF stage (conv_mrf.cu): all resblock convolutions of the stage packed as [tap][cout][cin]
+  bool mrf = false;
+  void* mrf_w = nullptr;
+  int mrf_taps = 0;
+  int tap_base[MRF_MAX_RB][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}};
 };
 struct TcVoice {
   bool built = false;

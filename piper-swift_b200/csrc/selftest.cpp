@@ -80,7 +80,8 @@ int Context::selftest_conv(int mode, int cin, int cout, int k, int dil, int stri
 
     DevBuf dw(hw.size() * 4), db(hb.size() * 4), dx(hx.size() * 4), dx16(hx.size() * 2), dres(hres.size() * 4);
     DevBuf dutt(rows * 4), dref((size_t)Rout * cout * 4), dtc((size_t)Rout * cout * 4), dact((size_t)Rout * cout * 2);
-    DevBuf dref2((size_t)Rout * cout * 4);
+    DevBuf dref2((size_t)Rout * cout * 4), dtc2((size_t)Rout * cout * 4);
+    CUDA_OK(cudaMemcpy(dtc2.p, hres.data(), hres.size() * 4, cudaMemcpyHostToDevice));
     CUDA_OK(cudaMemcpy(dw.p, hw.data(), hw.size() * 4, cudaMemcpyHostToDevice));
     CUDA_OK(cudaMemcpy(db.p, hb.data(), hb.size() * 4, cudaMemcpyHostToDevice));
     CUDA_OK(cudaMemcpy(dx.p, hx.data(), hx.size() * 4, cudaMemcpyHostToDevice));
@@ -132,8 +133,6 @@ int Context::selftest_conv(int mode, int cin, int cout, int k, int dil, int stri
     if (ct) { a.tap_step = -1; a.out_mul = stride; }
     else { a.tap_step = dil; a.in_off = -cw.pad_l; }
     auto pick = [](int c) { for (int nt : {128, 96, 64, 48, 32, 16}) if (c % nt == 0) return nt; return 16; };
-    DevBuf dtc2((size_t)Rout * cout * 4);
-    CUDA_OK(cudaMemcpy(dtc2.p, hres.data(), hres.size() * 4, cudaMemcpyHostToDevice));
     if (mode == 1) {
       a.gate = 1; a.n_groups = 2; a.nt = pick(H); a.n_tiles = H / a.nt;
       a.e[0].row0 = 0; a.e[0].bias = cw.b; a.e[1].row0 = H; a.e[1].bias = cw.b + H;
