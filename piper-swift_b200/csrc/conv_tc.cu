@@ -30,7 +30,7 @@ struct TcKernelParams {
   int Q, taps, tap_step, in_off, kblocks, kb;
   int nt, n_groups, cout_rows;      // cout_rows = weight rows per (phase, tap)
   int phases, ct_pad, out_mul;
-  int gate, f16, window;
+  int gate, f16, window, a_col0, relu;
   TcEpi e[2];
   const float* uttbias; int ldub;
   const int* row_utt; int valid_div;
@@ -68,7 +68,6 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
   const int phase = blockIdx.z;
   int in_off = p.in_off;
   if (p.phases > 1) in_off = (phase + p.ct_pad) / p.phases;
-  const int n_it = p.taps * p.kblocks;
   const int span = (p.taps - 1) * p.tap_step;          // row offset of the last tap (may be negative)
   const int win_row0 = m0 + in_off + (span < 0 ? span : 0);
 
@@ -97,82 +96,84 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
-      for (int it = 0; it < n_it; ++it) {
-        const int s = it % stages;
-        const uint32_t ph = (uint32_t)(it / stages) & 1u;
-        int tap, kbi;
-        if (p.window) {                                 // K block outer, tap inner
-          kbi = it / p.taps; tap = it - kbi * p.taps;
-          if (tap == 0) {
-            const int slot = kbi & 1;
-            mbar_wait(&a_empty[slot], (((uint32_t)kbi >> 1) & 1u) ^ 1u);
-            uint8_t* aw = smem + (size_t)slot * 2 * a_bytes;
-            mbar_expect_tx(&a_full[slot], (uint32_t)(2 * a_bytes));
-            if (p.window == 2) {   // [channel group][row][8 channels], no swizzle
-              tma_load_3d(&tmap_ans, &a_full[slot], aw, 0, win_row0, kbi * (p.kb / 8));
-            } else {
-              tma_load_2d(&tmap_a, &a_full[slot], aw, kbi * p.kb, win_row0);
-              tma_load_2d(&tmap_a, &a_full[slot], aw + a_bytes, kbi * p.kb, win_row0 + TC_BM);
-            }
+      int s = 0; uint32_t ph = 0;
+      if (p.window) {                                   // K block outer, tap inner
+        for (int kbi = 0; kbi < p.kblocks; ++kbi) {
+          const int slot = kbi & 1;
+          mbar_wait(&a_empty[slot], (((uint32_t)kbi >> 1) & 1u) ^ 1u);
+          uint8_t* aw = smem + (size_t)slot * 2 * a_bytes;
+          mbar_expect_tx(&a_full[slot], (uint32_t)(2 * a_bytes));
+          if (p.window == 2) {   // [channel group][row][8 channels], no swizzle
+            tma_load_3d(&tmap_ans, &a_full[slot], aw, 0, win_row0, kbi * (p.kb / 8));
+          } else {
+            tma_load_2d(&tmap_a, &a_full[slot], aw, kbi * p.kb, win_row0);
+            tma_load_2d(&tmap_a, &a_full[slot], aw + a_bytes, kbi * p.kb, win_row0 + TC_BM);
           }
-        } else {
-          tap = it / p.kblocks; kbi = it - tap * p.kblocks;
+          for (int tap = 0; tap < p.taps; ++tap) {
+            mbar_wait(&empty[s], ph ^ 1u);
+            uint8_t* st = stage_base + (size_t)s * stage_bytes;
+            mbar_expect_tx(&full[s], (uint32_t)stage_bytes);
+            const int wrow = (phase * p.taps + tap) * p.cout_rows + ntile * p.nt;
+            for (int g = 0; g < p.n_groups; ++g)
+              tma_load_2d(&tmap_b, &full[s], st + g * b_bytes, kbi * p.kb, wrow + p.e[g].row0);
+            if (++s == stages) { s = 0; ph ^= 1u; }
+          }
         }
-        mbar_wait(&empty[s], ph ^ 1u);
-        uint8_t* st = stage_base + (size_t)s * stage_bytes;
-        mbar_expect_tx(&full[s], (uint32_t)stage_bytes);
-        if (!p.window) {
-          tma_load_2d(&tmap_a, &full[s], st, kbi * p.kb, m0 + in_off + tap * p.tap_step);
-          st += a_bytes;
+      } else {
+        for (int tap = 0; tap < p.taps; ++tap) {
+          const int arow = m0 + in_off + tap * p.tap_step;
+          const int wrow = (phase * p.taps + tap) * p.cout_rows + ntile * p.nt;
+          for (int kbi = 0; kbi < p.kblocks; ++kbi) {
+            mbar_wait(&empty[s], ph ^ 1u);
+            uint8_t* st = stage_base + (size_t)s * stage_bytes;
+            mbar_expect_tx(&full[s], (uint32_t)stage_bytes);
+            tma_load_2d(&tmap_a, &full[s], st, p.a_col0 + kbi * p.kb, arow);
+            for (int g = 0; g < p.n_groups; ++g)
+              tma_load_2d(&tmap_b, &full[s], st + a_bytes + g * b_bytes, kbi * p.kb, wrow + p.e[g].row0);
+            if (++s == stages) { s = 0; ph ^= 1u; }
+          }
         }
-        const int wrow = (phase * p.taps + tap) * p.cout_rows + ntile * p.nt;
-        for (int g = 0; g < p.n_groups; ++g)
-          tma_load_2d(&tmap_b, &full[s], st + g * b_bytes, kbi * p.kb, wrow + p.e[g].row0);
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one thread) =====
+    // ===== MMA issuer: warp-uniform control flow, one elected lane issues =====
     const uint32_t idesc = make_idesc(p.nt, p.f16);
-    for (int it = 0; it < n_it; ++it) {
-      const int s = it % stages;
-      const uint32_t ph = (uint32_t)(it / stages) & 1u;
-      int tap = 0, kbi = 0;
+    const int ksteps = p.kb / 16;
+    const uint64_t b_hi = make_smem_desc(0, p.kb);
+    const uint64_t a_hi = p.window == 2 ? make_smem_desc_ns(0, 2 * TC_BM * 16, 128) : b_hi;
+    const uint32_t a_kstep = p.window == 2 ? (uint32_t)(2 * 2 * TC_BM * 16) >> 4 : 2u;   // descriptor units of 16 bytes
+    const uint32_t a_tapstep = (uint32_t)(p.tap_step * (p.window == 2 ? 16 : row_bytes) / 16);   // may be negative
+    const uint32_t stage_lo = smem_u32(stage_base) >> 4, ring_lo = smem_u32(smem) >> 4;
+    const uint32_t stage16 = (uint32_t)stage_bytes >> 4, a16 = (uint32_t)a_bytes >> 4, b16 = (uint32_t)b_bytes >> 4;
+    int s = 0; uint32_t ph = 0;
+    const int outer = p.window ? p.kblocks : p.taps, inner = p.window ? p.taps : p.kblocks;
+    uint32_t first = 1;
+    for (int o = 0; o < outer; ++o) {
+      uint32_t a_lo = 0;
       if (p.window) {
-        kbi = it / p.taps; tap = it - kbi * p.taps;
-        if (tap == 0) mbar_wait(&a_full[kbi & 1], ((uint32_t)kbi >> 1) & 1u);
+        mbar_wait(&a_full[o & 1], ((uint32_t)o >> 1) & 1u);
+        a_lo = ring_lo + (uint32_t)(o & 1) * 2u * a16 +
+               (uint32_t)(-(span < 0 ? span : 0) * (p.window == 2 ? 16 : row_bytes) / 16);
       }
-      mbar_wait(&full[s], ph);
-      tc_fence_after();
-      if (lane == 0) {
-        uint32_t a_addr, b_addr = smem_u32(stage_base + (size_t)s * stage_bytes);
-        if (p.window) {   // tap shift = descriptor start address moved by whole rows inside the swizzled window
-          a_addr = smem_u32(smem + (size_t)(kbi & 1) * 2 * a_bytes) +
-                   (uint32_t)((tap * p.tap_step - (span < 0 ? span : 0)) * row_bytes);
-        } else {
-          a_addr = b_addr;
-          b_addr += a_bytes;
+      for (int i = 0; i < inner; ++i) {
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        uint32_t al = a_lo, bl = stage_lo + (uint32_t)s * stage16;
+        if (!p.window) { al = bl; bl += a16; }
+        if (elect_one()) {
+          for (int g = 0; g < p.n_groups; ++g)
+            for (int k = 0; k < ksteps; ++k)
+              umma_f16(tmem_base + (uint32_t)(g * p.nt), a_hi | (uint64_t)(al + a_kstep * (uint32_t)k),
+                       b_hi | (uint64_t)(bl + (uint32_t)g * b16 + 2u * (uint32_t)k), idesc, (first && k == 0) ? 0u : 1u);
+          umma_commit(&empty[s]);                 // frees the smem slot when these MMAs retire
         }
-        uint64_t a_desc = make_smem_desc(a_addr, p.kb);
-        uint64_t a_kstep = 2;                   // +32 bytes per K=16 step inside the swizzle atom
-        if (p.window == 2) {                    // no-swizzle window: rows 16 B apart, channel groups 2*TC_BM*16 B apart
-          a_addr = smem_u32(smem + (size_t)(kbi & 1) * 2 * a_bytes) +
-                   (uint32_t)((tap * p.tap_step - (span < 0 ? span : 0)) * 16);
-          a_desc = make_smem_desc_ns(a_addr, 2 * TC_BM * 16, 128);
-          a_kstep = (uint64_t)(2 * 2 * TC_BM * 16) >> 4;
-        }
-        const int ksteps = p.kb / 16;
-        for (int g = 0; g < p.n_groups; ++g) {
-          const uint64_t b_desc = make_smem_desc(b_addr + g * b_bytes, p.kb);
-          for (int k = 0; k < ksteps; ++k)
-            umma_f16(tmem_base + (uint32_t)(g * p.nt), a_desc + a_kstep * (uint64_t)k, b_desc + (uint64_t)(2 * k), idesc,
-                     (it > 0 || k > 0) ? 1u : 0u);
-        }
-        umma_commit(&empty[s]);                 // frees the smem slot when these MMAs retire
-        if (p.window && tap == p.taps - 1) umma_commit(&a_empty[kbi & 1]);
-        if (it == n_it - 1) umma_commit(tmem_full);
+        first = 0;
+        a_lo += a_tapstep;
+        if (++s == stages) { s = 0; ph ^= 1u; }
       }
-      __syncwarp();
+      if (p.window && elect_one()) umma_commit(&a_empty[o & 1]);
     }
+    if (elect_one()) umma_commit(tmem_full);
   } else {
     // ===== epilogue: warps 2..5, TMEM lane quarter = warp % 4 =====
     const int quarter = warp & 3;
