@@ -139,7 +139,7 @@ def main():
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--t-lo", type=int, default=80)
     ap.add_argument("--t-hi", type=int, default=120)
-    ap.add_argument("--precision", default=os.environ.get("PIPER_B200_PRECISION", "fp32"))
+    ap.add_argument("--precision", default=os.environ.get("PIPER_B200_PRECISION", "f16"))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -172,7 +172,7 @@ def main():
 
     def step_resident():
         return rt.synthesize_packed(None, lengths, ns, ls, nw, sids, ids_device_ptr=ids_dev.data_ptr(),
-                                    keep_on_device=True)
+                                    keep_on_device=True, profile=True)
 
     def step_e2e():
         return rt.synthesize_packed(ids_pinned.numpy(), lengths, ns, ls, nw, sids, copy=False)
@@ -187,11 +187,17 @@ def main():
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         samples, launches, tm = 0, 0, None
+        cls = {"ms": [0.0] * 3, "flops": [0.0] * 3, "launches": [0] * 3}
         for _ in range(steps):
             r = fn()
             samples += r.total_samples
             tm = rt.last_run_timings
             launches += tm["kernel_launches"]
+            for i in range(3):
+                cls["ms"][i] += tm["class_ms"][i]
+                cls["flops"][i] += tm["class_flops"][i]
+                cls["launches"][i] += tm["class_launches"][i]
+        tm["cls"] = cls
         e1.record(stream)
         barrier()
         ms = e0.elapsed_time(e1)
@@ -224,6 +230,20 @@ def main():
             pass
         peak = peaks.get("bf16_tflops_sustained", 1400.0)
         back_tflops = (tm["dec_flops"] + tm["flow_flops"]) / (tm["decoder_ms"] / 1000.0) / 1e12
+        # dominant tensor-core kernel class by device time inside the timed region (CUDA events around each launch
+        # on the library's stream): 0 conv_tc_kernel, 1 mrf_tc_kernel, 2 conv_f32_kernel
+        names = ["conv_tc_kernel (tcgen05 implicit-GEMM conv: flow, conv_pre, ups, C>=128 resblocks)",
+                 "mrf_tc_kernel (fused HiFi-GAN MRF stage, tcgen05)",
+                 "conv_f32_kernel (fp32 CUDA-core conv: text encoder + duration predictor)"]
+        cls = tm["cls"]
+        tc_classes = [i for i in (0, 1) if cls["launches"][i] > 0]
+        top = max(tc_classes, key=lambda i: cls["ms"][i]) if tc_classes else 2
+        top_tflops = cls["flops"][top] / max(cls["ms"][top], 1e-9) / 1e9
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "dominant_kernel_traffic.json"))).get(str(top))
+        except Exception:
+            pass
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -231,10 +251,19 @@ def main():
             "data": "synthetic", "config": config_dict(args, world),
             "ms_per_utterance": ms / args.steps / args.batch,
             "stage_ms": {k: tm[k] for k in ("front_ms", "flow_ms", "decoder_ms", "h2d_ms", "d2h_ms", "gpu_ms")},
-            "roofline": {"bound": "tensor", "achieved": back_tflops, "peak": peak, "unit": "TFLOP/s",
-                         "frac": back_tflops / peak, "traffic": None,
-                         "kernel": "flow+HiFi-GAN conv kernels (aggregate of the back end, per step)",
-                         "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1.4 PF"},
+            "roofline": {"bound": "tensor", "achieved": top_tflops, "peak": peak, "unit": "TFLOP/s",
+                         "frac": top_tflops / peak, "traffic": traffic, "kernel": names[top],
+                         "launches_per_step": cls["launches"][top] / args.steps,
+                         "avg_launch_ms": cls["ms"][top] / max(cls["launches"][top], 1),
+                         "flops_per_launch": cls["flops"][top] / max(cls["launches"][top], 1),
+                         "share_of_step": cls["ms"][top] / ms,
+                         "peak_source": ("MEASURED_PEAKS.json bf16_tflops_sustained (of measured)" if peaks
+                                         else "fallback 1.4 PF (of fallback)"),
+                         "back_end_aggregate_tflops": back_tflops,
+                         "by_class": {names[i].split(" ")[0]: {"ms_per_step": cls["ms"][i] / args.steps,
+                                                                "tflops": cls["flops"][i] / max(cls["ms"][i], 1e-9) / 1e9,
+                                                                "launches_per_step": cls["launches"][i] / args.steps}
+                                      for i in range(3)}},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": tm_e["h2d_bytes"],
                     "d2h_bytes_per_step": tm_e["d2h_bytes"], "ms_per_step": ms_e / args.steps},
             "gpu_launches": launches, "clocks": sampler.result(),

@@ -56,6 +56,7 @@ extern "C" {
 #define PIPER_B200_FLAG_KEEP_ON_DEVICE 2u  /* leave audio in HBM: result.audio is a device pointer */
 #define PIPER_B200_FLAG_KEEP_STAGES 4u     /* retain stage tensors for piper_b200_get_stage */
 #define PIPER_B200_FLAG_PCM16 8u           /* also produce int16 PCM (WavFileWriter.swift:20-30 rule) */
+#define PIPER_B200_FLAG_PROFILE 16u        /* CUDA events around every GEMM-class kernel launch (PIPER_PROFILE, GraphExecutor.swift:163-175) */
 
 typedef struct piper_b200_ctx piper_b200_ctx;
 
@@ -121,6 +122,11 @@ typedef struct piper_b200_timings {
   int64_t kernel_launches;      /* kernels launched by the call */
   int64_t h2d_bytes, d2h_bytes;
   double dec_flops, flow_flops; /* algorithmic FLOPs executed by the call */
+  /* per kernel class, only with PIPER_B200_FLAG_PROFILE: 0 = conv_tc_kernel (tcgen05 implicit-GEMM conv),
+   * 1 = mrf_tc_kernel (fused generator stage), 2 = conv_f32_kernel (CUDA-core conv) */
+  double class_ms[3];           /* summed device time of the class's launches (CUDA events on the stream) */
+  double class_flops[3];        /* algorithmic FLOPs of those launches */
+  int64_t class_launches[3];
 } piper_b200_timings;
 
 int piper_b200_abi_version(void);

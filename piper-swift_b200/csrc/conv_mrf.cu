@@ -389,6 +389,7 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   const size_t smem = (size_t)2 * win_bytes + (size_t)ring * tap_bytes + 1024 + 3072;
   if (smem > (size_t)TC_SMEM_MAX) throw std::runtime_error("conv_mrf: shared memory budget exceeded");
   const int grid = std::min(p.n_windows, num_sms);
+  ProfScope ps(ex, Prof::MRF, 2.0 * a.R * a.C * a.C * (double)a.total_taps);
   if (a.C == 32) mrf_tc_kernel<32><<<grid, MRF_THREADS, smem, ex.st>>>(tw, p);
   else mrf_tc_kernel<64><<<grid, MRF_THREADS, smem, ex.st>>>(tw, p);
   ++ex.launches;

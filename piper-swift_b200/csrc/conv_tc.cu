@@ -342,6 +342,7 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
   CUtensorMap tans = ta;
   if (p.window == 2) tans = make_map_ns(a.in, (uint64_t)a.cin, (uint64_t)a.R_in, (uint64_t)a.ldin, 2 * TC_BM, w.kb / 8, a.f16);
   dim3 grid((a.Q + TC_BM - 1) / TC_BM, a.n_tiles, w.phases);
+  ProfScope ps(ex, Prof::CONV_TC, 2.0 * a.Q * w.phases * w.taps * w.cin * (double)(a.n_groups * a.nt * a.n_tiles));
   conv_tc_kernel<<<grid, TC_THREADS, smem, ex.st>>>(ta, tb, tans, p, stages);
   ++ex.launches;
 }

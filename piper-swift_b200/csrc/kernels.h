@@ -7,12 +7,46 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cstdint>
+#include <vector>
 
 namespace piper {
+
+// optional per-kernel-class device timing (PIPER_B200_FLAG_PROFILE): CUDA events around every launch of
+// the three GEMM-class kernels, summed after the call's final synchronisation
+struct Prof {
+  enum { CONV_TC = 0, MRF = 1, CONV_F32 = 2, NCLS = 3 };
+  struct Span { cudaEvent_t a, b; int cls; double flops; };
+  std::vector<Span> spans;
+  std::vector<cudaEvent_t> pool;
+  size_t used = 0;
+  cudaEvent_t get() {
+    if (used == pool.size()) {
+      cudaEvent_t e = nullptr;
+      cudaEventCreate(&e);
+      pool.push_back(e);
+    }
+    return pool[used++];
+  }
+  void reset() { used = 0; spans.clear(); }
+  void release() { for (cudaEvent_t e : pool) cudaEventDestroy(e); pool.clear(); reset(); }
+};
 
 struct Exec {
   cudaStream_t st = nullptr;
   int64_t launches = 0;
+  Prof* prof = nullptr;
+};
+
+struct ProfScope {
+  Exec& ex; cudaEvent_t b = nullptr;
+  ProfScope(Exec& e, int cls, double flops) : ex(e) {
+    if (!ex.prof) return;
+    cudaEvent_t a = ex.prof->get();
+    b = ex.prof->get();
+    cudaEventRecord(a, ex.st);
+    ex.prof->spans.push_back({a, b, cls, flops});
+  }
+  ~ProfScope() { if (b) cudaEventRecord(b, ex.st); }
 };
 
 // out[orow][co] = epi( bias[co] + uttbias[utt][co] + sum_{tap,ci} act(in[q+in_off+tap*tap_step][ci]) * w[tap][ci][co] )

@@ -127,6 +127,7 @@ __global__ void __launch_bounds__(256) conv_f32_kernel(ConvArgs a) {
 void launch_conv_f32(Exec& ex, const ConvArgs& a) {
   if (a.Q <= 0) return;
   dim3 grid((a.Q + CBM - 1) / CBM, (a.cout + CBN - 1) / CBN, a.phases);
+  ProfScope ps(ex, Prof::CONV_F32, 2.0 * a.Q * a.phases * a.taps * a.cin * a.cout);
   conv_f32_kernel<<<grid, 256, 0, ex.st>>>(a);
   KLAUNCH(ex);
 }

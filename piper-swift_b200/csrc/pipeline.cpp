@@ -59,6 +59,7 @@ void Context::destroy() {
   cudaSetDevice(device);
   if (stream) cudaStreamSynchronize(stream);
   tc.release();
+  prof.release();
   voice.release();
   front.release();
   back.release();

@@ -100,6 +100,7 @@ struct Context {
   piper_b200_timings timings{};
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   StageDump dump;
+  Prof prof;
   float* d_audio_dense = nullptr;   // inside `back`
 
   int gap_p = 0, gap_f = 0;         // zero rows between utterances (phoneme / frame level)

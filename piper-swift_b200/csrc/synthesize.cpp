@@ -102,6 +102,8 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
     CUDA_OK(cudaSetDevice(device));
     Exec ex;
     ex.st = stream;
+    prof.reset();
+    if (rq.flags & PIPER_B200_FLAG_PROFILE) ex.prof = &prof;
     timings = piper_b200_timings{};
     if (use_tc && (!tc.built || tc.f16 != want_f16)) {
       try {
@@ -375,6 +377,11 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
     timings.d2h_bytes = (int64_t)d2h;
     timings.dec_flops = hp.dec_flops_per_frame * (double)total_frames;
     timings.flow_flops = hp.flow_flops_per_frame * (double)total_frames;
+    for (const Prof::Span& sp : prof.spans) {
+      timings.class_ms[sp.cls] += ms_between(sp.a, sp.b);
+      timings.class_flops[sp.cls] += sp.flops;
+      timings.class_launches[sp.cls] += 1;
+    }
     timings.wall_ms = std::chrono::duration<double, std::milli>(clk::now() - t_wall0).count();
     return PIPER_B200_OK;
   } catch (const std::exception& e) {

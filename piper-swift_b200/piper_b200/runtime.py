@@ -25,7 +25,7 @@ LIB_PATH = os.path.join(os.path.dirname(_HERE), "libpiper_b200.so")
 
 OK = 0
 PRECISION = {"fp32": 0, "bf16": 1, "f16": 2}
-FLAG_IDS_ON_DEVICE, FLAG_KEEP_ON_DEVICE, FLAG_KEEP_STAGES, FLAG_PCM16 = 1, 2, 4, 8
+FLAG_IDS_ON_DEVICE, FLAG_KEEP_ON_DEVICE, FLAG_KEEP_STAGES, FLAG_PCM16, FLAG_PROFILE = 1, 2, 4, 8, 16
 ERR_NAMES = {1: "invalid_argument", 2: "io", 3: "decode", 4: "unsupported", 5: "cuda", 6: "state", 7: "capacity"}
 
 
@@ -62,10 +62,15 @@ class Timings(C.Structure):
     _fields_ = [("wall_ms", C.c_double), ("gpu_ms", C.c_double), ("front_ms", C.c_double),
                 ("flow_ms", C.c_double), ("decoder_ms", C.c_double), ("h2d_ms", C.c_double),
                 ("d2h_ms", C.c_double), ("kernel_launches", C.c_int64), ("h2d_bytes", C.c_int64),
-                ("d2h_bytes", C.c_int64), ("dec_flops", C.c_double), ("flow_flops", C.c_double)]
+                ("d2h_bytes", C.c_int64), ("dec_flops", C.c_double), ("flow_flops", C.c_double),
+                ("class_ms", C.c_double * 3), ("class_flops", C.c_double * 3), ("class_launches", C.c_int64 * 3)]
 
     def as_dict(self):
-        return {k: getattr(self, k) for k, _ in self._fields_}
+        d = {}
+        for k, _ in self._fields_:
+            v = getattr(self, k)
+            d[k] = list(v) if hasattr(v, "__len__") else v
+        return d
 
 
 _lib = None
@@ -246,7 +251,7 @@ class PiperCUDARuntime:
     def synthesize_packed(self, ids: np.ndarray, lengths: np.ndarray, noise_scale=None, length_scale=None,
                           noise_w=None, speaker_ids=None, noise_dp=None, noise_main=None, seed=None,
                           keep_stages=False, pcm16=False, copy=True, ids_device_ptr: Optional[int] = None,
-                          keep_on_device: bool = False) -> BatchResult:
+                          keep_on_device: bool = False, profile: bool = False) -> BatchResult:
         B = int(len(lengths))
         lengths = np.ascontiguousarray(lengths, dtype=np.int64)
         rq = Request()
@@ -284,6 +289,7 @@ class PiperCUDARuntime:
             rq.noise_main_stride = stride
         rq.seed = self.options.seed if seed is None else seed
         rq.flags = ((FLAG_KEEP_STAGES if keep_stages else 0) | (FLAG_PCM16 if pcm16 else 0) |
+                    (FLAG_PROFILE if profile else 0) |
                     (FLAG_IDS_ON_DEVICE if ids_device_ptr is not None else 0) |
                     (FLAG_KEEP_ON_DEVICE if keep_on_device else 0))
         rs = Result()

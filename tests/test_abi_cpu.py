@@ -31,7 +31,7 @@ def test_struct_sizes_match_header():
     # layout guard for the ctypes mirrors (x86-64 / aarch64 LP64)
     assert C.sizeof(runtime.Request) == 80
     assert C.sizeof(runtime.Result) == 56
-    assert C.sizeof(runtime.Timings) == 96
+    assert C.sizeof(runtime.Timings) == 168
     assert C.sizeof(runtime.VoiceInfo) == 80
 
 
