@@ -328,7 +328,8 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
   int stages = TC_STAGES;
   while (stages > 2 && a_ring + stages * stage_bytes + 2048 > TC_SMEM_MAX) --stages;
   // two CTAs per SM (one's epilogue under the other's main loop) beat a deeper pipeline
-  while (stages > 3 && 2 * (a_ring + stages * stage_bytes + 2048) > TC_SMEM_MAX) --stages;
+  static const int min_stages = [] { const char* e = getenv("PIPER_B200_TC_MINSTAGES"); return e ? atoi(e) : 2; }();
+  while (stages > min_stages && 2 * (a_ring + stages * stage_bytes + 2048) > TC_SMEM_MAX) --stages;
   const int n_it = w.taps * p.kblocks;
   if (stages > n_it) stages = n_it < 2 ? 2 : n_it;
   const size_t smem = (size_t)a_ring + (size_t)stages * stage_bytes + 1024 + 256;

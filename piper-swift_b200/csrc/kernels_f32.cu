@@ -124,8 +124,133 @@ __global__ void __launch_bounds__(256) conv_f32_kernel(ConvArgs a) {
   }
 }
 
+// Large-problem variant: 128x128 output tile, 8x8 register micro-tile (as two 4-wide halves 64 apart so that
+// every shared-memory read is a conflict-free 128-bit load), K chunks of 16 double-buffered through shared
+// memory with register prefetch.  The K order (tap, channel) is the same as in conv_f32_kernel, so both
+// kernels produce bit-identical fp32 results.
+constexpr int LBM = 128, LBN = 128, LBK = 16;
+
+__global__ void __launch_bounds__(256, 2) conv_f32_big_kernel(ConvArgs a) {
+  __shared__ __align__(16) float As[2][LBK][LBM];
+  __shared__ __align__(16) float Bs[2][LBK][LBN];
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int q0 = blockIdx.x * LBM;
+  const int n0 = blockIdx.y * LBN;
+  int in_off = a.in_off, out_add = a.out_add;
+  const float* wbase = a.w;
+  if (a.phases > 1) {
+    const int ph = blockIdx.z;
+    out_add = ph;
+    in_off = (ph + a.ct_pad) / a.phases;
+    wbase += (size_t)ph * a.taps * a.cin * a.ldw;
+  }
+  float acc[8][8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+
+  // loaders: A = 128 rows x 16 channels (2 float4 per thread), B = 16 channels x 128 columns (2 float4 per thread)
+  const int arow = tid & 127, akq = tid >> 7;          // akq in {0,1}: float4 index 2*akq, 2*akq+1 of the chunk
+  const int bk = tid >> 5, bn4 = tid & 31;             // bk in 0..7 (and +8)
+  const int kchunks = (a.cin + LBK - 1) / LBK;
+  const int n_it = a.taps * kchunks;
+  float4 pa[2], pb[2];
+  auto fetch = [&](int it) {
+    const int tap = it / kchunks, ci0 = (it - tap * kchunks) * LBK;
+    const int srow = q0 + arow + in_off + tap * a.tap_step;
+    const bool row_ok = (q0 + arow) < a.Q && srow >= 0 && srow < a.R_in;
+    const float* ap = a.in + (size_t)(row_ok ? srow : 0) * a.ldin;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int ci = ci0 + (akq * 2 + h) * 4;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (row_ok && ci < a.cin) v = *reinterpret_cast<const float4*>(ap + ci);
+      if (a.in_act) {
+        v.x = v.x >= 0.f ? v.x : v.x * a.in_slope;
+        v.y = v.y >= 0.f ? v.y : v.y * a.in_slope;
+        v.z = v.z >= 0.f ? v.z : v.z * a.in_slope;
+        v.w = v.w >= 0.f ? v.w : v.w * a.in_slope;
+      }
+      pa[h] = v;
+      const int kk = bk + 8 * h;
+      float4 w4 = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (ci0 + kk < a.cin && n0 + bn4 * 4 < a.ldw)
+        w4 = *reinterpret_cast<const float4*>(wbase + ((size_t)tap * a.cin + ci0 + kk) * a.ldw + n0 + bn4 * 4);
+      pb[h] = w4;
+    }
+  };
+  auto stash = [&](int buf) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int kq = (akq * 2 + h) * 4;
+      As[buf][kq + 0][arow] = pa[h].x;
+      As[buf][kq + 1][arow] = pa[h].y;
+      As[buf][kq + 2][arow] = pa[h].z;
+      As[buf][kq + 3][arow] = pa[h].w;
+      *reinterpret_cast<float4*>(&Bs[buf][bk + 8 * h][bn4 * 4]) = pb[h];
+    }
+  };
+  fetch(0);
+  stash(0);
+  __syncthreads();
+  for (int it = 0; it < n_it; ++it) {
+    const int buf = it & 1;
+    if (it + 1 < n_it) fetch(it + 1);
+#pragma unroll
+    for (int k = 0; k < LBK; ++k) {
+      const float4 a0 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 4]);
+      const float4 a1 = *reinterpret_cast<const float4*>(&As[buf][k][64 + ty * 4]);
+      const float4 b0 = *reinterpret_cast<const float4*>(&Bs[buf][k][tx * 4]);
+      const float4 b1 = *reinterpret_cast<const float4*>(&Bs[buf][k][64 + tx * 4]);
+      const float ar[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+      const float br[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(ar[i], br[j], acc[i][j]);
+    }
+    if (it + 1 < n_it) {
+      stash(buf ^ 1);
+      __syncthreads();
+    }
+  }
+  // epilogue (same semantics as conv_f32_kernel)
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int q = q0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
+    if (q >= a.Q) continue;
+    const int orow = q * a.out_mul + out_add;
+    int utt = 0;
+    if (a.row_utt) utt = a.row_utt[orow / a.valid_div];
+    const bool valid = utt >= 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int co = n0 + (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
+      if (co >= a.cout) continue;
+      float v = acc[i][j];
+      if (a.bias) v += a.bias[co];
+      if (a.uttbias && valid) v += a.uttbias[(size_t)utt * a.ldub + co];
+      if (a.relu) v = fmaxf(v, 0.f);
+      if (a.res) v += a.res[(size_t)orow * a.ldres + co];
+      float* o = a.out + (size_t)orow * a.ldout + co;
+      if (a.accum) v += *o;
+      if (a.div != 0.f) v = v / a.div;
+      *o = valid ? v : 0.f;
+    }
+  }
+}
+
 void launch_conv_f32(Exec& ex, const ConvArgs& a) {
   if (a.Q <= 0) return;
+  if (a.Q >= 4096 && a.cout >= 96 && a.cin % 4 == 0) {
+    dim3 grid((a.Q + LBM - 1) / LBM, (a.cout + LBN - 1) / LBN, a.phases);
+    ProfScope ps(ex, Prof::CONV_F32, 2.0 * a.Q * a.phases * a.taps * a.cin * a.cout);
+    conv_f32_big_kernel<<<grid, 256, 0, ex.st>>>(a);
+    KLAUNCH(ex);
+    return;
+  }
   dim3 grid((a.Q + CBM - 1) / CBM, (a.cout + CBN - 1) / CBN, a.phases);
   ProfScope ps(ex, Prof::CONV_F32, 2.0 * a.Q * a.phases * a.taps * a.cin * a.cout);
   conv_f32_kernel<<<grid, 256, 0, ex.st>>>(a);
