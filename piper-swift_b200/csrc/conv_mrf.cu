@@ -1,19 +1,23 @@
-// Fused MRF stage (see conv_mrf.h).  Persistent kernel, one CTA per SM, 320 threads:
-//   warp 0     : TMA producer - the 16-bit lrelu(x) window ((m+1) boxes of 128 rows, halo included)
-//                and the weight taps (ring of C x C tiles; resident for the whole kernel when they fit)
-//   warp 1     : TMEM allocation + the single thread issuing tcgen05.mma.  conv1 of a resblock
-//                accumulates tile i into D_i (fresh), conv2 accumulates into S_i on top of sum_r y1_r;
-//                tap shifts are descriptor row offsets into the swizzled operand windows
-//   warps 2..9 : two epilogue warpgroups (tiles alternate).  After conv1: y1 = D + x + b1 (fp32),
-//                S += y1 (TMEM read-modify-write), lrelu(y1)*mask -> 16-bit -> swizzled smem operand
-//                of conv2.  After the last resblock: out = (S + sum b2) / nk -> global.
+// Fused MRF stage (see conv_mrf.h).  Persistent kernel, one CTA per SM, 64 + 128*MRF_EG threads:
+//   warp 0      : TMA producer - the 16-bit lrelu(x) window ((m+1)*128 rows, halo included, group-planar
+//                 without swizzle) and the weight taps (ring of C x C tiles; resident when they all fit)
+//   warp 1      : TMEM allocation + the elected thread issuing tcgen05.mma.  conv1 of a resblock
+//                 accumulates tile i into D_i (fresh), conv2 accumulates into S_i on top of sum_r y1_r;
+//                 tap shifts are 16-byte-granular descriptor offsets into the planar operand windows.
+//                 Issue order conv1(0); { conv2(n), conv1(n+1) } so epilogue and MMA overlap
+//   warps 2..   : MRF_EG epilogue warpgroups over (tile, 32-column half) units.  After conv1:
+//                 y1 = D + x + b1 (fp32), S += y1 (TMEM read-modify-write), lrelu(y1)*mask -> 16-bit ->
+//                 planar smem operand of conv2.  After the last resblock: out = (S + sum b2) / nk -> global.
 // A window of W = 128*m rows yields V = W - 2*HALO valid rows (HALO = max_r pad0_r + pad1_r):
 // rows closer than HALO to a window edge see truncated receptive fields and are recomputed by
 // the neighbouring window.
 #include "conv_mrf.h"
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
+#include <string>
+#include <vector>
 
 #include "tc_common.cuh"
 
@@ -24,9 +28,9 @@ using namespace tc;
 namespace {
 
 constexpr int MRF_G = 64;          // guard rows on both sides of the operand windows (>= largest tap shift)
-constexpr int MRF_THREADS = 320;
 constexpr int MRF_MAX_M = 8;
 constexpr int MRF_MAX_RING = 32;
+constexpr uint32_t MRF_TRACE_EVENTS = 4096;
 
 struct MrfParams {
   int R, C, nk, m, V, halo, n_windows;
@@ -41,10 +45,11 @@ struct MrfParams {
   float* out_f32;
   int f16, ring, resident;
   uint32_t tmem_cols;
+  uint32_t* trace;            // debug timeline of CTA 0 (PIPER_B200_MRF_TRACE), else null
 };
 
-template <int C>
-__global__ void __launch_bounds__(MRF_THREADS, 1) mrf_tc_kernel(const __grid_constant__ CUtensorMap tmap_w,
+template <int C, int MRF_EG>   // channels, epilogue warpgroups
+__global__ void __launch_bounds__(64 + 128 * MRF_EG, 1) mrf_tc_kernel(const __grid_constant__ CUtensorMap tmap_w,
                                                                 const MrfParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -73,7 +78,20 @@ __global__ void __launch_bounds__(MRF_THREADS, 1) mrf_tc_kernel(const __grid_con
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_full + MRF_MAX_M);
   float* sbias = reinterpret_cast<float*>(tmem_slot + 4);   // [nk][C] b1 then [C] sum_r b2
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // warp index and TMEM base go through a shuffle so that the compiler can prove them warp-uniform: the
+  // role branches become uniform and the MMA descriptors live in uniform registers (without this every
+  // tcgen05.mma pays for several R2UR moves - measured 100 vs 55 cycles per issue, tools/micro/umma_bench.cu)
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+  // debug timeline: lane 0 of every warp of CTA 0 appends (tag<<24 | n<<8 | i, clock) pairs to its own region
+  uint32_t trace_n = 0;
+  auto TRACE = [&](uint32_t tag, uint32_t n, uint32_t i) {
+    if (p.trace && blockIdx.x == 0 && lane == 0 && trace_n < MRF_TRACE_EVENTS) {
+      uint32_t* t = p.trace + ((size_t)warp * MRF_TRACE_EVENTS + trace_n) * 2;
+      t[0] = (tag << 24) | ((n & 0xFFFFu) << 8) | (i & 0xFFu);
+      t[1] = (uint32_t)clock64();
+      ++trace_n;
+    }
+  };
 
   // zero the conv2 operand window once (its guard rows are never written afterwards)
   for (int i = threadIdx.x; i < win_bytes / 16; i += blockDim.x)
@@ -96,8 +114,8 @@ __global__ void __launch_bounds__(MRF_THREADS, 1) mrf_tc_kernel(const __grid_con
     }
     for (int i = 0; i < m; ++i) {
       mbar_init(&d_full[i], 1);
-      mbar_init(&d_empty[i], 4);
-      mbar_init(&y_ready[i], 4);
+      mbar_init(&d_empty[i], 4 * (C / 32));   // one arrival per epilogue warp of every column half
+      mbar_init(&y_ready[i], 4 * (C / 32));
       mbar_init(&s_full[i], 1);
     }
     fence_barrier_init();
@@ -108,30 +126,59 @@ __global__ void __launch_bounds__(MRF_THREADS, 1) mrf_tc_kernel(const __grid_con
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
   const uint32_t d_col = 0, s_col = (uint32_t)(m * C);
+
+  // Convolution pairs are numbered n = it*nk + r over the windows this CTA owns.  The issue order is
+  //   conv1(0);  then for n = 0,1,..:  conv2(n) and conv1(n+1)
+  // so that the epilogue of pair n+1 never waits for the whole of conv2(n): with resident weights the two
+  // are interleaved tile by tile, with the streamed weight ring conv1(n+1) goes first as a block (it only
+  // needs D_i back from the epilogue of pair n) and conv2(n) follows.  Producer and MMA warp walk the same
+  // sequence, which keeps the single producer thread deadlock-free.
+  const int n_it = p.n_windows > (int)blockIdx.x ? (p.n_windows - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  const uint32_t n_total = (uint32_t)(n_it * p.nk);
 
   if (warp == 0) {
     // ===== TMA producer =====
-    if (lane == 0) {
+    if (lane == 0 && n_it > 0) {
       uint32_t slot = 0, wph = 0;
-      int it = 0;
-      for (int win = blockIdx.x; win < p.n_windows; win += gridDim.x, ++it) {
-        const int w0 = win * p.V - p.halo;
+      auto load_x = [&](int it) {
+        const int w0 = ((int)blockIdx.x + it * (int)gridDim.x) * p.V - p.halo;
+        TRACE(20u, (uint32_t)it, 0u);
         mbar_wait(x_empty, ((uint32_t)it & 1u) ^ 1u);
+        TRACE(21u, (uint32_t)it, 0u);
         mbar_expect_tx(x_full, (uint32_t)win_bytes);
         for (int g = 0; g < NP; ++g)
           bulk_load(X0 + (size_t)g * plane_bytes,
                     p.x_act + ((size_t)g * p.act_rows + (size_t)(p.act_pad + w0 - MRF_G)) * 8, (uint32_t)plane_bytes, x_full);
-        if (!p.resident || it == 0) {
-          for (int r = 0; r < p.nk; ++r)
-            for (int j = 0; j < 2; ++j)
-              for (int t = 0; t < p.k[r]; ++t) {
-                mbar_wait(&w_empty[slot], wph ^ 1u);
-                mbar_expect_tx(&w_full[slot], (uint32_t)tap_bytes);
-                tma_load_2d(&tmap_w, &w_full[slot], WR + (size_t)slot * tap_bytes, 0, (p.tap_base[r][j] + t) * C);
-                if (++slot == (uint32_t)p.ring) { slot = 0; wph ^= 1u; }
-              }
+      };
+      auto load_w = [&](int r, int j) {
+        for (int t = 0; t < p.k[r]; ++t) {
+          mbar_wait(&w_empty[slot], wph ^ 1u);
+          mbar_expect_tx(&w_full[slot], (uint32_t)tap_bytes);
+          tma_load_2d(&tmap_w, &w_full[slot], WR + (size_t)slot * tap_bytes, 0, (p.tap_base[r][j] + t) * C);
+          if (++slot == (uint32_t)p.ring) { slot = 0; wph ^= 1u; }
+        }
+      };
+      load_x(0);
+      if (p.resident) {
+        for (int t = 0; t < p.ring; ++t) {          // ring == total taps: slot t holds tap t for the whole kernel
+          mbar_expect_tx(&w_full[t], (uint32_t)tap_bytes);
+          tma_load_2d(&tmap_w, &w_full[t], WR + (size_t)t * tap_bytes, 0, t * C);
+        }
+        for (int it = 1; it < n_it; ++it) load_x(it);
+      } else {
+        load_w(0, 0);
+        int it = 0, r = 0;
+        for (uint32_t n = 0; n < n_total; ++n) {
+          int it1 = it, r1 = r + 1;
+          if (r1 == p.nk) { r1 = 0; ++it1; }
+          if (n + 1 < n_total) {
+            if (r1 == 0) load_x(it1);
+            load_w(r1, 0);
+          }
+          load_w(r, 1);
+          it = it1; r = r1;
         }
       }
     }
@@ -146,123 +193,179 @@ __global__ void __launch_bounds__(MRF_THREADS, 1) mrf_tc_kernel(const __grid_con
     constexpr uint32_t tap16 = tap_bytes >> 4;
     const uint32_t ring = (uint32_t)p.ring;
     uint32_t slot = 0, wph = 0;      // ring position of the next convolution's first tap (streaming mode)
-    int it = 0;
-    for (int win = blockIdx.x; win < p.n_windows; win += gridDim.x, ++it) {
-      mbar_wait(x_full, (uint32_t)it & 1u);
-      const bool wait_w = !p.resident || it == 0;
-      for (int r = 0; r < p.nk; ++r) {
-        const uint32_t n = (uint32_t)(it * p.nk + r);
-        const int k = p.k[r];
-        for (int j = 0; j < 2; ++j) {
-          const int dil = j ? p.d1[r] : p.d0[r];
-          const uint32_t op_lo = (j ? y1_lo : x0_lo) - (uint32_t)(((k - 1) / 2) * dil);
-          const uint32_t slot0 = p.resident ? (uint32_t)p.tap_base[r][j] : slot;
-          const uint32_t wph0 = wph;
-          uint32_t s_end = slot0, ph_end = wph0;
-          for (int i = 0; i < m; ++i) {
-            if (j == 0) {
-              mbar_wait(&d_empty[i], (n & 1u) ^ 1u);           // epilogue of the previous resblock drained D_i
-            } else {
-              if (i == 0) mbar_wait(&y_ready[0], n & 1u);      // conv2 operand rows of tiles i-1, i, i+1
-              if (i + 1 < m) mbar_wait(&y_ready[i + 1], n & 1u);
-            }
-            tc_fence_after();
-            const uint32_t acc = tmem_base + (j ? s_col : d_col) + (uint32_t)(i * C);
-            uint32_t a_lo = op_lo + (uint32_t)(128 * i);
-            uint32_t s = slot0, ph = wph0;
-            for (int t = 0; t < k; ++t) {
-              if (i == 0 && wait_w) {
-                mbar_wait(&w_full[s], ph);
-                tc_fence_after();
-              }
-              const uint32_t b_lo = wr_lo + s * tap16;
-              if (elect_one()) {
-#pragma unroll
-                for (int ks = 0; ks < KS; ++ks)   // K step of 16 channels = two planes of A, 32 bytes of B
-                  umma_f16(acc, a_hi | (uint64_t)(a_lo + (uint32_t)ks * 2u * plane16), b_hi | (uint64_t)(b_lo + 2u * ks),
-                           idesc, (j == 1 || t > 0 || ks > 0) ? 1u : 0u);
-              }
-              a_lo += (uint32_t)dil;
-              if (++s == ring) { s = 0; ph ^= 1u; }
-            }
-            if (elect_one()) umma_commit(j ? &s_full[i] : &d_full[i]);
-            s_end = s; ph_end = ph;
-          }
-          if (!p.resident) {
-            uint32_t s = slot0;
-            for (int t = 0; t < k; ++t) {
-              if (elect_one()) umma_commit(&w_empty[s]);
-              if (++s == ring) s = 0;
-            }
-            slot = s_end; wph = ph_end;
-          }
-          if (j == 0 && r == p.nk - 1 && elect_one()) umma_commit(x_empty);   // the lrelu(x) window may be refilled
-        }
+    uint32_t s_end = 0, ph_end = 0;
+
+    // one 128-row tile of one convolution: k taps x KS tcgen05 K steps, then the commit for the epilogue
+    auto tile = [&](uint32_t n, int r, int j, int i, uint32_t slot0, uint32_t wph0, bool wait_w) {
+      const int k = p.k[r];
+      const int dil = j ? p.d1[r] : p.d0[r];
+      TRACE(1u + (uint32_t)j * 4u, n, (uint32_t)i);
+      if (j == 0) {
+        mbar_wait(&d_empty[i], (n & 1u) ^ 1u);           // epilogue of the previous pair drained D_i
+      } else {
+        if (i == 0) mbar_wait(&y_ready[0], n & 1u);      // conv2 operand rows of tiles i-1, i, i+1
+        if (i + 1 < m) mbar_wait(&y_ready[i + 1], n & 1u);
       }
+      tc_fence_after();
+      TRACE(2u + (uint32_t)j * 4u, n, (uint32_t)i);
+      const uint32_t acc = tmem_base + (j ? s_col : d_col) + (uint32_t)(i * C);
+      uint32_t a_lo = (j ? y1_lo : x0_lo) - (uint32_t)(((k - 1) / 2) * dil) + (uint32_t)(128 * i);
+      uint32_t s = slot0, ph = wph0;
+      for (int t = 0; t < k; ++t) {
+        if (wait_w) {
+          mbar_wait(&w_full[s], ph);
+          tc_fence_after();
+        }
+        const uint32_t b_lo = wr_lo + s * tap16;
+        if (elect_one()) {
+#pragma unroll
+          for (int ks = 0; ks < KS; ++ks)   // K step of 16 channels = two planes of A, 32 bytes of B
+            umma_f16(acc, a_hi | (uint64_t)(a_lo + (uint32_t)ks * 2u * plane16), b_hi | (uint64_t)(b_lo + 2u * ks),
+                     idesc, (j == 1 || t > 0 || ks > 0) ? 1u : 0u);
+        }
+        a_lo += (uint32_t)dil;
+        if (++s == ring) { s = 0; ph ^= 1u; }
+      }
+      if (elect_one()) umma_commit(j ? &s_full[i] : &d_full[i]);
+      TRACE(3u + (uint32_t)j * 4u, n, (uint32_t)i);
+      s_end = s; ph_end = ph;
+    };
+    // streaming mode: hand the ring slots of a finished convolution back to the producer
+    auto release = [&](int r) {
+      uint32_t s = slot;
+      for (int t = 0; t < p.k[r]; ++t) {
+        if (elect_one()) umma_commit(&w_empty[s]);
+        if (++s == ring) s = 0;
+      }
+      slot = s_end; wph = ph_end;
+    };
+
+    if (n_it > 0) {
+      mbar_wait(x_full, 0u);
+      for (int i = 0; i < m; ++i)
+        tile(0u, 0, 0, i, p.resident ? (uint32_t)p.tap_base[0][0] : slot, p.resident ? 0u : wph, i == 0);
+      if (!p.resident) release(0);
+      if (p.nk == 1 && elect_one()) umma_commit(x_empty);
+    }
+    int it = 0, r = 0;
+    for (uint32_t n = 0; n < n_total; ++n) {
+      int it1 = it, r1 = r + 1;
+      if (r1 == p.nk) { r1 = 0; ++it1; }
+      const bool has_next = n + 1 < n_total;
+      if (has_next && r1 == 0) mbar_wait(x_full, (uint32_t)it1 & 1u);
+      if (p.resident) {
+        for (int i = 0; i < m; ++i) {
+          tile(n, r, 1, i, (uint32_t)p.tap_base[r][1], 0u, it == 0 && i == 0);
+          if (has_next) tile(n + 1u, r1, 0, i, (uint32_t)p.tap_base[r1][0], 0u, it1 == 0 && i == 0);
+        }
+      } else {
+        if (has_next) {
+          for (int i = 0; i < m; ++i) tile(n + 1u, r1, 0, i, slot, wph, i == 0);
+          release(r1);
+        }
+        for (int i = 0; i < m; ++i) tile(n, r, 1, i, slot, wph, i == 0);
+        release(r);
+      }
+      // the lrelu(x) window may be refilled once the last conv1 reading it has been issued
+      if (has_next && r1 == p.nk - 1 && elect_one()) umma_commit(x_empty);
+      it = it1; r = r1;
     }
   } else {
-    // ===== epilogue warpgroups: warps 2..5 (group 0) and 6..9 (group 1) =====
+    // ===== epilogue: MRF_EG groups of four warps.  A unit of work is (tile, 32-column half); group g takes
+    // units g, g + MRF_EG, ...  Every thread owns one row and 32 columns: one 128-byte line of the fp32
+    // residual, two TMEM loads of D, and two planes of the conv2 operand. =====
+    constexpr int HALVES = C / 32;
     const int group = (warp - 2) >> 2;
     const int quarter = warp & 3;                        // TMEM lane quarter this warp may access
     const uint32_t lane_sel = (uint32_t)(quarter * 32) << 16;
     const float inv_nk = 1.0f / (float)p.nk;
-    int it = 0;
-    for (int win = blockIdx.x; win < p.n_windows; win += gridDim.x, ++it) {
-      const int w0 = win * p.V - p.halo;
-      for (int r = 0; r < p.nk; ++r) {
-        const uint32_t n = (uint32_t)(it * p.nk + r);
+    const int units = m * HALVES;
+    uint32_t n = 0;
+    for (int it = 0; it < n_it; ++it) {
+      const int w0 = ((int)blockIdx.x + it * (int)gridDim.x) * p.V - p.halo;
+      for (int r = 0; r < p.nk; ++r, ++n) {
         const float* b1 = sbias + r * C;
-        for (int i = group; i < m; i += 2) {
+        for (int u = group; u < units; u += MRF_EG) {
+          const int i = u / HALVES, cb = (u % HALVES) * 32;
           const int row_in_win = 128 * i + quarter * 32 + lane;
           const int grow = w0 + row_in_win;
           const bool inr = grow >= 0 && grow < p.R;
-          // the fp32 residual row does not depend on the MMAs: fetch it before waiting for them
-          float4 xr[C / 4];
+          // the fp32 residual line and the validity flag do not depend on the MMAs: fetch them before waiting
+          float4 xr[8];
+          int ru = 0;
           if (inr) {
-            const float4* x4 = reinterpret_cast<const float4*>(p.x + (size_t)grow * C);
+            const float4* x4 = reinterpret_cast<const float4*>(p.x + (size_t)grow * C + cb);
 #pragma unroll
-            for (int q4 = 0; q4 < C / 4; ++q4) xr[q4] = x4[q4];
+            for (int q4 = 0; q4 < 8; ++q4) xr[q4] = x4[q4];
+            if (p.row_utt) ru = p.row_utt[grow / p.valid_div];
           } else {
 #pragma unroll
-            for (int q4 = 0; q4 < C / 4; ++q4) xr[q4] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int q4 = 0; q4 < 8; ++q4) xr[q4] = make_float4(0.f, 0.f, 0.f, 0.f);
           }
-          bool valid = inr;
-          if (inr && p.row_utt) valid = p.row_utt[grow / p.valid_div] >= 0;
-          if (n > 0) {   // conv2 of the previous resblock must have finished with S_i and with Y1 rows of tile i
+          TRACE(10u, n, (uint32_t)u);
+          if (n > 0) {   // conv2 of the previous pair must have finished with S_i and with Y1 rows of tiles i-1..i+1
             for (int ii = (i > 0 ? i - 1 : 0); ii <= (i + 1 < m ? i + 1 : m - 1); ++ii)
               mbar_wait(&s_full[ii], (n - 1u) & 1u);
           }
+          TRACE(11u, n, (uint32_t)u);
           mbar_wait(&d_full[i], n & 1u);
           tc_fence_after();
+          TRACE(12u, n, (uint32_t)u);
+          asm volatile("" : "+r"(ru));                   // keep the flag's load in flight across the waits
+          const bool valid = inr && ru >= 0;
           const uint32_t row_off = (uint32_t)((MRF_G + row_in_win) * 16);
+          const uint32_t dcol = tmem_base + lane_sel + d_col + (uint32_t)(i * C + cb);
+          const uint32_t scol = tmem_base + lane_sel + s_col + (uint32_t)(i * C + cb);
+          float d0[16], d1[16];
+          uint32_t t0[16], t1[16], t2[16], t3[16];
+          __syncwarp();
+          tmem_ld16_async(dcol, t0);
+          tmem_ld16_async(dcol + 16u, t1);
+          if (r > 0) {
+            tmem_ld16_async(scol, t2);
+            tmem_ld16_async(scol + 16u, t3);
+          }
+          tmem_wait_ld();
 #pragma unroll
-          for (int c0 = 0; c0 < C; c0 += 16) {
-            float d[16], s[16];
-            __syncwarp();
-            tmem_ld16(tmem_base + lane_sel + d_col + (uint32_t)(i * C + c0), d);
+          for (int e = 0; e < 16; ++e) { d0[e] = __uint_as_float(t0[e]); d1[e] = __uint_as_float(t1[e]); }
+          if (r > 0) {
+            float s0[16], s1[16];
 #pragma unroll
-            for (int e = 0; e < 16; ++e) d[e] += b1[c0 + e];
+            for (int e = 0; e < 16; ++e) { s0[e] = __uint_as_float(t2[e]); s1[e] = __uint_as_float(t3[e]); }
+#pragma unroll
+            for (int e = 0; e < 16; ++e) { d0[e] += b1[cb + e]; d1[e] += b1[cb + 16 + e]; }
 #pragma unroll
             for (int q4 = 0; q4 < 4; ++q4) {
-              const float4 xv = xr[c0 / 4 + q4];
-              d[4 * q4] += xv.x; d[4 * q4 + 1] += xv.y; d[4 * q4 + 2] += xv.z; d[4 * q4 + 3] += xv.w;
+              const float4 xa = xr[q4], xb = xr[4 + q4];
+              d0[4 * q4] += xa.x; d0[4 * q4 + 1] += xa.y; d0[4 * q4 + 2] += xa.z; d0[4 * q4 + 3] += xa.w;
+              d1[4 * q4] += xb.x; d1[4 * q4 + 1] += xb.y; d1[4 * q4 + 2] += xb.z; d1[4 * q4 + 3] += xb.w;
             }
-            if (r > 0) {
-              tmem_ld16(tmem_base + lane_sel + s_col + (uint32_t)(i * C + c0), s);
 #pragma unroll
-              for (int e = 0; e < 16; ++e) s[e] += d[e];
-              tmem_st16(tmem_base + lane_sel + s_col + (uint32_t)(i * C + c0), s);
-            } else {
-              tmem_st16(tmem_base + lane_sel + s_col + (uint32_t)(i * C + c0), d);
+            for (int e = 0; e < 16; ++e) { s0[e] += d0[e]; s1[e] += d1[e]; }
+            tmem_st16(scol, s0);
+            tmem_st16(scol + 16u, s1);
+          } else {
+#pragma unroll
+            for (int e = 0; e < 16; ++e) { d0[e] += b1[cb + e]; d1[e] += b1[cb + 16 + e]; }
+#pragma unroll
+            for (int q4 = 0; q4 < 4; ++q4) {
+              const float4 xa = xr[q4], xb = xr[4 + q4];
+              d0[4 * q4] += xa.x; d0[4 * q4 + 1] += xa.y; d0[4 * q4 + 2] += xa.z; d0[4 * q4 + 3] += xa.w;
+              d1[4 * q4] += xb.x; d1[4 * q4 + 1] += xb.y; d1[4 * q4 + 2] += xb.z; d1[4 * q4 + 3] += xb.w;
             }
-            uint32_t pk[8];
-#pragma unroll
-            for (int e = 0; e < 8; ++e)
-              pk[e] = valid ? pack2(lrelu(d[2 * e], 0.1f), lrelu(d[2 * e + 1], 0.1f), p.f16) : 0u;
-            uint8_t* y = Y1 + (size_t)(c0 >> 3) * plane_bytes + row_off;   // planes c0/8 and c0/8 + 1
-            *reinterpret_cast<uint4*>(y) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-            *reinterpret_cast<uint4*>(y + plane_bytes) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+            tmem_st16(scol, d0);
+            tmem_st16(scol + 16u, d1);
           }
+          uint32_t pk[16];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            pk[e] = valid ? pack2(lrelu(d0[2 * e], 0.1f), lrelu(d0[2 * e + 1], 0.1f), p.f16) : 0u;
+            pk[8 + e] = valid ? pack2(lrelu(d1[2 * e], 0.1f), lrelu(d1[2 * e + 1], 0.1f), p.f16) : 0u;
+          }
+          uint8_t* y = Y1 + (size_t)(cb >> 3) * plane_bytes + row_off;   // planes cb/8 .. cb/8 + 3
+#pragma unroll
+          for (int g = 0; g < 4; ++g)
+            *reinterpret_cast<uint4*>(y + (size_t)g * plane_bytes) = make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
           tmem_wait_st();
           fence_proxy_async();
           tc_fence_before();
@@ -271,43 +374,64 @@ __global__ void __launch_bounds__(MRF_THREADS, 1) mrf_tc_kernel(const __grid_con
             mbar_arrive(&y_ready[i]);
             mbar_arrive(&d_empty[i]);
           }
+          TRACE(13u, n, (uint32_t)u);
         }
       }
       // ---- stage output: (S + sum_r b2_r) / nk over the window's valid rows ----
-      const uint32_t nl = (uint32_t)(it * p.nk + p.nk - 1);
+      const uint32_t nl = n - 1u;
       const float* b2s = sbias + p.nk * C;
-      for (int i = group; i < m; i += 2) {
-        mbar_wait(&s_full[i], nl & 1u);
-        tc_fence_after();
+      for (int u = group; u < units; u += MRF_EG) {
+        const int i = u / HALVES, cb = (u % HALVES) * 32;
         const int row_in_win = 128 * i + quarter * 32 + lane;
         const int grow = w0 + row_in_win;
         const bool owned = row_in_win >= p.halo && row_in_win < p.halo + p.V && grow >= 0 && grow < p.R;
-        bool valid = owned;
-        if (owned && p.row_utt) valid = p.row_utt[grow / p.valid_div] >= 0;
-#pragma unroll
-        for (int c0 = 0; c0 < C; c0 += 16) {
-          float s[16];
+        int ru = 0;
+        if (owned && p.row_utt) ru = p.row_utt[grow / p.valid_div];
+        TRACE(14u, nl, (uint32_t)u);
+        mbar_wait(&s_full[i], nl & 1u);
+        tc_fence_after();
+        TRACE(15u, nl, (uint32_t)u);
+        asm volatile("" : "+r"(ru));
+        const bool valid = owned && ru >= 0;
+        const uint32_t scol = tmem_base + lane_sel + s_col + (uint32_t)(i * C + cb);
+        float s0[16], s1[16];
+        {
+          uint32_t t0[16], t1[16];
           __syncwarp();
-          tmem_ld16(tmem_base + lane_sel + s_col + (uint32_t)(i * C + c0), s);
-          if (owned) {
+          tmem_ld16_async(scol, t0);
+          tmem_ld16_async(scol + 16u, t1);
+          tmem_wait_ld();
 #pragma unroll
-            for (int e = 0; e < 16; ++e) s[e] = valid ? (s[e] + b2s[c0 + e]) * inv_nk : 0.f;
-            if (p.out_f32) {
-              float4* o4 = reinterpret_cast<float4*>(p.out_f32 + (size_t)grow * C + c0);
+          for (int e = 0; e < 16; ++e) { s0[e] = __uint_as_float(t0[e]); s1[e] = __uint_as_float(t1[e]); }
+        }
+        if (owned) {
 #pragma unroll
-              for (int q4 = 0; q4 < 4; ++q4) o4[q4] = make_float4(s[4 * q4], s[4 * q4 + 1], s[4 * q4 + 2], s[4 * q4 + 3]);
+          for (int e = 0; e < 16; ++e) {
+            s0[e] = valid ? (s0[e] + b2s[cb + e]) * inv_nk : 0.f;
+            s1[e] = valid ? (s1[e] + b2s[cb + 16 + e]) * inv_nk : 0.f;
+          }
+          if (p.out_f32) {
+            float4* o4 = reinterpret_cast<float4*>(p.out_f32 + (size_t)grow * C + cb);
+#pragma unroll
+            for (int q4 = 0; q4 < 4; ++q4) {
+              o4[q4] = make_float4(s0[4 * q4], s0[4 * q4 + 1], s0[4 * q4 + 2], s0[4 * q4 + 3]);
+              o4[4 + q4] = make_float4(s1[4 * q4], s1[4 * q4 + 1], s1[4 * q4 + 2], s1[4 * q4 + 3]);
             }
-            if (p.out_act) {
-              uint32_t pk[8];
+          }
+          if (p.out_act) {
+            uint32_t pk[16];
 #pragma unroll
-              for (int e = 0; e < 8; ++e) pk[e] = pack2(lrelu(s[2 * e], p.act_slope), lrelu(s[2 * e + 1], p.act_slope), p.f16);
-              uint4* dst = reinterpret_cast<uint4*>(static_cast<uint16_t*>(p.out_act) + (size_t)grow * C + c0);
-              dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-              dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+            for (int e = 0; e < 8; ++e) {
+              pk[e] = pack2(lrelu(s0[2 * e], p.act_slope), lrelu(s0[2 * e + 1], p.act_slope), p.f16);
+              pk[8 + e] = pack2(lrelu(s1[2 * e], p.act_slope), lrelu(s1[2 * e + 1], p.act_slope), p.f16);
             }
+            uint4* dst = reinterpret_cast<uint4*>(static_cast<uint16_t*>(p.out_act) + (size_t)grow * C + cb);
+#pragma unroll
+            for (int g = 0; g < 4; ++g) dst[g] = make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
           }
         }
         tc_fence_before();
+        TRACE(16u, nl, (uint32_t)u);
       }
     }
   }
@@ -341,8 +465,12 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
     cudaGetDevice(&dev);
     if (cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || num_sms <= 0)
       throw std::runtime_error("cuda: cannot query the SM count");
-    if (cudaFuncSetAttribute(mrf_tc_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
-        cudaFuncSetAttribute(mrf_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess)
+    if (cudaFuncSetAttribute(mrf_tc_kernel<32, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
+        cudaFuncSetAttribute(mrf_tc_kernel<64, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
+        cudaFuncSetAttribute(mrf_tc_kernel<32, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
+        cudaFuncSetAttribute(mrf_tc_kernel<64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
+        cudaFuncSetAttribute(mrf_tc_kernel<32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
+        cudaFuncSetAttribute(mrf_tc_kernel<64, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess)
       throw std::runtime_error("cuda: cannot raise dynamic shared memory limit for mrf_tc_kernel");
   }
   MrfParams p{};
@@ -390,9 +518,41 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   if (smem > (size_t)TC_SMEM_MAX) throw std::runtime_error("conv_mrf: shared memory budget exceeded");
   const int grid = std::min(p.n_windows, num_sms);
   ProfScope ps(ex, Prof::MRF, 2.0 * a.R * a.C * a.C * (double)a.total_taps);
-  if (a.C == 32) mrf_tc_kernel<32><<<grid, MRF_THREADS, smem, ex.st>>>(tw, p);
-  else mrf_tc_kernel<64><<<grid, MRF_THREADS, smem, ex.st>>>(tw, p);
+  static const char* trace_path = getenv("PIPER_B200_MRF_TRACE");
+  const size_t trace_words = (size_t)(64 + 128 * 4) / 32 * MRF_TRACE_EVENTS * 2;
+  if (trace_path) {
+    if (cudaMalloc(&p.trace, trace_words * 4) != cudaSuccess) throw std::runtime_error("conv_mrf: trace buffer");
+    cudaMemsetAsync(p.trace, 0, trace_words * 4, ex.st);
+  }
+  static const int eg_env = [] { const char* e = getenv("PIPER_B200_MRF_EG"); return e ? atoi(e) : 0; }();
+  const int eg = eg_env >= 2 && eg_env <= 4 ? eg_env : 3;
+  const int threads = 64 + 128 * eg;
+  if (a.C == 32) {
+    if (eg == 2) mrf_tc_kernel<32, 2><<<grid, threads, smem, ex.st>>>(tw, p);
+    else if (eg == 3) mrf_tc_kernel<32, 3><<<grid, threads, smem, ex.st>>>(tw, p);
+    else mrf_tc_kernel<32, 4><<<grid, threads, smem, ex.st>>>(tw, p);
+  } else {
+    if (eg == 2) mrf_tc_kernel<64, 2><<<grid, threads, smem, ex.st>>>(tw, p);
+    else if (eg == 3) mrf_tc_kernel<64, 3><<<grid, threads, smem, ex.st>>>(tw, p);
+    else mrf_tc_kernel<64, 4><<<grid, threads, smem, ex.st>>>(tw, p);
+  }
   ++ex.launches;
+  if (trace_path) {   // debug only: dump "C m warp tag n i clock" lines, one file per stage width
+    std::vector<uint32_t> h(trace_words);
+    cudaStreamSynchronize(ex.st);
+    cudaMemcpy(h.data(), p.trace, trace_words * 4, cudaMemcpyDeviceToHost);
+    cudaFree(p.trace);
+    const std::string fn = std::string(trace_path) + "." + std::to_string(a.C);
+    if (FILE* f = fopen(fn.c_str(), "w")) {
+      for (size_t w = 0; w < trace_words / 2 / MRF_TRACE_EVENTS; ++w)
+        for (size_t e = 0; e < MRF_TRACE_EVENTS; ++e) {
+          const uint32_t a0 = h[(w * MRF_TRACE_EVENTS + e) * 2], c = h[(w * MRF_TRACE_EVENTS + e) * 2 + 1];
+          if (!a0) break;
+          fprintf(f, "%d %d %zu %u %u %u %u\n", a.C, p.m, w, a0 >> 24, (a0 >> 8) & 0xFFFFu, a0 & 0xFFu, c);
+        }
+      fclose(f);
+    }
+  }
 }
 
 }  // namespace piper

@@ -62,7 +62,10 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
   uint64_t* tmem_full = a_empty + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // warp index and TMEM base go through a shuffle so that the compiler can prove them warp-uniform: the
+  // role branches become uniform and the MMA descriptors live in uniform registers (without this every
+  // tcgen05.mma pays for several R2UR moves - measured 100 vs 55 cycles per issue, tools/micro/umma_bench.cu)
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const int m0 = blockIdx.x * TC_BM;
   const int ntile = blockIdx.y;
   const int phase = blockIdx.z;
@@ -91,7 +94,7 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
   if (warp == 0) {
     // ===== TMA producer =====

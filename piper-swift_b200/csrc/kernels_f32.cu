@@ -128,15 +128,17 @@ __global__ void __launch_bounds__(256) conv_f32_kernel(ConvArgs a) {
 // every shared-memory read is a conflict-free 128-bit load), K chunks of 16 double-buffered through shared
 // memory with register prefetch.  The K order (tap, channel) is the same as in conv_f32_kernel, so both
 // kernels produce bit-identical fp32 results.
-constexpr int LBM = 128, LBN = 128, LBK = 16;
+constexpr int LBM = 128, LBK = 16;
 
+template <int BN>   // 128 or 64 output columns per CTA
 __global__ void __launch_bounds__(256, 2) conv_f32_big_kernel(ConvArgs a) {
+  constexpr int NJ = BN / 16;                          // columns per thread (8 or 4)
   __shared__ __align__(16) float As[2][LBK][LBM];
-  __shared__ __align__(16) float Bs[2][LBK][LBN];
+  __shared__ __align__(16) float Bs[2][LBK][BN];
   const int tid = threadIdx.x;
   const int tx = tid & 15, ty = tid >> 4;
   const int q0 = blockIdx.x * LBM;
-  const int n0 = blockIdx.y * LBN;
+  const int n0 = blockIdx.y * BN;
   int in_off = a.in_off, out_add = a.out_add;
   const float* wbase = a.w;
   if (a.phases > 1) {
@@ -145,18 +147,20 @@ __global__ void __launch_bounds__(256, 2) conv_f32_big_kernel(ConvArgs a) {
     in_off = (ph + a.ct_pad) / a.phases;
     wbase += (size_t)ph * a.taps * a.cin * a.ldw;
   }
-  float acc[8][8];
+  float acc[8][NJ];
 #pragma unroll
   for (int i = 0; i < 8; ++i)
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+    for (int j = 0; j < NJ; ++j) acc[i][j] = 0.f;
 
-  // loaders: A = 128 rows x 16 channels (2 float4 per thread), B = 16 channels x 128 columns (2 float4 per thread)
+  // loaders: A = 128 rows x 16 channels (2 float4 per thread), B = 16 channels x BN columns
   const int arow = tid & 127, akq = tid >> 7;          // akq in {0,1}: float4 index 2*akq, 2*akq+1 of the chunk
-  const int bk = tid >> 5, bn4 = tid & 31;             // bk in 0..7 (and +8)
+  constexpr int BN4 = BN / 4;                          // float4 per B row
+  constexpr int BH = BN == 128 ? 2 : 1;                // B float4 per thread
+  const int bk = tid / BN4, bn4 = tid % BN4;
   const int kchunks = (a.cin + LBK - 1) / LBK;
   const int n_it = a.taps * kchunks;
-  float4 pa[2], pb[2];
+  float4 pa[2], pb[BH];
   auto fetch = [&](int it) {
     const int tap = it / kchunks, ci0 = (it - tap * kchunks) * LBK;
     const int srow = q0 + arow + in_off + tap * a.tap_step;
@@ -174,7 +178,10 @@ __global__ void __launch_bounds__(256, 2) conv_f32_big_kernel(ConvArgs a) {
         v.w = v.w >= 0.f ? v.w : v.w * a.in_slope;
       }
       pa[h] = v;
-      const int kk = bk + 8 * h;
+    }
+#pragma unroll
+    for (int h = 0; h < BH; ++h) {
+      const int kk = bk + (256 / BN4) * h;
       float4 w4 = make_float4(0.f, 0.f, 0.f, 0.f);
       if (ci0 + kk < a.cin && n0 + bn4 * 4 < a.ldw)
         w4 = *reinterpret_cast<const float4*>(wbase + ((size_t)tap * a.cin + ci0 + kk) * a.ldw + n0 + bn4 * 4);
@@ -189,8 +196,9 @@ __global__ void __launch_bounds__(256, 2) conv_f32_big_kernel(ConvArgs a) {
       As[buf][kq + 1][arow] = pa[h].y;
       As[buf][kq + 2][arow] = pa[h].z;
       As[buf][kq + 3][arow] = pa[h].w;
-      *reinterpret_cast<float4*>(&Bs[buf][bk + 8 * h][bn4 * 4]) = pb[h];
     }
+#pragma unroll
+    for (int h = 0; h < BH; ++h) *reinterpret_cast<float4*>(&Bs[buf][bk + (256 / BN4) * h][bn4 * 4]) = pb[h];
   };
   fetch(0);
   stash(0);
@@ -202,14 +210,18 @@ __global__ void __launch_bounds__(256, 2) conv_f32_big_kernel(ConvArgs a) {
     for (int k = 0; k < LBK; ++k) {
       const float4 a0 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 4]);
       const float4 a1 = *reinterpret_cast<const float4*>(&As[buf][k][64 + ty * 4]);
-      const float4 b0 = *reinterpret_cast<const float4*>(&Bs[buf][k][tx * 4]);
-      const float4 b1 = *reinterpret_cast<const float4*>(&Bs[buf][k][64 + tx * 4]);
       const float ar[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-      const float br[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+      float br[NJ];
+      const float4 b0 = *reinterpret_cast<const float4*>(&Bs[buf][k][tx * 4]);
+      br[0] = b0.x; br[1] = b0.y; br[2] = b0.z; br[3] = b0.w;
+      if (NJ == 8) {
+        const float4 b1 = *reinterpret_cast<const float4*>(&Bs[buf][k][(BN / 2) + tx * 4]);
+        br[NJ - 4] = b1.x; br[NJ - 3] = b1.y; br[NJ - 2] = b1.z; br[NJ - 1] = b1.w;
+      }
 #pragma unroll
       for (int i = 0; i < 8; ++i)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(ar[i], br[j], acc[i][j]);
+        for (int j = 0; j < NJ; ++j) acc[i][j] = fmaf(ar[i], br[j], acc[i][j]);
     }
     if (it + 1 < n_it) {
       stash(buf ^ 1);
@@ -226,8 +238,8 @@ __global__ void __launch_bounds__(256, 2) conv_f32_big_kernel(ConvArgs a) {
     if (a.row_utt) utt = a.row_utt[orow / a.valid_div];
     const bool valid = utt >= 0;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int co = n0 + (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
+    for (int j = 0; j < NJ; ++j) {
+      const int co = n0 + (j < 4 ? tx * 4 + j : (BN / 2) + tx * 4 + (j - 4));
       if (co >= a.cout) continue;
       float v = acc[i][j];
       if (a.bias) v += a.bias[co];
@@ -245,9 +257,12 @@ __global__ void __launch_bounds__(256, 2) conv_f32_big_kernel(ConvArgs a) {
 void launch_conv_f32(Exec& ex, const ConvArgs& a) {
   if (a.Q <= 0) return;
   if (a.Q >= 4096 && a.cout >= 96 && a.cin % 4 == 0) {
-    dim3 grid((a.Q + LBM - 1) / LBM, (a.cout + LBN - 1) / LBN, a.phases);
+    const bool wide = a.cout > 64;   // measured: the 128-wide tile wins even for cout = 192 (half-empty second tile)
+    const int bn = wide ? 128 : 64;
+    dim3 grid((a.Q + LBM - 1) / LBM, (a.cout + bn - 1) / bn, a.phases);
     ProfScope ps(ex, Prof::CONV_F32, 2.0 * a.Q * a.phases * a.taps * a.cin * a.cout);
-    conv_f32_big_kernel<<<grid, 256, 0, ex.st>>>(a);
+    if (wide) conv_f32_big_kernel<128><<<grid, 256, 0, ex.st>>>(a);
+    else conv_f32_big_kernel<64><<<grid, 256, 0, ex.st>>>(a);
     KLAUNCH(ex);
     return;
   }
