@@ -285,7 +285,7 @@ float* run_back_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep) 
       a.Q = R; a.tap_step = -1; a.out_mul = s.stride;
       a.n_groups = 1; a.nt = pick_nt(C); a.n_tiles = C / a.nt;
       a.e[0].bias = ts.up.bias;
-      a.e[0].out_f32 = xu; a.e[0].ld_f32 = C;
+      a.e[0].out_f32 = use_mrf ? nullptr : xu; a.e[0].ld_f32 = C;   // the fused stage takes its residual from the 16-bit copy
       a.e[0].out_act = xub; a.e[0].ld_act = C; a.e[0].act_slope = 0.1f;
       if (use_mrf) { a.e[0].act_planar = 1; a.e[0].act_rows = act_rows; a.e[0].act_pad = act_pad; }
       a.row_utt = in.frow_utt; a.valid_div = U;
@@ -302,7 +302,7 @@ float* run_back_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep) 
         a.b1[j] = s.rbs[j].c1[0].b; a.b2[j] = s.rbs[j].c1[1].b;
       }
       a.w = ts.mrf_w; a.total_taps = ts.mrf_taps;
-      a.x = xu; a.x_act = xub; a.act_rows = act_rows; a.act_pad = act_pad;
+      a.x_act = xub; a.act_rows = act_rows; a.act_pad = act_pad;
       a.row_utt = in.frow_utt; a.valid_div = U;
       if (last_stage) a.out_f32 = xs;
       else { a.out_act = xsb; a.act_slope = 0.1f; }

@@ -1,11 +1,10 @@
-// Fused MRF stage (see conv_mrf.h).  Persistent kernel, one CTA per SM, 64 + 128*MRF_EG threads:
+// Fused MRF stage (see conv_mrf.h).  Persistent kernel, one CTA per SM, 96 + 128*MRF_EG threads:
 //   warp 0      : TMA producer - the 16-bit lrelu(x) window ((m+1)*128 rows, halo included, group-planar
 //                 without swizzle) and the weight taps (ring of C x C tiles; resident when they all fit)
-//   warp 1      : TMEM allocation + the elected thread issuing tcgen05.mma.  conv1 of a resblock
-//                 accumulates tile i into D_i (fresh), conv2 accumulates into S_i on top of sum_r y1_r;
-//                 tap shifts are 16-byte-granular descriptor offsets into the planar operand windows.
-//                 Issue order conv1(0); { conv2(n), conv1(n+1) } so epilogue and MMA overlap
-//   warps 2..   : MRF_EG epilogue warpgroups over (tile, 32-column half) units.  After conv1:
+//   warps 1, 2 : tcgen05.mma issuers (warp 1 also owns the TMEM allocation).  Warp 1 issues conv1 of every
+//                 resblock (tile i into D_i, fresh), warp 2 issues conv2 (accumulating into S_i on top of
+//                 sum_r y1_r); tap shifts are 16-byte-granular descriptor offsets into the planar windows
+//   warps 3..   : MRF_EG epilogue warpgroups over (tile, 32-column half) units.  After conv1:
 //                 y1 = D + x + b1 (fp32), S += y1 (TMEM read-modify-write), lrelu(y1)*mask -> 16-bit ->
 //                 planar smem operand of conv2.  After the last resblock: out = (S + sum b2) / nk -> global.
 // A window of W = 128*m rows yields V = W - 2*HALO valid rows (HALO = max_r pad0_r + pad1_r):
@@ -38,7 +37,6 @@ struct MrfParams {
   int tap_base[MRF_MAX_RB][2];
   const float* b1[MRF_MAX_RB];
   const float* b2[MRF_MAX_RB];
-  const float* x;
   const uint16_t* x_act; int64_t act_rows; int act_pad;   // group-planar 16-bit lrelu(x): [C/8][act_rows][8]
   const int* row_utt; int valid_div;
   void* out_act; float act_slope;
@@ -49,7 +47,7 @@ struct MrfParams {
 };
 
 template <int C, int MRF_EG>   // channels, epilogue warpgroups
-__global__ void __launch_bounds__(64 + 128 * MRF_EG, 1) mrf_tc_kernel(const __grid_constant__ CUtensorMap tmap_w,
+__global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __grid_constant__ CUtensorMap tmap_w,
                                                                 const MrfParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -107,7 +105,7 @@ __global__ void __launch_bounds__(64 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_w);
     mbar_init(x_full, 1);
-    mbar_init(x_empty, 1);
+    mbar_init(x_empty, 1 + 4 * MRF_EG);   // the last conv1's commit + every epilogue warp (they read the residual from X0)
     for (int s = 0; s < p.ring; ++s) {
       mbar_init(&w_full[s], 1);
       mbar_init(&w_empty[s], 1);
@@ -182,8 +180,8 @@ __global__ void __launch_bounds__(64 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
         }
       }
     }
-  } else if (warp == 1) {
-    // ===== MMA issuer: the whole warp runs the (warp-uniform) control flow, one elected lane issues =====
+  } else if (warp == 1 || warp == 2) {
+    // ===== MMA issuers: the whole warp runs the (warp-uniform) control flow, one elected lane issues =====
     const uint32_t idesc = make_idesc(C, p.f16);
     const uint32_t plane16 = (uint32_t)plane_bytes >> 4;                 // descriptor address units are 16 bytes:
     const uint64_t a_hi = make_smem_desc_ns(0, (uint32_t)plane_bytes, 128);   // one operand row = one unit
@@ -192,90 +190,97 @@ __global__ void __launch_bounds__(64 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
     const uint32_t wr_lo = smem_u32(WR) >> 4;
     constexpr uint32_t tap16 = tap_bytes >> 4;
     const uint32_t ring = (uint32_t)p.ring;
-    uint32_t slot = 0, wph = 0;      // ring position of the next convolution's first tap (streaming mode)
-    uint32_t s_end = 0, ph_end = 0;
+    // warp 1 issues every conv1, warp 2 every conv2: the two streams only meet through the epilogue's
+    // barriers, and one warp alone cannot issue the small N = C MMAs fast enough (tools/micro/umma_bench.cu).
+    // In streaming mode both walk the producer's ring order  c1(0); { c1(n+1), c2(n) }  and skip the
+    // other stream's slots.
+    const int J = warp - 1;
+    uint32_t slot = 0, wph = 0;      // ring position of the next convolution in ring order (streaming mode)
+    auto skip = [&](int k) {         // advance over a convolution of the other stream
+      slot += (uint32_t)k;
+      if (slot >= ring) { slot -= ring; wph ^= 1u; }
+    };
 
-    // one 128-row tile of one convolution: k taps x KS tcgen05 K steps, then the commit for the epilogue
-    auto tile = [&](uint32_t n, int r, int j, int i, uint32_t slot0, uint32_t wph0, bool wait_w) {
+    // one convolution over all tiles: per tile k taps x KS tcgen05 K steps, then the commit for the epilogue
+    auto conv = [&](uint32_t n, int r, int j, bool first_use) {
       const int k = p.k[r];
       const int dil = j ? p.d1[r] : p.d0[r];
-      TRACE(1u + (uint32_t)j * 4u, n, (uint32_t)i);
-      if (j == 0) {
-        mbar_wait(&d_empty[i], (n & 1u) ^ 1u);           // epilogue of the previous pair drained D_i
-      } else {
-        if (i == 0) mbar_wait(&y_ready[0], n & 1u);      // conv2 operand rows of tiles i-1, i, i+1
-        if (i + 1 < m) mbar_wait(&y_ready[i + 1], n & 1u);
-      }
-      tc_fence_after();
-      TRACE(2u + (uint32_t)j * 4u, n, (uint32_t)i);
-      const uint32_t acc = tmem_base + (j ? s_col : d_col) + (uint32_t)(i * C);
-      uint32_t a_lo = (j ? y1_lo : x0_lo) - (uint32_t)(((k - 1) / 2) * dil) + (uint32_t)(128 * i);
-      uint32_t s = slot0, ph = wph0;
-      for (int t = 0; t < k; ++t) {
-        if (wait_w) {
-          mbar_wait(&w_full[s], ph);
-          tc_fence_after();
+      const uint32_t slot0 = p.resident ? (uint32_t)p.tap_base[r][j] : slot;
+      const uint32_t wph0 = p.resident ? 0u : wph;
+      for (int i = 0; i < m; ++i) {
+        TRACE(1u + (uint32_t)j * 4u, n, (uint32_t)i);
+        if (j == 0) {
+          mbar_wait(&d_empty[i], (n & 1u) ^ 1u);           // epilogue of the previous pair drained D_i
+        } else {
+          if (i == 0) mbar_wait(&y_ready[0], n & 1u);      // conv2 operand rows of tiles i-1, i, i+1
+          if (i + 1 < m) mbar_wait(&y_ready[i + 1], n & 1u);
         }
-        const uint32_t b_lo = wr_lo + s * tap16;
-        if (elect_one()) {
+        tc_fence_after();
+        TRACE(2u + (uint32_t)j * 4u, n, (uint32_t)i);
+        const uint32_t acc = tmem_base + (j ? s_col : d_col) + (uint32_t)(i * C);
+        uint32_t a_lo = (j ? y1_lo : x0_lo) - (uint32_t)(((k - 1) / 2) * dil) + (uint32_t)(128 * i);
+        uint32_t s = slot0, ph = wph0;
+        for (int t = 0; t < k; ++t) {
+          if (first_use && i == 0) {
+            mbar_wait(&w_full[s], ph);
+            tc_fence_after();
+          }
+          const uint32_t b_lo = wr_lo + s * tap16;
+          if (elect_one()) {
 #pragma unroll
-          for (int ks = 0; ks < KS; ++ks)   // K step of 16 channels = two planes of A, 32 bytes of B
-            umma_f16(acc, a_hi | (uint64_t)(a_lo + (uint32_t)ks * 2u * plane16), b_hi | (uint64_t)(b_lo + 2u * ks),
-                     idesc, (j == 1 || t > 0 || ks > 0) ? 1u : 0u);
+            for (int ks = 0; ks < KS; ++ks)   // K step of 16 channels = two planes of A, 32 bytes of B
+              umma_f16(acc, a_hi | (uint64_t)(a_lo + (uint32_t)ks * 2u * plane16), b_hi | (uint64_t)(b_lo + 2u * ks),
+                       idesc, (j == 1 || t > 0 || ks > 0) ? 1u : 0u);
+          }
+          a_lo += (uint32_t)dil;
+          if (++s == ring) { s = 0; ph ^= 1u; }
         }
-        a_lo += (uint32_t)dil;
-        if (++s == ring) { s = 0; ph ^= 1u; }
+        if (elect_one()) umma_commit(j ? &s_full[i] : &d_full[i]);
+        TRACE(3u + (uint32_t)j * 4u, n, (uint32_t)i);
       }
-      if (elect_one()) umma_commit(j ? &s_full[i] : &d_full[i]);
-      TRACE(3u + (uint32_t)j * 4u, n, (uint32_t)i);
-      s_end = s; ph_end = ph;
-    };
-    // streaming mode: hand the ring slots of a finished convolution back to the producer
-    auto release = [&](int r) {
-      uint32_t s = slot;
-      for (int t = 0; t < p.k[r]; ++t) {
-        if (elect_one()) umma_commit(&w_empty[s]);
-        if (++s == ring) s = 0;
+      if (!p.resident) {   // hand the ring slots back to the producer once every tile has used them
+        uint32_t s = slot;
+        for (int t = 0; t < k; ++t) {
+          if (elect_one()) umma_commit(&w_empty[s]);
+          if (++s == ring) s = 0;
+        }
+        skip(k);
       }
-      slot = s_end; wph = ph_end;
     };
 
-    if (n_it > 0) {
-      mbar_wait(x_full, 0u);
-      for (int i = 0; i < m; ++i)
-        tile(0u, 0, 0, i, p.resident ? (uint32_t)p.tap_base[0][0] : slot, p.resident ? 0u : wph, i == 0);
-      if (!p.resident) release(0);
-      if (p.nk == 1 && elect_one()) umma_commit(x_empty);
-    }
     int it = 0, r = 0;
-    for (uint32_t n = 0; n < n_total; ++n) {
-      int it1 = it, r1 = r + 1;
-      if (r1 == p.nk) { r1 = 0; ++it1; }
-      const bool has_next = n + 1 < n_total;
-      if (has_next && r1 == 0) mbar_wait(x_full, (uint32_t)it1 & 1u);
-      if (p.resident) {
-        for (int i = 0; i < m; ++i) {
-          tile(n, r, 1, i, (uint32_t)p.tap_base[r][1], 0u, it == 0 && i == 0);
-          if (has_next) tile(n + 1u, r1, 0, i, (uint32_t)p.tap_base[r1][0], 0u, it1 == 0 && i == 0);
-        }
-      } else {
-        if (has_next) {
-          for (int i = 0; i < m; ++i) tile(n + 1u, r1, 0, i, slot, wph, i == 0);
-          release(r1);
-        }
-        for (int i = 0; i < m; ++i) tile(n, r, 1, i, slot, wph, i == 0);
-        release(r);
+    if (J == 0) {
+      if (n_it > 0) {
+        mbar_wait(x_full, 0u);
+        conv(0u, 0, 0, true);
+        if (p.nk == 1 && elect_one()) umma_commit(x_empty);
       }
-      // the lrelu(x) window may be refilled once the last conv1 reading it has been issued
-      if (has_next && r1 == p.nk - 1 && elect_one()) umma_commit(x_empty);
-      it = it1; r = r1;
+      for (uint32_t n = 0; n + 1 < n_total; ++n) {
+        int it1 = it, r1 = r + 1;
+        if (r1 == p.nk) { r1 = 0; ++it1; }
+        if (r1 == 0) mbar_wait(x_full, (uint32_t)it1 & 1u);
+        conv(n + 1u, r1, 0, !p.resident || it1 == 0);
+        // the lrelu(x) window may be refilled once the last conv1 reading it has been issued
+        if (r1 == p.nk - 1 && elect_one()) umma_commit(x_empty);
+        if (!p.resident) skip(p.k[r]);                       // c2(n) belongs to the other stream
+        it = it1; r = r1;
+      }
+    } else {
+      if (!p.resident && n_it > 0) skip(p.k[0]);             // c1(0)
+      for (uint32_t n = 0; n < n_total; ++n) {
+        int it1 = it, r1 = r + 1;
+        if (r1 == p.nk) { r1 = 0; ++it1; }
+        if (!p.resident && n + 1 < n_total) skip(p.k[r1]);   // c1(n+1)
+        conv(n, r, 1, !p.resident || it == 0);
+        it = it1; r = r1;
+      }
     }
   } else {
     // ===== epilogue: MRF_EG groups of four warps.  A unit of work is (tile, 32-column half); group g takes
     // units g, g + MRF_EG, ...  Every thread owns one row and 32 columns: one 128-byte line of the fp32
     // residual, two TMEM loads of D, and two planes of the conv2 operand. =====
     constexpr int HALVES = C / 32;
-    const int group = (warp - 2) >> 2;
+    const int group = (warp - 3) >> 2;
     const int quarter = warp & 3;                        // TMEM lane quarter this warp may access
     const uint32_t lane_sel = (uint32_t)(quarter * 32) << 16;
     const float inv_nk = 1.0f / (float)p.nk;
@@ -283,6 +288,7 @@ __global__ void __launch_bounds__(64 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
     uint32_t n = 0;
     for (int it = 0; it < n_it; ++it) {
       const int w0 = ((int)blockIdx.x + it * (int)gridDim.x) * p.V - p.halo;
+      mbar_wait(x_full, (uint32_t)it & 1u);   // the epilogue reads the window itself (residual)
       for (int r = 0; r < p.nk; ++r, ++n) {
         const float* b1 = sbias + r * C;
         for (int u = group; u < units; u += MRF_EG) {
@@ -290,18 +296,17 @@ __global__ void __launch_bounds__(64 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
           const int row_in_win = 128 * i + quarter * 32 + lane;
           const int grow = w0 + row_in_win;
           const bool inr = grow >= 0 && grow < p.R;
-          // the fp32 residual line and the validity flag do not depend on the MMAs: fetch them before waiting
-          float4 xr[8];
-          int ru = 0;
-          if (inr) {
-            const float4* x4 = reinterpret_cast<const float4*>(p.x + (size_t)grow * C + cb);
+          // the residual x0 is recovered from the 16-bit lrelu(x0) operand window (x0 = v >= 0 ? v : 10 v): no
+          // fp32 copy of the stage input exists.  Window rows and the validity flag do not depend on the MMAs
+          const uint32_t row_off = (uint32_t)((MRF_G + row_in_win) * 16);
+          uint4 xq[4];
+          {
+            const uint8_t* xrow = X0 + (size_t)(cb >> 3) * plane_bytes + row_off;
 #pragma unroll
-            for (int q4 = 0; q4 < 8; ++q4) xr[q4] = x4[q4];
-            if (p.row_utt) ru = p.row_utt[grow / p.valid_div];
-          } else {
-#pragma unroll
-            for (int q4 = 0; q4 < 8; ++q4) xr[q4] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int g = 0; g < 4; ++g) xq[g] = *reinterpret_cast<const uint4*>(xrow + (size_t)g * plane_bytes);
           }
+          int ru = 0;
+          if (inr && p.row_utt) ru = p.row_utt[grow / p.valid_div];
           TRACE(10u, n, (uint32_t)u);
           if (n > 0) {   // conv2 of the previous pair must have finished with S_i and with Y1 rows of tiles i-1..i+1
             for (int ii = (i > 0 ? i - 1 : 0); ii <= (i + 1 < m ? i + 1 : m - 1); ++ii)
@@ -313,9 +318,20 @@ __global__ void __launch_bounds__(64 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
           TRACE(12u, n, (uint32_t)u);
           asm volatile("" : "+r"(ru));                   // keep the flag's load in flight across the waits
           const bool valid = inr && ru >= 0;
-          const uint32_t row_off = (uint32_t)((MRF_G + row_in_win) * 16);
           const uint32_t dcol = tmem_base + lane_sel + d_col + (uint32_t)(i * C + cb);
           const uint32_t scol = tmem_base + lane_sel + s_col + (uint32_t)(i * C + cb);
+          auto add_x = [&](float* e0, float* e1) {   // planes g = 0,1 hold columns cb..cb+15, planes 2,3 the next 16
+            const uint32_t w[16] = {xq[0].x, xq[0].y, xq[0].z, xq[0].w, xq[1].x, xq[1].y, xq[1].z, xq[1].w,
+                                    xq[2].x, xq[2].y, xq[2].z, xq[2].w, xq[3].x, xq[3].y, xq[3].z, xq[3].w};
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const float2 a = unpack2(w[e], p.f16), b = unpack2(w[8 + e], p.f16);
+              e0[2 * e] += a.x >= 0.f ? a.x : a.x * 10.f;
+              e0[2 * e + 1] += a.y >= 0.f ? a.y : a.y * 10.f;
+              e1[2 * e] += b.x >= 0.f ? b.x : b.x * 10.f;
+              e1[2 * e + 1] += b.y >= 0.f ? b.y : b.y * 10.f;
+            }
+          };
           float d0[16], d1[16];
           uint32_t t0[16], t1[16], t2[16], t3[16];
           __syncwarp();
@@ -334,12 +350,7 @@ __global__ void __launch_bounds__(64 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
             for (int e = 0; e < 16; ++e) { s0[e] = __uint_as_float(t2[e]); s1[e] = __uint_as_float(t3[e]); }
 #pragma unroll
             for (int e = 0; e < 16; ++e) { d0[e] += b1[cb + e]; d1[e] += b1[cb + 16 + e]; }
-#pragma unroll
-            for (int q4 = 0; q4 < 4; ++q4) {
-              const float4 xa = xr[q4], xb = xr[4 + q4];
-              d0[4 * q4] += xa.x; d0[4 * q4 + 1] += xa.y; d0[4 * q4 + 2] += xa.z; d0[4 * q4 + 3] += xa.w;
-              d1[4 * q4] += xb.x; d1[4 * q4 + 1] += xb.y; d1[4 * q4 + 2] += xb.z; d1[4 * q4 + 3] += xb.w;
-            }
+            add_x(d0, d1);
 #pragma unroll
             for (int e = 0; e < 16; ++e) { s0[e] += d0[e]; s1[e] += d1[e]; }
             tmem_st16(scol, s0);
@@ -347,12 +358,7 @@ __global__ void __launch_bounds__(64 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
           } else {
 #pragma unroll
             for (int e = 0; e < 16; ++e) { d0[e] += b1[cb + e]; d1[e] += b1[cb + 16 + e]; }
-#pragma unroll
-            for (int q4 = 0; q4 < 4; ++q4) {
-              const float4 xa = xr[q4], xb = xr[4 + q4];
-              d0[4 * q4] += xa.x; d0[4 * q4 + 1] += xa.y; d0[4 * q4 + 2] += xa.z; d0[4 * q4 + 3] += xa.w;
-              d1[4 * q4] += xb.x; d1[4 * q4 + 1] += xb.y; d1[4 * q4 + 2] += xb.z; d1[4 * q4 + 3] += xb.w;
-            }
+            add_x(d0, d1);
             tmem_st16(scol, d0);
             tmem_st16(scol + 16u, d1);
           }
@@ -375,6 +381,10 @@ __global__ void __launch_bounds__(64 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
             mbar_arrive(&d_empty[i]);
           }
           TRACE(13u, n, (uint32_t)u);
+        }
+        if (r == p.nk - 1) {   // this warp is done with the lrelu(x) window
+          __syncwarp();
+          if (lane == 0) mbar_arrive(x_empty);
         }
       }
       // ---- stage output: (S + sum_r b2_r) / nk over the window's valid rows ----
@@ -496,6 +506,8 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   while (m > 2 && (a.R + (128 * m - 2 * halo) - 1) / (128 * m - 2 * halo) < num_sms) --m;
   static const int m_env = [] { const char* e = getenv("PIPER_B200_MRF_M"); return e ? atoi(e) : 0; }();
   if (m_env >= 2 && m_env <= MRF_MAX_M && 2 * m_env * a.C <= 512 && fits(m_env)) m = m_env;
+  static const int m64_env = [] { const char* e = getenv("PIPER_B200_MRF_M64"); return e ? atoi(e) : 0; }();
+  if (a.C == 64 && m64_env >= 2 && 2 * m64_env * a.C <= 512 && fits(m64_env)) m = m64_env;
   if (!fits(m)) throw std::runtime_error("conv_mrf: stage does not fit in shared memory");
   p.m = m;
   p.V = 128 * m - 2 * halo;
@@ -507,7 +519,7 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   if (p.resident) ring = a.total_taps;
   p.ring = ring;
   p.x_act = static_cast<const uint16_t*>(a.x_act); p.act_rows = a.act_rows; p.act_pad = a.act_pad;
-  p.x = a.x; p.row_utt = a.row_utt; p.valid_div = a.valid_div < 1 ? 1 : a.valid_div;
+  p.row_utt = a.row_utt; p.valid_div = a.valid_div < 1 ? 1 : a.valid_div;
   p.out_act = a.out_act; p.act_slope = a.act_slope; p.out_f32 = a.out_f32;
   p.f16 = a.f16;
   uint32_t cols = 32;
@@ -519,14 +531,14 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   const int grid = std::min(p.n_windows, num_sms);
   ProfScope ps(ex, Prof::MRF, 2.0 * a.R * a.C * a.C * (double)a.total_taps);
   static const char* trace_path = getenv("PIPER_B200_MRF_TRACE");
-  const size_t trace_words = (size_t)(64 + 128 * 4) / 32 * MRF_TRACE_EVENTS * 2;
+  const size_t trace_words = (size_t)(96 + 128 * 4) / 32 * MRF_TRACE_EVENTS * 2;
   if (trace_path) {
     if (cudaMalloc(&p.trace, trace_words * 4) != cudaSuccess) throw std::runtime_error("conv_mrf: trace buffer");
     cudaMemsetAsync(p.trace, 0, trace_words * 4, ex.st);
   }
   static const int eg_env = [] { const char* e = getenv("PIPER_B200_MRF_EG"); return e ? atoi(e) : 0; }();
   const int eg = eg_env >= 2 && eg_env <= 4 ? eg_env : 3;
-  const int threads = 64 + 128 * eg;
+  const int threads = 96 + 128 * eg;
   if (a.C == 32) {
     if (eg == 2) mrf_tc_kernel<32, 2><<<grid, threads, smem, ex.st>>>(tw, p);
     else if (eg == 3) mrf_tc_kernel<32, 3><<<grid, threads, smem, ex.st>>>(tw, p);

@@ -4,9 +4,11 @@
 //                                   y2_r = y1_r + conv_{k_r,d1_r}(lrelu(y1_r)) + b2_r
 // i.e. the graph's LeakyRelu/Conv/Add chains, the Add across kernels and the Div
 // (GraphExecutor.swift:1739-1810, 2047-2069; conv1d.metal:28-71) with every intermediate on
-// chip: operands in swizzled shared memory, the fp32 residual stream and the cross-resblock sum
-// in tensor memory.  HBM traffic per element: read x (fp32) + lrelu(x) (16-bit), write the
-// stage output once - instead of ~12 bytes per element per convolution.
+// chip: operands in planar shared memory, y1 and the cross-resblock sum in fp32 in tensor memory.
+// The stage input is read ONCE, as the 16-bit lrelu(x) operand; the residual term x is recovered from
+// it (x = v >= 0 ? v : 10 v), so x enters with 16-bit rounding like every conv operand does.
+// HBM traffic per element: read lrelu(x) (2 bytes), write the stage output once - instead of ~12
+// bytes per element per convolution.
 #pragma once
 #include <cuda_runtime.h>
 
@@ -29,8 +31,7 @@ struct MrfArgs {
   const float* b2[MRF_MAX_RB] = {nullptr, nullptr, nullptr, nullptr};
   const void* w = nullptr;       // 16-bit weights [total_taps][C cout][C cin]
   int total_taps = 0;
-  const float* x = nullptr;      // fp32 stage input [R][C] (ConvTranspose output)
-  // 16-bit lrelu(x), group-planar [C/8][act_rows][8]; signal row r at plane row act_pad + r; the rows before
+  // the stage input as 16-bit lrelu(x, 0.1), group-planar [C/8][act_rows][8]; signal row r at plane row act_pad + r; the rows before
   // act_pad and after act_pad + R must be zero (act_pad >= 128, act_rows >= R + act_pad + 1152)
   const void* x_act = nullptr;
   int64_t act_rows = 0; int act_pad = 0;

@@ -169,6 +169,10 @@ __device__ __forceinline__ uint32_t pack2(float a, float b, int f16) {
   return *reinterpret_cast<const uint32_t*>(&h);
 }
 __device__ __forceinline__ float lrelu(float v, float s) { return v >= 0.f ? v : v * s; }
+__device__ __forceinline__ float2 unpack2(uint32_t u, int f16) {
+  if (f16) return __half22float2(*reinterpret_cast<const __half2*>(&u));
+  return make_float2(__uint_as_float(u << 16), __uint_as_float(u & 0xFFFF0000u));   // bf16 = upper half of an fp32
+}
 
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {

@@ -22,10 +22,10 @@ for w, lst in by_w.items():
         out.append((c + base, w, tag, n, i))
 out.sort()
 t0 = None
-sel = [e for e in out if n_lo <= e[3] <= n_hi and e[2] < 20 and (e[1] in (1, 2, 6, 10))]
+sel = [e for e in out if n_lo <= e[3] <= n_hi and e[2] < 20 and (e[1] in (1, 2, 3, 7))]
 if sel: t0 = sel[0][0]
 for (c, w, tag, n, i) in sel:
-    col = {1: 0, 2: 1, 6: 2, 10: 3}[w]
+    col = {1: 0, 2: 1, 3: 2, 7: 3}[w]
     print("%8d  %s%-8s n=%d i=%d" % (c - t0, " " * (24 * col), TAG.get(tag, str(tag)), n, i))
 # summary: per-phase durations
 def dur(w, a, b):
@@ -37,8 +37,8 @@ def dur(w, a, b):
     return tot / max(cnt, 1), cnt
 span = out[-1][0] - out[0][0]
 print("total span cycles", span)
-for name, w, a, b in [("mma conv1 wait", 1, 1, 2), ("mma conv1 issue", 1, 2, 3), ("mma conv2 wait", 1, 5, 6), ("mma conv2 issue", 1, 6, 7),
-                      ("epi g0 s wait", 2, 10, 11), ("epi g0 d wait", 2, 11, 12), ("epi g0 work", 2, 12, 13), ("epi g0 out wait", 2, 14, 15),
-                      ("epi g0 out work", 2, 15, 16), ("prod x wait", 0, 20, 21)]:
+for name, w, a, b in [("mma conv1 wait", 1, 1, 2), ("mma conv1 issue", 1, 2, 3), ("mma conv2 wait", 2, 5, 6), ("mma conv2 issue", 2, 6, 7),
+                      ("epi g0 s wait", 3, 10, 11), ("epi g0 d wait", 3, 11, 12), ("epi g0 work", 3, 12, 13), ("epi g0 out wait", 3, 14, 15),
+                      ("epi g0 out work", 3, 15, 16), ("prod x wait", 0, 20, 21)]:
     d, c = dur(w, a, b)
     print("%-18s avg %8.0f cycles x %5d = %5.1f%% of span" % (name, d, c, 100.0 * d * c / span))
