@@ -299,12 +299,6 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
           // the residual x0 is recovered from the 16-bit lrelu(x0) operand window (x0 = v >= 0 ? v : 10 v): no
           // fp32 copy of the stage input exists.  Window rows and the validity flag do not depend on the MMAs
           const uint32_t row_off = (uint32_t)((MRF_G + row_in_win) * 16);
-          uint4 xq[4];
-          {
-            const uint8_t* xrow = X0 + (size_t)(cb >> 3) * plane_bytes + row_off;
-#pragma unroll
-            for (int g = 0; g < 4; ++g) xq[g] = *reinterpret_cast<const uint4*>(xrow + (size_t)g * plane_bytes);
-          }
           int ru = 0;
           if (inr && p.row_utt) ru = p.row_utt[grow / p.valid_div];
           TRACE(10u, n, (uint32_t)u);
@@ -320,58 +314,51 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
           const bool valid = inr && ru >= 0;
           const uint32_t dcol = tmem_base + lane_sel + d_col + (uint32_t)(i * C + cb);
           const uint32_t scol = tmem_base + lane_sel + s_col + (uint32_t)(i * C + cb);
-          auto add_x = [&](float* e0, float* e1) {   // planes g = 0,1 hold columns cb..cb+15, planes 2,3 the next 16
-            const uint32_t w[16] = {xq[0].x, xq[0].y, xq[0].z, xq[0].w, xq[1].x, xq[1].y, xq[1].z, xq[1].w,
-                                    xq[2].x, xq[2].y, xq[2].z, xq[2].w, xq[3].x, xq[3].y, xq[3].z, xq[3].w};
+          // two chunks of 16 columns (= two operand planes) each, processed one after the other to keep the
+          // register footprint small enough for MRF_EG = 4 warpgroups
+#pragma unroll 1
+          for (int hc = 0; hc < 2; ++hc) {
+            const int c0 = cb + hc * 16;
+            const uint8_t* xrow = X0 + (size_t)(c0 >> 3) * plane_bytes + row_off;
+            const uint4 xa = *reinterpret_cast<const uint4*>(xrow);
+            const uint4 xb = *reinterpret_cast<const uint4*>(xrow + plane_bytes);
+            uint32_t t0[16], t2[16];
+            __syncwarp();
+            tmem_ld16_async(dcol + (uint32_t)(hc * 16), t0);
+            if (r > 0) tmem_ld16_async(scol + (uint32_t)(hc * 16), t2);
+            float d[16];
+            {   // x0 + b1 while the TMEM loads are in flight; x0 = min(v, 10 v) undoes lrelu(., 0.1)
+              const uint32_t w[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
+              const float4* b4 = reinterpret_cast<const float4*>(b1 + c0);
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              const float2 a = unpack2(w[e], p.f16), b = unpack2(w[8 + e], p.f16);
-              e0[2 * e] += a.x >= 0.f ? a.x : a.x * 10.f;
-              e0[2 * e + 1] += a.y >= 0.f ? a.y : a.y * 10.f;
-              e1[2 * e] += b.x >= 0.f ? b.x : b.x * 10.f;
-              e1[2 * e + 1] += b.y >= 0.f ? b.y : b.y * 10.f;
+              for (int q4 = 0; q4 < 4; ++q4) {
+                const float4 bb = b4[q4];
+                const float2 x01 = unpack2(w[2 * q4], p.f16), x23 = unpack2(w[2 * q4 + 1], p.f16);
+                d[4 * q4] = bb.x + fminf(x01.x, x01.x * 10.f);
+                d[4 * q4 + 1] = bb.y + fminf(x01.y, x01.y * 10.f);
+                d[4 * q4 + 2] = bb.z + fminf(x23.x, x23.x * 10.f);
+                d[4 * q4 + 3] = bb.w + fminf(x23.y, x23.y * 10.f);
+              }
             }
-          };
-          float d0[16], d1[16];
-          uint32_t t0[16], t1[16], t2[16], t3[16];
-          __syncwarp();
-          tmem_ld16_async(dcol, t0);
-          tmem_ld16_async(dcol + 16u, t1);
-          if (r > 0) {
-            tmem_ld16_async(scol, t2);
-            tmem_ld16_async(scol + 16u, t3);
+            tmem_wait_ld();
+#pragma unroll
+            for (int e = 0; e < 16; ++e) d[e] += __uint_as_float(t0[e]);
+            if (r > 0) {
+              float sv[16];
+#pragma unroll
+              for (int e = 0; e < 16; ++e) sv[e] = __uint_as_float(t2[e]) + d[e];
+              tmem_st16(scol + (uint32_t)(hc * 16), sv);
+            } else {
+              tmem_st16(scol + (uint32_t)(hc * 16), d);
+            }
+            uint32_t pk[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e)   // lrelu(v, 0.1) = max(v, 0.1 v)
+              pk[e] = valid ? pack2(fmaxf(d[2 * e], d[2 * e] * 0.1f), fmaxf(d[2 * e + 1], d[2 * e + 1] * 0.1f), p.f16) : 0u;
+            uint8_t* y = Y1 + (size_t)(c0 >> 3) * plane_bytes + row_off;   // planes c0/8 and c0/8 + 1
+            *reinterpret_cast<uint4*>(y) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            *reinterpret_cast<uint4*>(y + plane_bytes) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
           }
-          tmem_wait_ld();
-#pragma unroll
-          for (int e = 0; e < 16; ++e) { d0[e] = __uint_as_float(t0[e]); d1[e] = __uint_as_float(t1[e]); }
-          if (r > 0) {
-            float s0[16], s1[16];
-#pragma unroll
-            for (int e = 0; e < 16; ++e) { s0[e] = __uint_as_float(t2[e]); s1[e] = __uint_as_float(t3[e]); }
-#pragma unroll
-            for (int e = 0; e < 16; ++e) { d0[e] += b1[cb + e]; d1[e] += b1[cb + 16 + e]; }
-            add_x(d0, d1);
-#pragma unroll
-            for (int e = 0; e < 16; ++e) { s0[e] += d0[e]; s1[e] += d1[e]; }
-            tmem_st16(scol, s0);
-            tmem_st16(scol + 16u, s1);
-          } else {
-#pragma unroll
-            for (int e = 0; e < 16; ++e) { d0[e] += b1[cb + e]; d1[e] += b1[cb + 16 + e]; }
-            add_x(d0, d1);
-            tmem_st16(scol, d0);
-            tmem_st16(scol + 16u, d1);
-          }
-          uint32_t pk[16];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            pk[e] = valid ? pack2(lrelu(d0[2 * e], 0.1f), lrelu(d0[2 * e + 1], 0.1f), p.f16) : 0u;
-            pk[8 + e] = valid ? pack2(lrelu(d1[2 * e], 0.1f), lrelu(d1[2 * e + 1], 0.1f), p.f16) : 0u;
-          }
-          uint8_t* y = Y1 + (size_t)(cb >> 3) * plane_bytes + row_off;   // planes cb/8 .. cb/8 + 3
-#pragma unroll
-          for (int g = 0; g < 4; ++g)
-            *reinterpret_cast<uint4*>(y + (size_t)g * plane_bytes) = make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
           tmem_wait_st();
           fence_proxy_async();
           tc_fence_before();
@@ -479,6 +466,8 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
         cudaFuncSetAttribute(mrf_tc_kernel<64, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
         cudaFuncSetAttribute(mrf_tc_kernel<32, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
         cudaFuncSetAttribute(mrf_tc_kernel<64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
+        cudaFuncSetAttribute(mrf_tc_kernel<32, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
+        cudaFuncSetAttribute(mrf_tc_kernel<64, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
         cudaFuncSetAttribute(mrf_tc_kernel<32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
         cudaFuncSetAttribute(mrf_tc_kernel<64, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess)
       throw std::runtime_error("cuda: cannot raise dynamic shared memory limit for mrf_tc_kernel");
@@ -531,22 +520,24 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   const int grid = std::min(p.n_windows, num_sms);
   ProfScope ps(ex, Prof::MRF, 2.0 * a.R * a.C * a.C * (double)a.total_taps);
   static const char* trace_path = getenv("PIPER_B200_MRF_TRACE");
-  const size_t trace_words = (size_t)(96 + 128 * 4) / 32 * MRF_TRACE_EVENTS * 2;
+  const size_t trace_words = (size_t)(96 + 128 * 5) / 32 * MRF_TRACE_EVENTS * 2;
   if (trace_path) {
     if (cudaMalloc(&p.trace, trace_words * 4) != cudaSuccess) throw std::runtime_error("conv_mrf: trace buffer");
     cudaMemsetAsync(p.trace, 0, trace_words * 4, ex.st);
   }
   static const int eg_env = [] { const char* e = getenv("PIPER_B200_MRF_EG"); return e ? atoi(e) : 0; }();
-  const int eg = eg_env >= 2 && eg_env <= 4 ? eg_env : 3;
+  const int eg = eg_env >= 2 && eg_env <= 5 ? eg_env : 4;
   const int threads = 96 + 128 * eg;
   if (a.C == 32) {
     if (eg == 2) mrf_tc_kernel<32, 2><<<grid, threads, smem, ex.st>>>(tw, p);
     else if (eg == 3) mrf_tc_kernel<32, 3><<<grid, threads, smem, ex.st>>>(tw, p);
-    else mrf_tc_kernel<32, 4><<<grid, threads, smem, ex.st>>>(tw, p);
+    else if (eg == 4) mrf_tc_kernel<32, 4><<<grid, threads, smem, ex.st>>>(tw, p);
+    else mrf_tc_kernel<32, 5><<<grid, threads, smem, ex.st>>>(tw, p);
   } else {
     if (eg == 2) mrf_tc_kernel<64, 2><<<grid, threads, smem, ex.st>>>(tw, p);
     else if (eg == 3) mrf_tc_kernel<64, 3><<<grid, threads, smem, ex.st>>>(tw, p);
-    else mrf_tc_kernel<64, 4><<<grid, threads, smem, ex.st>>>(tw, p);
+    else if (eg == 4) mrf_tc_kernel<64, 4><<<grid, threads, smem, ex.st>>>(tw, p);
+    else mrf_tc_kernel<64, 5><<<grid, threads, smem, ex.st>>>(tw, p);
   }
   ++ex.launches;
   if (trace_path) {   // debug only: dump "C m warp tag n i clock" lines, one file per stage width
