@@ -6,6 +6,8 @@
 // replaces; none of them is a translation of the one-thread-per-output Metal kernels.
 #include "kernels.h"
 
+#include <cstdlib>
+
 #include <cfloat>
 #include <cmath>
 #include <cstdio>
@@ -254,8 +256,148 @@ __global__ void __launch_bounds__(256, 2) conv_f32_big_kernel(ConvArgs a) {
   }
 }
 
+// 96 x 192 tile for the text-encoder widths (cout = 192, 576, 768): with ~27.5k rows per step this gives
+// 287 row tiles, i.e. ONE wave of 2 CTAs per SM on 148 SMs, and no half-empty column tile at cout = 192
+// (the 128 x 128 grid needed 1.45 waves of 75 %-full tiles there).  256 threads, 6 x 12 outputs each;
+// same tap-major / channel-ascending accumulation order as the other fp32 kernels.
+constexpr int WBM = 96, WBN = 192, WBK = 16;
+
+__global__ void __launch_bounds__(256, 2) conv_f32_w192_kernel(ConvArgs a) {
+  __shared__ __align__(16) float As[2][WBK][WBM];
+  __shared__ __align__(16) float Bs[2][WBK][WBN];
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int q0 = blockIdx.x * WBM;
+  const int n0 = blockIdx.y * WBN;
+  int in_off = a.in_off, out_add = a.out_add;
+  const float* wbase = a.w;
+  if (a.phases > 1) {
+    const int ph = blockIdx.z;
+    out_add = ph;
+    in_off = (ph + a.ct_pad) / a.phases;
+    wbase += (size_t)ph * a.taps * a.cin * a.ldw;
+  }
+  float acc[6][12];
+#pragma unroll
+  for (int i = 0; i < 6; ++i)
+#pragma unroll
+    for (int j = 0; j < 12; ++j) acc[i][j] = 0.f;
+
+  // loaders: A = 96 rows x 16 channels = 384 float4 (threads 0..127 take a second one), B = 16 x 192 = 768 float4
+  const int kchunks = (a.cin + WBK - 1) / WBK;
+  const int n_it = a.taps * kchunks;
+  float4 pa[2], pb[3];
+  auto fetch = [&](int it) {
+    const int tap = it / kchunks, ci0 = (it - tap * kchunks) * WBK;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int f = tid + 256 * h;                      // float4 index: row f / 4, channel quad f % 4
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (f < WBM * 4) {
+        const int row = f >> 2, ci = ci0 + (f & 3) * 4;
+        const int srow = q0 + row + in_off + tap * a.tap_step;
+        if ((q0 + row) < a.Q && srow >= 0 && srow < a.R_in && ci < a.cin)
+          v = *reinterpret_cast<const float4*>(a.in + (size_t)srow * a.ldin + ci);
+        if (a.in_act) {
+          v.x = v.x >= 0.f ? v.x : v.x * a.in_slope;
+          v.y = v.y >= 0.f ? v.y : v.y * a.in_slope;
+          v.z = v.z >= 0.f ? v.z : v.z * a.in_slope;
+          v.w = v.w >= 0.f ? v.w : v.w * a.in_slope;
+        }
+      }
+      pa[h] = v;
+    }
+#pragma unroll
+    for (int h = 0; h < 3; ++h) {
+      const int f = tid + 256 * h;                      // float4 index: channel f / 48, column quad f % 48
+      const int kk = f / 48, c4 = f - kk * 48;
+      float4 w4 = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (ci0 + kk < a.cin && n0 + c4 * 4 < a.ldw)
+        w4 = *reinterpret_cast<const float4*>(wbase + ((size_t)tap * a.cin + ci0 + kk) * a.ldw + n0 + c4 * 4);
+      pb[h] = w4;
+    }
+  };
+  auto stash = [&](int buf) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int f = tid + 256 * h;
+      if (f < WBM * 4) {
+        const int row = f >> 2, kq = (f & 3) * 4;
+        As[buf][kq + 0][row] = pa[h].x;
+        As[buf][kq + 1][row] = pa[h].y;
+        As[buf][kq + 2][row] = pa[h].z;
+        As[buf][kq + 3][row] = pa[h].w;
+      }
+    }
+#pragma unroll
+    for (int h = 0; h < 3; ++h) {
+      const int f = tid + 256 * h;
+      const int kk = f / 48, c4 = f - kk * 48;
+      *reinterpret_cast<float4*>(&Bs[buf][kk][c4 * 4]) = pb[h];
+    }
+  };
+  fetch(0);
+  stash(0);
+  __syncthreads();
+  for (int it = 0; it < n_it; ++it) {
+    const int buf = it & 1;
+    if (it + 1 < n_it) fetch(it + 1);
+#pragma unroll
+    for (int k = 0; k < WBK; ++k) {
+      float ar[6], br[12];
+#pragma unroll
+      for (int g = 0; g < 3; ++g) {                     // rows g*32 + ty*2 + {0,1}; columns g*64 + tx*4 + {0..3}
+        const float2 a2 = *reinterpret_cast<const float2*>(&As[buf][k][g * 32 + ty * 2]);
+        ar[2 * g] = a2.x; ar[2 * g + 1] = a2.y;
+        const float4 b4 = *reinterpret_cast<const float4*>(&Bs[buf][k][g * 64 + tx * 4]);
+        br[4 * g] = b4.x; br[4 * g + 1] = b4.y; br[4 * g + 2] = b4.z; br[4 * g + 3] = b4.w;
+      }
+#pragma unroll
+      for (int i = 0; i < 6; ++i)
+#pragma unroll
+        for (int j = 0; j < 12; ++j) acc[i][j] = fmaf(ar[i], br[j], acc[i][j]);
+    }
+    if (it + 1 < n_it) {
+      stash(buf ^ 1);
+      __syncthreads();
+    }
+  }
+  // epilogue (same semantics as conv_f32_kernel)
+#pragma unroll
+  for (int i = 0; i < 6; ++i) {
+    const int q = q0 + (i >> 1) * 32 + ty * 2 + (i & 1);
+    if (q >= a.Q) continue;
+    const int orow = q * a.out_mul + out_add;
+    int utt = 0;
+    if (a.row_utt) utt = a.row_utt[orow / a.valid_div];
+    const bool valid = utt >= 0;
+#pragma unroll
+    for (int j = 0; j < 12; ++j) {
+      const int co = n0 + (j >> 2) * 64 + tx * 4 + (j & 3);
+      if (co >= a.cout) continue;
+      float v = acc[i][j];
+      if (a.bias) v += a.bias[co];
+      if (a.uttbias && valid) v += a.uttbias[(size_t)utt * a.ldub + co];
+      if (a.relu) v = fmaxf(v, 0.f);
+      if (a.res) v += a.res[(size_t)orow * a.ldres + co];
+      float* o = a.out + (size_t)orow * a.ldout + co;
+      if (a.accum) v += *o;
+      if (a.div != 0.f) v = v / a.div;
+      *o = valid ? v : 0.f;
+    }
+  }
+}
+
 void launch_conv_f32(Exec& ex, const ConvArgs& a) {
   if (a.Q <= 0) return;
+  static const int w192_env = [] { const char* e = getenv("PIPER_B200_F32_W192"); return e ? atoi(e) : 1; }();
+  if (w192_env && a.Q >= 4096 && a.cout % WBN == 0 && a.cin % 4 == 0 && a.ldw % 4 == 0) {
+    dim3 grid((a.Q + WBM - 1) / WBM, a.cout / WBN, a.phases);
+    ProfScope ps(ex, Prof::CONV_F32, 2.0 * a.Q * a.phases * a.taps * a.cin * a.cout);
+    conv_f32_w192_kernel<<<grid, 256, 0, ex.st>>>(a);
+    KLAUNCH(ex);
+    return;
+  }
   if (a.Q >= 4096 && a.cout >= 96 && a.cin % 4 == 0) {
     const bool wide = a.cout > 64;   // measured: the 128-wide tile wins even for cout = 192 (half-empty second tile)
     const int bn = wide ? 128 : 64;
