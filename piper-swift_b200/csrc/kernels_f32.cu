@@ -7,6 +7,7 @@
 #include "kernels.h"
 
 #include <cstdlib>
+#include <stdexcept>
 
 #include <cfloat>
 #include <cmath>
@@ -614,6 +615,176 @@ __global__ void __launch_bounds__(ATT_WARPS * 32) attention_kernel(
   }
 }
 
+// Tiled variant for head dim 96 (every Piper voice: hidden 192, 2 heads): one CTA per (utterance, head,
+// 64 queries), 16 x 16 threads.  Per 64-key tile: S = Q K^T as a register-tiled 64 x 64 x 96 product
+// (thread (ty,tx) owns queries ty+16r and keys tx+16c), banded relative-key term from the precomputed
+// q.rel_k table, online softmax with half-warp shuffles, P through shared memory, then O += P V with the
+// thread owning the same 4 queries and columns tx+16e, plus the banded relative-value term.  K and V of an
+// utterance are read ceil(T/64) times instead of ceil(T/8) times, and the inner loops are FMA-bound.
+constexpr int AT2_Q = 64, AT2_K = 64, AT2_D = 96, AT2_LD = 100, AT2_LDP = 68, AT2_MAXREL = 17;
+
+__global__ void __launch_bounds__(256, 2) attention96_kernel(
+    const float* __restrict__ qkv, const float* __restrict__ rel_k, const float* __restrict__ rel_v,
+    float* __restrict__ out, const int* __restrict__ utt_start, const int* __restrict__ utt_len,
+    int H, int window) {
+  extern __shared__ __align__(16) float sm[];
+  float* Qs = sm;                               // [64][100]  (scaled by 1/sqrt(96))
+  float* Ks = Qs + AT2_Q * AT2_LD;              // [64][100]
+  float* Vs = Ks + AT2_K * AT2_LD;              // [64][96]
+  float* Ps = Vs + AT2_K * AT2_D;               // [64][68]
+  float* RK = Ps + AT2_Q * AT2_LDP;             // [nrel][96]
+  float* RV = RK + AT2_MAXREL * AT2_D;          // [nrel][96]
+  float* QR = RV + AT2_MAXREL * AT2_D;          // [64][nrel]
+  const int b = blockIdx.z, head = blockIdx.y;
+  const int T = utt_len[b];
+  const int i0 = blockIdx.x * AT2_Q;
+  if (i0 >= T) return;
+  const int row0 = utt_start[b];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int nrel = 2 * window + 1;
+  const int ld = 3 * H;
+  const float qscale = 1.0f / sqrtf((float)AT2_D);
+  for (int t = tid; t < nrel * AT2_D; t += 256) {
+    RK[t] = rel_k[t];
+    RV[t] = rel_v[t];
+  }
+  for (int f = tid; f < AT2_Q * (AT2_D / 4); f += 256) {
+    const int r = f / (AT2_D / 4), d4 = f - r * (AT2_D / 4);
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i0 + r < T) {
+      v = *reinterpret_cast<const float4*>(qkv + (size_t)(row0 + i0 + r) * ld + head * AT2_D + d4 * 4);
+      v.x /= sqrtf((float)AT2_D); v.y /= sqrtf((float)AT2_D); v.z /= sqrtf((float)AT2_D); v.w /= sqrtf((float)AT2_D);
+    }
+    *reinterpret_cast<float4*>(Qs + r * AT2_LD + d4 * 4) = v;
+  }
+  (void)qscale;
+  __syncthreads();
+  for (int t = tid; t < AT2_Q * nrel; t += 256) {   // q_i . rel_k[m]
+    const int r = t / nrel, m = t - r * nrel;
+    float acc = 0.f;
+    for (int d = 0; d < AT2_D; ++d) acc = fmaf(Qs[r * AT2_LD + d], RK[m * AT2_D + d], acc);
+    QR[t] = acc;
+  }
+  float mrun[4], lrun[4], o[4][6];
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    mrun[r] = -FLT_MAX; lrun[r] = 0.f;
+#pragma unroll
+    for (int e = 0; e < 6; ++e) o[r][e] = 0.f;
+  }
+  for (int j0 = 0; j0 < T; j0 += AT2_K) {
+    __syncthreads();                             // previous tile's K, V, P fully consumed (and QR written)
+    for (int f = tid; f < AT2_K * (AT2_D / 4); f += 256) {
+      const int r = f / (AT2_D / 4), d4 = f - r * (AT2_D / 4);
+      float4 kv = make_float4(0.f, 0.f, 0.f, 0.f), vv = kv;
+      if (j0 + r < T) {
+        const float* rowp = qkv + (size_t)(row0 + j0 + r) * ld + head * AT2_D + d4 * 4;
+        kv = *reinterpret_cast<const float4*>(rowp + H);
+        vv = *reinterpret_cast<const float4*>(rowp + 2 * H);
+      }
+      *reinterpret_cast<float4*>(Ks + r * AT2_LD + d4 * 4) = kv;
+      *reinterpret_cast<float4*>(Vs + r * AT2_D + d4 * 4) = vv;
+    }
+    __syncthreads();
+    // ---- S = Q K^T ----
+    float sacc[4][4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) sacc[r][c] = 0.f;
+#pragma unroll 2
+    for (int d4 = 0; d4 < AT2_D / 4; ++d4) {
+      float4 q4[4], k4[4];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) q4[r] = *reinterpret_cast<const float4*>(Qs + (ty + 16 * r) * AT2_LD + d4 * 4);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) k4[c] = *reinterpret_cast<const float4*>(Ks + (tx + 16 * c) * AT2_LD + d4 * 4);
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          sacc[r][c] = fmaf(q4[r].x, k4[c].x, sacc[r][c]);
+          sacc[r][c] = fmaf(q4[r].y, k4[c].y, sacc[r][c]);
+          sacc[r][c] = fmaf(q4[r].z, k4[c].z, sacc[r][c]);
+          sacc[r][c] = fmaf(q4[r].w, k4[c].w, sacc[r][c]);
+        }
+    }
+    // ---- relative-key band, mask, online softmax ----
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int i = i0 + ty + 16 * r;
+      float mx = -FLT_MAX;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const int j = j0 + tx + 16 * c;
+        const int rel = j - i;
+        float v = sacc[r][c];
+        if (rel >= -window && rel <= window) v += QR[(ty + 16 * r) * nrel + rel + window];
+        v = j < T ? v : -FLT_MAX;
+        sacc[r][c] = v;
+        mx = fmaxf(mx, v);
+      }
+#pragma unroll
+      for (int off = 8; off > 0; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+      const float mnew = fmaxf(mrun[r], mx);
+      float sum = 0.f;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const float pv = (j0 + tx + 16 * c) < T ? expf(sacc[r][c] - mnew) : 0.f;
+        Ps[(ty + 16 * r) * AT2_LDP + tx + 16 * c] = pv;
+        sum += pv;
+      }
+#pragma unroll
+      for (int off = 8; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
+      const float corr = expf(mrun[r] - mnew);
+      lrun[r] = lrun[r] * corr + sum;
+      mrun[r] = mnew;
+#pragma unroll
+      for (int e = 0; e < 6; ++e) o[r][e] *= corr;
+    }
+    __syncthreads();
+    // ---- O += P V ----
+    const int jn = min(AT2_K, T - j0);
+    for (int jj = 0; jj < jn; jj += 4) {           // rows jj..jj+3 beyond jn hold p = 0 and zero V
+      float4 p4[4];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) p4[r] = *reinterpret_cast<const float4*>(Ps + (ty + 16 * r) * AT2_LDP + jj);
+#pragma unroll
+      for (int e = 0; e < 6; ++e) {
+        const float v0 = Vs[(jj + 0) * AT2_D + tx + 16 * e], v1 = Vs[(jj + 1) * AT2_D + tx + 16 * e];
+        const float v2 = Vs[(jj + 2) * AT2_D + tx + 16 * e], v3 = Vs[(jj + 3) * AT2_D + tx + 16 * e];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          o[r][e] = fmaf(p4[r].x, v0, o[r][e]);
+          o[r][e] = fmaf(p4[r].y, v1, o[r][e]);
+          o[r][e] = fmaf(p4[r].z, v2, o[r][e]);
+          o[r][e] = fmaf(p4[r].w, v3, o[r][e]);
+        }
+      }
+    }
+    // ---- relative-value band ----
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int i = i0 + ty + 16 * r;
+      for (int m = 0; m < nrel; ++m) {
+        const int jl = i + m - window - j0;
+        if (jl < 0 || jl >= jn) continue;
+        const float pv = Ps[(ty + 16 * r) * AT2_LDP + jl];
+#pragma unroll
+        for (int e = 0; e < 6; ++e) o[r][e] = fmaf(pv, RV[m * AT2_D + tx + 16 * e], o[r][e]);
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int i = i0 + ty + 16 * r;
+    if (i >= T) continue;
+    float* op = out + (size_t)(row0 + i) * H + head * AT2_D;
+#pragma unroll
+    for (int e = 0; e < 6; ++e) op[tx + 16 * e] = o[r][e] / lrun[r];
+  }
+}
+
 void launch_attention(Exec& ex, const float* qkv, const float* rel_k, const float* rel_v, float* out,
                       const int* utt_start, const int* utt_len, int batch, int max_len, int H,
                       int n_heads, int window) {
@@ -621,6 +792,21 @@ void launch_attention(Exec& ex, const float* qkv, const float* rel_k, const floa
   const int kc = H / n_heads;
   const int nrel = 2 * window + 1;
   const size_t smem = sizeof(float) * (2 * ATT_KT * (kc + 1) + ATT_WARPS * kc + 2 * nrel * kc + ATT_WARPS * nrel);
+  static const int at2_env = [] { const char* e = getenv("PIPER_B200_ATT96"); return e ? atoi(e) : 1; }();
+  if (at2_env && kc == AT2_D && nrel <= AT2_MAXREL && H % 4 == 0) {
+    const size_t smem2 = sizeof(float) * (AT2_Q * AT2_LD + AT2_K * AT2_LD + AT2_K * AT2_D + AT2_Q * AT2_LDP +
+                                          2 * AT2_MAXREL * AT2_D + AT2_Q * AT2_MAXREL);
+    static bool attr_set = false;
+    if (!attr_set) {
+      if (cudaFuncSetAttribute(attention96_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2) != cudaSuccess)
+        throw std::runtime_error("cuda: cannot raise dynamic shared memory limit for attention96_kernel");
+      attr_set = true;
+    }
+    dim3 grid2((max_len + AT2_Q - 1) / AT2_Q, n_heads, batch);
+    attention96_kernel<<<grid2, 256, smem2, ex.st>>>(qkv, rel_k, rel_v, out, utt_start, utt_len, H, window);
+    KLAUNCH(ex);
+    return;
+  }
   dim3 grid((max_len + ATT_WARPS - 1) / ATT_WARPS, n_heads, batch);
   attention_kernel<<<grid, ATT_WARPS * 32, smem, ex.st>>>(qkv, rel_k, rel_v, out, utt_start, utt_len, H,
                                                          n_heads, window);
