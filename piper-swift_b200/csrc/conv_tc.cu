@@ -41,6 +41,146 @@ struct TcKernelParams {
 
 namespace {
 
+// Epilogue of one 128-row x (n_groups * nt) accumulator tile, run by the four warps of a warpgroup (TMEM lane
+// quarter = warp % 4): waits for `bar`, then bias / utterance bias / residual / accumulate / mask and the
+// fp32 and 16-bit stores, or the tanh * sigmoid gate.
+__device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tmem_base, int m0, int ntile, int phase,
+                                          int warp, int lane, uint64_t* bar, uint32_t bar_parity) {
+  const int quarter = warp & 3;
+  const int q = m0 + quarter * 32 + lane;
+  const bool active = q < p.Q;
+  const int orow = active ? q * p.out_mul + (p.phases > 1 ? phase : 0) : 0;
+  int utt = 0;
+  if (active && p.row_utt) utt = p.row_utt[orow / p.valid_div];
+  const bool valid = utt >= 0;
+  mbar_wait(bar, bar_parity);
+  tc_fence_after();
+  const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
+  const int chunks = p.nt / 16;
+  if (p.gate) {
+    const TcEpi& e0 = p.e[0];
+    const TcEpi& e1 = p.e[1];
+    for (int c = 0; c < chunks; ++c) {
+      float va[16], vb[16];
+      __syncwarp();
+      tmem_ld16(lane_base + (uint32_t)(c * 16), va);
+      tmem_ld16(lane_base + (uint32_t)(p.nt + c * 16), vb);
+      if (!active) continue;
+      const int j = ntile * p.nt + c * 16;
+      uint32_t pk[8];
+      // bias and per-utterance conditioning come in as 16-byte vectors; the gate uses the hardware tanh
+      // (tanh.approx, rel. error ~2^-11 - the result is rounded to 16 bits right after):
+      // tanh(a) * sigmoid(b) = tanh(a) * (0.5 + 0.5 tanh(b / 2))
+      if (e0.bias) {
+        const float4* b0 = reinterpret_cast<const float4*>(e0.bias + j);
+        const float4* b1 = reinterpret_cast<const float4*>(e1.bias + j);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 x = __ldg(b0 + i), y = __ldg(b1 + i);
+          va[4 * i] += x.x; va[4 * i + 1] += x.y; va[4 * i + 2] += x.z; va[4 * i + 3] += x.w;
+          vb[4 * i] += y.x; vb[4 * i + 1] += y.y; vb[4 * i + 2] += y.z; vb[4 * i + 3] += y.w;
+        }
+      }
+      if (p.uttbias && valid) {
+        const float4* u0 = reinterpret_cast<const float4*>(p.uttbias + (size_t)utt * p.ldub + e0.ub_off + j);
+        const float4* u1 = reinterpret_cast<const float4*>(p.uttbias + (size_t)utt * p.ldub + e1.ub_off + j);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 x = __ldg(u0 + i), y = __ldg(u1 + i);
+          va[4 * i] += x.x; va[4 * i + 1] += x.y; va[4 * i + 2] += x.z; va[4 * i + 3] += x.w;
+          vb[4 * i] += y.x; vb[4 * i + 1] += y.y; vb[4 * i + 2] += y.z; vb[4 * i + 3] += y.w;
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 16; i += 2) {
+        float o[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          float ta, sb;
+          asm("tanh.approx.f32 %0, %1;" : "=f"(ta) : "f"(va[i + h]));
+          asm("tanh.approx.f32 %0, %1;" : "=f"(sb) : "f"(vb[i + h] * 0.5f));
+          o[h] = valid ? ta * fmaf(sb, 0.5f, 0.5f) : 0.f;
+        }
+        pk[i / 2] = pack2(o[0], o[1], p.f16);
+      }
+      uint4* dst = reinterpret_cast<uint4*>(static_cast<uint16_t*>(e0.out_act) + (size_t)orow * e0.ld_act + e0.col0 + j);
+      dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+      dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+    }
+  } else {
+    for (int g = 0; g < p.n_groups; ++g) {
+      const TcEpi& e = p.e[g];
+      for (int c = 0; c < chunks; ++c) {
+        float v[16];
+        __syncwarp();
+        tmem_ld16(lane_base + (uint32_t)(g * p.nt + c * 16), v);
+        if (!active) continue;
+        const int j = ntile * p.nt + c * 16;
+        const size_t ocol = (size_t)e.col0 + j;
+        if (e.bias) {
+          const float4* b4 = reinterpret_cast<const float4*>(e.bias + j);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 x = __ldg(b4 + i);
+            v[4 * i] += x.x; v[4 * i + 1] += x.y; v[4 * i + 2] += x.z; v[4 * i + 3] += x.w;
+          }
+        }
+        if (p.uttbias && valid) {
+          const float4* u4 = reinterpret_cast<const float4*>(p.uttbias + (size_t)utt * p.ldub + e.ub_off + j);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 x = __ldg(u4 + i);
+            v[4 * i] += x.x; v[4 * i + 1] += x.y; v[4 * i + 2] += x.z; v[4 * i + 3] += x.w;
+          }
+        }
+        if (e.res) {
+          const float4* r4 = reinterpret_cast<const float4*>(e.res + (size_t)orow * e.ld_res + ocol);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 r = r4[i];
+            v[4 * i] += r.x; v[4 * i + 1] += r.y; v[4 * i + 2] += r.z; v[4 * i + 3] += r.w;
+          }
+        }
+        float4* o4 = e.out_f32 ? reinterpret_cast<float4*>(e.out_f32 + (size_t)orow * e.ld_f32 + ocol) : nullptr;
+        if (e.accum) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 r = o4[i];
+            v[4 * i] += r.x; v[4 * i + 1] += r.y; v[4 * i + 2] += r.z; v[4 * i + 3] += r.w;
+          }
+        }
+        if (e.div != 0.f) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = v[i] / e.div;
+        }
+        if (!valid) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = 0.f;
+        }
+        if (o4) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
+        if (e.out_act) {
+          uint32_t pk[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            pk[i] = pack2(lrelu(v[2 * i], e.act_slope), lrelu(v[2 * i + 1], e.act_slope), p.f16);
+          if (e.act_planar) {
+            uint16_t* base = static_cast<uint16_t*>(e.out_act) + ((size_t)(ocol >> 3) * e.act_rows + e.act_pad + orow) * 8;
+            *reinterpret_cast<uint4*>(base) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            *reinterpret_cast<uint4*>(base + (size_t)e.act_rows * 8) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+          } else {
+            uint4* dst = reinterpret_cast<uint4*>(static_cast<uint16_t*>(e.out_act) + (size_t)orow * e.ld_act + ocol);
+            dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+          }
+        }
+      }
+    }
+  }
+  }
+
 __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
                                                              const __grid_constant__ CUtensorMap tmap_b,
                                                              const __grid_constant__ CUtensorMap tmap_ans,
@@ -179,111 +319,132 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
     if (elect_one()) umma_commit(tmem_full);
   } else {
     // ===== epilogue: warps 2..5, TMEM lane quarter = warp % 4 =====
-    const int quarter = warp & 3;
-    const int q = m0 + quarter * 32 + lane;
-    const bool active = q < p.Q;
-    const int orow = active ? q * p.out_mul + (p.phases > 1 ? phase : 0) : 0;
-    int utt = 0;
-    if (active && p.row_utt) utt = p.row_utt[orow / p.valid_div];
-    const bool valid = utt >= 0;
-    mbar_wait(tmem_full, 0);
-    tc_fence_after();
-    const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
-    const int chunks = p.nt / 16;
-    if (p.gate) {
-      const TcEpi& e0 = p.e[0];
-      const TcEpi& e1 = p.e[1];
-      for (int c = 0; c < chunks; ++c) {
-        float va[16], vb[16];
-        __syncwarp();
-        tmem_ld16(lane_base + (uint32_t)(c * 16), va);
-        tmem_ld16(lane_base + (uint32_t)(p.nt + c * 16), vb);
-        if (!active) continue;
-        const int j = ntile * p.nt + c * 16;
-        uint32_t pk[8];
-#pragma unroll
-        for (int i = 0; i < 16; i += 2) {
-          float o[2];
-#pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            float ta = va[i + h] + (e0.bias ? e0.bias[j + i + h] : 0.f);
-            float sa = vb[i + h] + (e1.bias ? e1.bias[j + i + h] : 0.f);
-            if (p.uttbias && valid) {
-              ta += p.uttbias[(size_t)utt * p.ldub + e0.ub_off + j + i + h];
-              sa += p.uttbias[(size_t)utt * p.ldub + e1.ub_off + j + i + h];
-            }
-            o[h] = valid ? tanhf(ta) * (1.0f / (1.0f + expf(-sa))) : 0.f;
-          }
-          pk[i / 2] = pack2(o[0], o[1], p.f16);
-        }
-        uint4* dst = reinterpret_cast<uint4*>(static_cast<uint16_t*>(e0.out_act) + (size_t)orow * e0.ld_act + e0.col0 + j);
-        dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-        dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-      }
-    } else {
-      for (int g = 0; g < p.n_groups; ++g) {
-        const TcEpi& e = p.e[g];
-        for (int c = 0; c < chunks; ++c) {
-          float v[16];
-          __syncwarp();
-          tmem_ld16(lane_base + (uint32_t)(g * p.nt + c * 16), v);
-          if (!active) continue;
-          const int j = ntile * p.nt + c * 16;
-          const size_t ocol = (size_t)e.col0 + j;
-          if (e.bias) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] += e.bias[j + i];
-          }
-          if (p.uttbias && valid) {
-            const float* ub = p.uttbias + (size_t)utt * p.ldub + e.ub_off + j;
-#pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] += ub[i];
-          }
-          if (e.res) {
-            const float4* r4 = reinterpret_cast<const float4*>(e.res + (size_t)orow * e.ld_res + ocol);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const float4 r = r4[i];
-              v[4 * i] += r.x; v[4 * i + 1] += r.y; v[4 * i + 2] += r.z; v[4 * i + 3] += r.w;
-            }
-          }
-          float4* o4 = e.out_f32 ? reinterpret_cast<float4*>(e.out_f32 + (size_t)orow * e.ld_f32 + ocol) : nullptr;
-          if (e.accum) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const float4 r = o4[i];
-              v[4 * i] += r.x; v[4 * i + 1] += r.y; v[4 * i + 2] += r.z; v[4 * i + 3] += r.w;
-            }
-          }
-          if (e.div != 0.f) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] = v[i] / e.div;
-          }
-          if (!valid) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] = 0.f;
-          }
-          if (o4) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-          }
-          if (e.out_act) {
-            uint32_t pk[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-              pk[i] = pack2(lrelu(v[2 * i], e.act_slope), lrelu(v[2 * i + 1], e.act_slope), p.f16);
-            if (e.act_planar) {
-              uint16_t* base = static_cast<uint16_t*>(e.out_act) + ((size_t)(ocol >> 3) * e.act_rows + e.act_pad + orow) * 8;
-              *reinterpret_cast<uint4*>(base) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-              *reinterpret_cast<uint4*>(base + (size_t)e.act_rows * 8) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-            } else {
-              uint4* dst = reinterpret_cast<uint4*>(static_cast<uint16_t*>(e.out_act) + (size_t)orow * e.ld_act + ocol);
-              dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-              dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-            }
+    tc_epilogue(p, tmem_base, m0, ntile, phase, warp, lane, tmem_full, 0u);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, p.tmem_cols);
+}
+
+// Persistent variant: one CTA per SM walks the (row tile, column tile, phase) list; the smem ring runs across
+// tiles (up to 8 stages) and the accumulator is double-buffered in TMEM, so the epilogue of tile i (two
+// warpgroups, one per TMEM buffer) overlaps the TMA/MMA main loop of tile i+1 inside the same CTA.
+constexpr int TCP_MAX_STAGES = 8;
+constexpr int TCP_THREADS = 64 + 2 * 128;
+
+__global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const __grid_constant__ CUtensorMap tmap_a,
+                                                                         const __grid_constant__ CUtensorMap tmap_b,
+                                                                         const TcKernelParams p, const int stages,
+                                                                         const int m_tiles, const int n_tiles,
+                                                                         const int total_tiles) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int row_bytes = p.kb * 2;
+  const int a_bytes = TC_BM * row_bytes;
+  const int b_bytes = p.nt * row_bytes;
+  const int stage_bytes = a_bytes + p.n_groups * b_bytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)stages * stage_bytes);
+  uint64_t* empty = full + TCP_MAX_STAGES;
+  uint64_t* acc_full = empty + TCP_MAX_STAGES;
+  uint64_t* acc_empty = acc_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmap_a);
+    prefetch_tmap(&tmap_b);
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&acc_full[s], 1);
+      mbar_init(&acc_empty[s], 4);
+    }
+    fence_barrier_init();
+  } else if (warp == 1) {
+    tmem_alloc(tmem_slot, p.tmem_cols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+  const uint32_t acc_stride = (uint32_t)(p.n_groups * p.nt);
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int s = 0; uint32_t ph = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int mt = t % m_tiles, rest = t / m_tiles;
+        const int ntile = rest % n_tiles, phase = rest / n_tiles;
+        const int m0 = mt * TC_BM;
+        const int in_off = p.phases > 1 ? (phase + p.ct_pad) / p.phases : p.in_off;
+        for (int tap = 0; tap < p.taps; ++tap) {
+          const int arow = m0 + in_off + tap * p.tap_step;
+          const int wrow = (phase * p.taps + tap) * p.cout_rows + ntile * p.nt;
+          for (int kbi = 0; kbi < p.kblocks; ++kbi) {
+            mbar_wait(&empty[s], ph ^ 1u);
+            uint8_t* st = smem + (size_t)s * stage_bytes;
+            const int dbg = p.relu;   // DEBUG timing probe: 1 skips the activation loads, 2 the weight loads
+            mbar_expect_tx(&full[s], (uint32_t)((dbg == 1 ? 0 : a_bytes) + (dbg == 2 ? 0 : p.n_groups * b_bytes)));
+            if (dbg != 1) tma_load_2d(&tmap_a, &full[s], st, kbi * p.kb, arow);
+            if (dbg != 2)
+              for (int g = 0; g < p.n_groups; ++g)
+                tma_load_2d(&tmap_b, &full[s], st + a_bytes + g * b_bytes, kbi * p.kb, wrow + p.e[g].row0);
+            if (dbg == 3) mbar_arrive(&full[s]);
+            if (++s == stages) { s = 0; ph ^= 1u; }
           }
         }
       }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: warp-uniform control flow, one elected lane issues =====
+    const uint32_t idesc = make_idesc(p.nt, p.f16);
+    const int ksteps = p.kb / 16;
+    const uint64_t d_hi = make_smem_desc(0, p.kb);
+    const uint32_t stage_lo = smem_u32(smem) >> 4;
+    const uint32_t stage16 = (uint32_t)stage_bytes >> 4, a16 = (uint32_t)a_bytes >> 4, b16 = (uint32_t)b_bytes >> 4;
+    const int n_it = p.taps * p.kblocks;
+    int s = 0; uint32_t ph = 0, li = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++li) {
+      const uint32_t buf = li & 1u;
+      mbar_wait(&acc_empty[buf], ((li >> 1) & 1u) ^ 1u);     // the epilogue drained this accumulator buffer
+      tc_fence_after();
+      const uint32_t acc = tmem_base + buf * acc_stride;
+      for (int i = 0; i < n_it; ++i) {
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        const uint32_t al = stage_lo + (uint32_t)s * stage16, bl = al + a16;
+        if (elect_one()) {
+          if (p.relu != 5)   // DEBUG timing probe: 5 issues no MMAs
+          for (int g = 0; g < p.n_groups; ++g)
+            for (int k = 0; k < ksteps; ++k)
+              umma_f16(acc + (uint32_t)(g * p.nt), d_hi | (uint64_t)(al + 2u * (uint32_t)k),
+                       d_hi | (uint64_t)(bl + (uint32_t)g * b16 + 2u * (uint32_t)k), idesc, (i == 0 && k == 0) ? 0u : 1u);
+          umma_commit(&empty[s]);                 // frees the smem slot when these MMAs retire
+        }
+        if (++s == stages) { s = 0; ph ^= 1u; }
+      }
+      if (elect_one()) umma_commit(&acc_full[buf]);
+    }
+  } else {
+    // ===== epilogue: warpgroup g (warps 2..5 / 6..9) owns TMEM buffer g, i.e. every other tile =====
+    const uint32_t group = (uint32_t)(warp - 2) >> 2;
+    uint32_t li = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++li) {
+      if ((li & 1u) != group) continue;
+      const int mt = t % m_tiles, rest = t / m_tiles;
+      const int ntile = rest % n_tiles, phase = rest / n_tiles;
+      if (p.relu == 4) {   // DEBUG timing probe: no epilogue work
+        mbar_wait(&acc_full[group], (li >> 1) & 1u);
+        tc_fence_after();
+      } else
+      tc_epilogue(p, tmem_base + group * acc_stride, mt * TC_BM, ntile, phase, warp, lane, &acc_full[group], (li >> 1) & 1u);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[group]);
     }
   }
   tc_fence_before();
@@ -319,6 +480,38 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
   p.tmem_cols = cols;
 
   const CUtensorMap ta = make_map(a.in, (uint64_t)a.cin, (uint64_t)a.R_in, (uint64_t)a.ldin, w.kb, TC_BM, a.f16);
+  static const int persist_env = [] { const char* e = getenv("PIPER_B200_TC_PERSIST"); return e ? atoi(e) : 1; }();
+  if (persist_env && a.n_groups * a.nt <= 256) {
+    static int num_sms = 0;
+    if (!num_sms) {
+      int dev = 0;
+      cudaGetDevice(&dev);
+      if (cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || num_sms <= 0)
+        throw std::runtime_error("cuda: cannot query the SM count");
+      if (cudaFuncSetAttribute(conv_tc_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess)
+        throw std::runtime_error("cuda: cannot raise dynamic shared memory limit for conv_tc_persist_kernel");
+    }
+    const CUtensorMap tbp = make_map(w.w, (uint64_t)w.cin_pad, (uint64_t)w.phases * w.taps * w.cout, (uint64_t)w.cin_pad,
+                                     w.kb, a.nt, a.f16);
+    p.window = 0;
+    static const int dbg_env = [] { const char* e = getenv("PIPER_B200_TC_DEBUG_SKIP"); return e ? atoi(e) : 0; }();
+    p.relu = dbg_env;
+    uint32_t pc = 32;
+    while ((int)pc < 2 * a.n_groups * a.nt) pc <<= 1;
+    p.tmem_cols = pc;
+    const int sb = TC_BM * w.kb * 2 + a.n_groups * a.nt * w.kb * 2;
+    int st = (TC_SMEM_MAX - 2048) / sb;
+    if (st > TCP_MAX_STAGES) st = TCP_MAX_STAGES;
+    if (st < 2) throw std::runtime_error("conv_tc: tile does not fit in shared memory");
+    const int m_tiles = (a.Q + TC_BM - 1) / TC_BM;
+    const int total = m_tiles * a.n_tiles * w.phases;
+    const int grid = total < num_sms ? total : num_sms;
+    const size_t smem = (size_t)st * sb + 1024 + 512;
+    ProfScope ps(ex, Prof::CONV_TC, 2.0 * a.Q * w.phases * w.taps * w.cin * (double)(a.n_groups * a.nt * a.n_tiles));
+    conv_tc_persist_kernel<<<grid, TCP_THREADS, smem, ex.st>>>(ta, tbp, p, st, m_tiles, a.n_tiles, total);
+    ++ex.launches;
+    return;
+  }
   const CUtensorMap tb = make_map(w.w, (uint64_t)w.cin_pad, (uint64_t)w.phases * w.taps * w.cout, (uint64_t)w.cin_pad,
                                   w.kb, a.nt, a.f16);
   const int span = (w.taps - 1) * (a.tap_step < 0 ? -a.tap_step : a.tap_step);
