@@ -45,7 +45,7 @@ namespace {
 // quarter = warp % 4): waits for `bar`, then bias / utterance bias / residual / accumulate / mask and the
 // fp32 and 16-bit stores, or the tanh * sigmoid gate.
 __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tmem_base, int m0, int ntile, int phase,
-                                          int warp, int lane, uint64_t* bar, uint32_t bar_parity) {
+                                          int warp, int lane, uint64_t* bar, uint32_t bar_parity, float* tbuf) {
   const int quarter = warp & 3;
   const int q = m0 + quarter * 32 + lane;
   const bool active = q < p.Q;
@@ -106,6 +106,94 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
       uint4* dst = reinterpret_cast<uint4*>(static_cast<uint16_t*>(e0.out_act) + (size_t)orow * e0.ld_act + e0.col0 + j);
       dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
       dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+    }
+  } else if (tbuf && (p.nt & 31) == 0) {
+    // Coalesced path: 32-column chunks.  Bias / conditioning are added with lane = row (TMEM layout); the
+    // chunk then goes through a per-warp 32 x 36 float buffer so that residual loads, accumulation and the
+    // fp32 / 16-bit stores run with 8 lanes per row: every warp instruction touches 4 full 128-byte lines
+    // instead of 32 lines (the lane = row form made the L1 tag stage the limit of every epilogue).
+    const uint32_t act_mask = __ballot_sync(0xffffffffu, active);
+    const uint32_t valid_mask = __ballot_sync(0xffffffffu, valid);
+    const int sub = lane >> 3, c4 = (lane & 7) * 4;
+    const int row_base = m0 + quarter * 32;
+    for (int g = 0; g < p.n_groups; ++g) {
+      const TcEpi& e = p.e[g];
+      const bool planar = e.out_act && e.act_planar;      // only used by plain convolutions (no residual)
+      for (int c = 0; c < p.nt / 32; ++c) {
+        float v[32];
+        __syncwarp();
+        tmem_ld16(lane_base + (uint32_t)(g * p.nt + c * 32), v);
+        tmem_ld16(lane_base + (uint32_t)(g * p.nt + c * 32 + 16), v + 16);
+        const int j = ntile * p.nt + c * 32;
+        const size_t ocol = (size_t)e.col0 + j;
+        if (e.bias) {
+          const float4* b4 = reinterpret_cast<const float4*>(e.bias + j);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 x = __ldg(b4 + i);
+            v[4 * i] += x.x; v[4 * i + 1] += x.y; v[4 * i + 2] += x.z; v[4 * i + 3] += x.w;
+          }
+        }
+        if (p.uttbias && active && valid) {
+          const float4* u4 = reinterpret_cast<const float4*>(p.uttbias + (size_t)utt * p.ldub + e.ub_off + j);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 x = __ldg(u4 + i);
+            v[4 * i] += x.x; v[4 * i + 1] += x.y; v[4 * i + 2] += x.z; v[4 * i + 3] += x.w;
+          }
+        }
+        if (planar && active) {   // group-planar operand of the fused MRF stage: 16 bytes per (row, plane)
+          uint16_t* base = static_cast<uint16_t*>(e.out_act) + ((size_t)(ocol >> 3) * e.act_rows + e.act_pad + orow) * 8;
+#pragma unroll
+          for (int pl = 0; pl < 4; ++pl) {
+            uint32_t pk[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              pk[i] = valid ? pack2(lrelu(v[8 * pl + 2 * i], e.act_slope), lrelu(v[8 * pl + 2 * i + 1], e.act_slope), p.f16) : 0u;
+            *reinterpret_cast<uint4*>(base + (size_t)pl * e.act_rows * 8) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+          }
+        }
+        if (!e.out_f32 && (planar || !e.out_act)) continue;
+        __syncwarp();                                     // the previous chunk's readers are done with tbuf
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          *reinterpret_cast<float4*>(tbuf + lane * 36 + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        __syncwarp();
+        // all global loads of the chunk are issued before the first use (8-16 independent 16-byte loads per
+        // lane in flight): with only eight epilogue warps per SM the epilogue is latency-, not bandwidth-bound
+        float4 rr[8], aa[8];
+        const size_t orow0 = (size_t)(row_base + sub) * p.out_mul + (p.phases > 1 ? phase : 0);
+        const size_t rstep = (size_t)4 * p.out_mul;
+        float* of = e.out_f32 ? e.out_f32 + orow0 * e.ld_f32 + ocol + c4 : nullptr;
+        if (e.res) {
+          const float* rp = e.res + orow0 * e.ld_res + ocol + c4;
+#pragma unroll
+          for (int it = 0; it < 8; ++it)
+            if ((act_mask >> (it * 4 + sub)) & 1u) rr[it] = *reinterpret_cast<const float4*>(rp + it * rstep * e.ld_res);
+        }
+        if (e.accum) {
+#pragma unroll
+          for (int it = 0; it < 8; ++it)
+            if ((act_mask >> (it * 4 + sub)) & 1u) aa[it] = *reinterpret_cast<const float4*>(of + it * rstep * e.ld_f32);
+        }
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          const int row = it * 4 + sub;
+          if (!((act_mask >> row) & 1u)) continue;
+          float4 x = *reinterpret_cast<const float4*>(tbuf + row * 36 + c4);
+          if (e.res) { x.x += rr[it].x; x.y += rr[it].y; x.z += rr[it].z; x.w += rr[it].w; }
+          if (e.accum) { x.x += aa[it].x; x.y += aa[it].y; x.z += aa[it].z; x.w += aa[it].w; }
+          if (e.div != 0.f) { x.x = x.x / e.div; x.y = x.y / e.div; x.z = x.z / e.div; x.w = x.w / e.div; }
+          if (!((valid_mask >> row) & 1u)) x = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (of) *reinterpret_cast<float4*>(of + it * rstep * e.ld_f32) = x;
+          if (e.out_act && !planar) {
+            const uint32_t lo = pack2(lrelu(x.x, e.act_slope), lrelu(x.y, e.act_slope), p.f16);
+            const uint32_t hi = pack2(lrelu(x.z, e.act_slope), lrelu(x.w, e.act_slope), p.f16);
+            *reinterpret_cast<uint2*>(static_cast<uint16_t*>(e.out_act) + (orow0 + it * rstep) * e.ld_act + ocol + c4) =
+                make_uint2(lo, hi);
+          }
+        }
+      }
     }
   } else {
     for (int g = 0; g < p.n_groups; ++g) {
@@ -319,7 +407,7 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
     if (elect_one()) umma_commit(tmem_full);
   } else {
     // ===== epilogue: warps 2..5, TMEM lane quarter = warp % 4 =====
-    tc_epilogue(p, tmem_base, m0, ntile, phase, warp, lane, tmem_full, 0u);
+    tc_epilogue(p, tmem_base, m0, ntile, phase, warp, lane, tmem_full, 0u, nullptr);
   }
   tc_fence_before();
   __syncthreads();
@@ -348,6 +436,7 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
   uint64_t* acc_full = empty + TCP_MAX_STAGES;
   uint64_t* acc_empty = acc_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  float* tbuf_base = reinterpret_cast<float*>(smem + (size_t)stages * stage_bytes + 512);   // 8 warps x 32 x 36 floats
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
@@ -441,7 +530,8 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
         mbar_wait(&acc_full[group], (li >> 1) & 1u);
         tc_fence_after();
       } else
-      tc_epilogue(p, tmem_base + group * acc_stride, mt * TC_BM, ntile, phase, warp, lane, &acc_full[group], (li >> 1) & 1u);
+      tc_epilogue(p, tmem_base + group * acc_stride, mt * TC_BM, ntile, phase, warp, lane, &acc_full[group], (li >> 1) & 1u,
+                  tbuf_base + (warp - 2) * (32 * 36));
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[group]);
@@ -500,13 +590,14 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
     while ((int)pc < 2 * a.n_groups * a.nt) pc <<= 1;
     p.tmem_cols = pc;
     const int sb = TC_BM * w.kb * 2 + a.n_groups * a.nt * w.kb * 2;
-    int st = (TC_SMEM_MAX - 2048) / sb;
+    constexpr int TBUF_BYTES = 8 * 32 * 36 * 4;
+    int st = (TC_SMEM_MAX - 2048 - TBUF_BYTES) / sb;
     if (st > TCP_MAX_STAGES) st = TCP_MAX_STAGES;
     if (st < 2) throw std::runtime_error("conv_tc: tile does not fit in shared memory");
     const int m_tiles = (a.Q + TC_BM - 1) / TC_BM;
     const int total = m_tiles * a.n_tiles * w.phases;
     const int grid = total < num_sms ? total : num_sms;
-    const size_t smem = (size_t)st * sb + 1024 + 512;
+    const size_t smem = (size_t)st * sb + 1024 + 512 + TBUF_BYTES;
     ProfScope ps(ex, Prof::CONV_TC, 2.0 * a.Q * w.phases * w.taps * w.cin * (double)(a.n_groups * a.nt * a.n_tiles));
     conv_tc_persist_kernel<<<grid, TCP_THREADS, smem, ex.st>>>(ta, tbp, p, st, m_tiles, a.n_tiles, total);
     ++ex.launches;
