@@ -45,7 +45,8 @@ namespace {
 // quarter = warp % 4): waits for `bar`, then bias / utterance bias / residual / accumulate / mask and the
 // fp32 and 16-bit stores, or the tanh * sigmoid gate.
 __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tmem_base, int m0, int ntile, int phase,
-                                          int warp, int lane, uint64_t* bar, uint32_t bar_parity, float* tbuf) {
+                                          int warp, int lane, uint64_t* bar, uint32_t bar_parity, float* tbuf,
+                                            int part, int nparts) {   // this warpgroup's share of the column chunks
   const int quarter = warp & 3;
   const int q = m0 + quarter * 32 + lane;
   const bool active = q < p.Q;
@@ -60,7 +61,7 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
   if (p.gate) {
     const TcEpi& e0 = p.e[0];
     const TcEpi& e1 = p.e[1];
-    for (int c = 0; c < chunks; ++c) {
+    for (int c = part * chunks / nparts; c < (part + 1) * chunks / nparts; ++c) {
       float va[16], vb[16];
       __syncwarp();
       tmem_ld16(lane_base + (uint32_t)(c * 16), va);
@@ -116,10 +117,12 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
     const uint32_t valid_mask = __ballot_sync(0xffffffffu, valid);
     const int sub = lane >> 3, c4 = (lane & 7) * 4;
     const int row_base = m0 + quarter * 32;
-    for (int g = 0; g < p.n_groups; ++g) {
+    const int cpg = p.nt / 32, nunits = p.n_groups * cpg;
+    for (int f = part * nunits / nparts; f < (part + 1) * nunits / nparts; ++f) {
+      const int g = f / cpg, c = f - g * cpg;
       const TcEpi& e = p.e[g];
       const bool planar = e.out_act && e.act_planar;      // only used by plain convolutions (no residual)
-      for (int c = 0; c < p.nt / 32; ++c) {
+      {
         float v[32];
         __syncwarp();
         tmem_ld16(lane_base + (uint32_t)(g * p.nt + c * 32), v);
@@ -196,9 +199,11 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
       }
     }
   } else {
-    for (int g = 0; g < p.n_groups; ++g) {
+    const int nunits = p.n_groups * chunks;
+    for (int f = part * nunits / nparts; f < (part + 1) * nunits / nparts; ++f) {
+      const int g = f / chunks, c = f - g * chunks;
       const TcEpi& e = p.e[g];
-      for (int c = 0; c < chunks; ++c) {
+      {
         float v[16];
         __syncwarp();
         tmem_ld16(lane_base + (uint32_t)(g * p.nt + c * 16), v);
@@ -407,7 +412,7 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
     if (elect_one()) umma_commit(tmem_full);
   } else {
     // ===== epilogue: warps 2..5, TMEM lane quarter = warp % 4 =====
-    tc_epilogue(p, tmem_base, m0, ntile, phase, warp, lane, tmem_full, 0u, nullptr);
+    tc_epilogue(p, tmem_base, m0, ntile, phase, warp, lane, tmem_full, 0u, nullptr, 0, 1);
   }
   tc_fence_before();
   __syncthreads();
@@ -418,7 +423,8 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
 // tiles (up to 8 stages) and the accumulator is double-buffered in TMEM, so the epilogue of tile i (two
 // warpgroups, one per TMEM buffer) overlaps the TMA/MMA main loop of tile i+1 inside the same CTA.
 constexpr int TCP_MAX_STAGES = 8;
-constexpr int TCP_THREADS = 64 + 2 * 128;
+constexpr int TCP_EG = 1;                      // epilogue warpgroups per TMEM buffer (column split); 2 starves registers
+constexpr int TCP_THREADS = 64 + 2 * TCP_EG * 128;   // producer, MMA issuer, epilogue warpgroups
 
 __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const __grid_constant__ CUtensorMap tmap_a,
                                                                          const __grid_constant__ CUtensorMap tmap_b,
@@ -436,7 +442,7 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
   uint64_t* acc_full = empty + TCP_MAX_STAGES;
   uint64_t* acc_empty = acc_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
-  float* tbuf_base = reinterpret_cast<float*>(smem + (size_t)stages * stage_bytes + 512);   // 8 warps x 32 x 36 floats
+  float* tbuf_base = reinterpret_cast<float*>(smem + (size_t)stages * stage_bytes + 512);   // one 32 x 36 float tile per epilogue warp
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
@@ -448,7 +454,7 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&acc_full[s], 1);
-      mbar_init(&acc_empty[s], 4);
+      mbar_init(&acc_empty[s], 4 * TCP_EG);   // every warp of the warpgroups draining this buffer
     }
     fence_barrier_init();
   } else if (warp == 1) {
@@ -466,8 +472,10 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
     if (lane == 0) {
       int s = 0; uint32_t ph = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const int mt = t % m_tiles, rest = t / m_tiles;
-        const int ntile = rest % n_tiles, phase = rest / n_tiles;
+        // phase fastest: the polyphase outputs of one row tile interleave in memory (row = q * stride + phase), so
+        // they are produced back to back and merge in L2 instead of rewriting every line `phases` times
+        const int phase = t % p.phases, rest = t / p.phases;
+        const int mt = rest % m_tiles, ntile = rest / m_tiles;
         const int m0 = mt * TC_BM;
         const int in_off = p.phases > 1 ? (phase + p.ct_pad) / p.phases : p.in_off;
         for (int tap = 0; tap < p.taps; ++tap) {
@@ -519,19 +527,19 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
       if (elect_one()) umma_commit(&acc_full[buf]);
     }
   } else {
-    // ===== epilogue: warpgroup g (warps 2..5 / 6..9) owns TMEM buffer g, i.e. every other tile =====
-    const uint32_t group = (uint32_t)(warp - 2) >> 2;
+    // ===== epilogue: four warpgroups = (TMEM buffer, i.e. every other tile) x (half of the column chunks) =====
+    const uint32_t group = ((uint32_t)(warp - 2) >> 2) & 1u, half = (uint32_t)(warp - 2) >> 3;
     uint32_t li = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++li) {
       if ((li & 1u) != group) continue;
-      const int mt = t % m_tiles, rest = t / m_tiles;
-      const int ntile = rest % n_tiles, phase = rest / n_tiles;
+      const int phase = t % p.phases, rest = t / p.phases;
+      const int mt = rest % m_tiles, ntile = rest / m_tiles;
       if (p.relu == 4) {   // DEBUG timing probe: no epilogue work
         mbar_wait(&acc_full[group], (li >> 1) & 1u);
         tc_fence_after();
       } else
       tc_epilogue(p, tmem_base + group * acc_stride, mt * TC_BM, ntile, phase, warp, lane, &acc_full[group], (li >> 1) & 1u,
-                  tbuf_base + (warp - 2) * (32 * 36));
+                  tbuf_base + (warp - 2) * (32 * 36), (int)half, TCP_EG);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[group]);
@@ -590,7 +598,7 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
     while ((int)pc < 2 * a.n_groups * a.nt) pc <<= 1;
     p.tmem_cols = pc;
     const int sb = TC_BM * w.kb * 2 + a.n_groups * a.nt * w.kb * 2;
-    constexpr int TBUF_BYTES = 8 * 32 * 36 * 4;
+    constexpr int TBUF_BYTES = 2 * TCP_EG * 4 * 32 * 36 * 4;
     int st = (TC_SMEM_MAX - 2048 - TBUF_BYTES) / sb;
     if (st > TCP_MAX_STAGES) st = TCP_MAX_STAGES;
     if (st < 2) throw std::runtime_error("conv_tc: tile does not fit in shared memory");
