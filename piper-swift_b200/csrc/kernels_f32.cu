@@ -278,11 +278,14 @@ __global__ void __launch_bounds__(256, 2) conv_f32_w192_kernel(ConvArgs a) {
     in_off = (ph + a.ct_pad) / a.phases;
     wbase += (size_t)ph * a.taps * a.cin * a.ldw;
   }
-  float acc[6][12];
+  // accumulators are kept as f32x2 pairs (columns j, j+1): the inner product runs on FFMA2 (fma.rn.f32x2, one
+  // instruction = two IEEE fmas with the row value broadcast), which halves the issue slots the FMAs need -
+  // the scalar form was issue-bound at ~60 % FMA-pipe utilisation.  Same rounding as fmaf per element.
+  unsigned long long acc2[6][6];
 #pragma unroll
   for (int i = 0; i < 6; ++i)
 #pragma unroll
-    for (int j = 0; j < 12; ++j) acc[i][j] = 0.f;
+    for (int j = 0; j < 6; ++j) acc2[i][j] = 0ull;
 
   // loaders: A = 96 rows x 16 channels = 384 float4 (threads 0..127 take a second one), B = 16 x 192 = 768 float4
   const int kchunks = (a.cin + WBK - 1) / WBK;
@@ -345,18 +348,22 @@ __global__ void __launch_bounds__(256, 2) conv_f32_w192_kernel(ConvArgs a) {
     if (it + 1 < n_it) fetch(it + 1);
 #pragma unroll
     for (int k = 0; k < WBK; ++k) {
-      float ar[6], br[12];
+      float ar[6];
+      unsigned long long br2[6];
 #pragma unroll
       for (int g = 0; g < 3; ++g) {                     // rows g*32 + ty*2 + {0,1}; columns g*64 + tx*4 + {0..3}
         const float2 a2 = *reinterpret_cast<const float2*>(&As[buf][k][g * 32 + ty * 2]);
         ar[2 * g] = a2.x; ar[2 * g + 1] = a2.y;
-        const float4 b4 = *reinterpret_cast<const float4*>(&Bs[buf][k][g * 64 + tx * 4]);
-        br[4 * g] = b4.x; br[4 * g + 1] = b4.y; br[4 * g + 2] = b4.z; br[4 * g + 3] = b4.w;
+        const ulonglong2 b4 = *reinterpret_cast<const ulonglong2*>(&Bs[buf][k][g * 64 + tx * 4]);
+        br2[2 * g] = b4.x; br2[2 * g + 1] = b4.y;
       }
 #pragma unroll
-      for (int i = 0; i < 6; ++i)
+      for (int i = 0; i < 6; ++i) {
+        unsigned long long a2;
+        asm("mov.b64 %0, {%1, %1};" : "=l"(a2) : "f"(ar[i]));
 #pragma unroll
-        for (int j = 0; j < 12; ++j) acc[i][j] = fmaf(ar[i], br[j], acc[i][j]);
+        for (int j = 0; j < 6; ++j) asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc2[i][j]) : "l"(a2), "l"(br2[j]));
+      }
     }
     if (it + 1 < n_it) {
       stash(buf ^ 1);
@@ -364,6 +371,12 @@ __global__ void __launch_bounds__(256, 2) conv_f32_w192_kernel(ConvArgs a) {
     }
   }
   // epilogue (same semantics as conv_f32_kernel)
+  float acc[6][12];
+#pragma unroll
+  for (int i = 0; i < 6; ++i)
+#pragma unroll
+    for (int j = 0; j < 6; ++j)
+      asm("mov.b64 {%0, %1}, %2;" : "=f"(acc[i][2 * j]), "=f"(acc[i][2 * j + 1]) : "l"(acc2[i][j]));
 #pragma unroll
   for (int i = 0; i < 6; ++i) {
     const int q = q0 + (i >> 1) * 32 + ty * 2 + (i & 1);
