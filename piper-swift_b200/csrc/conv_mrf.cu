@@ -80,7 +80,9 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
   // role branches become uniform and the MMA descriptors live in uniform registers (without this every
   // tcgen05.mma pays for several R2UR moves - measured 100 vs 55 cycles per issue, tools/micro/umma_bench.cu)
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
-  // debug timeline: lane 0 of every warp of CTA 0 appends (tag<<24 | n<<8 | i, clock) pairs to its own region
+  // debug timeline (build with -DPIPER_MRF_TRACE, run with PIPER_B200_MRF_TRACE=<path>, read with
+  // tools/mrf_trace.py): lane 0 of every warp of CTA 0 appends (tag<<24 | n<<8 | i, clock) to its own region
+#ifdef PIPER_MRF_TRACE
   uint32_t trace_n = 0;
   auto TRACE = [&](uint32_t tag, uint32_t n, uint32_t i) {
     if (p.trace && blockIdx.x == 0 && lane == 0 && trace_n < MRF_TRACE_EVENTS) {
@@ -90,6 +92,9 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
       ++trace_n;
     }
   };
+#else
+  auto TRACE = [](uint32_t, uint32_t, uint32_t) {};
+#endif
 
   // zero the conv2 operand window once (its guard rows are never written afterwards)
   for (int i = threadIdx.x; i < win_bytes / 16; i += blockDim.x)
@@ -519,7 +524,11 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   if (smem > (size_t)TC_SMEM_MAX) throw std::runtime_error("conv_mrf: shared memory budget exceeded");
   const int grid = std::min(p.n_windows, num_sms);
   ProfScope ps(ex, Prof::MRF, 2.0 * a.R * a.C * a.C * (double)a.total_taps);
+#ifdef PIPER_MRF_TRACE
   static const char* trace_path = getenv("PIPER_B200_MRF_TRACE");
+#else
+  static const char* trace_path = nullptr;
+#endif
   const size_t trace_words = (size_t)(96 + 128 * 5) / 32 * MRF_TRACE_EVENTS * 2;
   if (trace_path) {
     if (cudaMalloc(&p.trace, trace_words * 4) != cudaSuccess) throw std::runtime_error("conv_mrf: trace buffer");

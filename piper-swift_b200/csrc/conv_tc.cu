@@ -484,13 +484,10 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
           for (int kbi = 0; kbi < p.kblocks; ++kbi) {
             mbar_wait(&empty[s], ph ^ 1u);
             uint8_t* st = smem + (size_t)s * stage_bytes;
-            const int dbg = p.relu;   // DEBUG timing probe: 1 skips the activation loads, 2 the weight loads
-            mbar_expect_tx(&full[s], (uint32_t)((dbg == 1 ? 0 : a_bytes) + (dbg == 2 ? 0 : p.n_groups * b_bytes)));
-            if (dbg != 1) tma_load_2d(&tmap_a, &full[s], st, kbi * p.kb, arow);
-            if (dbg != 2)
-              for (int g = 0; g < p.n_groups; ++g)
-                tma_load_2d(&tmap_b, &full[s], st + a_bytes + g * b_bytes, kbi * p.kb, wrow + p.e[g].row0);
-            if (dbg == 3) mbar_arrive(&full[s]);
+            mbar_expect_tx(&full[s], (uint32_t)stage_bytes);
+            tma_load_2d(&tmap_a, &full[s], st, kbi * p.kb, arow);
+            for (int g = 0; g < p.n_groups; ++g)
+              tma_load_2d(&tmap_b, &full[s], st + a_bytes + g * b_bytes, kbi * p.kb, wrow + p.e[g].row0);
             if (++s == stages) { s = 0; ph ^= 1u; }
           }
         }
@@ -515,7 +512,6 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
         tc_fence_after();
         const uint32_t al = stage_lo + (uint32_t)s * stage16, bl = al + a16;
         if (elect_one()) {
-          if (p.relu != 5)   // DEBUG timing probe: 5 issues no MMAs
           for (int g = 0; g < p.n_groups; ++g)
             for (int k = 0; k < ksteps; ++k)
               umma_f16(acc + (uint32_t)(g * p.nt), d_hi | (uint64_t)(al + 2u * (uint32_t)k),
@@ -534,10 +530,6 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
       if ((li & 1u) != group) continue;
       const int phase = t % p.phases, rest = t / p.phases;
       const int mt = rest % m_tiles, ntile = rest / m_tiles;
-      if (p.relu == 4) {   // DEBUG timing probe: no epilogue work
-        mbar_wait(&acc_full[group], (li >> 1) & 1u);
-        tc_fence_after();
-      } else
       tc_epilogue(p, tmem_base + group * acc_stride, mt * TC_BM, ntile, phase, warp, lane, &acc_full[group], (li >> 1) & 1u,
                   tbuf_base + (warp - 2) * (32 * 36), (int)half, TCP_EG);
       tc_fence_before();
@@ -592,8 +584,6 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
     const CUtensorMap tbp = make_map(w.w, (uint64_t)w.cin_pad, (uint64_t)w.phases * w.taps * w.cout, (uint64_t)w.cin_pad,
                                      w.kb, a.nt, a.f16);
     p.window = 0;
-    static const int dbg_env = [] { const char* e = getenv("PIPER_B200_TC_DEBUG_SKIP"); return e ? atoi(e) : 0; }();
-    p.relu = dbg_env;
     uint32_t pc = 32;
     while ((int)pc < 2 * a.n_groups * a.nt) pc <<= 1;
     p.tmem_cols = pc;

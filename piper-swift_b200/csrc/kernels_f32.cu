@@ -1306,9 +1306,79 @@ __global__ void __launch_bounds__(CP_ROWS) conv_post_tanh_kernel(const float* __
   }
   out[r] = tanhf(acc);
 }
+// Warp-per-row-block variant for k <= 7 and C = 32 * n (n <= 4): lane c owns channels c, c+32, ..; the taps'
+// weights sit in registers, input rows are read straight from global memory (one coalesced 128-byte load per
+// row and channel group, ~40 independent loads in flight per lane), 32 rows are reduced at once with a
+// butterfly transpose (31 shuffles per 32 rows) and stored with one coalesced write.  No shared memory: the
+// staged kernel above is bound by its 2 LDS per FMA; this one by HBM.
+constexpr int CPW_ROWS = 32, CPW_MAXK = 7, CPW_MAXN = 4;
+template <int N>
+__global__ void __launch_bounds__(256) conv_post_tanh_warp_kernel(const float* __restrict__ in, const float* __restrict__ w,
+                                                                  int k, float slope, const int* __restrict__ row_utt,
+                                                                  int valid_div, float* __restrict__ out, int R) {
+  constexpr int C = 32 * N;
+  const int lane = threadIdx.x & 31;
+  const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t r0 = (int64_t)wid * CPW_ROWS;
+  if (r0 >= R) return;
+  const int pad = (k - 1) / 2;
+  float wv[N][CPW_MAXK];
+#pragma unroll
+  for (int n = 0; n < N; ++n)
+#pragma unroll
+    for (int t = 0; t < CPW_MAXK; ++t) wv[n][t] = t < k ? w[t * C + n * 32 + lane] : 0.f;
+  float v[CPW_ROWS];
+#pragma unroll
+  for (int i = 0; i < CPW_ROWS; ++i) v[i] = 0.f;
+#pragma unroll
+  for (int n = 0; n < N; ++n) {
+    float x[CPW_ROWS + CPW_MAXK - 1];
+#pragma unroll
+    for (int i = 0; i < CPW_ROWS + CPW_MAXK - 1; ++i) {
+      const int64_t gr = r0 + i - pad;
+      float xv = 0.f;
+      if (i < CPW_ROWS + k - 1 && gr >= 0 && gr < R) xv = in[gr * C + n * 32 + lane];
+      x[i] = xv >= 0.f ? xv : xv * slope;
+    }
+#pragma unroll
+    for (int i = 0; i < CPW_ROWS; ++i)
+#pragma unroll
+      for (int t = 0; t < CPW_MAXK; ++t) v[i] = fmaf(x[i + t], wv[n][t], v[i]);
+  }
+  // butterfly transpose-reduce: afterwards lane l holds the channel sum of row r0 + l
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) {
+#pragma unroll
+    for (int j = 0; j < s; ++j) {
+      const bool up = (lane & s) != 0;
+      const float keep = up ? v[j + s] : v[j];
+      const float send = up ? v[j] : v[j + s];
+      v[j] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+    }
+  }
+  const int64_t r = r0 + lane;
+  if (r < R) {
+    const bool valid = !row_utt || row_utt[r / valid_div] >= 0;
+    out[r] = valid ? tanhf(v[0]) : 0.f;
+  }
+}
+
 void launch_conv_post_tanh(Exec& ex, const float* in, int C, const float* w, int k, float slope,
                            const int* row_utt, int valid_div, float* out, int R) {
   if (R <= 0) return;
+  static const int cpw_env = [] { const char* e = getenv("PIPER_B200_CONV_POST_WARP"); return e ? atoi(e) : 1; }();
+  if (cpw_env && k <= CPW_MAXK && (k & 1) && C % 32 == 0 && C / 32 <= CPW_MAXN) {
+    const int warps = (R + CPW_ROWS - 1) / CPW_ROWS;
+    const unsigned grid = (unsigned)((warps + 7) / 8);
+    switch (C / 32) {
+      case 1: conv_post_tanh_warp_kernel<1><<<grid, 256, 0, ex.st>>>(in, w, k, slope, row_utt, valid_div, out, R); break;
+      case 2: conv_post_tanh_warp_kernel<2><<<grid, 256, 0, ex.st>>>(in, w, k, slope, row_utt, valid_div, out, R); break;
+      case 3: conv_post_tanh_warp_kernel<3><<<grid, 256, 0, ex.st>>>(in, w, k, slope, row_utt, valid_div, out, R); break;
+      default: conv_post_tanh_warp_kernel<4><<<grid, 256, 0, ex.st>>>(in, w, k, slope, row_utt, valid_div, out, R); break;
+    }
+    KLAUNCH(ex);
+    return;
+  }
   const size_t smem = sizeof(float) * ((size_t)k * C + (size_t)(CP_ROWS + k - 1) * (C + 1));
   conv_post_tanh_kernel<<<(R + CP_ROWS - 1) / CP_ROWS, CP_ROWS, smem, ex.st>>>(in, C, w, k, slope, row_utt,
                                                                               valid_div, out, R);
