@@ -174,6 +174,16 @@ int piper_b200_length_regulate(piper_b200_ctx* ctx, const float* logw, const int
                                int32_t batch, float length_scale, int32_t* durations,
                                int64_t* frame_lengths, int32_t* frame_index, int64_t frame_capacity);
 
+/* IPA text -> phoneme ids with the voice's phoneme_id_map: BOS "^", id + blank "_" per Unicode scalar,
+ * EOS "$" (ESpeakPhonemizer.phonemeIDs, Sources/PiperCLI/ESpeakPhonemizer.swift:73-100; idsFromIPA,
+ * PiperCLI.swift:115-136).  Host-only table lookup, needs a voice loaded from files (route A).
+ * Writes at most `capacity` ids and always the full count to *n_ids; a count above capacity returns
+ * PIPER_B200_ERR_CAPACITY, an unmapped symbol PIPER_B200_ERR_INVALID_ARGUMENT naming it. */
+int piper_b200_ipa_to_ids(piper_b200_ctx* ctx, const char* ipa_utf8, int64_t* ids, int64_t capacity, int64_t* n_ids);
+/* the same lookup straight from a voice's `*.onnx.json` (PiperConfig.load, PiperConfig.swift:41-45): no context, no GPU */
+int piper_b200_config_ipa_to_ids(const char* config_path, const char* ipa_utf8, int64_t* ids, int64_t capacity,
+                                 int64_t* n_ids);
+
 /* RandomNormalLike with the reference's generator (elementwise.metal:132-163). */
 int piper_b200_random_normal(piper_b200_ctx* ctx, uint64_t seed, int64_t count, float* dst_host);
 

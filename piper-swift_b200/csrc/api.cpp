@@ -22,6 +22,7 @@ int classify(const std::string& msg) {
     return PIPER_B200_ERR_DECODE;
   if (msg.rfind("unsupported:", 0) == 0) return PIPER_B200_ERR_UNSUPPORTED;
   if (msg.rfind("capacity", 0) == 0) return PIPER_B200_ERR_CAPACITY;
+  if (msg.rfind("state:", 0) == 0) return PIPER_B200_ERR_STATE;
   if (msg.rfind("cuda:", 0) == 0) return PIPER_B200_ERR_CUDA;
   return PIPER_B200_ERR_INVALID_ARGUMENT;
 }
@@ -287,6 +288,41 @@ int piper_b200_length_regulate(piper_b200_ctx* ctx, const float* logw, const int
   return guarded(ctx, [&] {
     return ctx->c.length_regulate(logw, lengths, batch, length_scale, durations, frame_lengths, frame_index,
                                   frame_capacity);
+  });
+}
+
+int piper_b200_ipa_to_ids(piper_b200_ctx* ctx, const char* ipa_utf8, int64_t* ids, int64_t capacity, int64_t* n_ids) {
+  if (!ctx || !ipa_utf8 || !n_ids || capacity < 0 || (capacity > 0 && !ids)) {
+    g_error = "invalid argument";
+    return PIPER_B200_ERR_INVALID_ARGUMENT;
+  }
+  return guarded(ctx, [&] {
+    Context& c = ctx->c;
+    if (!c.have_config || c.config.phoneme_id_map.empty())
+      throw std::runtime_error("state: no phoneme_id_map (load the voice with piper_b200_load_voice)");
+    const std::vector<int64_t> v = c.config.ipa_to_ids(ipa_utf8);
+    *n_ids = (int64_t)v.size();
+    const int64_t n = (int64_t)v.size() < capacity ? (int64_t)v.size() : capacity;
+    for (int64_t i = 0; i < n; ++i) ids[i] = v[(size_t)i];
+    if ((int64_t)v.size() > capacity) throw std::runtime_error("capacity: id buffer too small");
+    return PIPER_B200_OK;
+  });
+}
+
+int piper_b200_config_ipa_to_ids(const char* config_path, const char* ipa_utf8, int64_t* ids, int64_t capacity,
+                                 int64_t* n_ids) {
+  if (!config_path || !ipa_utf8 || !n_ids || capacity < 0 || (capacity > 0 && !ids)) {
+    g_error = "invalid argument";
+    return PIPER_B200_ERR_INVALID_ARGUMENT;
+  }
+  return guarded(nullptr, [&] {
+    const piper::PiperConfig cfg = piper::PiperConfig::load(config_path);
+    const std::vector<int64_t> v = cfg.ipa_to_ids(ipa_utf8);
+    *n_ids = (int64_t)v.size();
+    const int64_t n = (int64_t)v.size() < capacity ? (int64_t)v.size() : capacity;
+    for (int64_t i = 0; i < n; ++i) ids[i] = v[(size_t)i];
+    if ((int64_t)v.size() > capacity) throw std::runtime_error("capacity: id buffer too small");
+    return PIPER_B200_OK;
   });
 }
 

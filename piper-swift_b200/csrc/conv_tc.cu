@@ -549,7 +549,9 @@ namespace {
 
 }  // namespace
 
-bool tc_conv_supported(int cin, int cout) { return cin % 32 == 0 && cout % 16 == 0 && cin >= 32 && cout >= 16; }
+// cin only has to be a multiple of the tcgen05 K step: the last K block may be partial (TMA zero-fills the
+// channels beyond cin, the packed weights are zero-padded to cin_pad)
+bool tc_conv_supported(int cin, int cout) { return cin % 16 == 0 && cout % 16 == 0 && cin >= 32 && cout >= 16; }
 
 void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
   if (a.Q <= 0) return;

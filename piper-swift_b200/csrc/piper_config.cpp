@@ -176,4 +176,54 @@ PiperConfig PiperConfig::load(const std::string& path) {
   return from_json(ss.str());
 }
 
+namespace {
+// Unicode general category Cf (format), Unicode 15 ranges
+bool is_format_scalar(uint32_t c) {
+  static const uint32_t r[][2] = {
+      {0x00AD, 0x00AD}, {0x0600, 0x0605}, {0x061C, 0x061C}, {0x06DD, 0x06DD}, {0x070F, 0x070F}, {0x0890, 0x0891},
+      {0x08E2, 0x08E2}, {0x180E, 0x180E}, {0x200B, 0x200F}, {0x202A, 0x202E}, {0x2060, 0x2064}, {0x2066, 0x206F},
+      {0xFEFF, 0xFEFF}, {0xFFF9, 0xFFFB}, {0x110BD, 0x110BD}, {0x110CD, 0x110CD}, {0x13430, 0x1343F},
+      {0x1BCA0, 0x1BCA3}, {0x1D173, 0x1D17A}, {0xE0001, 0xE0001}, {0xE0020, 0xE007F}};
+  for (auto& x : r)
+    if (c >= x[0] && c <= x[1]) return true;
+  return false;
+}
+}  // namespace
+
+std::vector<int64_t> PiperConfig::ipa_to_ids(const std::string& s) const {
+  auto first_id = [&](const char* sym) -> int64_t {
+    auto it = phoneme_id_map.find(sym);
+    if (it == phoneme_id_map.end() || it->second.empty())
+      throw std::runtime_error("invalid argument: ^/$/_ missing from phoneme_id_map");
+    return it->second.front();
+  };
+  const int64_t bos = first_id("^"), eos = first_id("$"), blank = first_id("_");
+  std::vector<int64_t> ids;
+  ids.reserve(2 * s.size() + 2);
+  ids.push_back(bos);
+  size_t i = 0;
+  while (i < s.size()) {
+    const unsigned char b0 = (unsigned char)s[i];
+    size_t len = b0 < 0x80 ? 1 : (b0 >> 5) == 0x6 ? 2 : (b0 >> 4) == 0xE ? 3 : (b0 >> 3) == 0x1E ? 4 : 0;
+    if (len == 0 || i + len > s.size()) throw std::runtime_error("invalid argument: malformed UTF-8 in the IPA string");
+    uint32_t cp = len == 1 ? b0 : b0 & (0xFF >> (len + 1));
+    for (size_t k = 1; k < len; ++k) {
+      const unsigned char bk = (unsigned char)s[i + k];
+      if ((bk & 0xC0) != 0x80) throw std::runtime_error("invalid argument: malformed UTF-8 in the IPA string");
+      cp = (cp << 6) | (bk & 0x3F);
+    }
+    const std::string sym = s.substr(i, len);
+    i += len;
+    if (cp == '\n' || cp == '\r') continue;
+    if (cp == 0x200B || cp == 0x200C || cp == 0x200D || cp == 0xFE0E || cp == 0xFE0F || is_format_scalar(cp)) continue;
+    auto it = phoneme_id_map.find(sym);
+    if (it == phoneme_id_map.end() || it->second.empty())
+      throw std::runtime_error("invalid argument: unknown phoneme symbol '" + sym + "'");
+    ids.push_back(it->second.front());
+    ids.push_back(blank);
+  }
+  ids.push_back(eos);
+  return ids;
+}
+
 }  // namespace piper

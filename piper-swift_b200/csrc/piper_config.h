@@ -37,6 +37,12 @@ struct PiperConfig {
   int num_speakers = 1;
   std::map<std::string, int64_t> speaker_id_map;
 
+  // IPA string -> phoneme ids with the rule of ESpeakPhonemizer.phonemeIDs (Sources/PiperCLI/ESpeakPhonemizer.swift:73-100)
+  // and idsFromIPA (PiperCLI.swift:115-136): BOS "^", then per Unicode scalar its id followed by the blank "_",
+  // EOS "$" without a trailing blank; CR / LF, format characters (general category Cf) and U+200B/C/D,
+  // U+FE0E/F are skipped; a scalar missing from phoneme_id_map is an error naming the symbol.
+  std::vector<int64_t> ipa_to_ids(const std::string& ipa_utf8) const;
+
   static PiperConfig load(const std::string& path);             // PiperConfig.load(from:) :41-45
   static PiperConfig from_json(const std::string& text);
 };

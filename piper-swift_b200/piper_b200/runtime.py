@@ -104,6 +104,9 @@ def load_library(path: str = LIB_PATH):
         "piper_b200_length_regulate": (C.c_int, [P, P, P, C.c_int32, C.c_float, P, P, P, C.c_int64]),
         "piper_b200_random_normal": (C.c_int, [P, C.c_uint64, C.c_int64, P]),
         "piper_b200_selftest_conv": (C.c_int, [P] + [C.c_int32] * 8 + [C.POINTER(C.c_float)]),
+        "piper_b200_ipa_to_ids": (C.c_int, [P, C.c_char_p, C.POINTER(C.c_int64), C.c_int64, C.POINTER(C.c_int64)]),
+        "piper_b200_config_ipa_to_ids": (C.c_int, [C.c_char_p, C.c_char_p, C.POINTER(C.c_int64), C.c_int64,
+                                                   C.POINTER(C.c_int64)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -118,8 +121,22 @@ EXPORTED_SYMBOLS = [
     "piper_b200_load_voice", "piper_b200_set_weight", "piper_b200_set_conv_attr", "piper_b200_set_config",
     "piper_b200_finalize", "piper_b200_get_voice_info", "piper_b200_set_precision", "piper_b200_set_stream",
     "piper_b200_synthesize", "piper_b200_get_timings", "piper_b200_get_stage", "piper_b200_length_regulate",
-    "piper_b200_random_normal", "piper_b200_selftest_conv",
+    "piper_b200_random_normal", "piper_b200_selftest_conv", "piper_b200_ipa_to_ids", "piper_b200_config_ipa_to_ids",
 ]
+
+
+def config_ipa_to_ids(config_path: str, ipa: str) -> List[int]:
+    """idsFromIPA (PiperCLI.swift:115-136) / ESpeakPhonemizer.phonemeIDs (ESpeakPhonemizer.swift:73-100) on a
+    voice's `*.onnx.json`: host-only, no context and no GPU needed."""
+    lib = load_library()
+    raw = ipa.encode("utf-8")
+    cap = 2 * len(raw) + 2
+    buf = (C.c_int64 * cap)()
+    n = C.c_int64(0)
+    rc = lib.piper_b200_config_ipa_to_ids(config_path.encode(), raw, buf, cap, C.byref(n))
+    if rc != 0:
+        raise PiperB200Error(rc, lib.piper_b200_last_error(None).decode())
+    return list(buf[: n.value])
 
 
 @dataclass
@@ -220,6 +237,20 @@ class PiperCUDARuntime:
         r = self.synthesize_batch([phoneme_ids], noise_scale, length_scale, noise_w,
                                   speaker_ids=None if speaker_id is None else [speaker_id])
         return r.audio[0]
+
+    def ipa_to_ids(self, ipa: str) -> List[int]:
+        """IPA string -> phoneme ids with the loaded voice's phoneme_id_map (ESpeakPhonemizer.swift:73-100)."""
+        raw = ipa.encode("utf-8")
+        cap = 2 * len(raw) + 2
+        buf = (C.c_int64 * cap)()
+        n = C.c_int64(0)
+        self._check(self._lib.piper_b200_ipa_to_ids(self._ctx, raw, buf, cap, C.byref(n)))
+        return list(buf[: n.value])
+
+    def synthesize_ipa(self, ipa: str, noise_scale: Optional[float] = None, length_scale: Optional[float] = None,
+                       noise_w: Optional[float] = None) -> np.ndarray:
+        """The CLI's text path minus espeak-ng (PiperCLI.swift:115-136 -> :173): IPA in, waveform out."""
+        return self.synthesize(self.ipa_to_ids(ipa), noise_scale, length_scale, noise_w)
 
     def synthesize_stream(self, phoneme_ids: Sequence[int], noise_scale: Optional[float] = None,
                           length_scale: Optional[float] = None, noise_w: Optional[float] = None,

@@ -74,6 +74,11 @@ HIGH = VoiceSpec(
 
 MEDIUM_MULTISPEAKER = VoiceSpec(name="medium-multispeaker", n_speakers=904, gin=512)
 
+# the x_low quality tier of rhasspy/piper (16 kHz, half-width text encoder / flow: hidden 96, FFN 384; SURVEY.md
+# section 8f rank 3 "remaining voice families").  Head dim 48 and hidden 96 exercise the generic attention and
+# fp32 conv kernels and the 96-wide tensor-core tiles.
+X_LOW = VoiceSpec(name="x_low", sample_rate=16000, hidden=96, filter_channels=384)
+
 # reduced-size variant used only to keep CPU unit tests fast (same structure, fewer channels)
 TINY = VoiceSpec(
     name="tiny",
@@ -88,7 +93,7 @@ TINY = VoiceSpec(
     rb_dilations=((1, 2), (2, 3)),
 )
 
-SPECS = {s.name: s for s in (MEDIUM, HIGH, MEDIUM_MULTISPEAKER, TINY)}
+SPECS = {s.name: s for s in (MEDIUM, HIGH, MEDIUM_MULTISPEAKER, X_LOW, TINY)}
 
 # fixture of the reference: bench/fixtures/test_summary.json:8,16-18 and SmokeTests.swift:15-16
 FIXTURE_IDS = [1, 20, 0, 120, 0, 61, 0, 24, 0, 59, 0, 100, 0, 2]

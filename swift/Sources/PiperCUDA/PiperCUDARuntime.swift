@@ -67,6 +67,14 @@ public final class PiperCUDARuntime: @unchecked Sendable {
                                    noiseW: noiseW, speakerIDs: speakerID.map { [$0] })[0]
     }
 
+    /// idsFromIPA (PiperCLI.swift:115-136) / ESpeakPhonemizer.phonemeIDs (ESpeakPhonemizer.swift:73-100)
+    public func phonemeIDs(ipa: String) throws -> [Int] {
+        var n: Int64 = 0
+        var buf = [Int64](repeating: 0, count: 2 * ipa.utf8.count + 2)
+        try Self.check(piper_b200_ipa_to_ids(ctx, ipa, &buf, Int64(buf.count), &n), ctx)
+        return buf.prefix(Int(n)).map(Int.init)
+    }
+
     /// additive: a ragged batch of utterances in one call (BASELINE configs 3 and 5)
     public func synthesizeBatch(phonemeIDs: [[Int]], noiseScale: Float? = nil, lengthScale: Float? = nil,
                                 noiseW: Float? = nil, speakerIDs: [Int]? = nil) throws -> [[Float]] {

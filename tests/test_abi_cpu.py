@@ -63,3 +63,26 @@ def test_product_path_does_not_import_the_oracle():
             if f.endswith((".py", ".cpp", ".cu", ".h", ".swift")):
                 src = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "import oracle" not in src and "from oracle" not in src, f
+
+
+def test_ipa_to_ids_follows_the_reference_rule():
+    """ESpeakPhonemizer.phonemeIDs (ESpeakPhonemizer.swift:73-100) / idsFromIPA (PiperCLI.swift:115-136):
+    BOS, id + blank per scalar, EOS without trailing blank; CR/LF, Cf and ZW*/VS15/16 scalars skipped."""
+    _, cfg = voice_files("tiny")
+    id_of = {c: 3 + i for i, c in enumerate(" !',-.:;?abcdefghijklmnopqrstuvwxyz")}
+    text = "hi, you"
+    want = [1] + [v for ch in text for v in (id_of[ch], 0)] + [2]
+    assert runtime.config_ipa_to_ids(cfg, text) == want
+    assert len(want) == 2 * len(text) + 2 and want[-2:] == [0, 2]
+    noisy = "h‍i️,\r\n ­you⁠"          # ZWJ, VS16, CR LF, soft hyphen (Cf), word joiner (Cf)
+    assert runtime.config_ipa_to_ids(cfg, noisy) == want
+    assert runtime.config_ipa_to_ids(cfg, "") == [1, 2]
+    with pytest.raises(runtime.PiperB200Error) as e:
+        runtime.config_ipa_to_ids(cfg, "hé")              # not in phoneme_id_map
+    assert "é" in str(e.value)
+    lib = runtime.load_library()
+    n = C.c_int64(0)
+    buf = (C.c_int64 * 4)()
+    rc = lib.piper_b200_config_ipa_to_ids(cfg.encode(), b"hello", buf, 4, C.byref(n))
+    assert rc == 7 and n.value == 12 and list(buf) == [1, id_of["h"], 0, id_of["e"]]   # capacity: count still reported
+    assert lib.piper_b200_config_ipa_to_ids(b"/nonexistent.json", b"a", buf, 4, C.byref(n)) == 2

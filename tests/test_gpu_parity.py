@@ -40,7 +40,7 @@ def oracle_run(name, ids, sid=None, scales=S.FIXTURE_SCALES, nd=None, nm=None):
 
 @pytest.mark.parametrize("name,factor,sid", [("tiny", 1, None), ("tiny", 4, None), ("medium", 1, None),
                                              ("medium", 2, None), ("medium", 8, None), ("high", 2, None),
-                                             ("medium-multispeaker", 2, 7)])
+                                             ("medium-multispeaker", 2, 7), ("x_low", 4, None)])
 def test_stage_and_audio_parity(name, factor, sid):
     ids = fixture_ids(factor, S.SPECS[name].n_vocab)
     o = oracle_run(name, ids, sid)
@@ -85,6 +85,22 @@ def test_reference_api_surface():
     assert chunks[0].format.sample_rate == 22050
     t = r.last_run_timings
     assert t["kernel_launches"] > 100 and t["gpu_ms"] > 0
+
+
+def test_ipa_front_door_and_profile_flag():
+    """idsFromIPA -> synthesize (PiperCLI.swift:115-136 -> :173) through the context, and the per-class kernel
+    timings the bench reads (PIPER_B200_FLAG_PROFILE)."""
+    r = rt("medium")
+    ids = r.ipa_to_ids("hello world.")
+    assert ids[0] == 1 and ids[-1] == 2 and ids[2:-1:2] == [0] * 12 and len(ids) == 2 * 12 + 2
+    assert np.array_equal(r.synthesize_ipa("hello world."), r.synthesize(ids))
+    with pytest.raises(PiperB200Error):
+        r.ipa_to_ids("h\u00e9llo")
+    arr = np.asarray(ids, dtype=np.int64)
+    out = r.synthesize_packed(arr, np.asarray([len(ids)], dtype=np.int64), profile=True)
+    t = r.last_run_timings
+    assert sum(t["class_launches"]) > 0 and sum(t["class_ms"]) > 0 and sum(t["class_ms"]) <= t["gpu_ms"] * 1.05
+    assert out.total_samples > 0
 
 
 def test_injected_noise_overrides():

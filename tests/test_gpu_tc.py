@@ -60,7 +60,7 @@ TOL = {"f16": (58.0, 4e-3), "bf16": (40.0, 3e-2)}
 
 @pytest.mark.parametrize("prec", ["f16", "bf16"])
 @pytest.mark.parametrize("name,factor,sid", [("medium", 1, None), ("medium", 8, None), ("high", 2, None),
-                                             ("medium-multispeaker", 2, 7)])
+                                             ("medium-multispeaker", 2, 7), ("x_low", 4, None)])
 def test_tc_modes_against_oracle(name, factor, sid, prec):
     ids = fixture_ids(factor)
     ns, ls, nw = S.FIXTURE_SCALES

@@ -12,7 +12,8 @@ from oracle import refrng                                          # noqa: E402
 from piper_b200.runtime import PiperCUDARuntime, Options           # noqa: E402
 
 if __name__ == "__main__":
-    for name, factor, sid in (("medium", 1, None), ("medium", 8, None), ("high", 2, None), ("medium-multispeaker", 2, 7)):
+    for name, factor, sid in (("medium", 1, None), ("medium", 8, None), ("high", 2, None), ("medium-multispeaker", 2, 7),
+                              ("x_low", 4, None)):
         ids = fixture_ids(factor)
         ns, ls, nw = S.FIXTURE_SCALES
         o = oracle(name).infer(ids, ns, ls, nw, refrng.noise_dp(len(ids)), noise_main_fn=refrng.noise_main, sid=sid)
