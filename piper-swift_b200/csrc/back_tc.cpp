@@ -6,6 +6,7 @@
 // epilogue of the in_layer convolution, res|skip is one GEMM with two column groups, and
 // every producer also emits the 16-bit (leaky-relu'd) operand copy its consumer reads.
 // Residual streams, skip sums and the cross-resblock mean stay in fp32.
+#include <algorithm>
 #include <cstdlib>
 #include <stdexcept>
 
@@ -73,6 +74,40 @@ void TcVoice::build(Exec& ex, const Voice& v, int f16_) {
   for (const StageW& s : v.stages) {
     TcStage t;
     t.up = make_tcw(ex, allocs, s.up, nullptr, f16);
+    {   // merged polyphase form: column block ph * cout .. of union tap u holds W[ph][tap] when the phase's tap reads
+        // input row q + first_off + u, zeros otherwise (tap t of phase ph reads row q + (ph + ct_pad) / phases - t)
+      const ConvW& c = s.up;
+      const int P = c.phases, T = c.taps;
+      static const int merge_env = [] { const char* e = getenv("PIPER_B200_UPS_MERGED"); return e ? atoi(e) : 1; }();
+      if (merge_env && P > 1 && P <= 16 && c.cout % 32 == 0 && (P * c.cout) % 128 == 0) {
+        int omin = 1 << 30, omax = -(1 << 30);
+        for (int ph = 0; ph < P; ++ph) {
+          const int o = (ph + c.ct_pad) / P;
+          omin = std::min(omin, o - (T - 1));
+          omax = std::max(omax, o);
+        }
+        const int U = omax - omin + 1;
+        TcW m = t.up;
+        m.w = nullptr;
+        m.taps = U; m.phases = 1; m.cout = P * c.cout;
+        m.phase_cols = c.cout; m.merged_phases = P; m.first_off = omin;
+        const size_t n = (size_t)U * m.cout * m.cin_pad;
+        CUDA_OK(cudaMalloc(&m.w, n * 2));
+        allocs.push_back(m.w);
+        CUDA_OK(cudaMemsetAsync(m.w, 0, n * 2, ex.st));
+        for (int ph = 0; ph < P; ++ph) {
+          m.phase_tapmask[ph] = 0;
+          for (int tt = 0; tt < T; ++tt) {
+            const int u = (ph + c.ct_pad) / P - tt - omin;
+            m.phase_tapmask[ph] |= 1u << u;
+            launch_pack_tc_weights(ex, c.w + (size_t)(ph * T + tt) * c.cin * c.ldw, c.ldw, 1, c.cin, c.cout,
+                                   static_cast<uint16_t*>(m.w) + (size_t)u * m.cout * m.cin_pad, m.cout, ph * c.cout,
+                                   m.cin_pad, f16);
+          }
+        }
+        t.up_merged = m;
+      }
+    }
     for (const ResBlockW& rb : s.rbs) {
       if (rb.c2.empty() && rb.c1.size() > 2)
         throw std::runtime_error("unsupported: ResBlock2 with more than two dilations");
@@ -279,11 +314,23 @@ float* run_back_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep) 
       CUDA_OK(cudaMemset2DAsync(xub + ((size_t)act_pad + Rn) * 8, (size_t)act_rows * 16, 0, (size_t)1152 * 16, C / 8, ex.st));
     }
     {   // LeakyRelu(0.1) [already in the operand copy] + ConvTranspose, one polyphase GEMM per phase
+      static const int persist_env = [] { const char* e = getenv("PIPER_B200_TC_PERSIST"); return e ? atoi(e) : 1; }();
+      const bool merged = ts.up_merged.w != nullptr && persist_env;
       TcConvArgs a;
       a.in = act[cur]; a.ldin = ts.up.cin; a.R_in = R; a.cin = ts.up.cin;
-      a.w = &ts.up;
-      a.Q = R; a.tap_step = -1; a.out_mul = s.stride;
-      a.n_groups = 1; a.nt = pick_nt(C); a.n_tiles = C / a.nt;
+      a.Q = R; a.out_mul = s.stride;
+      a.n_groups = 1;
+      if (merged) {   // all phases of a row tile in one pass: N = phases * C columns, union of the row offsets as taps
+        a.w = &ts.up_merged;
+        a.tap_step = 1; a.in_off = ts.up_merged.first_off;
+        const int total = ts.up_merged.cout;
+        a.nt = total % 256 == 0 ? 256 : 128;
+        a.n_tiles = total / a.nt;
+      } else {
+        a.w = &ts.up;
+        a.tap_step = -1;
+        a.nt = pick_nt(C); a.n_tiles = C / a.nt;
+      }
       a.e[0].bias = ts.up.bias;
       a.e[0].out_f32 = use_mrf ? nullptr : xu; a.e[0].ld_f32 = C;   // the fused stage takes its residual from the 16-bit copy
       a.e[0].out_act = xub; a.e[0].ld_act = C; a.e[0].act_slope = 0.1f;

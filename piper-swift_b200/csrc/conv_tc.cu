@@ -31,6 +31,8 @@ struct TcKernelParams {
   int nt, n_groups, cout_rows;      // cout_rows = weight rows per (phase, tap)
   int phases, ct_pad, out_mul;
   int gate, f16, window, a_col0, relu;
+  int phase_cols;                   // merged polyphase ConvTranspose: columns per phase (0 = off)
+  uint32_t tap_mask[8];             // per column tile: taps to run (merged polyphase weights are zero elsewhere)
   TcEpi e[2];
   const float* uttbias; int ldub;
   const int* row_utt; int valid_div;
@@ -117,6 +119,51 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
     const uint32_t valid_mask = __ballot_sync(0xffffffffu, valid);
     const int sub = lane >> 3, c4 = (lane & 7) * 4;
     const int row_base = m0 + quarter * 32;
+    const TcEpi& em = p.e[0];
+    if (p.phase_cols && em.out_act && em.act_planar && !em.out_f32 && nparts == 1) {
+      // Merged polyphase ConvTranspose -> group-planar 16-bit operand.  This tile holds ppt consecutive phases of
+      // each input row q, i.e. ppt consecutive OUTPUT rows (16 bytes each per plane).  Two planes at a time are
+      // assembled in the warp's buffer as [plane][q][phase] and written with every lane storing an adjacent
+      // 16-byte piece (512 contiguous bytes per instruction); the lane = row form touched 32 lines per store.
+      const int Cp = p.phase_cols, ppt = p.nt / Cp, ph0 = ntile * ppt;
+      uint4* tb = reinterpret_cast<uint4*>(tbuf);
+      const int pieces = 32 * ppt;                       // per plane
+      for (int pp = 0; pp < Cp / 16; ++pp) {
+        __syncwarp();
+        for (int k = 0; k < ppt; ++k) {
+          float v[16];
+          tmem_ld16(lane_base + (uint32_t)(k * Cp + pp * 16), v);
+          if (em.bias) {
+            const float4* b4 = reinterpret_cast<const float4*>(em.bias + pp * 16);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const float4 x = __ldg(b4 + i);
+              v[4 * i] += x.x; v[4 * i + 1] += x.y; v[4 * i + 2] += x.z; v[4 * i + 3] += x.w;
+            }
+          }
+          uint32_t pk[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            pk[i] = valid ? pack2(lrelu(v[2 * i], em.act_slope), lrelu(v[2 * i + 1], em.act_slope), p.f16) : 0u;
+          const int slot = k ^ (lane & (ppt - 1));       // spreads the lanes' 16-byte stores over the banks
+          tb[lane * ppt + slot] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+          tb[pieces + lane * ppt + slot] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+        }
+        __syncwarp();
+        for (int pl = 0; pl < 2; ++pl) {
+          uint16_t* plane = static_cast<uint16_t*>(em.out_act) +
+                            ((size_t)(em.col0 / 8 + pp * 2 + pl) * em.act_rows + em.act_pad) * 8;
+          for (int i = lane; i < pieces; i += 32) {
+            const int qq = i / ppt, sl = i - qq * ppt;
+            if (!((act_mask >> qq) & 1u)) continue;
+            const int k = sl ^ (qq & (ppt - 1));
+            const size_t orow_r = (size_t)(row_base + qq) * p.out_mul + ph0 + k;
+            *reinterpret_cast<uint4*>(plane + orow_r * 8) = tb[pl * pieces + i];
+          }
+        }
+      }
+      return;
+    }
     const int cpg = p.nt / 32, nunits = p.n_groups * cpg;
     for (int f = part * nunits / nparts; f < (part + 1) * nunits / nparts; ++f) {
       const int g = f / cpg, c = f - g * cpg;
@@ -127,8 +174,13 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
         __syncwarp();
         tmem_ld16(lane_base + (uint32_t)(g * p.nt + c * 32), v);
         tmem_ld16(lane_base + (uint32_t)(g * p.nt + c * 32 + 16), v + 16);
-        const int j = ntile * p.nt + c * 32;
+        int j = ntile * p.nt + c * 32, ph_c = p.phases > 1 ? phase : 0;
+        if (p.phase_cols) {   // merged polyphase weights: the chunk's columns are channels j % phase_cols of phase j / phase_cols
+          ph_c = j / p.phase_cols;
+          j -= ph_c * p.phase_cols;
+        }
         const size_t ocol = (size_t)e.col0 + j;
+        const int orow_c = active ? q * p.out_mul + ph_c : 0;
         if (e.bias) {
           const float4* b4 = reinterpret_cast<const float4*>(e.bias + j);
 #pragma unroll
@@ -146,7 +198,7 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
           }
         }
         if (planar && active) {   // group-planar operand of the fused MRF stage: 16 bytes per (row, plane)
-          uint16_t* base = static_cast<uint16_t*>(e.out_act) + ((size_t)(ocol >> 3) * e.act_rows + e.act_pad + orow) * 8;
+          uint16_t* base = static_cast<uint16_t*>(e.out_act) + ((size_t)(ocol >> 3) * e.act_rows + e.act_pad + orow_c) * 8;
 #pragma unroll
           for (int pl = 0; pl < 4; ++pl) {
             uint32_t pk[4];
@@ -165,7 +217,7 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
         // all global loads of the chunk are issued before the first use (8-16 independent 16-byte loads per
         // lane in flight): with only eight epilogue warps per SM the epilogue is latency-, not bandwidth-bound
         float4 rr[8], aa[8];
-        const size_t orow0 = (size_t)(row_base + sub) * p.out_mul + (p.phases > 1 ? phase : 0);
+        const size_t orow0 = (size_t)(row_base + sub) * p.out_mul + ph_c;
         const size_t rstep = (size_t)4 * p.out_mul;
         float* of = e.out_f32 ? e.out_f32 + orow0 * e.ld_f32 + ocol + c4 : nullptr;
         if (e.res) {
@@ -479,6 +531,7 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
         const int m0 = mt * TC_BM;
         const int in_off = p.phases > 1 ? (phase + p.ct_pad) / p.phases : p.in_off;
         for (int tap = 0; tap < p.taps; ++tap) {
+          if (!((p.tap_mask[ntile & 7] >> tap) & 1u)) continue;
           const int arow = m0 + in_off + tap * p.tap_step;
           const int wrow = (phase * p.taps + tap) * p.cout_rows + ntile * p.nt;
           for (int kbi = 0; kbi < p.kblocks; ++kbi) {
@@ -500,9 +553,10 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
     const uint64_t d_hi = make_smem_desc(0, p.kb);
     const uint32_t stage_lo = smem_u32(smem) >> 4;
     const uint32_t stage16 = (uint32_t)stage_bytes >> 4, a16 = (uint32_t)a_bytes >> 4, b16 = (uint32_t)b_bytes >> 4;
-    const int n_it = p.taps * p.kblocks;
     int s = 0; uint32_t ph = 0, li = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++li) {
+      const int ntile_m = (t / p.phases) / m_tiles;
+      const int n_it = __popc(p.tap_mask[ntile_m & 7]) * p.kblocks;
       const uint32_t buf = li & 1u;
       mbar_wait(&acc_empty[buf], ((li >> 1) & 1u) ^ 1u);     // the epilogue drained this accumulator buffer
       tc_fence_after();
@@ -570,9 +624,25 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
   uint32_t cols = 32;
   while ((int)cols < a.n_groups * a.nt) cols <<= 1;
   p.tmem_cols = cols;
+  p.phase_cols = w.phase_cols;
+  for (int t = 0; t < 8; ++t) p.tap_mask[t] = 0xFFFFFFFFu >> (32 - (w.taps < 32 ? w.taps : 32));
+  if (w.phase_cols) {   // merged polyphase ConvTranspose: only the persistent kernel's coalesced epilogue maps columns to phases
+    const int ppt_ = a.nt / w.phase_cols;
+    if (a.n_groups != 1 || (a.nt & 31) || w.phase_cols % 32 || a.nt % w.phase_cols || a.n_tiles > 8 || a.gate ||
+        (ppt_ & (ppt_ - 1)) || ppt_ > 4)   // ppt: power of two, [2 planes][32][ppt] 16-byte pieces must fit the warp buffer
+      throw std::runtime_error("conv_tc: bad tiling for merged polyphase weights");
+    const int ppt = a.nt / w.phase_cols;   // phases per column tile
+    for (int t = 0; t < a.n_tiles; ++t) {
+      uint32_t m = 0;
+      for (int ph = t * ppt; ph < (t + 1) * ppt && ph < 16; ++ph) m |= w.phase_tapmask[ph];
+      p.tap_mask[t] = m;
+    }
+  }
 
   const CUtensorMap ta = make_map(a.in, (uint64_t)a.cin, (uint64_t)a.R_in, (uint64_t)a.ldin, w.kb, TC_BM, a.f16);
   static const int persist_env = [] { const char* e = getenv("PIPER_B200_TC_PERSIST"); return e ? atoi(e) : 1; }();
+  if (w.phase_cols && !(persist_env && a.n_groups * a.nt <= 256))
+    throw std::runtime_error("conv_tc: merged polyphase weights need the persistent kernel");
   if (persist_env && a.n_groups * a.nt <= 256) {
     static int num_sms = 0;
     if (!num_sms) {
@@ -598,7 +668,13 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
     const int total = m_tiles * a.n_tiles * w.phases;
     const int grid = total < num_sms ? total : num_sms;
     const size_t smem = (size_t)st * sb + 1024 + 512 + TBUF_BYTES;
-    ProfScope ps(ex, Prof::CONV_TC, 2.0 * a.Q * w.phases * w.taps * w.cin * (double)(a.n_groups * a.nt * a.n_tiles));
+    double flops = 2.0 * a.Q * w.phases * w.taps * w.cin * (double)(a.n_groups * a.nt * a.n_tiles);
+    if (w.phase_cols) {   // algorithmic work only: the zero blocks of the merged weights do not count
+      int used = 0;
+      for (int ph = 0; ph < w.merged_phases; ++ph) used += __builtin_popcount(w.phase_tapmask[ph]);
+      flops = 2.0 * a.Q * w.cin * (double)w.phase_cols * used;
+    }
+    ProfScope ps(ex, Prof::CONV_TC, flops);
     conv_tc_persist_kernel<<<grid, TCP_THREADS, smem, ex.st>>>(ta, tbp, p, st, m_tiles, a.n_tiles, total);
     ++ex.launches;
     return;

@@ -25,6 +25,12 @@ struct TcW {
   int cin = 0, cin_pad = 0, cout = 0;
   int taps = 1, phases = 1, ct_pad = 0, dil = 1, pad_l = 0;
   int kb = 64;              // K elements per pipeline stage (64 -> 128B swizzle, 32 -> 64B swizzle)
+  // polyphase ConvTranspose merged into ONE convolution (persistent kernel only): the weight rows are
+  // [union tap][phase * phase_cols + c][cin_pad], zero where a phase does not use a row offset; column n
+  // belongs to output row q * stride + n / phase_cols, channel n % phase_cols.  taps = union taps,
+  // phases = 1, first_off = input row offset of union tap 0 (tap step +1).
+  int phase_cols = 0, merged_phases = 0, first_off = 0;
+  uint32_t phase_tapmask[16] = {0};   // per phase: bit u set when union tap u carries weights of that phase
 };
 
 struct TcEpi {

@@ -63,6 +63,7 @@ struct TcResBlock {
 };
 struct TcStage {
   TcW up;
+  TcW up_merged;   // the same ConvTranspose as one convolution over the union of the phases' row offsets (w == nullptr: not built)
   std::vector<TcResBlock> rbs;
   // fused MRF stage (conv_mrf.cu): all resblock convolutions of the stage packed as [tap][cout][cin]
   bool mrf = false;
