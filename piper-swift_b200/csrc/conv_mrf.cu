@@ -26,13 +26,13 @@ using namespace tc;
 
 namespace {
 
-constexpr int MRF_G = 64;          // guard rows on both sides of the operand windows (>= largest tap shift)
+constexpr int MRF_G = 64;          // upper bound of the guard rows on both sides of the operand windows (p.G >= largest tap shift)
 constexpr int MRF_MAX_M = 8;
 constexpr int MRF_MAX_RING = 32;
 constexpr uint32_t MRF_TRACE_EVENTS = 4096;
 
 struct MrfParams {
-  int R, C, nk, m, V, halo, n_windows;
+  int R, C, nk, m, V, halo, n_windows, G;   // G: guard rows actually used (multiple of 8, <= MRF_G)
   int k[MRF_MAX_RB], d0[MRF_MAX_RB], d1[MRF_MAX_RB];
   int tap_base[MRF_MAX_RB][2];
   const float* b1[MRF_MAX_RB];
@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
   constexpr int KS = C / 16;                          // tcgen05 K steps per tap
   constexpr int NP = C / 8;                           // planes
   constexpr int tap_bytes = C * C * 2;
-  const int win_rows = (m + 1) * 128;                 // W + 2*G rows
+  const int win_rows = m * 128 + 2 * p.G;             // W + 2*G rows
   const int plane_bytes = win_rows * 16;
   const int win_bytes = NP * plane_bytes;
   uint8_t* X0 = smem;
@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
         mbar_expect_tx(x_full, (uint32_t)win_bytes);
         for (int g = 0; g < NP; ++g)
           bulk_load(X0 + (size_t)g * plane_bytes,
-                    p.x_act + ((size_t)g * p.act_rows + (size_t)(p.act_pad + w0 - MRF_G)) * 8, (uint32_t)plane_bytes, x_full);
+                    p.x_act + ((size_t)g * p.act_rows + (size_t)(p.act_pad + w0 - p.G)) * 8, (uint32_t)plane_bytes, x_full);
       };
       auto load_w = [&](int r, int j) {
         for (int t = 0; t < p.k[r]; ++t) {
@@ -191,7 +191,7 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
     const uint32_t plane16 = (uint32_t)plane_bytes >> 4;                 // descriptor address units are 16 bytes:
     const uint64_t a_hi = make_smem_desc_ns(0, (uint32_t)plane_bytes, 128);   // one operand row = one unit
     const uint64_t b_hi = make_smem_desc(0, C);
-    const uint32_t x0_lo = (smem_u32(X0) >> 4) + MRF_G, y1_lo = (smem_u32(Y1) >> 4) + MRF_G;
+    const uint32_t x0_lo = (smem_u32(X0) >> 4) + (uint32_t)p.G, y1_lo = (smem_u32(Y1) >> 4) + (uint32_t)p.G;
     const uint32_t wr_lo = smem_u32(WR) >> 4;
     constexpr uint32_t tap16 = tap_bytes >> 4;
     const uint32_t ring = (uint32_t)p.ring;
@@ -303,7 +303,7 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
           const bool inr = grow >= 0 && grow < p.R;
           // the residual x0 is recovered from the 16-bit lrelu(x0) operand window (x0 = v >= 0 ? v : 10 v): no
           // fp32 copy of the stage input exists.  Window rows and the validity flag do not depend on the MMAs
-          const uint32_t row_off = (uint32_t)((MRF_G + row_in_win) * 16);
+          const uint32_t row_off = (uint32_t)((p.G + row_in_win) * 16);
           int ru = 0;
           if (inr && p.row_utt) ru = p.row_utt[grow / p.valid_div];
           TRACE(10u, n, (uint32_t)u);
@@ -493,8 +493,14 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
     throw std::runtime_error("conv_mrf: planar operand needs zero pad rows around the signal");
   // window height: TMEM holds D and S for every tile (2*m*C columns <= 512); smem holds two operand
   // windows of (m+1)*128 rows plus at least kmax weight taps
+  int shift = 0;
+  for (int r = 0; r < a.nk; ++r) shift = std::max(shift, (a.k[r] - 1) / 2 * std::max(a.d0[r], a.d1[r]));
+  static const int g_env = [] { const char* e = getenv("PIPER_B200_MRF_G"); return e ? atoi(e) : 0; }();
+  int G = (shift + 7) & ~7;
+  if (g_env >= G && g_env <= MRF_G && g_env % 8 == 0) G = g_env;
+  p.G = G;
   int m = std::min(MRF_MAX_M, 512 / (2 * a.C));
-  auto fits = [&](int mm) { return 2 * (mm + 1) * 128 * row_bytes + kmax * tap_bytes + 4096 <= TC_SMEM_MAX; };
+  auto fits = [&](int mm) { return 2 * (mm * 128 + 2 * G) * row_bytes + kmax * tap_bytes + 4096 <= TC_SMEM_MAX; };
   while (m > 2 && !fits(m)) --m;
   // small inputs: prefer more, shorter windows so that every SM has one
   while (m > 2 && (a.R + (128 * m - 2 * halo) - 1) / (128 * m - 2 * halo) < num_sms) --m;
@@ -506,7 +512,7 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   p.m = m;
   p.V = 128 * m - 2 * halo;
   p.n_windows = (a.R + p.V - 1) / p.V;
-  const int win_bytes = (m + 1) * 128 * row_bytes;
+  const int win_bytes = (m * 128 + 2 * G) * row_bytes;
   int ring = (TC_SMEM_MAX - 4096 - 2 * win_bytes) / tap_bytes;
   if (ring > MRF_MAX_RING) ring = MRF_MAX_RING;
   p.resident = a.total_taps <= ring ? 1 : 0;
