@@ -56,6 +56,10 @@ extern "C" {
 #define PIPER_B200_FLAG_KEEP_ON_DEVICE 2u  /* leave audio in HBM: result.audio is a device pointer */
 #define PIPER_B200_FLAG_KEEP_STAGES 4u     /* retain stage tensors for piper_b200_get_stage */
 #define PIPER_B200_FLAG_PCM16 8u           /* also produce int16 PCM (WavFileWriter.swift:20-30 rule) */
+#define PIPER_B200_FLAG_STREAM 32u         /* batch == 1: run text encoder, durations and flow, keep the latent in HBM and return
+                                            * without audio; the waveform is then decoded chunk by chunk with
+                                            * piper_b200_stream_next (the incremental decode synthesizeStream intends,
+                                            * PiperMetalRuntime.swift:82-121) */
 #define PIPER_B200_FLAG_PROFILE 16u        /* CUDA events around every GEMM-class kernel launch (PIPER_PROFILE, GraphExecutor.swift:163-175) */
 
 typedef struct piper_b200_ctx piper_b200_ctx;
@@ -157,6 +161,14 @@ int piper_b200_set_stream(piper_b200_ctx* ctx, void* cuda_stream);   /* NULL -> 
 /* GraphExecutor.executeOutput (GraphExecutor.swift:156) for a ragged batch. */
 int piper_b200_synthesize(piper_b200_ctx* ctx, const piper_b200_request* req, piper_b200_result* res);
 int piper_b200_get_timings(const piper_b200_ctx* ctx, piper_b200_timings* out);
+
+/* Incremental decoding after a synthesize with PIPER_B200_FLAG_STREAM: runs the HiFi-GAN generator over the
+ * next `max_frames` frames (plus the generator's receptive-field halo, recomputed) and returns their samples:
+ * res->audio (pinned host, total_samples values; frame n covers samples [n*hop, (n+1)*hop)), res->total_frames
+ * = frames decoded by this call.  *is_final = 1 with the last chunk.  The concatenated chunks are bit-identical
+ * to the one-shot synthesize of the same request.  Replaces the chunk loop of PiperMetalRuntime.synthesizeStream
+ * (PiperMetalRuntime.swift:84-121, PiperAudioChunk PiperAudio.swift:13-25). */
+int piper_b200_stream_next(piper_b200_ctx* ctx, int64_t max_frames, piper_b200_result* res, int32_t* is_final);
 
 /* Parity hooks = GraphExecutor.execute(inputs:maxNodeIndex:overrides:) (GraphExecutor.swift:75-152),
  * which returns intermediates for node-by-node diffing.  After a synthesize with

@@ -238,6 +238,14 @@ int piper_b200_synthesize(piper_b200_ctx* ctx, const piper_b200_request* req, pi
   return guarded(ctx, [&] { return ctx->c.synthesize(*req, *res); });
 }
 
+int piper_b200_stream_next(piper_b200_ctx* ctx, int64_t max_frames, piper_b200_result* res, int32_t* is_final) {
+  if (!ctx || !res || !is_final) {
+    g_error = "invalid argument: null context, result or is_final";
+    return PIPER_B200_ERR_INVALID_ARGUMENT;
+  }
+  return guarded(ctx, [&] { return ctx->c.stream_next(max_frames, *res, is_final); });
+}
+
 int piper_b200_get_timings(const piper_b200_ctx* ctx, piper_b200_timings* out) {
   if (!ctx || !out) {
     g_error = "invalid argument: null pointer";

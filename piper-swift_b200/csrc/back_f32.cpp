@@ -47,7 +47,7 @@ size_t back_f32_bytes(const Context& ctx, int Rf, int batch) {
   return bytes;
 }
 
-float* run_back_f32(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep) {
+FlowOut run_flow_f32(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep) {
   Voice& v = ctx.voice;
   Arena& A = ctx.back;
   const int H = v.hp.hidden, Rf = in.Rf;
@@ -85,7 +85,24 @@ float* run_back_f32(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep)
       throw std::runtime_error("cuda: copy of flow output failed");
   }
 
-  // ---- HiFi-GAN ----------------------------------------------------------------------------
+  FlowOut out;
+  out.z = z;
+  return out;
+}
+
+float* run_back_f32(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep) {
+  const FlowOut f = run_flow_f32(ctx, ex, in, z_keep);
+  DecoderIn d;
+  d.z = f.z; d.frow_utt = in.frow_utt; d.rows = in.Rf; d.batch = in.batch; d.cond_dec = in.cond_dec;
+  return run_decoder_f32(ctx, ex, d);
+}
+
+// ---- HiFi-GAN ------------------------------------------------------------------------------
+float* run_decoder_f32(Context& ctx, Exec& ex, const DecoderIn& in) {
+  Voice& v = ctx.voice;
+  Arena& A = ctx.back;
+  const int H = v.hp.hidden, Rf = in.rows;
+  const float* z = in.z;
   size_t per_row_max = v.hp.dec_c0;
   {
     int U = 1;

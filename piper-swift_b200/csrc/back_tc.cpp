@@ -203,7 +203,7 @@ size_t back_tc_bytes(const Context& ctx, int Rf, int batch) {
   return bytes;
 }
 
-float* run_back_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep) {
+FlowOut run_flow_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep) {
   Voice& v = ctx.voice;
   TcVoice& tv = ctx.tc;
   Arena& A = ctx.back;
@@ -274,8 +274,26 @@ float* run_back_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep) 
     }
   }
   if (z_keep) CUDA_OK(cudaMemcpyAsync(z_keep, z, (size_t)Rf * H * 4, cudaMemcpyDeviceToDevice, ex.st));
+  FlowOut out;
+  out.z = z; out.z16 = zb;
+  return out;
+}
 
-  // ---- HiFi-GAN ----------------------------------------------------------------------------
+float* run_back_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep) {
+  const FlowOut f = run_flow_tc(ctx, ex, in, z_keep);
+  DecoderIn d;
+  d.z = f.z; d.z16 = f.z16; d.frow_utt = in.frow_utt; d.rows = in.Rf; d.batch = in.batch; d.cond_dec = in.cond_dec;
+  return run_decoder_tc(ctx, ex, d);
+}
+
+// ---- HiFi-GAN ------------------------------------------------------------------------------
+float* run_decoder_tc(Context& ctx, Exec& ex, const DecoderIn& in) {
+  Voice& v = ctx.voice;
+  TcVoice& tv = ctx.tc;
+  Arena& A = ctx.back;
+  const int f16 = tv.f16;
+  const int H = v.hp.hidden, Rf = in.rows;
+  const uint16_t* zb = static_cast<const uint16_t*>(in.z16);
   const size_t P = per_row_max_of(v);
   float* xu = A.alloc<float>((size_t)Rf * P);
   float* yb = A.alloc<float>((size_t)Rf * P);

@@ -171,4 +171,27 @@ int Context::length_regulate(const float* logw_h, const int64_t* lengths, int ba
   }
 }
 
+// Receptive half-width of the generator in frames: walk from the waveform back to the latent.  Every stage adds
+// the deepest resblock chain ((k-1)/2 * dilation per convolution) at its own rate, a transposed convolution maps a
+// need of n output rows to ceil(n / stride) + taps input rows; conv_pre and conv_post add (k-1)/2.
+int decoder_halo_frames(const Voice& v) {
+  long need = (v.post_k - 1) / 2;
+  for (int si = (int)v.stages.size() - 1; si >= 0; --si) {
+    const StageW& s = v.stages[(size_t)si];
+    long rb = 0;
+    for (const ResBlockW& r : s.rbs) {
+      long h = 0;
+      for (size_t m = 0; m < r.c1.size(); ++m) {
+        h += (long)(r.c1[m].k - 1) / 2 * r.c1[m].dil;
+        if (!r.c2.empty()) h += (long)(r.c2[m].k - 1) / 2 * r.c2[m].dil;
+      }
+      rb = std::max(rb, h);
+    }
+    need += rb;
+    need = (need + s.stride - 1) / s.stride + s.up.taps;
+  }
+  need += (v.dec_pre.k - 1) / 2;
+  return (int)need + 2;
+}
+
 }  // namespace piper

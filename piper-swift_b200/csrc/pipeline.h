@@ -106,6 +106,21 @@ struct Context {
 
   int gap_p = 0, gap_f = 0;         // zero rows between utterances (phoneme / frame level)
 
+  // incremental decoding (PIPER_B200_FLAG_STREAM + piper_b200_stream_next): the flow output stays in `back`
+  struct StreamState {
+    bool active = false, use_tc = false, want_pcm = false;
+    int Rf = 0, f0 = 0, halo = 0;       // packed frame rows, first row of the utterance, generator halo (frames)
+    int64_t y_len = 0, next = 0;        // frames of the utterance / frames already returned
+    float* z = nullptr;
+    void* z16 = nullptr;
+    const int* frow_utt = nullptr;
+    const float* cond_dec = nullptr;
+    size_t arena_mark = 0;
+    int64_t chunk_offsets[2] = {0, 0};
+    int64_t chunk_frames = 0;
+  } sstate;
+  int stream_next(int64_t max_frames, piper_b200_result& rs, int32_t* is_final);
+
   void init(int dev);
   void destroy();
   void finalize_voice();            // voice.finalize() + derived layout constants
@@ -123,6 +138,27 @@ struct BackInputs {
   const float* cond_flow = nullptr; // [n_flows][batch][2H*layers] or null
   const float* cond_dec = nullptr;  // [batch][C0] or null
 };
+// Both back ends are two steps that can also be called separately (incremental decoding, synthesize.cpp):
+//   flow    : updates zp in place to the flow output z (and, for the tensor-core back end, returns the 16-bit
+//             operand copy of z the decoder's first convolution reads)
+//   decoder : HiFi-GAN over ANY window of packed frame rows [row0, row0 + rows): rows outside the window read
+//             as zeros, so only outputs at least `decoder_halo_frames` rows inside the window are exact
+struct FlowOut {
+  float* z = nullptr;         // [Rf][H] fp32 (== in.zp)
+  void* z16 = nullptr;        // [Rf][H] 16-bit (tensor-core back end) or null
+};
+struct DecoderIn {
+  const float* z = nullptr;   // window start
+  const void* z16 = nullptr;
+  const int* frow_utt = nullptr;
+  int rows = 0, batch = 0;
+  const float* cond_dec = nullptr;
+};
+FlowOut run_flow_f32(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep);
+float* run_decoder_f32(Context& ctx, Exec& ex, const DecoderIn& in);
+FlowOut run_flow_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep);
+float* run_decoder_tc(Context& ctx, Exec& ex, const DecoderIn& in);
+int decoder_halo_frames(const Voice& v);   // receptive half-width of the generator, in frames
 // returns packed audio [Rf*hop] (device, inside ctx.back); z_out (if non-null) receives the flow output
 float* run_back_f32(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep);
 size_t back_f32_bytes(const Context& ctx, int Rf, int batch);

@@ -68,6 +68,12 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
   const bool keep_dev = rq.flags & PIPER_B200_FLAG_KEEP_ON_DEVICE;
   const bool keep_stages = rq.flags & PIPER_B200_FLAG_KEEP_STAGES;
   const bool want_pcm = rq.flags & PIPER_B200_FLAG_PCM16;
+  const bool stream_begin = rq.flags & PIPER_B200_FLAG_STREAM;
+  sstate.active = false;
+  if (stream_begin && (rq.batch != 1 || keep_dev || keep_stages)) {
+    last_error = "invalid argument: PIPER_B200_FLAG_STREAM needs batch == 1 and host output";
+    return PIPER_B200_ERR_INVALID_ARGUMENT;
+  }
   const float noise_scale = std::isnan(rq.noise_scale) ? config.noise_scale : rq.noise_scale;
   const float length_scale = std::isnan(rq.length_scale) ? config.length_scale : rq.length_scale;
   const float noise_w = std::isnan(rq.noise_w) ? config.noise_w : rq.noise_w;
@@ -331,8 +337,18 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
     bi.zp = zp; bi.frow_utt = frow_utt; bi.Rf = Rf; bi.batch = B;
     bi.cond_flow = cond_flow; bi.cond_dec = cond_dec;
     CUDA_OK(cudaEventRecord(ev[3], stream));
-    float* packed = use_tc ? run_back_tc(*this, ex, bi, z_keep) : run_back_f32(*this, ex, bi, z_keep);
-    launch_gather_audio(ex, packed, d_fstart, d_ylen, d_soff, B, hp.hop, dense, pcm, total_samples);
+    if (stream_begin) {   // flow only; the generator runs chunk by chunk in stream_next()
+      const FlowOut fo = use_tc ? run_flow_tc(*this, ex, bi, nullptr) : run_flow_f32(*this, ex, bi, nullptr);
+      sstate = StreamState{};
+      sstate.use_tc = use_tc; sstate.want_pcm = want_pcm;
+      sstate.Rf = Rf; sstate.f0 = (int)h_fstart[0]; sstate.halo = decoder_halo_frames(voice);
+      sstate.y_len = h_ylen[0]; sstate.next = 0;
+      sstate.z = fo.z; sstate.z16 = fo.z16; sstate.frow_utt = frow_utt; sstate.cond_dec = cond_dec;
+      sstate.arena_mark = back.off;
+    } else {
+      float* packed = use_tc ? run_back_tc(*this, ex, bi, z_keep) : run_back_f32(*this, ex, bi, z_keep);
+      launch_gather_audio(ex, packed, d_fstart, d_ylen, d_soff, B, hp.hop, dense, pcm, total_samples);
+    }
     CUDA_OK(cudaEventRecord(ev[4], stream));
     if (keep_stages) {
       CUDA_OK(cudaMemcpyAsync(dump.z.data(), z_keep, dump.z.size() * 4, cudaMemcpyDeviceToHost, stream));
@@ -341,7 +357,9 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
 
     // ---- D2H ---------------------------------------------------------------------------------------------------------
     rs = piper_b200_result{};
-    if (keep_dev) {
+    if (stream_begin) {
+      rs.audio = nullptr;
+    } else if (keep_dev) {
       rs.audio = dense;
       rs.pcm16 = pcm;
     } else {
@@ -359,6 +377,7 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
     CUDA_OK(cudaEventRecord(ev[5], stream));
     CUDA_OK(cudaStreamSynchronize(stream));
     CUDA_OK(cudaGetLastError());
+    if (stream_begin) sstate.active = true;
     d_audio_dense = dense;
     rs.sample_offsets = sample_offsets.data();
     rs.frame_lengths = frame_lengths.data();
@@ -387,6 +406,69 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
   } catch (const std::exception& e) {
     last_error = e.what();
     cudaGetLastError();
+    return last_error.rfind("capacity", 0) == 0 ? PIPER_B200_ERR_CAPACITY : PIPER_B200_ERR_CUDA;
+  }
+}
+
+// Incremental decoding: the generator over frames [next, next + max_frames) of the streamed utterance plus the
+// receptive-field halo on both sides; window rows outside the packed frame range do not exist (read as zeros by
+// the kernels' bounds handling), rows of the halo are recomputed by the neighbouring chunk.
+int Context::stream_next(int64_t max_frames, piper_b200_result& rs, int32_t* is_final) {
+  if (!sstate.active) {
+    last_error = "state: no streamed utterance (call synthesize with PIPER_B200_FLAG_STREAM first)";
+    return PIPER_B200_ERR_STATE;
+  }
+  if (max_frames <= 0 || !is_final) {
+    last_error = "invalid argument: max_frames must be positive";
+    return PIPER_B200_ERR_INVALID_ARGUMENT;
+  }
+  using clk = std::chrono::steady_clock;
+  const auto t_wall0 = clk::now();
+  try {
+    CUDA_OK(cudaSetDevice(device));
+    Exec ex;
+    ex.st = stream;
+    const VoiceHParams& hp = voice.hp;
+    const int H = hp.hidden;
+    const int64_t n0 = sstate.next, n1 = std::min(sstate.y_len, n0 + max_frames);
+    const int w0 = (int)std::max<int64_t>(0, sstate.f0 + n0 - sstate.halo);
+    const int w1 = (int)std::min<int64_t>(sstate.Rf, sstate.f0 + n1 + sstate.halo);
+    back.off = sstate.arena_mark;
+    DecoderIn d;
+    d.z = sstate.z + (size_t)w0 * H;
+    d.z16 = sstate.z16 ? static_cast<const uint16_t*>(sstate.z16) + (size_t)w0 * H : nullptr;
+    d.frow_utt = sstate.frow_utt + w0;
+    d.rows = w1 - w0; d.batch = 1; d.cond_dec = sstate.cond_dec;
+    CUDA_OK(cudaEventRecord(ev[0], stream));
+    float* packed = sstate.use_tc ? run_decoder_tc(*this, ex, d) : run_decoder_f32(*this, ex, d);
+    const int64_t n_samples = (n1 - n0) * hp.hop;
+    const float* src = packed + (size_t)(sstate.f0 + n0 - w0) * hp.hop;
+    h_audio.reserve((size_t)n_samples * 4);
+    CUDA_OK(cudaMemcpyAsync(h_audio.p, src, (size_t)n_samples * 4, cudaMemcpyDeviceToHost, stream));
+    CUDA_OK(cudaEventRecord(ev[5], stream));
+    CUDA_OK(cudaStreamSynchronize(stream));
+    CUDA_OK(cudaGetLastError());
+    rs = piper_b200_result{};
+    rs.audio = static_cast<const float*>(h_audio.p);
+    sstate.chunk_offsets[0] = 0; sstate.chunk_offsets[1] = n_samples;
+    sstate.chunk_frames = n1 - n0;
+    rs.sample_offsets = sstate.chunk_offsets;
+    rs.frame_lengths = &sstate.chunk_frames;
+    rs.total_samples = n_samples;
+    rs.total_frames = n1 - n0;
+    sstate.next = n1;
+    *is_final = n1 >= sstate.y_len ? 1 : 0;
+    if (*is_final) sstate.active = false;
+    timings = piper_b200_timings{};
+    timings.gpu_ms = timings.decoder_ms = ms_between(ev[0], ev[5]);
+    timings.kernel_launches = ex.launches;
+    timings.d2h_bytes = n_samples * 4;
+    timings.wall_ms = std::chrono::duration<double, std::milli>(clk::now() - t_wall0).count();
+    return PIPER_B200_OK;
+  } catch (const std::exception& e) {
+    last_error = e.what();
+    cudaGetLastError();
+    sstate.active = false;
     return last_error.rfind("capacity", 0) == 0 ? PIPER_B200_ERR_CAPACITY : PIPER_B200_ERR_CUDA;
   }
 }

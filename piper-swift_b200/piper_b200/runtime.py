@@ -25,7 +25,7 @@ LIB_PATH = os.path.join(os.path.dirname(_HERE), "libpiper_b200.so")
 
 OK = 0
 PRECISION = {"fp32": 0, "bf16": 1, "f16": 2}
-FLAG_IDS_ON_DEVICE, FLAG_KEEP_ON_DEVICE, FLAG_KEEP_STAGES, FLAG_PCM16, FLAG_PROFILE = 1, 2, 4, 8, 16
+FLAG_IDS_ON_DEVICE, FLAG_KEEP_ON_DEVICE, FLAG_KEEP_STAGES, FLAG_PCM16, FLAG_PROFILE, FLAG_STREAM = 1, 2, 4, 8, 16, 32
 ERR_NAMES = {1: "invalid_argument", 2: "io", 3: "decode", 4: "unsupported", 5: "cuda", 6: "state", 7: "capacity"}
 
 
@@ -100,6 +100,7 @@ def load_library(path: str = LIB_PATH):
         "piper_b200_set_stream": (C.c_int, [P, P]),
         "piper_b200_synthesize": (C.c_int, [P, C.POINTER(Request), C.POINTER(Result)]),
         "piper_b200_get_timings": (C.c_int, [P, C.POINTER(Timings)]),
+        "piper_b200_stream_next": (C.c_int, [P, C.c_int64, C.POINTER(Result), C.POINTER(C.c_int32)]),
         "piper_b200_get_stage": (C.c_int, [P, C.c_char_p, C.c_int32, P, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
         "piper_b200_length_regulate": (C.c_int, [P, P, P, C.c_int32, C.c_float, P, P, P, C.c_int64]),
         "piper_b200_random_normal": (C.c_int, [P, C.c_uint64, C.c_int64, P]),
@@ -122,6 +123,7 @@ EXPORTED_SYMBOLS = [
     "piper_b200_finalize", "piper_b200_get_voice_info", "piper_b200_set_precision", "piper_b200_set_stream",
     "piper_b200_synthesize", "piper_b200_get_timings", "piper_b200_get_stage", "piper_b200_length_regulate",
     "piper_b200_random_normal", "piper_b200_selftest_conv", "piper_b200_ipa_to_ids", "piper_b200_config_ipa_to_ids",
+    "piper_b200_stream_next",
 ]
 
 
@@ -255,15 +257,32 @@ class PiperCUDARuntime:
     def synthesize_stream(self, phoneme_ids: Sequence[int], noise_scale: Optional[float] = None,
                           length_scale: Optional[float] = None, noise_w: Optional[float] = None,
                           chunk_size: int = 2048) -> Iterator[PiperAudioChunk]:
-        """synthesizeStream (:84-121): chunks the finished waveform, as the reference does today."""
+        """synthesizeStream (:84-121).  The reference chunks the finished waveform; here the generator itself
+        runs chunk by chunk (PIPER_B200_FLAG_STREAM + piper_b200_stream_next): the front end and the flow run
+        once, then every chunk decodes `chunk_size` samples (rounded up to whole frames) plus the generator's
+        receptive-field halo.  The concatenated chunks are bit-identical to synthesize()."""
         assert chunk_size > 0
         fmt = PiperAudioFormat(self.sample_rate, 1)
-        samples = self.synthesize(phoneme_ids, noise_scale, length_scale, noise_w)
-        idx = 0
-        while idx < len(samples):
-            end = min(len(samples), idx + chunk_size)
-            yield PiperAudioChunk(fmt, idx, samples[idx:end].copy(), end == len(samples))
-            idx = end
+        hop = int(self.info.hop)
+        frames = max(1, -(-chunk_size // hop))
+        ids = np.asarray(phoneme_ids, dtype=np.int64)
+        self.synthesize_packed(ids, np.array([len(ids)], np.int64), noise_scale, length_scale, noise_w,
+                               stream=True)
+        idx, final = 0, C.c_int32(0)
+        pending = np.zeros(0, np.float32)
+        while not final.value:
+            rs = Result()
+            self._check(self._lib.piper_b200_stream_next(self._ctx, frames, C.byref(rs), C.byref(final)))
+            n = int(rs.total_samples)
+            if n:
+                got = np.ctypeslib.as_array(C.cast(rs.audio, C.POINTER(C.c_float)), shape=(n,))
+                pending = np.concatenate([pending, got])
+            while len(pending) >= chunk_size and not (final.value and len(pending) == chunk_size):
+                yield PiperAudioChunk(fmt, idx, pending[:chunk_size].copy(), False)
+                pending = pending[chunk_size:]
+                idx += chunk_size
+        if len(pending):
+            yield PiperAudioChunk(fmt, idx, pending.copy(), True)
 
     # ---- additive: ragged batch, speakers, injected noise, device-resident inputs ---------------
     def synthesize_batch(self, utterances: Sequence[Sequence[int]], noise_scale: Optional[float] = None,
@@ -282,7 +301,7 @@ class PiperCUDARuntime:
     def synthesize_packed(self, ids: np.ndarray, lengths: np.ndarray, noise_scale=None, length_scale=None,
                           noise_w=None, speaker_ids=None, noise_dp=None, noise_main=None, seed=None,
                           keep_stages=False, pcm16=False, copy=True, ids_device_ptr: Optional[int] = None,
-                          keep_on_device: bool = False, profile: bool = False) -> BatchResult:
+                          keep_on_device: bool = False, profile: bool = False, stream: bool = False) -> BatchResult:
         B = int(len(lengths))
         lengths = np.ascontiguousarray(lengths, dtype=np.int64)
         rq = Request()
@@ -320,7 +339,7 @@ class PiperCUDARuntime:
             rq.noise_main_stride = stride
         rq.seed = self.options.seed if seed is None else seed
         rq.flags = ((FLAG_KEEP_STAGES if keep_stages else 0) | (FLAG_PCM16 if pcm16 else 0) |
-                    (FLAG_PROFILE if profile else 0) |
+                    (FLAG_PROFILE if profile else 0) | (FLAG_STREAM if stream else 0) |
                     (FLAG_IDS_ON_DEVICE if ids_device_ptr is not None else 0) |
                     (FLAG_KEEP_ON_DEVICE if keep_on_device else 0))
         rs = Result()
@@ -334,6 +353,8 @@ class PiperCUDARuntime:
         out = BatchResult([], fl, durs, int(rs.total_samples), int(rs.total_frames))
         if keep_on_device:
             out.device_ptr = int(rs.audio)
+            return out
+        if stream:      # audio follows through piper_b200_stream_next
             return out
         total = int(rs.total_samples)
         flat = np.ctypeslib.as_array(C.cast(rs.audio, C.POINTER(C.c_float)), shape=(total,))

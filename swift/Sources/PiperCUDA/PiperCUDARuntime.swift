@@ -110,21 +110,50 @@ public final class PiperCUDARuntime: @unchecked Sendable {
         return out
     }
 
-    /// synthesizeStream(...) - PiperMetalRuntime.swift:84-121: chunks the finished waveform
+    /// synthesizeStream(...) - PiperMetalRuntime.swift:84-121.  The reference chunks the finished waveform; here
+    /// the generator runs chunk by chunk: PIPER_B200_FLAG_STREAM runs the front end and the flow once, then every
+    /// piper_b200_stream_next decodes the next frames (plus the receptive-field halo).  Concatenated chunks are
+    /// bit-identical to synthesize(); the first chunk is available after front end + flow + one window.
     public func synthesizeStream(phonemeIDs: [Int], noiseScale: Float? = nil, lengthScale: Float? = nil,
                                  noiseW: Float? = nil, chunkSize: Int = 2048)
         -> AsyncThrowingStream<PiperAudioChunk, Error> {
         AsyncThrowingStream { continuation in
             do {
-                let audio = try self.synthesize(phonemeIDs: phonemeIDs, noiseScale: noiseScale,
-                                                lengthScale: lengthScale, noiseW: noiseW)
+                let ids = phonemeIDs.map { Int64($0) }
+                let lengths = [Int64(ids.count)]
+                var res = piper_b200_result()
+                try ids.withUnsafeBufferPointer { idp in
+                    try lengths.withUnsafeBufferPointer { lp in
+                        var rq = piper_b200_request()
+                        rq.phoneme_ids = idp.baseAddress
+                        rq.lengths = lp.baseAddress
+                        rq.batch = 1
+                        rq.noise_scale = noiseScale ?? .nan
+                        rq.length_scale = lengthScale ?? .nan
+                        rq.noise_w = noiseW ?? .nan
+                        rq.seed = self.options.seed
+                        rq.flags = UInt32(PIPER_B200_FLAG_STREAM)
+                        try Self.check(piper_b200_synthesize(self.ctx, &rq, &res), self.ctx)
+                    }
+                }
                 let fmt = PiperAudioFormat(sampleRate: Int(info.sample_rate), channels: 1)
-                var i = 0
-                while i < audio.count {
-                    let j = min(i + chunkSize, audio.count)
-                    continuation.yield(PiperAudioChunk(format: fmt, startSampleIndex: i,
-                                                       samples: Array(audio[i..<j]), isFinal: j == audio.count))
-                    i = j
+                let frames = Int64(max(1, (chunkSize + Int(info.hop) - 1) / Int(info.hop)))
+                var pending: [Float] = []
+                var start = 0
+                var isFinal: Int32 = 0
+                while isFinal == 0 {
+                    try Self.check(piper_b200_stream_next(self.ctx, frames, &res, &isFinal), self.ctx)
+                    pending.append(contentsOf: UnsafeBufferPointer(start: res.audio, count: Int(res.total_samples)))
+                    while pending.count >= chunkSize && !(isFinal != 0 && pending.count == chunkSize) {
+                        continuation.yield(PiperAudioChunk(format: fmt, startSampleIndex: start,
+                                                           samples: Array(pending[0..<chunkSize]), isFinal: false))
+                        pending.removeFirst(chunkSize)
+                        start += chunkSize
+                    }
+                }
+                if !pending.isEmpty {
+                    continuation.yield(PiperAudioChunk(format: fmt, startSampleIndex: start, samples: pending,
+                                                       isFinal: true))
                 }
                 continuation.finish()
             } catch { continuation.finish(throwing: error) }

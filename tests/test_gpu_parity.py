@@ -78,13 +78,39 @@ def test_reference_api_surface():
     b = r.synthesize(S.FIXTURE_IDS, noise_scale=0.667, length_scale=1.0, noise_w=0.8)
     assert a.dtype == np.float32 and a.ndim == 1 and a.size > 0 and np.isfinite(a).all()   # SmokeTests.swift:18-19
     assert np.array_equal(a, b)
+    t = r.last_run_timings
+    assert t["kernel_launches"] > 100 and t["gpu_ms"] > 0
     chunks = list(r.synthesize_stream(S.FIXTURE_IDS, chunk_size=2048))
     assert all(c.samples.size == 2048 for c in chunks[:-1]) and chunks[-1].is_final
     assert [c.start_sample_index for c in chunks] == list(range(0, a.size, 2048))
     assert np.array_equal(np.concatenate([c.samples for c in chunks]), a)
     assert chunks[0].format.sample_rate == 22050
-    t = r.last_run_timings
-    assert t["kernel_launches"] > 100 and t["gpu_ms"] > 0
+
+
+@pytest.mark.parametrize("name,precision,chunk", [("medium", "fp32", 2048), ("medium", "fp32", 5000),
+                                                  ("medium", "f16", 4096), ("medium", "bf16", 8192),
+                                                  ("high", "fp32", 4096), ("high", "f16", 3000),
+                                                  ("x_low", "f16", 2048), ("tiny", "fp32", 512)])
+def test_incremental_stream_is_bit_identical(name, precision, chunk):
+    """true streaming.  piper_b200_stream_next decodes `chunk` samples at a time (plus the
+    generator's receptive-field halo); the concatenation must equal the one-shot waveform bit for bit, in every
+    precision mode, and the chunk boundaries must follow synthesizeStream (PiperMetalRuntime.swift:84-121)."""
+    r = rt(name, precision)
+    ids = fixture_ids(4, S.SPECS[name].n_vocab)
+    a = r.synthesize(ids)
+    chunks = list(r.synthesize_stream(ids, chunk_size=chunk))
+    assert len(chunks) == -(-a.size // chunk) and len(chunks) > 2
+    assert all(c.samples.size == chunk and not c.is_final for c in chunks[:-1]) and chunks[-1].is_final
+    assert [c.start_sample_index for c in chunks] == list(range(0, a.size, chunk))
+    assert np.array_equal(np.concatenate([c.samples for c in chunks]), a)
+    assert r.last_run_timings["kernel_launches"] > 0
+    # the C-ABI state machine: no stream open -> ERR_STATE; a batch of two cannot stream
+    import ctypes as C
+    rs, fin = runtime.Result(), C.c_int32(0)
+    assert r._lib.piper_b200_stream_next(r._ctx, 8, C.byref(rs), C.byref(fin)) == 6   # PIPER_B200_ERR_STATE
+    with pytest.raises(PiperB200Error):
+        r.synthesize_packed(np.asarray(ids + ids, np.int64), np.asarray([len(ids)] * 2, np.int64), stream=True)
+    assert np.array_equal(r.synthesize(ids), a)
 
 
 def test_ipa_front_door_and_profile_flag():
