@@ -357,7 +357,7 @@ int piper_b200_random_normal(piper_b200_ctx* ctx, uint64_t seed, int64_t count, 
 
 int piper_b200_selftest_conv(piper_b200_ctx* ctx, int32_t mode, int32_t cin, int32_t cout, int32_t k,
                              int32_t dilation, int32_t stride, int32_t rows, int32_t precision, float* out4) {
-  if (!ctx || !out4 || mode < 0 || mode > 3 || cin <= 0 || cout <= 0 || k <= 0 || dilation <= 0 || rows <= 0) {
+  if (!ctx || !out4 || mode < 0 || mode > 5 || cin <= 0 || cout <= 0 || k <= 0 || dilation <= 0 || rows <= 0) {
     g_error = "invalid argument";
     if (ctx) ctx->c.last_error = g_error;
     return PIPER_B200_ERR_INVALID_ARGUMENT;

@@ -55,6 +55,26 @@ TcW make_tcw(Exec& ex, std::vector<void*>& allocs, const ConvW& a, const ConvW* 
   return t;
 }
 
+// bf16x6 fp32-emulation weights (conv_tc.h: TcW::split); cin must be a whole number of K blocks
+TcW make_tcw_split(Exec& ex, std::vector<void*>& allocs, const ConvW& a) {
+  TcW t;
+  t.cin = a.cin;
+  t.kb = a.cin % 64 == 0 ? 64 : 32;
+  t.cin_pad = a.cin;
+  t.cout = a.cout;
+  t.taps = a.taps; t.phases = a.phases; t.ct_pad = a.ct_pad; t.dil = a.dil; t.pad_l = a.pad_l;
+  t.bias = a.b;
+  t.split = 1;
+  if (a.cin % 32 || a.cout % 32 || a.phases != 1)
+    throw std::runtime_error("unsupported: convolution " + std::to_string(a.cin) + "->" + std::to_string(a.cout) +
+                             " does not fit the split tensor-core tiles");
+  const size_t n = (size_t)t.taps * t.cout * t.cin_pad * 6;
+  CUDA_OK(cudaMalloc(&t.w, n * 2));
+  allocs.push_back(t.w);
+  launch_pack_tc_weights_split(ex, a.w, a.ldw, a.taps, a.cin, a.cout, t.w, t.cout, 0, t.cin_pad);
+  return t;
+}
+
 void TcVoice::build(Exec& ex, const Voice& v, int f16_) {
   release();
   f16 = f16_;
@@ -71,6 +91,23 @@ void TcVoice::build(Exec& ex, const Voice& v, int f16_) {
     flows.push_back(t);
   }
   dec_pre = make_tcw(ex, allocs, v.dec_pre, nullptr, f16);
+  {   // text encoder: the four large convolutions of every layer, fp32 emulated (same weights in f16 and bf16 mode)
+    static const int front_env = [] { const char* e = getenv("PIPER_B200_FRONT_TC"); return e ? atoi(e) : 1; }();
+    bool ok = front_env != 0;
+    for (const EncLayerW& l : v.enc)
+      for (const ConvW* c : {&l.qkv, &l.o, &l.ffn1, &l.ffn2})
+        ok = ok && c->cin % 32 == 0 && c->cout % 32 == 0 && c->phases == 1;
+    enc.clear();
+    if (ok)
+      for (const EncLayerW& l : v.enc) {
+        TcEncLayer t;
+        t.qkv = make_tcw_split(ex, allocs, l.qkv);
+        t.o = make_tcw_split(ex, allocs, l.o);
+        t.ffn1 = make_tcw_split(ex, allocs, l.ffn1);
+        t.ffn2 = make_tcw_split(ex, allocs, l.ffn2);
+        enc.push_back(t);
+      }
+  }
   for (const StageW& s : v.stages) {
     TcStage t;
     t.up = make_tcw(ex, allocs, s.up, nullptr, f16);
@@ -155,6 +192,7 @@ void TcVoice::release() {
   allocs.clear();
   flows.clear();
   stages.clear();
+  enc.clear();
   built = false;
 }
 

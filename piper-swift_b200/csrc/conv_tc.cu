@@ -33,6 +33,7 @@ struct TcKernelParams {
   int gate, f16, window, a_col0, relu;
   int phase_cols;                   // merged polyphase ConvTranspose: columns per phase (0 = off)
   uint32_t tap_mask[8];             // per column tile: taps to run (merged polyphase weights are zero elsewhere)
+  int split_kbc;                    // bf16x6 fp32 emulation: K blocks per operand plane (0 = off)
   TcEpi e[2];
   const float* uttbias; int ldub;
   const int* row_utt; int valid_div;
@@ -42,6 +43,24 @@ struct TcKernelParams {
 }  // namespace
 
 namespace {
+
+// x = b0 + b1 + b2 with bf16 terms (round to nearest each time; the remainders are exact in fp32)
+__device__ __forceinline__ void split3(float x, uint16_t& b0, uint16_t& b1, uint16_t& b2) {
+  const __nv_bfloat16 h0 = __float2bfloat16_rn(x);
+  const float r1 = x - __bfloat162float(h0);
+  const __nv_bfloat16 h1 = __float2bfloat16_rn(r1);
+  const float r2 = r1 - __bfloat162float(h1);
+  const __nv_bfloat16 h2 = __float2bfloat16_rn(r2);
+  b0 = __bfloat16_as_ushort(h0); b1 = __bfloat16_as_ushort(h1); b2 = __bfloat16_as_ushort(h2);
+}
+__device__ __forceinline__ void split3x4(const float4& x, uint2& t0, uint2& t1, uint2& t2) {
+  uint16_t a[4], b[4], c[4];
+  split3(x.x, a[0], b[0], c[0]); split3(x.y, a[1], b[1], c[1]);
+  split3(x.z, a[2], b[2], c[2]); split3(x.w, a[3], b[3], c[3]);
+  t0 = make_uint2((uint32_t)a[0] | ((uint32_t)a[1] << 16), (uint32_t)a[2] | ((uint32_t)a[3] << 16));
+  t1 = make_uint2((uint32_t)b[0] | ((uint32_t)b[1] << 16), (uint32_t)b[2] | ((uint32_t)b[3] << 16));
+  t2 = make_uint2((uint32_t)c[0] | ((uint32_t)c[1] << 16), (uint32_t)c[2] | ((uint32_t)c[3] << 16));
+}
 
 // Epilogue of one 128-row x (n_groups * nt) accumulator tile, run by the four warps of a warpgroup (TMEM lane
 // quarter = warp % 4): waits for `bar`, then bias / utterance bias / residual / accumulate / mask and the
@@ -197,6 +216,10 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
             v[4 * i] += x.x; v[4 * i + 1] += x.y; v[4 * i + 2] += x.z; v[4 * i + 3] += x.w;
           }
         }
+        if (e.relu) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
+        }
         if (planar && active) {   // group-planar operand of the fused MRF stage: 16 bytes per (row, plane)
           uint16_t* base = static_cast<uint16_t*>(e.out_act) + ((size_t)(ocol >> 3) * e.act_rows + e.act_pad + orow_c) * 8;
 #pragma unroll
@@ -208,7 +231,7 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
             *reinterpret_cast<uint4*>(base + (size_t)pl * e.act_rows * 8) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
           }
         }
-        if (!e.out_f32 && (planar || !e.out_act)) continue;
+        if (!e.out_f32 && !e.out_split && (planar || !e.out_act)) continue;
         __syncwarp();                                     // the previous chunk's readers are done with tbuf
 #pragma unroll
         for (int i = 0; i < 8; ++i)
@@ -241,6 +264,14 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
           if (e.div != 0.f) { x.x = x.x / e.div; x.y = x.y / e.div; x.z = x.z / e.div; x.w = x.w / e.div; }
           if (!((valid_mask >> row) & 1u)) x = make_float4(0.f, 0.f, 0.f, 0.f);
           if (of) *reinterpret_cast<float4*>(of + it * rstep * e.ld_f32) = x;
+          if (e.out_split) {
+            uint16_t* sp = static_cast<uint16_t*>(e.out_split) + (orow0 + it * rstep) * e.ld_split + ocol + c4;
+            uint2 t0, t1, t2;
+            split3x4(x, t0, t1, t2);
+            *reinterpret_cast<uint2*>(sp) = t0;
+            *reinterpret_cast<uint2*>(sp + e.split_c) = t1;
+            *reinterpret_cast<uint2*>(sp + 2 * e.split_c) = t2;
+          }
           if (e.out_act && !planar) {
             const uint32_t lo = pack2(lrelu(x.x, e.act_slope), lrelu(x.y, e.act_slope), p.f16);
             const uint32_t hi = pack2(lrelu(x.z, e.act_slope), lrelu(x.w, e.act_slope), p.f16);
@@ -530,18 +561,26 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
         const int mt = rest % m_tiles, ntile = rest / m_tiles;
         const int m0 = mt * TC_BM;
         const int in_off = p.phases > 1 ? (phase + p.ct_pad) / p.phases : p.in_off;
-        for (int tap = 0; tap < p.taps; ++tap) {
-          if (!((p.tap_mask[ntile & 7] >> tap) & 1u)) continue;
-          const int arow = m0 + in_off + tap * p.tap_step;
-          const int wrow = (phase * p.taps + tap) * p.cout_rows + ntile * p.nt;
-          for (int kbi = 0; kbi < p.kblocks; ++kbi) {
-            mbar_wait(&empty[s], ph ^ 1u);
-            uint8_t* st = smem + (size_t)s * stage_bytes;
-            mbar_expect_tx(&full[s], (uint32_t)stage_bytes);
-            tma_load_2d(&tmap_a, &full[s], st, kbi * p.kb, arow);
-            for (int g = 0; g < p.n_groups; ++g)
-              tma_load_2d(&tmap_b, &full[s], st + a_bytes + g * b_bytes, kbi * p.kb, wrow + p.e[g].row0);
-            if (++s == stages) { s = 0; ph ^= 1u; }
+        // split (fp32-emulation) weights: operand plane outermost, so that every small term of every tap is
+        // accumulated before the first large one (the tensor core aligns addends to the largest exponent and
+        // drops what falls below its accumulator width)
+        const int kb_inner = p.split_kbc ? p.split_kbc : p.kblocks;
+        const int n_outer = p.split_kbc ? 6 : 1;
+        for (int pl = 0; pl < n_outer; ++pl) {
+          const int a_plane = p.split_kbc ? (int)((0x010210u >> (4 * pl)) & 0xFu) : 0;   // {0,1,2,0,1,0}
+          for (int tap = 0; tap < p.taps; ++tap) {
+            if (!((p.tap_mask[ntile & 7] >> tap) & 1u)) continue;
+            const int arow = m0 + in_off + tap * p.tap_step;
+            const int wrow = (phase * p.taps + tap) * p.cout_rows + ntile * p.nt;
+            for (int kbi = 0; kbi < kb_inner; ++kbi) {
+              mbar_wait(&empty[s], ph ^ 1u);
+              uint8_t* st = smem + (size_t)s * stage_bytes;
+              mbar_expect_tx(&full[s], (uint32_t)stage_bytes);
+              tma_load_2d(&tmap_a, &full[s], st, (a_plane * kb_inner + kbi) * p.kb, arow);
+              for (int g = 0; g < p.n_groups; ++g)
+                tma_load_2d(&tmap_b, &full[s], st + a_bytes + g * b_bytes, (pl * kb_inner + kbi) * p.kb, wrow + p.e[g].row0);
+              if (++s == stages) { s = 0; ph ^= 1u; }
+            }
           }
         }
       }
@@ -615,6 +654,16 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
   TcKernelParams p{};
   p.Q = a.Q; p.taps = w.taps; p.tap_step = a.tap_step; p.in_off = a.in_off;
   p.kb = w.kb; p.kblocks = w.cin_pad / w.kb;
+  const int kmul = w.split ? 6 : 1, amul = w.split ? 3 : 1;
+  if (w.split) {
+    if (a.f16 || a.gate || w.phase_cols || a.n_groups * a.nt > 256 || w.cin != w.cin_pad)
+      throw std::runtime_error("conv_tc: split (fp32-emulation) weights need bf16 operands, whole K blocks and the persistent kernel");
+    p.split_kbc = p.kblocks;
+    p.kblocks *= 6;
+  }
+  for (int g = 0; g < a.n_groups; ++g)
+    if ((a.e[g].relu || a.e[g].out_split) && (a.nt & 31))
+      throw std::runtime_error("conv_tc: relu / split outputs need 32-column tiles");
   p.nt = a.nt; p.n_groups = a.n_groups; p.cout_rows = w.cout;
   p.phases = w.phases; p.ct_pad = w.ct_pad; p.out_mul = a.out_mul;
   p.gate = a.gate; p.f16 = a.f16;
@@ -639,11 +688,11 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
     }
   }
 
-  const CUtensorMap ta = make_map(a.in, (uint64_t)a.cin, (uint64_t)a.R_in, (uint64_t)a.ldin, w.kb, TC_BM, a.f16);
+  const CUtensorMap ta = make_map(a.in, (uint64_t)a.cin * amul, (uint64_t)a.R_in, (uint64_t)a.ldin, w.kb, TC_BM, a.f16);
   static const int persist_env = [] { const char* e = getenv("PIPER_B200_TC_PERSIST"); return e ? atoi(e) : 1; }();
   if (w.phase_cols && !(persist_env && a.n_groups * a.nt <= 256))
     throw std::runtime_error("conv_tc: merged polyphase weights need the persistent kernel");
-  if (persist_env && a.n_groups * a.nt <= 256) {
+  if ((persist_env || w.split) && a.n_groups * a.nt <= 256) {
     static int num_sms = 0;
     if (!num_sms) {
       int dev = 0;
@@ -653,8 +702,8 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
       if (cudaFuncSetAttribute(conv_tc_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess)
         throw std::runtime_error("cuda: cannot raise dynamic shared memory limit for conv_tc_persist_kernel");
     }
-    const CUtensorMap tbp = make_map(w.w, (uint64_t)w.cin_pad, (uint64_t)w.phases * w.taps * w.cout, (uint64_t)w.cin_pad,
-                                     w.kb, a.nt, a.f16);
+    const CUtensorMap tbp = make_map(w.w, (uint64_t)w.cin_pad * kmul, (uint64_t)w.phases * w.taps * w.cout,
+                                     (uint64_t)w.cin_pad * kmul, w.kb, a.nt, a.f16);
     p.window = 0;
     uint32_t pc = 32;
     while ((int)pc < 2 * a.n_groups * a.nt) pc <<= 1;
@@ -733,6 +782,37 @@ __global__ void pack_tc_weights_kernel(const float* __restrict__ w, int ldw, int
   dst[((size_t)pt * cout_total + row_off + co) * cin_pad + ci] = bits;
 }
 
+// weights of a split convolution: row (pt, co) holds the planes [B2 B1 B0 B1 B0 B0] of cin_pad channels each
+__global__ void pack_tc_weights_split_kernel(const float* __restrict__ w, int ldw, int cin, int cout,
+                                             uint16_t* __restrict__ dst, int cout_total, int row_off, int cin_pad, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int ci = (int)(i % cin_pad);
+  const int co = (int)((i / cin_pad) % cout);
+  const int pt = (int)(i / ((int64_t)cin_pad * cout));
+  float v = 0.f;
+  if (ci < cin) v = w[((size_t)pt * cin + ci) * ldw + co];
+  uint16_t b[3];
+  split3(v, b[0], b[1], b[2]);
+  uint16_t* row = dst + ((size_t)pt * cout_total + row_off + co) * (size_t)(6 * cin_pad) + ci;
+  row[0] = b[2]; row[cin_pad] = b[1]; row[2 * cin_pad] = b[0];
+  row[3 * cin_pad] = b[1]; row[4 * cin_pad] = b[0]; row[5 * cin_pad] = b[0];
+}
+
+__global__ void split3_kernel(const float* __restrict__ src, int ldsrc, int64_t R, int C4, uint16_t* __restrict__ dst, int cpad) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= R * C4) return;
+  const int64_t r = i / C4;
+  const int c = (int)(i - r * C4) * 4;
+  const float4 x = *reinterpret_cast<const float4*>(src + r * ldsrc + c);
+  uint2 t0, t1, t2;
+  split3x4(x, t0, t1, t2);
+  uint16_t* o = dst + r * (int64_t)(3 * cpad) + c;
+  *reinterpret_cast<uint2*>(o) = t0;
+  *reinterpret_cast<uint2*>(o + cpad) = t1;
+  *reinterpret_cast<uint2*>(o + 2 * cpad) = t2;
+}
+
 __global__ void to_act16_kernel(const float* __restrict__ src, uint32_t* __restrict__ dst, int64_t n2, float slope,
                                 int f16) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -749,6 +829,24 @@ void launch_pack_tc_weights(Exec& ex, const float* w_f32, int ldw, int phases_ta
   pack_tc_weights_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ex.st>>>(w_f32, ldw, cin, cout,
                                                                         static_cast<uint16_t*>(dst), cout_total, row_off,
                                                                         cin_pad, f16, n);
+  ++ex.launches;
+}
+
+void launch_pack_tc_weights_split(Exec& ex, const float* w_f32, int ldw, int phases_taps, int cin, int cout, void* dst,
+                                  int cout_total, int row_off, int cin_pad) {
+  const int64_t n = (int64_t)phases_taps * cout * cin_pad;
+  if (n <= 0) return;
+  pack_tc_weights_split_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ex.st>>>(w_f32, ldw, cin, cout,
+                                                                              static_cast<uint16_t*>(dst), cout_total,
+                                                                              row_off, cin_pad, n);
+  ++ex.launches;
+}
+
+void launch_split3(Exec& ex, const float* src, int ldsrc, int64_t R, int C, void* dst, int cpad) {
+  if (C % 4 || ldsrc % 4 || cpad % 4) throw std::runtime_error("split3: channel counts must be multiples of 4");
+  const int64_t n = R * (C / 4);
+  if (n <= 0) return;
+  split3_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ex.st>>>(src, ldsrc, R, C / 4, static_cast<uint16_t*>(dst), cpad);
   ++ex.launches;
 }
 

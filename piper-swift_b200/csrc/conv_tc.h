@@ -30,7 +30,11 @@ struct TcW {
   // belongs to output row q * stride + n / phase_cols, channel n % phase_cols.  taps = union taps,
   // phases = 1, first_off = input row offset of union tap 0 (tap step +1).
   int phase_cols = 0, merged_phases = 0, first_off = 0;
-  uint32_t phase_tapmask[16] = {0};   // per phase: bit u set when union tap u carries weights of that phase
+  uint32_t phase_tapmask[16] = {0};   // per phase: bit u set when union tap u carries weights of that phase  // fp32 emulation ("bf16x6"): both operands are split into three bf16 terms x = x0 + x1 + x2 (24 mantissa bits) and
+  // the six products with i + j <= 2 are accumulated in fp32, smallest first.  The weight rows then hold six
+  // planes of cin_pad channels [B2 B1 B0 B1 B0 B0]; the activation operand is [rows][3 * cin_pad] = [A0 A1 A2] and
+  // the kernel's producer reads planes [A0 A1 A2 A0 A1 A0] against them.
+  int split = 0;
 };
 
 struct TcEpi {
@@ -48,6 +52,10 @@ struct TcEpi {
   int accum = 0;                 // value += out_f32 (previous contents)
   float div = 0.f;               // if != 0: value /= div (after accum)
   float act_slope = 1.f;
+  int relu = 0;                  // max(acc + bias, 0) before residual / accumulate
+  // three-term bf16 split of the final fp32 value (operand of a `split` convolution): plane t of channel c at
+  // out_split[row * ld_split + t * split_c + col0 + c]
+  void* out_split = nullptr; int ld_split = 0, split_c = 0;
 };
 
 struct TcConvArgs {
@@ -76,6 +84,10 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a);
 // [ (ph*taps+t)*cout_total + row_off + co ][cin_pad]
 void launch_pack_tc_weights(Exec& ex, const float* w_f32, int ldw, int phases_taps, int cin, int cout,
                             void* dst, int cout_total, int row_off, int cin_pad, int f16);
+// split-operand helpers (fp32 emulation): weights [phases*taps][cout][6 * cin_pad], activations [R][3 * cpad]
+void launch_pack_tc_weights_split(Exec& ex, const float* w_f32, int ldw, int phases_taps, int cin, int cout,
+                                  void* dst, int cout_total, int row_off, int cin_pad);
+void launch_split3(Exec& ex, const float* src, int ldsrc, int64_t R, int C, void* dst, int cpad);
 // fp32 -> 16-bit copy of an activation tensor [R][C] (optional leaky-relu), used at stage boundaries
 void launch_to_act16(Exec& ex, const float* src, void* dst, int64_t n, float slope, int f16);
 

@@ -71,9 +71,14 @@ struct TcStage {
   int mrf_taps = 0;
   int tap_base[MRF_MAX_RB][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}};
 };
+// text-encoder convolutions as fp32-emulating tensor-core GEMMs (bf16x6 split operands, conv_tc.h)
+struct TcEncLayer {
+  TcW qkv, o, ffn1, ffn2;
+};
 struct TcVoice {
   bool built = false;
   int f16 = 0;
+  std::vector<TcEncLayer> enc;   // empty when PIPER_B200_FRONT_TC=0 or a shape does not fit
   std::vector<TcCoupling> flows;
   TcW dec_pre;
   std::vector<TcStage> stages;
@@ -82,6 +87,7 @@ struct TcVoice {
   void release();
 };
 TcW make_tcw(Exec& ex, std::vector<void*>& allocs, const ConvW& a, const ConvW* b, int f16);
+TcW make_tcw_split(Exec& ex, std::vector<void*>& allocs, const ConvW& a);   // bf16x6 fp32 emulation (conv_tc.h)
 
 struct Context {
   int device = 0;

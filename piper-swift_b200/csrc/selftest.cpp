@@ -47,9 +47,107 @@ float from16(uint16_t b, int f16) {
 
 // mode 0: conv (+bias +residual), 1: WN gate (cout = 2*H), 2: res|skip two-group (cout = 2*H, skip accumulates),
 // mode 3: transposed conv (stride, k multiple of stride)
+// modes 4 / 5: fp32 emulation on the tensor cores (bf16x6 split operands, conv_tc.h) against the fp32 CUDA-core
+// kernel, both measured against a float64 host reference on full-mantissa random data.
+// out4 = {err(tc), err(simt), tc ms (incl. the activation split), simt ms}; err = rms (4) or max-abs (5).
+static void selftest_split(Context& c, int mode, int cin, int cout, int k, int dil, int rows, float* out4) {
+  Exec ex;
+  ex.st = c.stream;
+  std::mt19937 rng(77u + cin * 7 + cout * 13 + k * 31);
+  std::normal_distribution<float> nd(0.f, 1.f);
+  const int ldw = (cout + 63) / 64 * 64;
+  std::vector<float> hw((size_t)k * cin * ldw, 0.f), hb(ldw, 0.f), hx((size_t)rows * cin);
+  const float ws = 1.0f / std::sqrt((float)(cin * k));
+  for (int t = 0; t < k; ++t)
+    for (int ci = 0; ci < cin; ++ci)
+      for (int co = 0; co < cout; ++co) hw[((size_t)t * cin + ci) * ldw + co] = nd(rng) * ws;
+  for (int co = 0; co < cout; ++co) hb[co] = nd(rng) * 0.1f;
+  for (auto& v : hx) v = nd(rng);
+  std::vector<int> hutt(rows, 0);
+  DevBuf dw(hw.size() * 4), db(hb.size() * 4), dx(hx.size() * 4), dxs(hx.size() * 6), dutt(rows * 4);
+  DevBuf dref((size_t)rows * cout * 4), dtc((size_t)rows * cout * 4);
+  CUDA_OK(cudaMemcpy(dw.p, hw.data(), hw.size() * 4, cudaMemcpyHostToDevice));
+  CUDA_OK(cudaMemcpy(db.p, hb.data(), hb.size() * 4, cudaMemcpyHostToDevice));
+  CUDA_OK(cudaMemcpy(dx.p, hx.data(), hx.size() * 4, cudaMemcpyHostToDevice));
+  CUDA_OK(cudaMemcpy(dutt.p, hutt.data(), rows * 4, cudaMemcpyHostToDevice));
+  ConvW cw;
+  cw.w = dw.as<float>(); cw.b = db.as<float>();
+  cw.cin = cin; cw.cout = cout; cw.k = k; cw.dil = dil; cw.ldw = ldw;
+  cw.taps = k; cw.phases = 1; cw.ct_pad = 0; cw.pad_l = dil * (k - 1) / 2;
+  std::vector<void*> allocs;
+  TcW tw = make_tcw_split(ex, allocs, cw);
+  cudaEvent_t e0, e1, e2;
+  CUDA_OK(cudaEventCreate(&e0)); CUDA_OK(cudaEventCreate(&e1)); CUDA_OK(cudaEventCreate(&e2));
+  ConvArgs r;
+  r.in = dx.as<float>(); r.ldin = cin;
+  r.w = cw.w; r.ldw = ldw; r.bias = cw.b;
+  r.out = dref.as<float>(); r.ldout = cout;
+  r.row_utt = dutt.as<int>(); r.valid_div = 1;
+  r.R_in = rows; r.Q = rows; r.cin = cin; r.cout = cout; r.taps = k;
+  r.tap_step = dil; r.in_off = -cw.pad_l;
+  TcConvArgs a;
+  a.in = dxs.p; a.ldin = 3 * cin; a.R_in = rows; a.cin = cin;
+  a.w = &tw; a.Q = rows;
+  a.row_utt = dutt.as<int>(); a.valid_div = 1;
+  a.f16 = 0; a.tap_step = dil; a.in_off = -cw.pad_l;
+  a.n_groups = 1;
+  a.nt = 32;
+  for (int nt : {256, 192, 128, 96, 64, 32}) if (cout % nt == 0) { a.nt = nt; break; }
+  if (const char* e = getenv("PIPER_B200_SELFTEST_NT")) { const int nt = atoi(e); if (nt >= 32 && cout % nt == 0) a.nt = nt; }
+  a.n_tiles = cout / a.nt;
+  a.e[0].bias = cw.b; a.e[0].out_f32 = dtc.as<float>(); a.e[0].ld_f32 = cout;
+  for (int rep = 0; rep < 2; ++rep) {   // second pass is the timed one
+    CUDA_OK(cudaEventRecord(e0, c.stream));
+    launch_conv_f32(ex, r);
+    CUDA_OK(cudaEventRecord(e1, c.stream));
+    launch_split3(ex, dx.as<float>(), cin, rows, cin, dxs.p, cin);
+    launch_conv_tc(ex, a);
+    CUDA_OK(cudaEventRecord(e2, c.stream));
+  }
+  CUDA_OK(cudaStreamSynchronize(c.stream));
+  CUDA_OK(cudaGetLastError());
+  float ms_ref = 0, ms_tc = 0;
+  cudaEventElapsedTime(&ms_ref, e0, e1);
+  cudaEventElapsedTime(&ms_tc, e1, e2);
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
+  std::vector<float> href((size_t)rows * cout), htc((size_t)rows * cout);
+  CUDA_OK(cudaMemcpy(href.data(), dref.p, href.size() * 4, cudaMemcpyDeviceToHost));
+  CUDA_OK(cudaMemcpy(htc.data(), dtc.p, htc.size() * 4, cudaMemcpyDeviceToHost));
+  for (void* p : allocs) cudaFree(p);
+  // float64 reference on a sample of rows (every row near the edges, then a stride)
+  double se_tc = 0, se_ref = 0, mx_tc = 0, mx_ref = 0;
+  size_t cnt = 0;
+  const int step = rows > 512 ? rows / 256 : 1;
+  for (int q = 0; q < rows; q += (q < 8 || q >= rows - 8) ? 1 : step) {
+    for (int co = 0; co < cout; ++co) {
+      double acc = hb[co];
+      for (int t = 0; t < k; ++t) {
+        const int ir = q - cw.pad_l + t * dil;
+        if (ir < 0 || ir >= rows) continue;
+        const float* xr = &hx[(size_t)ir * cin];
+        const float* wr = &hw[(size_t)t * cin * ldw + co];
+        for (int ci = 0; ci < cin; ++ci) acc += (double)xr[ci] * (double)wr[(size_t)ci * ldw];
+      }
+      const double d1 = std::fabs((double)htc[(size_t)q * cout + co] - acc);
+      const double d2 = std::fabs((double)href[(size_t)q * cout + co] - acc);
+      se_tc += d1 * d1; se_ref += d2 * d2;
+      mx_tc = std::max(mx_tc, std::isnan(d1) ? 1e30 : d1); mx_ref = std::max(mx_ref, d2);
+      ++cnt;
+    }
+  }
+  out4[0] = mode == 4 ? (float)std::sqrt(se_tc / cnt) : (float)mx_tc;
+  out4[1] = mode == 4 ? (float)std::sqrt(se_ref / cnt) : (float)mx_ref;
+  out4[2] = ms_tc; out4[3] = ms_ref;
+}
+
 int Context::selftest_conv(int mode, int cin, int cout, int k, int dil, int stride, int rows, int prec, float* out4) {
   try {
     CUDA_OK(cudaSetDevice(device));
+    if (mode == 4 || mode == 5) {
+      if (cin % 32 || cout % 32 || k < 1 || rows < 1) throw std::runtime_error("invalid argument: split selftest shape");
+      selftest_split(*this, mode, cin, cout, k, dil, rows, out4);
+      return PIPER_B200_OK;
+    }
     if (prec != PIPER_B200_PRECISION_BF16 && prec != PIPER_B200_PRECISION_F16)
       throw std::runtime_error("invalid argument: selftest precision must be bf16 or f16");
     const int f16 = prec == PIPER_B200_PRECISION_F16;

@@ -31,6 +31,23 @@ ConvArgs conv_args(const ConvW& w, const float* in, int ldin, float* out, int ld
   return a;
 }
 
+// a split (fp32-emulating) tensor-core convolution over the packed phoneme rows; `in` = [R][3 * cin] bf16
+TcConvArgs split_args(const TcW& w, const void* in, int R, const int* row_utt) {
+  TcConvArgs a;
+  a.in = in; a.ldin = 3 * w.cin; a.R_in = R; a.cin = w.cin;
+  a.w = &w; a.Q = R;
+  a.row_utt = row_utt; a.valid_div = 1;
+  a.f16 = 0;
+  a.tap_step = w.dil; a.in_off = -w.pad_l;
+  a.n_groups = 1;
+  a.nt = 32;
+  for (int nt : {256, 192, 128, 96, 64, 32})
+    if (w.cout % nt == 0) { a.nt = nt; break; }
+  a.n_tiles = w.cout / a.nt;
+  a.e[0].bias = w.bias;
+  return a;
+}
+
 // DDSConv: per layer depthwise conv + LN + GELU, 1x1 conv, LN + GELU, residual
 void run_dds(Exec& ex, const std::vector<DDSLayerW>& layers, float* h, float* t1, float* t2, const int* row_utt,
              int R, int C) {
@@ -130,6 +147,8 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
     fb += (size_t)Rp * 4 * (H * 8 + 3 * H + hp.filter + 2 * H + 32 + 2 + 1) + (size_t)Rp * 4 * 4;
     fb += (size_t)n_ids * 8 * 2 + (size_t)Rp * 8 + (size_t)B * (8 * 6 + 4 * 4) + (size_t)B * condw * 4;
     if (rq.noise_dp) fb += (size_t)n_ids * 2 * 4;
+    const bool front_tc = use_tc && !tc.enc.empty();
+    if (front_tc) fb += (size_t)Rp * 2 * 3 * (2 * H + hp.filter) + 3 * 256;   // split operands of x, att and the FFN mid
     fb += 64 * 256;
     front.reserve(fb);
     front.reset();
@@ -147,6 +166,10 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
     float* y = F.alloc<float>((size_t)Rp * H);
     float* mid = F.alloc<float>((size_t)Rp * hp.filter);
     float* stats = F.alloc<float>((size_t)Rp * 2 * H);
+    uint16_t* xs = front_tc ? F.alloc<uint16_t>((size_t)Rp * 3 * H) : nullptr;
+    uint16_t* atts = front_tc ? F.alloc<uint16_t>((size_t)Rp * 3 * H) : nullptr;
+    uint16_t* mids = front_tc ? F.alloc<uint16_t>((size_t)Rp * 3 * hp.filter) : nullptr;
+    if (front_tc && (!xs || !atts || !mids)) throw std::runtime_error("capacity: front arena sizing bug (split operands)");
     float* dph = F.alloc<float>((size_t)Rp * H);
     float* dpc = F.alloc<float>((size_t)Rp * H);
     float* hh = F.alloc<float>((size_t)Rp * H);
@@ -220,7 +243,45 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
     // ---- text encoder ------------------------------------------------------------------
     launch_embed(ex, d_ids_packed, voice.emb, x, Rp, H, hp.n_vocab, std::sqrt((float)H));
     CUDA_OK(cudaMemsetAsync(att, 0, (size_t)Rp * H * 4, stream));
-    for (const EncLayerW& l : voice.enc) {
+    for (size_t li = 0; front_tc && li < voice.enc.size(); ++li) {
+      // tensor-core form: every large convolution reads three-term bf16 splits of its fp32 input (fp32 emulation,
+      // conv_tc.h) - same graph, same fp32 tensors between the kernels
+      const EncLayerW& l = voice.enc[li];
+      const TcEncLayer& t = tc.enc[li];
+      launch_split3(ex, x, H, Rp, H, xs, H);
+      {
+        TcConvArgs a = split_args(t.qkv, xs, Rp, p_utt);
+        a.e[0].out_f32 = qkv; a.e[0].ld_f32 = 3 * H;
+        launch_conv_tc(ex, a);
+      }
+      launch_attention(ex, qkv, l.rel_k, l.rel_v, att, d_utt_start, d_utt_len, B, max_len, H, hp.n_heads, hp.window);
+      launch_split3(ex, att, H, Rp, H, atts, H);
+      {
+        TcConvArgs a = split_args(t.o, atts, Rp, p_utt);
+        a.e[0].out_f32 = y; a.e[0].ld_f32 = H;
+        launch_conv_tc(ex, a);
+      }
+      LNArgs n1;
+      n1.x = x; n1.y = y; n1.gamma = l.n1.gamma; n1.beta = l.n1.beta; n1.out = x; n1.row_utt = p_utt; n1.R = Rp; n1.C = H;
+      launch_layernorm(ex, n1);
+      launch_split3(ex, x, H, Rp, H, xs, H);
+      {
+        TcConvArgs a = split_args(t.ffn1, xs, Rp, p_utt);
+        a.e[0].relu = 1;
+        a.e[0].out_split = mids; a.e[0].ld_split = 3 * hp.filter; a.e[0].split_c = hp.filter;
+        launch_conv_tc(ex, a);
+      }
+      {
+        TcConvArgs a = split_args(t.ffn2, mids, Rp, p_utt);
+        a.e[0].out_f32 = y; a.e[0].ld_f32 = H;
+        launch_conv_tc(ex, a);
+      }
+      LNArgs n2 = n1;
+      n2.gamma = l.n2.gamma; n2.beta = l.n2.beta;
+      launch_layernorm(ex, n2);
+    }
+    for (size_t li = 0; !front_tc && li < voice.enc.size(); ++li) {
+      const EncLayerW& l = voice.enc[li];
       launch_conv_f32(ex, conv_args(l.qkv, x, H, qkv, 3 * H, Rp, p_utt));
       launch_attention(ex, qkv, l.rel_k, l.rel_v, att, d_utt_start, d_utt_len, B, max_len, H, hp.n_heads, hp.window);
       launch_conv_f32(ex, conv_args(l.o, att, H, y, H, Rp, p_utt));
