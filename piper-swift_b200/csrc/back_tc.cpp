@@ -345,6 +345,7 @@ float* run_decoder_tc(Context& ctx, Exec& ex, const DecoderIn& in) {
     throw std::runtime_error("capacity: back arena too small (decoder)");
 
   int cur = 0;
+  bool post_fused = false;
   {
     TcConvArgs a = tc_args(tv.dec_pre, zb, H, Rf, in.frow_utt, 1, f16);
     a.uttbias = in.cond_dec; a.ldub = v.hp.dec_c0;
@@ -407,7 +408,11 @@ float* run_decoder_tc(Context& ctx, Exec& ex, const DecoderIn& in) {
       a.w = ts.mrf_w; a.total_taps = ts.mrf_taps;
       a.x_act = xub; a.act_rows = act_rows; a.act_pad = act_pad;
       a.row_utt = in.frow_utt; a.valid_div = U;
-      if (last_stage) a.out_f32 = xs;
+      static const int post_env = [] { const char* e = getenv("PIPER_B200_MRF_POST"); return e ? atoi(e) : 1; }();
+      if (last_stage && post_env && mrf_post_supported(C, v.post_k)) {   // conv_post + tanh as the stage kernel's epilogue
+        a.post_w = v.post_w; a.post_k = v.post_k; a.post_slope = 0.01f; a.post_out = audio;
+        post_fused = true;
+      } else if (last_stage) a.out_f32 = xs;
       else { a.out_act = xsb; a.act_slope = 0.1f; }
       a.f16 = f16;
       launch_mrf_tc(ex, a);
@@ -447,7 +452,7 @@ float* run_decoder_tc(Context& ctx, Exec& ex, const DecoderIn& in) {
     cur ^= 1;
     R = Rn;
   }
-  launch_conv_post_tanh(ex, xs, v.stages.back().ch, v.post_w, v.post_k, 0.01f, in.frow_utt, U, audio, R);
+  if (!post_fused) launch_conv_post_tanh(ex, xs, v.stages.back().ch, v.post_w, v.post_k, 0.01f, in.frow_utt, U, audio, R);
   return audio;
 }
 

@@ -41,6 +41,7 @@ struct MrfParams {
   const int* row_utt; int valid_div;
   void* out_act; float act_slope;
   float* out_f32;
+  const float* post_w; int post_k; float post_slope; float* post_out;   // fused conv_post + tanh (C = 32 only)
   int f16, ring, resident;
   uint32_t tmem_cols;
   uint32_t* trace;            // debug timeline of CTA 0 (PIPER_B200_MRF_TRACE), else null
@@ -73,8 +74,13 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
   uint64_t* d_empty = d_full + MRF_MAX_M;
   uint64_t* y_ready = d_empty + MRF_MAX_M;
   uint64_t* s_full = y_ready + MRF_MAX_M;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_full + MRF_MAX_M);
+  uint64_t* e_ready = s_full + MRF_MAX_M;    // fused conv_post: tile i's edge partial sums are published
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(e_ready + MRF_MAX_M);
   float* sbias = reinterpret_cast<float*>(tmem_slot + 4);   // [nk][C] b1 then [C] sum_r b2
+  // fused conv_post: weights centred in a 7-tap frame [7][32], then the partial sums of the three first / last rows
+  // of every 32-row block [2 window parities][m*4][2][3][7] (what the neighbouring warps need of each other)
+  float* spost = sbias + (MRF_MAX_RB + 1) * C;
+  float* sedge = spost + 7 * 32;
 
   // warp index and TMEM base go through a shuffle so that the compiler can prove them warp-uniform: the
   // role branches become uniform and the MMA descriptors live in uniform registers (without this every
@@ -106,6 +112,13 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
     else for (int q = 0; q < p.nk; ++q) v += p.b2[q][c];
     sbias[i] = v;
   }
+  if (p.post_out) {
+    const int shift = 3 - (p.post_k - 1) / 2;
+    for (int i = threadIdx.x; i < 7 * 32; i += blockDim.x) {
+      const int t = i / 32 - shift, c = i & 31;
+      spost[i] = (t >= 0 && t < p.post_k && c < C) ? p.post_w[t * C + c] : 0.f;
+    }
+  }
   fence_proxy_async();
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_w);
@@ -120,6 +133,7 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
       mbar_init(&d_empty[i], 4 * (C / 32));   // one arrival per epilogue warp of every column half
       mbar_init(&y_ready[i], 4 * (C / 32));
       mbar_init(&s_full[i], 1);
+      mbar_init(&e_ready[i], 4);
     }
     fence_barrier_init();
   } else if (warp == 1) {
@@ -382,6 +396,94 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
       // ---- stage output: (S + sum_r b2_r) / nk over the window's valid rows ----
       const uint32_t nl = n - 1u;
       const float* b2s = sbias + p.nk * C;
+      if (C == 32 && p.post_out) {
+        // Fused conv_post + tanh.  Every thread owns one row with all 32 channels: it forms the seven per-tap channel
+        // sums q_t = sum_c w[t][c] * lrelu(out[row][c]); audio[r] = tanh(sum_t q_t[r + t - 3]) then needs the q of the
+        // three rows on either side - lanes of the same warp (shuffles) or, at the 32-row block edges, of a neighbouring
+        // warp (through `sedge`, published per tile on `e_ready`: only neighbouring tiles couple, and `sedge` is double
+        // buffered by window parity so that a fast warp cannot overwrite what a slow neighbour still reads).  The tap
+        // sum always runs t = 0..6 whatever the source, so a sample does not depend on where its row falls in a window.
+        float* sedge_w = sedge + (it & 1) * (4 * m * 42);
+        constexpr int MAXU = (MRF_MAX_M + MRF_EG - 1) / MRF_EG;
+        float q[MAXU][7];
+        uint32_t vmask = 0u;
+#pragma unroll
+        for (int ui = 0; ui < MAXU; ++ui) {
+          const int i = group + ui * MRF_EG;               // unit = tile (one 32-column half)
+          if (i < units) {
+            const int row_in_win = 128 * i + quarter * 32 + lane;
+            const int grow = w0 + row_in_win;
+            const bool inr = grow >= 0 && grow < p.R;
+            int ru = 0;
+            if (inr && p.row_utt) ru = p.row_utt[grow / p.valid_div];
+            TRACE(14u, nl, (uint32_t)i);
+            mbar_wait(&s_full[i], nl & 1u);
+            tc_fence_after();
+            TRACE(15u, nl, (uint32_t)i);
+            asm volatile("" : "+r"(ru));
+            const bool valid = inr && ru >= 0;
+            vmask |= (valid ? 1u : 0u) << ui;
+            const uint32_t scol = tmem_base + lane_sel + s_col + (uint32_t)(i * C);
+            uint32_t t0[16], t1[16];
+            __syncwarp();
+            tmem_ld16_async(scol, t0);
+            tmem_ld16_async(scol + 16u, t1);
+            tmem_wait_ld();
+            float x[32];
+#pragma unroll
+            for (int e = 0; e < 16; ++e) {
+              x[e] = valid ? lrelu((__uint_as_float(t0[e]) + b2s[e]) * inv_nk, p.post_slope) : 0.f;
+              x[16 + e] = valid ? lrelu((__uint_as_float(t1[e]) + b2s[16 + e]) * inv_nk, p.post_slope) : 0.f;
+            }
+#pragma unroll
+            for (int t = 0; t < 7; ++t) {
+              const float4* w4 = reinterpret_cast<const float4*>(spost + t * 32);
+              float a = 0.f;
+#pragma unroll
+              for (int c4 = 0; c4 < 8; ++c4) {
+                const float4 w = w4[c4];
+                a = fmaf(x[4 * c4], w.x, a);
+                a = fmaf(x[4 * c4 + 1], w.y, a);
+                a = fmaf(x[4 * c4 + 2], w.z, a);
+                a = fmaf(x[4 * c4 + 3], w.w, a);
+              }
+              q[ui][t] = a;
+            }
+            const int blk = i * 4 + quarter;
+            if (lane < 3 || lane >= 29) {
+              float* e = sedge_w + ((blk * 2 + (lane < 3 ? 0 : 1)) * 3 + (lane < 3 ? lane : lane - 29)) * 7;
+#pragma unroll
+              for (int t = 0; t < 7; ++t) e[t] = q[ui][t];
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&e_ready[i]);
+          }
+        }
+#pragma unroll
+        for (int ui = 0; ui < MAXU; ++ui) {
+          const int i = group + ui * MRF_EG;
+          if (i < units) {
+            const int row_in_win = 128 * i + quarter * 32 + lane;
+            const int grow = w0 + row_in_win;
+            const bool owned = row_in_win >= p.halo && row_in_win < p.halo + p.V && grow >= 0 && grow < p.R;
+            const int blk = i * 4 + quarter;
+            for (int ii = (i > 0 ? i - 1 : 0); ii <= (i + 1 < m ? i + 1 : m - 1); ++ii)
+              mbar_wait(&e_ready[ii], (uint32_t)it & 1u);
+            float sum = 0.f;
+#pragma unroll
+            for (int t = 0; t < 7; ++t) {
+              const int src = lane + t - 3;
+              float v = __shfl_sync(0xffffffffu, q[ui][t], src & 31);
+              if (src < 0) v = blk > 0 ? sedge_w[(((blk - 1) * 2 + 1) * 3 + (src + 3)) * 7 + t] : 0.f;
+              else if (src > 31) v = blk + 1 < 4 * m ? sedge_w[(((blk + 1) * 2) * 3 + (src - 32)) * 7 + t] : 0.f;
+              sum += v;
+            }
+            if (owned) p.post_out[grow] = ((vmask >> ui) & 1u) ? tanhf(sum) : 0.f;
+            TRACE(16u, nl, (uint32_t)i);
+          }
+        }
+      } else
       for (int u = group; u < units; u += MRF_EG) {
         const int i = u / HALVES, cb = (u % HALVES) * 32;
         const int row_in_win = 128 * i + quarter * 32 + lane;
@@ -458,8 +560,13 @@ bool mrf_tc_supported(int C, int nk, const int* k, const int* d0, const int* d1)
   return taps > 0;
 }
 
+bool mrf_post_supported(int C, int post_k) { return C == 32 && post_k >= 1 && post_k <= 7 && (post_k & 1) == 1; }
+
 void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   if (a.R <= 0) return;
+  const bool post = a.post_out != nullptr;
+  if (post && (!mrf_post_supported(a.C, a.post_k) || !a.post_w))
+    throw std::runtime_error("conv_mrf: fused conv_post needs C = 32 and an odd kernel of at most 7 taps");
   if (!mrf_tc_supported(a.C, a.nk, a.k, a.d0, a.d1)) throw std::runtime_error("conv_mrf: unsupported stage shape");
   static int num_sms = 0;
   if (!num_sms) {
@@ -487,6 +594,8 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
     halo = std::max(halo, (a.k[r] - 1) / 2 * (a.d0[r] + a.d1[r]));
     kmax = std::max(kmax, a.k[r]);
   }
+  // with the fused conv_post the owned rows also need correct neighbours (post_k - 1) / 2 rows away
+  if (post) halo += (a.post_k - 1) / 2;
   p.halo = halo;
   const int row_bytes = a.C * 2, tap_bytes = a.C * a.C * 2;
   if (a.act_pad < MRF_G + 64 || a.act_rows < (int64_t)a.R + a.act_pad + 128 * (MRF_MAX_M + 1))
@@ -500,7 +609,10 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   if (g_env >= G && g_env <= MRF_G && g_env % 8 == 0) G = g_env;
   p.G = G;
   int m = std::min(MRF_MAX_M, 512 / (2 * a.C));
-  auto fits = [&](int mm) { return 2 * (mm * 128 + 2 * G) * row_bytes + kmax * tap_bytes + 4096 <= TC_SMEM_MAX; };
+  auto post_bytes = [&](int mm) { return post ? (7 * 32 + 2 * mm * 4 * 2 * 3 * 7) * 4 + 64 : 0; };
+  auto fits = [&](int mm) {
+    return 2 * (mm * 128 + 2 * G) * row_bytes + kmax * tap_bytes + 4096 + post_bytes(mm) <= TC_SMEM_MAX;
+  };
   while (m > 2 && !fits(m)) --m;
   // small inputs: prefer more, shorter windows so that every SM has one
   while (m > 2 && (a.R + (128 * m - 2 * halo) - 1) / (128 * m - 2 * halo) < num_sms) --m;
@@ -513,7 +625,7 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   p.V = 128 * m - 2 * halo;
   p.n_windows = (a.R + p.V - 1) / p.V;
   const int win_bytes = (m * 128 + 2 * G) * row_bytes;
-  int ring = (TC_SMEM_MAX - 4096 - 2 * win_bytes) / tap_bytes;
+  int ring = (TC_SMEM_MAX - 4096 - post_bytes(m) - 2 * win_bytes) / tap_bytes;
   if (ring > MRF_MAX_RING) ring = MRF_MAX_RING;
   p.resident = a.total_taps <= ring ? 1 : 0;
   if (p.resident) ring = a.total_taps;
@@ -521,12 +633,13 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   p.x_act = static_cast<const uint16_t*>(a.x_act); p.act_rows = a.act_rows; p.act_pad = a.act_pad;
   p.row_utt = a.row_utt; p.valid_div = a.valid_div < 1 ? 1 : a.valid_div;
   p.out_act = a.out_act; p.act_slope = a.act_slope; p.out_f32 = a.out_f32;
+  p.post_w = a.post_w; p.post_k = a.post_k; p.post_slope = a.post_slope; p.post_out = a.post_out;
   p.f16 = a.f16;
   uint32_t cols = 32;
   while ((int)cols < 2 * m * a.C) cols <<= 1;
   p.tmem_cols = cols;
   const CUtensorMap tw = make_map(a.w, (uint64_t)a.C, (uint64_t)a.total_taps * a.C, (uint64_t)a.C, a.C, a.C, a.f16);
-  const size_t smem = (size_t)2 * win_bytes + (size_t)ring * tap_bytes + 1024 + 3072;
+  const size_t smem = (size_t)2 * win_bytes + (size_t)ring * tap_bytes + 1024 + 3072 + (size_t)post_bytes(m);
   if (smem > (size_t)TC_SMEM_MAX) throw std::runtime_error("conv_mrf: shared memory budget exceeded");
   const int grid = std::min(p.n_windows, num_sms);
   ProfScope ps(ex, Prof::MRF, 2.0 * a.R * a.C * a.C * (double)a.total_taps);

@@ -39,10 +39,17 @@ struct MrfArgs {
   void* out_act = nullptr;       // optional 16-bit lrelu(out, act_slope) [R][C]
   float act_slope = 1.f;
   float* out_f32 = nullptr;      // optional fp32 out [R][C]
+  // optional fused conv_post (last stage, C = 32): audio[r] = tanh(sum_t sum_c post_w[t][c] * lrelu(out[r + t - pad][c],
+  // post_slope)) - the final LeakyRelu / Conv(C -> 1, k <= 7, no bias) / Tanh of the generator
+  // (GraphExecutor.swift:2047-2069, 1739-1810, 2017) as the stage kernel's output epilogue; the stage output itself
+  // is then never written.  post_w = fp32 [post_k][C].
+  const float* post_w = nullptr; int post_k = 0; float post_slope = 0.01f;
+  float* post_out = nullptr;     // fp32 [R]
   int f16 = 0;
 };
 
 bool mrf_tc_supported(int C, int nk, const int* k, const int* d0, const int* d1);
+bool mrf_post_supported(int C, int post_k);
 void launch_mrf_tc(Exec& ex, const MrfArgs& a);
 
 }  // namespace piper
