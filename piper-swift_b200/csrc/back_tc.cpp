@@ -153,7 +153,7 @@ void TcVoice::build(Exec& ex, const Voice& v, int f16_) {
       for (const ConvW& c : rb.c2) r.c2.push_back(make_tcw(ex, allocs, c, nullptr, f16));
       t.rbs.push_back(r);
     }
-    {   // fused MRF stage when every resblock is a two-convolution ResBlock2 with 32 or 64 channels
+    {   // fused MRF stage when every resblock is a two-convolution ResBlock2 with 32, 64 or 128 channels
       const int nk = (int)s.rbs.size();
       int kk[MRF_MAX_RB] = {0, 0, 0, 0}, d0[MRF_MAX_RB] = {0, 0, 0, 0}, d1[MRF_MAX_RB] = {0, 0, 0, 0};
       bool ok = nk >= 1 && nk <= MRF_MAX_RB;
@@ -234,7 +234,7 @@ size_t back_tc_bytes(const Context& ctx, int Rf, int batch) {
   size_t bytes = 0;
   bytes += (size_t)Rf * H * (4 * 2 + 2 * 4);       // h, skip fp32; zb, hb, actsb, skipb 16-bit
   bytes += (size_t)Rf * P * (4 * 3 + 2 * 5);       // xu, yb, xs fp32; actA, actB, xub, ybb, tbb 16-bit
-  bytes += 64 * 1280 * 2 + 4096;                   // pad rows of the planar operand layout
+  bytes += 128 * 1280 * 2 + 4096;                  // pad rows of the planar operand layout
   bytes += (size_t)Rf * v.hp.hop * 4;              // packed audio
   bytes += 32 * 256;
   (void)batch;
@@ -337,7 +337,7 @@ float* run_decoder_tc(Context& ctx, Exec& ex, const DecoderIn& in) {
   float* yb = A.alloc<float>((size_t)Rf * P);
   float* xs = A.alloc<float>((size_t)Rf * P);
   uint16_t* act[2] = {A.alloc<uint16_t>((size_t)Rf * P), A.alloc<uint16_t>((size_t)Rf * P)};
-  uint16_t* xub = A.alloc<uint16_t>((size_t)Rf * P + 64 * 1280);   // + pad rows of the planar layout
+  uint16_t* xub = A.alloc<uint16_t>((size_t)Rf * P + 128 * 1280);   // + pad rows of the planar layout
   uint16_t* ybb = A.alloc<uint16_t>((size_t)Rf * P);
   uint16_t* tbb = A.alloc<uint16_t>((size_t)Rf * P);
   float* audio = A.alloc<float>((size_t)Rf * v.hp.hop);
@@ -362,7 +362,8 @@ float* run_decoder_tc(Context& ctx, Exec& ex, const DecoderIn& in) {
     U *= s.stride;
     const int C = s.ch;
     static const int mrf_env = [] { const char* e = getenv("PIPER_B200_MRF"); return e ? atoi(e) : 1; }();
-    const bool use_mrf = ts.mrf && mrf_env;
+    static const int c128_env = [] { const char* e = getenv("PIPER_B200_MRF_C128"); return e ? atoi(e) : 1; }();
+    const bool use_mrf = ts.mrf && mrf_env && (C < 128 || c128_env);
     // fused stages read lrelu(x) as a group-planar tensor [C/8][act_rows][8] with zero pad rows around the signal
     const int act_pad = 128;
     const int64_t act_rows = (int64_t)Rn + act_pad + 1152;

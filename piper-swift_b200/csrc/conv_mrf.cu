@@ -33,6 +33,8 @@ constexpr uint32_t MRF_TRACE_EVENTS = 4096;
 
 struct MrfParams {
   int R, C, nk, m, V, halo, n_windows, G;   // G: guard rows actually used (multiple of 8, <= MRF_G)
+  int GX;                                   // guard rows of the lrelu(x) window (conv1 shifts only; <= G)
+  int tap_outer;                            // weight ring shorter than a convolution: one issuing warp, taps outermost
   int k[MRF_MAX_RB], d0[MRF_MAX_RB], d1[MRF_MAX_RB];
   int tap_base[MRF_MAX_RB][2];
   const float* b1[MRF_MAX_RB];
@@ -59,11 +61,15 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
   constexpr int KS = C / 16;                          // tcgen05 K steps per tap
   constexpr int NP = C / 8;                           // planes
   constexpr int tap_bytes = C * C * 2;
-  const int win_rows = m * 128 + 2 * p.G;             // W + 2*G rows
-  const int plane_bytes = win_rows * 16;
+  constexpr int KB = C > 64 ? 64 : C;                 // channels per swizzled weight sub-tile (128-byte rows at most)
+  constexpr int KH = C / KB;                          // K sub-tiles per tap
+  constexpr int sub_bytes = C * KB * 2;
+  const int plane_x = (m * 128 + 2 * p.GX) * 16;      // lrelu(x) window: W + 2*GX rows
+  const int plane_bytes = (m * 128 + 2 * p.G) * 16;   // conv2 operand window: W + 2*G rows
+  const int win_x = NP * plane_x;
   const int win_bytes = NP * plane_bytes;
   uint8_t* X0 = smem;
-  uint8_t* Y1 = smem + win_bytes;
+  uint8_t* Y1 = smem + win_x;
   uint8_t* WR = Y1 + win_bytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(WR + (size_t)p.ring * tap_bytes);
   uint64_t* x_full = bars;
@@ -164,16 +170,19 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
         TRACE(20u, (uint32_t)it, 0u);
         mbar_wait(x_empty, ((uint32_t)it & 1u) ^ 1u);
         TRACE(21u, (uint32_t)it, 0u);
-        mbar_expect_tx(x_full, (uint32_t)win_bytes);
+        mbar_expect_tx(x_full, (uint32_t)win_x);
         for (int g = 0; g < NP; ++g)
-          bulk_load(X0 + (size_t)g * plane_bytes,
-                    p.x_act + ((size_t)g * p.act_rows + (size_t)(p.act_pad + w0 - p.G)) * 8, (uint32_t)plane_bytes, x_full);
+          bulk_load(X0 + (size_t)g * plane_x,
+                    p.x_act + ((size_t)g * p.act_rows + (size_t)(p.act_pad + w0 - p.GX)) * 8, (uint32_t)plane_x, x_full);
       };
       auto load_w = [&](int r, int j) {
         for (int t = 0; t < p.k[r]; ++t) {
           mbar_wait(&w_empty[slot], wph ^ 1u);
           mbar_expect_tx(&w_full[slot], (uint32_t)tap_bytes);
-          tma_load_2d(&tmap_w, &w_full[slot], WR + (size_t)slot * tap_bytes, 0, (p.tap_base[r][j] + t) * C);
+#pragma unroll
+          for (int kh = 0; kh < KH; ++kh)
+            tma_load_2d(&tmap_w, &w_full[slot], WR + (size_t)slot * tap_bytes + (size_t)kh * sub_bytes, kh * KB,
+                        (p.tap_base[r][j] + t) * C);
           if (++slot == (uint32_t)p.ring) { slot = 0; wph ^= 1u; }
         }
       };
@@ -181,7 +190,9 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
       if (p.resident) {
         for (int t = 0; t < p.ring; ++t) {          // ring == total taps: slot t holds tap t for the whole kernel
           mbar_expect_tx(&w_full[t], (uint32_t)tap_bytes);
-          tma_load_2d(&tmap_w, &w_full[t], WR + (size_t)t * tap_bytes, 0, t * C);
+#pragma unroll
+          for (int kh = 0; kh < KH; ++kh)
+            tma_load_2d(&tmap_w, &w_full[t], WR + (size_t)t * tap_bytes + (size_t)kh * sub_bytes, kh * KB, t * C);
         }
         for (int it = 1; it < n_it; ++it) load_x(it);
       } else {
@@ -202,10 +213,11 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
   } else if (warp == 1 || warp == 2) {
     // ===== MMA issuers: the whole warp runs the (warp-uniform) control flow, one elected lane issues =====
     const uint32_t idesc = make_idesc(C, p.f16);
-    const uint32_t plane16 = (uint32_t)plane_bytes >> 4;                 // descriptor address units are 16 bytes:
-    const uint64_t a_hi = make_smem_desc_ns(0, (uint32_t)plane_bytes, 128);   // one operand row = one unit
-    const uint64_t b_hi = make_smem_desc(0, C);
-    const uint32_t x0_lo = (smem_u32(X0) >> 4) + (uint32_t)p.G, y1_lo = (smem_u32(Y1) >> 4) + (uint32_t)p.G;
+    // descriptor address units are 16 bytes: one operand row = one unit
+    const uint32_t plane16_x = (uint32_t)plane_x >> 4, plane16_y = (uint32_t)plane_bytes >> 4;
+    const uint64_t a_hi_x = make_smem_desc_ns(0, (uint32_t)plane_x, 128), a_hi_y = make_smem_desc_ns(0, (uint32_t)plane_bytes, 128);
+    const uint64_t b_hi = make_smem_desc(0, KB);
+    const uint32_t x0_lo = (smem_u32(X0) >> 4) + (uint32_t)p.GX, y1_lo = (smem_u32(Y1) >> 4) + (uint32_t)p.G;
     const uint32_t wr_lo = smem_u32(WR) >> 4;
     constexpr uint32_t tap16 = tap_bytes >> 4;
     const uint32_t ring = (uint32_t)p.ring;
@@ -217,8 +229,10 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
     uint32_t slot = 0, wph = 0;      // ring position of the next convolution in ring order (streaming mode)
     auto skip = [&](int k) {         // advance over a convolution of the other stream
       slot += (uint32_t)k;
-      if (slot >= ring) { slot -= ring; wph ^= 1u; }
+      while (slot >= ring) { slot -= ring; wph ^= 1u; }
     };
+    // K step ks of a weight tap: 32 bytes further inside the swizzled rows, next sub-tile after KB channels
+    auto b_step = [&](int ks) { return (uint32_t)((ks / (KB / 16)) * (sub_bytes >> 4) + 2 * (ks % (KB / 16))); };
 
     // one convolution over all tiles: per tile k taps x KS tcgen05 K steps, then the commit for the epilogue
     auto conv = [&](uint32_t n, int r, int j, bool first_use) {
@@ -237,6 +251,8 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
         tc_fence_after();
         TRACE(2u + (uint32_t)j * 4u, n, (uint32_t)i);
         const uint32_t acc = tmem_base + (j ? s_col : d_col) + (uint32_t)(i * C);
+        const uint64_t a_hi = j ? a_hi_y : a_hi_x;
+        const uint32_t plane16 = j ? plane16_y : plane16_x;
         uint32_t a_lo = (j ? y1_lo : x0_lo) - (uint32_t)(((k - 1) / 2) * dil) + (uint32_t)(128 * i);
         uint32_t s = slot0, ph = wph0;
         for (int t = 0; t < k; ++t) {
@@ -248,7 +264,7 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
           if (elect_one()) {
 #pragma unroll
             for (int ks = 0; ks < KS; ++ks)   // K step of 16 channels = two planes of A, 32 bytes of B
-              umma_f16(acc, a_hi | (uint64_t)(a_lo + (uint32_t)ks * 2u * plane16), b_hi | (uint64_t)(b_lo + 2u * ks),
+              umma_f16(acc, a_hi | (uint64_t)(a_lo + (uint32_t)ks * 2u * plane16), b_hi | (uint64_t)(b_lo + b_step(ks)),
                        idesc, (j == 1 || t > 0 || ks > 0) ? 1u : 0u);
           }
           a_lo += (uint32_t)dil;
@@ -267,8 +283,62 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
       }
     };
 
+    // Weight ring shorter than a convolution (C = 128: two 32 KB taps): taps outermost, every tap used by all tiles
+    // and handed back at once; warp 1 alone walks the producer's order  c1(0); { c1(n+1), c2(n) }  (a second warp
+    // would have to wait several ring generations ahead, which an mbarrier parity cannot express)
+    auto conv_to = [&](uint32_t n, int r, int j) {
+      const int k = p.k[r];
+      const int dil = j ? p.d1[r] : p.d0[r];
+      for (int i = 0; i < m; ++i) {
+        if (j == 0) mbar_wait(&d_empty[i], (n & 1u) ^ 1u);
+        else mbar_wait(&y_ready[i], n & 1u);
+      }
+      tc_fence_after();
+      const uint64_t a_hi = j ? a_hi_y : a_hi_x;
+      const uint32_t plane16 = j ? plane16_y : plane16_x;
+      const uint32_t a_base = (j ? y1_lo : x0_lo) - (uint32_t)(((k - 1) / 2) * dil);
+      for (int t = 0; t < k; ++t) {
+        mbar_wait(&w_full[slot], wph);
+        tc_fence_after();
+        const uint32_t b_lo = wr_lo + slot * tap16;
+        if (elect_one()) {
+          for (int i = 0; i < m; ++i) {
+            const uint32_t acc = tmem_base + (j ? s_col : d_col) + (uint32_t)(i * C);
+            const uint32_t a_lo = a_base + (uint32_t)(t * dil + 128 * i);
+#pragma unroll
+            for (int ks = 0; ks < KS; ++ks)
+              umma_f16(acc, a_hi | (uint64_t)(a_lo + (uint32_t)ks * 2u * plane16), b_hi | (uint64_t)(b_lo + b_step(ks)),
+                       idesc, (j == 1 || t > 0 || ks > 0) ? 1u : 0u);
+          }
+          umma_commit(&w_empty[slot]);
+        }
+        __syncwarp();
+        if (++slot == ring) { slot = 0; wph ^= 1u; }
+      }
+      if (elect_one())
+        for (int i = 0; i < m; ++i) umma_commit(j ? &s_full[i] : &d_full[i]);
+      __syncwarp();
+    };
+
     int it = 0, r = 0;
-    if (J == 0) {
+    if (p.tap_outer) {
+      if (J == 0 && n_it > 0) {
+        mbar_wait(x_full, 0u);
+        conv_to(0u, 0, 0);
+        if (p.nk == 1 && elect_one()) umma_commit(x_empty);
+        for (uint32_t n = 0; n < n_total; ++n) {
+          int it1 = it, r1 = r + 1;
+          if (r1 == p.nk) { r1 = 0; ++it1; }
+          if (n + 1 < n_total) {
+            if (r1 == 0) mbar_wait(x_full, (uint32_t)it1 & 1u);
+            conv_to(n + 1u, r1, 0);
+            if (r1 == p.nk - 1 && elect_one()) umma_commit(x_empty);
+          }
+          conv_to(n, r, 1);
+          it = it1; r = r1;
+        }
+      }
+    } else if (J == 0) {
       if (n_it > 0) {
         mbar_wait(x_full, 0u);
         conv(0u, 0, 0, true);
@@ -318,6 +388,7 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
           // the residual x0 is recovered from the 16-bit lrelu(x0) operand window (x0 = v >= 0 ? v : 10 v): no
           // fp32 copy of the stage input exists.  Window rows and the validity flag do not depend on the MMAs
           const uint32_t row_off = (uint32_t)((p.G + row_in_win) * 16);
+          const uint32_t row_off_x = (uint32_t)((p.GX + row_in_win) * 16);
           int ru = 0;
           if (inr && p.row_utt) ru = p.row_utt[grow / p.valid_div];
           TRACE(10u, n, (uint32_t)u);
@@ -338,9 +409,9 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
 #pragma unroll 1
           for (int hc = 0; hc < 2; ++hc) {
             const int c0 = cb + hc * 16;
-            const uint8_t* xrow = X0 + (size_t)(c0 >> 3) * plane_bytes + row_off;
+            const uint8_t* xrow = X0 + (size_t)(c0 >> 3) * plane_x + row_off_x;
             const uint4 xa = *reinterpret_cast<const uint4*>(xrow);
-            const uint4 xb = *reinterpret_cast<const uint4*>(xrow + plane_bytes);
+            const uint4 xb = *reinterpret_cast<const uint4*>(xrow + plane_x);
             uint32_t t0[16], t2[16];
             __syncwarp();
             tmem_ld16_async(dcol + (uint32_t)(hc * 16), t0);
@@ -547,7 +618,7 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
 }  // namespace
 
 bool mrf_tc_supported(int C, int nk, const int* k, const int* d0, const int* d1) {
-  if (C != 32 && C != 64) return false;
+  if (C != 32 && C != 64 && C != 128) return false;
   if (nk < 1 || nk > MRF_MAX_RB) return false;
   int taps = 0;
   for (int r = 0; r < nk; ++r) {
@@ -581,7 +652,8 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
         cudaFuncSetAttribute(mrf_tc_kernel<32, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
         cudaFuncSetAttribute(mrf_tc_kernel<64, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
         cudaFuncSetAttribute(mrf_tc_kernel<32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
-        cudaFuncSetAttribute(mrf_tc_kernel<64, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess)
+        cudaFuncSetAttribute(mrf_tc_kernel<64, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
+        cudaFuncSetAttribute(mrf_tc_kernel<128, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess)
       throw std::runtime_error("cuda: cannot raise dynamic shared memory limit for mrf_tc_kernel");
   }
   MrfParams p{};
@@ -608,10 +680,18 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   int G = (shift + 7) & ~7;
   if (g_env >= G && g_env <= MRF_G && g_env % 8 == 0) G = g_env;
   p.G = G;
+  // the lrelu(x) window only sees the conv1 shifts
+  int shift_x = 0;
+  for (int r = 0; r < a.nk; ++r) shift_x = std::max(shift_x, (a.k[r] - 1) / 2 * a.d0[r]);
+  static const int gx_env = [] { const char* e = getenv("PIPER_B200_MRF_GX"); return e ? atoi(e) : 1; }();
+  const int GX = gx_env ? std::min(G, (shift_x + 7) & ~7) : G;
+  p.GX = GX;
+  // C = 128: a tap is 32 KB, the ring holds two of them and the taps-outermost issue order is used
+  const int need_ring = a.C > 64 ? 2 : kmax;
   int m = std::min(MRF_MAX_M, 512 / (2 * a.C));
   auto post_bytes = [&](int mm) { return post ? (7 * 32 + 2 * mm * 4 * 2 * 3 * 7) * 4 + 64 : 0; };
   auto fits = [&](int mm) {
-    return 2 * (mm * 128 + 2 * G) * row_bytes + kmax * tap_bytes + 4096 + post_bytes(mm) <= TC_SMEM_MAX;
+    return (2 * mm * 128 + 2 * G + 2 * GX) * row_bytes + need_ring * tap_bytes + 4096 + post_bytes(mm) <= TC_SMEM_MAX;
   };
   while (m > 2 && !fits(m)) --m;
   // small inputs: prefer more, shorter windows so that every SM has one
@@ -624,12 +704,13 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   p.m = m;
   p.V = 128 * m - 2 * halo;
   p.n_windows = (a.R + p.V - 1) / p.V;
-  const int win_bytes = (m * 128 + 2 * G) * row_bytes;
+  const int win_bytes = (m * 128 + G + GX) * row_bytes;   // mean of the two windows
   int ring = (TC_SMEM_MAX - 4096 - post_bytes(m) - 2 * win_bytes) / tap_bytes;
   if (ring > MRF_MAX_RING) ring = MRF_MAX_RING;
   p.resident = a.total_taps <= ring ? 1 : 0;
   if (p.resident) ring = a.total_taps;
   p.ring = ring;
+  p.tap_outer = (!p.resident && ring < kmax) ? 1 : 0;
   p.x_act = static_cast<const uint16_t*>(a.x_act); p.act_rows = a.act_rows; p.act_pad = a.act_pad;
   p.row_utt = a.row_utt; p.valid_div = a.valid_div < 1 ? 1 : a.valid_div;
   p.out_act = a.out_act; p.act_slope = a.act_slope; p.out_f32 = a.out_f32;
@@ -638,7 +719,7 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   uint32_t cols = 32;
   while ((int)cols < 2 * m * a.C) cols <<= 1;
   p.tmem_cols = cols;
-  const CUtensorMap tw = make_map(a.w, (uint64_t)a.C, (uint64_t)a.total_taps * a.C, (uint64_t)a.C, a.C, a.C, a.f16);
+  const CUtensorMap tw = make_map(a.w, (uint64_t)a.C, (uint64_t)a.total_taps * a.C, (uint64_t)a.C, std::min(a.C, 64), a.C, a.f16);
   const size_t smem = (size_t)2 * win_bytes + (size_t)ring * tap_bytes + 1024 + 3072 + (size_t)post_bytes(m);
   if (smem > (size_t)TC_SMEM_MAX) throw std::runtime_error("conv_mrf: shared memory budget exceeded");
   const int grid = std::min(p.n_windows, num_sms);
@@ -656,7 +737,9 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   static const int eg_env = [] { const char* e = getenv("PIPER_B200_MRF_EG"); return e ? atoi(e) : 0; }();
   const int eg = eg_env >= 2 && eg_env <= 5 ? eg_env : 4;
   const int threads = 96 + 128 * eg;
-  if (a.C == 32) {
+  if (a.C == 128) {
+    mrf_tc_kernel<128, 4><<<grid, 96 + 128 * 4, smem, ex.st>>>(tw, p);
+  } else if (a.C == 32) {
     if (eg == 2) mrf_tc_kernel<32, 2><<<grid, threads, smem, ex.st>>>(tw, p);
     else if (eg == 3) mrf_tc_kernel<32, 3><<<grid, threads, smem, ex.st>>>(tw, p);
     else if (eg == 4) mrf_tc_kernel<32, 4><<<grid, threads, smem, ex.st>>>(tw, p);
