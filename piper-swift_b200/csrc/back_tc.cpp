@@ -88,6 +88,27 @@ void TcVoice::build(Exec& ex, const Voice& v, int f16_) {
       else t.rs.push_back(make_tcw(ex, allocs, c.skip[l], nullptr, f16));
     }
     t.post = make_tcw(ex, allocs, c.post, nullptr, f16);
+    {   // skip-free form (see TcCoupling): fold post into the skip convolutions
+      static const int noskip_env = [] { const char* e = getenv("PIPER_B200_FLOW_NOSKIP"); return e ? atoi(e) : 1; }();
+      const int H = c.post.cin, half = c.post.cout;
+      bool ok = noskip_env && L >= 1 && c.post.taps == 1 && c.post.phases == 1 && (L * H) % 64 == 0;
+      for (int l = 0; ok && l < L; ++l) ok = c.skip[l].taps == 1 && c.skip[l].cin == H && c.skip[l].cout == H;
+      if (ok) {
+        for (int l = 0; l + 1 < L; ++l) t.res.push_back(make_tcw(ex, allocs, c.res[l], nullptr, f16));
+        float* wf = nullptr;
+        CUDA_OK(cudaMalloc(&wf, ((size_t)L * H * half + half) * 4));
+        allocs.push_back(wf);
+        float* bf = wf + (size_t)L * H * half;
+        if (c.post.b) CUDA_OK(cudaMemcpyAsync(bf, c.post.b, (size_t)half * 4, cudaMemcpyDeviceToDevice, ex.st));
+        else CUDA_OK(cudaMemsetAsync(bf, 0, (size_t)half * 4, ex.st));
+        for (int l = 0; l < L; ++l)
+          launch_fold_1x1(ex, c.skip[l].w, c.skip[l].ldw, c.skip[l].b, c.post.w, c.post.ldw, H, H, half, wf, half, l * H, bf);
+        ConvW fw;
+        fw.w = wf; fw.b = bf; fw.cin = L * H; fw.cout = half; fw.k = 1; fw.dil = 1; fw.ldw = half;
+        t.post_fused = make_tcw(ex, allocs, fw, nullptr, f16);
+        t.post_fused_w32 = wf;
+      }
+    }
     flows.push_back(t);
   }
   dec_pre = make_tcw(ex, allocs, v.dec_pre, nullptr, f16);
@@ -233,6 +254,7 @@ size_t back_tc_bytes(const Context& ctx, int Rf, int batch) {
   const size_t P = per_row_max_of(v);
   size_t bytes = 0;
   bytes += (size_t)Rf * H * (4 * 2 + 2 * 4);       // h, skip fp32; zb, hb, actsb, skipb 16-bit
+  bytes += (size_t)Rf * H * 2 * (size_t)std::max(0, v.hp.flow_wn_layers - 1);   // gated activations of every WN layer
   bytes += (size_t)Rf * P * (4 * 3 + 2 * 5);       // xu, yb, xs fp32; actA, actB, xub, ybb, tbb 16-bit
   bytes += 128 * 1280 * 2 + 4096;                  // pad rows of the planar operand layout
   bytes += (size_t)Rf * v.hp.hop * 4;              // packed audio
@@ -253,7 +275,9 @@ FlowOut run_flow_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep)
   float* skip = A.alloc<float>((size_t)Rf * H);
   uint16_t* zb = A.alloc<uint16_t>((size_t)Rf * H);
   uint16_t* hb = A.alloc<uint16_t>((size_t)Rf * H);
-  uint16_t* actsb = A.alloc<uint16_t>((size_t)Rf * H);
+  const bool noskip = !tv.flows.empty() && tv.flows[0].post_fused.w != nullptr;
+  const int LA = noskip ? L : 1;                       // the skip-free form keeps the gated activations of every layer
+  uint16_t* actsb = A.alloc<uint16_t>((size_t)Rf * H * LA);
   uint16_t* skipb = A.alloc<uint16_t>((size_t)Rf * H);
   if (!h || !skip || !zb || !hb || !actsb || !skipb) throw std::runtime_error("capacity: back arena too small (flow)");
 
@@ -277,14 +301,21 @@ FlowOut run_flow_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep)
         a.n_tiles = H / a.nt;
         a.e[0].row0 = 0; a.e[0].bias = t.in_layers[l].bias;
         a.e[1].row0 = H; a.e[1].bias = t.in_layers[l].bias + H;
-        a.e[0].out_act = actsb; a.e[0].ld_act = H;
+        a.e[0].out_act = actsb + (noskip ? l * H : 0); a.e[0].ld_act = H * LA;
         if (cond) {
           a.uttbias = cond; a.ldub = 2 * H * L;
           a.e[0].ub_off = l * 2 * H; a.e[1].ub_off = l * 2 * H + H;
         }
         launch_conv_tc(ex, a);
       }
-      {   // res | skip
+      if (noskip) {   // res only: x = (x + res_acts) * mask; the skip path is folded into the final convolution
+        if (l < L - 1) {
+          TcConvArgs a = tc_args(t.res[l], actsb + l * H, H * LA, Rf, in.frow_utt, 1, f16);
+          a.e[0].out_f32 = h; a.e[0].ld_f32 = H; a.e[0].res = h; a.e[0].ld_res = H;
+          a.e[0].out_act = hb; a.e[0].ld_act = H;
+          launch_conv_tc(ex, a);
+        }
+      } else {   // res | skip
         const bool last = l == L - 1;
         TcConvArgs a = tc_args(t.rs[l], actsb, H, Rf, in.frow_utt, 1, f16);
         a.nt = pick_nt(H); a.n_tiles = H / a.nt;
@@ -304,7 +335,8 @@ FlowOut run_flow_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep)
       }
     }
     {   // post (weights negated): x1 + (-m), masked
-      TcConvArgs a = tc_args(t.post, skipb, H, Rf, in.frow_utt, 1, f16);
+      TcConvArgs a = noskip ? tc_args(t.post_fused, actsb, H * LA, Rf, in.frow_utt, 1, f16)
+                            : tc_args(t.post, skipb, H, Rf, in.frow_utt, 1, f16);
       a.e[0].out_f32 = z + c.out_off; a.e[0].ld_f32 = H;
       a.e[0].res = z + c.out_off; a.e[0].ld_res = H;
       a.e[0].out_act = zb + c.out_off; a.e[0].ld_act = H;

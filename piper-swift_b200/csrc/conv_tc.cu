@@ -842,6 +842,29 @@ void launch_pack_tc_weights_split(Exec& ex, const float* w_f32, int ldw, int pha
   ++ex.launches;
 }
 
+__global__ void fold_1x1_kernel(const float* __restrict__ A, int lda, const float* __restrict__ ba,
+                                const float* __restrict__ B, int ldb, int n, int k, int cout, float* __restrict__ out,
+                                int ldo, int row_off, float* __restrict__ bias_out) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx < n * cout) {
+    const int ci = idx / cout, co = idx - ci * cout;
+    double acc = 0.0;
+    for (int m = 0; m < k; ++m) acc += (double)A[(size_t)ci * lda + m] * (double)B[(size_t)m * ldb + co];
+    out[(size_t)(row_off + ci) * ldo + co] = (float)acc;
+  } else if (bias_out && idx < (n + 1) * cout) {
+    const int co = idx - n * cout;
+    double acc = 0.0;
+    for (int m = 0; m < k; ++m) acc += (double)(ba ? ba[m] : 0.f) * (double)B[(size_t)m * ldb + co];
+    bias_out[co] += (float)acc;
+  }
+}
+
+void launch_fold_1x1(Exec& ex, const float* A, int lda, const float* ba, const float* B, int ldb, int n, int k, int cout,
+                     float* out, int ldo, int row_off, float* bias_out) {
+  const int total = (n + 1) * cout;
+  fold_1x1_kernel<<<(total + 255) / 256, 256, 0, ex.st>>>(A, lda, ba, B, ldb, n, k, cout, out, ldo, row_off, bias_out);
+}
+
 void launch_split3(Exec& ex, const float* src, int ldsrc, int64_t R, int C, void* dst, int cpad) {
   if (C % 4 || ldsrc % 4 || cpad % 4) throw std::runtime_error("split3: channel counts must be multiples of 4");
   const int64_t n = R * (C / 4);

@@ -87,6 +87,11 @@ void launch_pack_tc_weights(Exec& ex, const float* w_f32, int ldw, int phases_ta
 // split-operand helpers (fp32 emulation): weights [phases*taps][cout][6 * cin_pad], activations [R][3 * cpad]
 void launch_pack_tc_weights_split(Exec& ex, const float* w_f32, int ldw, int phases_taps, int cin, int cout,
                                   void* dst, int cout_total, int row_off, int cin_pad);
+// out[(row_off + ci) * ldo + co] = sum_m A[ci * lda + m] * B[m * ldb + co]   (ci < n, m < k, co < cout)  and, when
+// bias_out != null, bias_out[co] (+)= sum_m ba[m] * B[m * ldb + co]: folds a 1x1 convolution (A, ba) into the 1x1
+// convolution (B) that follows it.  One-time weight preparation.
+void launch_fold_1x1(Exec& ex, const float* A, int lda, const float* ba, const float* B, int ldb, int n, int k, int cout,
+                     float* out, int ldo, int row_off, float* bias_out);
 void launch_split3(Exec& ex, const float* src, int ldsrc, int64_t R, int C, void* dst, int cpad);
 // fp32 -> 16-bit copy of an activation tensor [R][C] (optional leaky-relu), used at stage boundaries
 void launch_to_act16(Exec& ex, const float* src, void* dst, int64_t n, float slope, int f16);

@@ -57,6 +57,11 @@ struct TcCoupling {
   TcW pre, post;
   std::vector<TcW> in_layers;
   std::vector<TcW> rs;      // res|skip merged (last layer: skip only)
+  // skip-free form: res[l] alone (l < L-1) and ONE final convolution over the concatenated gated activations of all
+  // layers, post o (sum_l skip_l) folded into its weights: m = sum_l (W_post W_skip_l) acts_l + (W_post sum_l b_skip_l + b_post)
+  std::vector<TcW> res;
+  TcW post_fused;           // cin = L * H (w == nullptr: not built)
+  float* post_fused_w32 = nullptr;   // fp32 [L*H][half] + bias [half] behind it (source of post_fused, kept for the bias)
 };
 struct TcResBlock {
   std::vector<TcW> c1, c2;
