@@ -56,7 +56,7 @@ TcW make_tcw(Exec& ex, std::vector<void*>& allocs, const ConvW& a, const ConvW* 
 }
 
 // bf16x6 fp32-emulation weights (conv_tc.h: TcW::split); cin must be a whole number of K blocks
-TcW make_tcw_split(Exec& ex, std::vector<void*>& allocs, const ConvW& a) {
+TcW make_tcw_split(Exec& ex, std::vector<void*>& allocs, const ConvW& a, int mode) {
   TcW t;
   t.cin = a.cin;
   t.kb = a.cin % 64 == 0 ? 64 : 32;
@@ -64,14 +64,15 @@ TcW make_tcw_split(Exec& ex, std::vector<void*>& allocs, const ConvW& a) {
   t.cout = a.cout;
   t.taps = a.taps; t.phases = a.phases; t.ct_pad = a.ct_pad; t.dil = a.dil; t.pad_l = a.pad_l;
   t.bias = a.b;
-  t.split = 1;
+  t.split = mode == 2 ? 2 : 1;
   if (a.cin % 32 || a.cout % 32 || a.phases != 1)
     throw std::runtime_error("unsupported: convolution " + std::to_string(a.cin) + "->" + std::to_string(a.cout) +
                              " does not fit the split tensor-core tiles");
-  const size_t n = (size_t)t.taps * t.cout * t.cin_pad * 6;
+  const size_t n = (size_t)t.taps * t.cout * t.cin_pad * (t.split == 2 ? 2 : 6);
   CUDA_OK(cudaMalloc(&t.w, n * 2));
   allocs.push_back(t.w);
-  launch_pack_tc_weights_split(ex, a.w, a.ldw, a.taps, a.cin, a.cout, t.w, t.cout, 0, t.cin_pad);
+  if (t.split == 2) launch_pack_tc_weights_split2(ex, a.w, a.ldw, a.taps, a.cin, a.cout, t.w, t.cout, 0, t.cin_pad);
+  else launch_pack_tc_weights_split(ex, a.w, a.ldw, a.taps, a.cin, a.cout, t.w, t.cout, 0, t.cin_pad);
   return t;
 }
 
@@ -122,10 +123,13 @@ void TcVoice::build(Exec& ex, const Voice& v, int f16_) {
     if (ok)
       for (const EncLayerW& l : v.enc) {
         TcEncLayer t;
-        t.qkv = make_tcw_split(ex, allocs, l.qkv);
-        t.o = make_tcw_split(ex, allocs, l.o);
-        t.ffn1 = make_tcw_split(ex, allocs, l.ffn1);
-        t.ffn2 = make_tcw_split(ex, allocs, l.ffn2);
+        // PIPER_B200_FRONT_SPLIT: 2 = f16x3 (two fp16 planes, three products; default), 1 = bf16x6
+        static const int split_env = [] { const char* e = getenv("PIPER_B200_FRONT_SPLIT"); return e ? atoi(e) : 2; }();
+        const int mode = split_env == 1 ? 1 : 2;
+        t.qkv = make_tcw_split(ex, allocs, l.qkv, mode);
+        t.o = make_tcw_split(ex, allocs, l.o, mode);
+        t.ffn1 = make_tcw_split(ex, allocs, l.ffn1, mode);
+        t.ffn2 = make_tcw_split(ex, allocs, l.ffn2, mode);
         enc.push_back(t);
       }
   }

@@ -34,6 +34,7 @@ struct TcKernelParams {
   int phase_cols;                   // merged polyphase ConvTranspose: columns per phase (0 = off)
   uint32_t tap_mask[8];             // per column tile: taps to run (merged polyphase weights are zero elsewhere)
   int split_kbc;                    // bf16x6 fp32 emulation: K blocks per operand plane (0 = off)
+  int split2;                       // f16x3 fp32 emulation (two planes, two accumulators; uses split_kbc too)
   TcEpi e[2];
   const float* uttbias; int ldub;
   const int* row_utt; int valid_div;
@@ -60,6 +61,21 @@ __device__ __forceinline__ void split3x4(const float4& x, uint2& t0, uint2& t1, 
   t0 = make_uint2((uint32_t)a[0] | ((uint32_t)a[1] << 16), (uint32_t)a[2] | ((uint32_t)a[3] << 16));
   t1 = make_uint2((uint32_t)b[0] | ((uint32_t)b[1] << 16), (uint32_t)b[2] | ((uint32_t)b[3] << 16));
   t2 = make_uint2((uint32_t)c[0] | ((uint32_t)c[1] << 16), (uint32_t)c[2] | ((uint32_t)c[3] << 16));
+}
+
+// x = hi + lo' * 2^-11 with fp16 terms (TcW::split == 2)
+__device__ __forceinline__ void split2h(float x, uint16_t& hi, uint16_t& lo) {
+  x = fminf(fmaxf(x, -65504.f), 65504.f);
+  const __half h = __float2half_rn(x);
+  const __half l = __float2half_rn((x - __half2float(h)) * 2048.f);
+  hi = __half_as_ushort(h); lo = __half_as_ushort(l);
+}
+__device__ __forceinline__ void split2x4(const float4& x, uint2& t0, uint2& t1) {
+  uint16_t a[4], b[4];
+  split2h(x.x, a[0], b[0]); split2h(x.y, a[1], b[1]);
+  split2h(x.z, a[2], b[2]); split2h(x.w, a[3], b[3]);
+  t0 = make_uint2((uint32_t)a[0] | ((uint32_t)a[1] << 16), (uint32_t)a[2] | ((uint32_t)a[3] << 16));
+  t1 = make_uint2((uint32_t)b[0] | ((uint32_t)b[1] << 16), (uint32_t)b[2] | ((uint32_t)b[3] << 16));
 }
 
 // Epilogue of one 128-row x (n_groups * nt) accumulator tile, run by the four warps of a warpgroup (TMEM lane
@@ -183,7 +199,7 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
       }
       return;
     }
-    const int cpg = p.nt / 32, nunits = p.n_groups * cpg;
+    const int cpg = p.nt / 32, nunits = (p.split2 ? 1 : p.n_groups) * cpg;
     for (int f = part * nunits / nparts; f < (part + 1) * nunits / nparts; ++f) {
       const int g = f / cpg, c = f - g * cpg;
       const TcEpi& e = p.e[g];
@@ -193,6 +209,13 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
         __syncwarp();
         tmem_ld16(lane_base + (uint32_t)(g * p.nt + c * 32), v);
         tmem_ld16(lane_base + (uint32_t)(g * p.nt + c * 32 + 16), v + 16);
+        if (p.split2) {   // f16x3: the cross terms sit in the second accumulator, scaled by 2^11
+          float w[32];
+          tmem_ld16(lane_base + (uint32_t)(p.nt + c * 32), w);
+          tmem_ld16(lane_base + (uint32_t)(p.nt + c * 32 + 16), w + 16);
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = fmaf(w[i], 1.0f / 2048.f, v[i]);
+        }
         int j = ntile * p.nt + c * 32, ph_c = p.phases > 1 ? phase : 0;
         if (p.phase_cols) {   // merged polyphase weights: the chunk's columns are channels j % phase_cols of phase j / phase_cols
           ph_c = j / p.phase_cols;
@@ -267,10 +290,16 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
           if (e.out_split) {
             uint16_t* sp = static_cast<uint16_t*>(e.out_split) + (orow0 + it * rstep) * e.ld_split + ocol + c4;
             uint2 t0, t1, t2;
-            split3x4(x, t0, t1, t2);
-            *reinterpret_cast<uint2*>(sp) = t0;
-            *reinterpret_cast<uint2*>(sp + e.split_c) = t1;
-            *reinterpret_cast<uint2*>(sp + 2 * e.split_c) = t2;
+            if (p.split2) {
+              split2x4(x, t0, t1);
+              *reinterpret_cast<uint2*>(sp) = t0;
+              *reinterpret_cast<uint2*>(sp + e.split_c) = t1;
+            } else {
+              split3x4(x, t0, t1, t2);
+              *reinterpret_cast<uint2*>(sp) = t0;
+              *reinterpret_cast<uint2*>(sp + e.split_c) = t1;
+              *reinterpret_cast<uint2*>(sp + 2 * e.split_c) = t2;
+            }
           }
           if (e.out_act && !planar) {
             const uint32_t lo = pack2(lrelu(x.x, e.act_slope), lrelu(x.y, e.act_slope), p.f16);
@@ -565,9 +594,11 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
         // accumulated before the first large one (the tensor core aligns addends to the largest exponent and
         // drops what falls below its accumulator width)
         const int kb_inner = p.split_kbc ? p.split_kbc : p.kblocks;
-        const int n_outer = p.split_kbc ? 6 : 1;
+        const int n_outer = p.split2 ? 2 : (p.split_kbc ? 6 : 1);
         for (int pl = 0; pl < n_outer; ++pl) {
-          const int a_plane = p.split_kbc ? (int)((0x010210u >> (4 * pl)) & 0xFu) : 0;   // {0,1,2,0,1,0}
+          // bf16x6: A planes {0,1,2,0,1,0} against weight planes 0..5; f16x3: A_hi against (B_hi -> D0, B_lo' -> D1),
+          // then A_lo' against B_hi -> D1 only
+          const int a_plane = p.split2 ? pl : (p.split_kbc ? (int)((0x010210u >> (4 * pl)) & 0xFu) : 0);
           for (int tap = 0; tap < p.taps; ++tap) {
             if (!((p.tap_mask[ntile & 7] >> tap) & 1u)) continue;
             const int arow = m0 + in_off + tap * p.tap_step;
@@ -575,10 +606,13 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
             for (int kbi = 0; kbi < kb_inner; ++kbi) {
               mbar_wait(&empty[s], ph ^ 1u);
               uint8_t* st = smem + (size_t)s * stage_bytes;
-              mbar_expect_tx(&full[s], (uint32_t)stage_bytes);
+              const int g0 = (p.split2 && pl == 1) ? 1 : 0;
+              mbar_expect_tx(&full[s], (uint32_t)(a_bytes + (p.n_groups - g0) * b_bytes));
               tma_load_2d(&tmap_a, &full[s], st, (a_plane * kb_inner + kbi) * p.kb, arow);
-              for (int g = 0; g < p.n_groups; ++g)
-                tma_load_2d(&tmap_b, &full[s], st + a_bytes + g * b_bytes, (pl * kb_inner + kbi) * p.kb, wrow + p.e[g].row0);
+              for (int g = g0; g < p.n_groups; ++g) {
+                const int b_plane = p.split2 ? (pl == 0 ? g : 0) : pl;
+                tma_load_2d(&tmap_b, &full[s], st + a_bytes + g * b_bytes, (b_plane * kb_inner + kbi) * p.kb, wrow + p.e[g].row0);
+              }
               if (++s == stages) { s = 0; ph ^= 1u; }
             }
           }
@@ -604,8 +638,9 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
         mbar_wait(&full[s], ph);
         tc_fence_after();
         const uint32_t al = stage_lo + (uint32_t)s * stage16, bl = al + a16;
+        const int g0 = (p.split2 && 2 * i >= n_it) ? 1 : 0;   // f16x3: the A_lo' half of the K loop feeds D1 only
         if (elect_one()) {
-          for (int g = 0; g < p.n_groups; ++g)
+          for (int g = g0; g < p.n_groups; ++g)
             for (int k = 0; k < ksteps; ++k)
               umma_f16(acc + (uint32_t)(g * p.nt), d_hi | (uint64_t)(al + 2u * (uint32_t)k),
                        d_hi | (uint64_t)(bl + (uint32_t)g * b16 + 2u * (uint32_t)k), idesc, (i == 0 && k == 0) ? 0u : 1u);
@@ -654,8 +689,16 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
   TcKernelParams p{};
   p.Q = a.Q; p.taps = w.taps; p.tap_step = a.tap_step; p.in_off = a.in_off;
   p.kb = w.kb; p.kblocks = w.cin_pad / w.kb;
-  const int kmul = w.split ? 6 : 1, amul = w.split ? 3 : 1;
-  if (w.split) {
+  const int kmul = w.split == 2 ? 2 : (w.split ? 6 : 1), amul = w.split == 2 ? 2 : (w.split ? 3 : 1);
+  int n_groups = a.n_groups;
+  if (w.split == 2) {
+    if (!a.f16 || a.gate || w.phase_cols || a.n_groups != 1 || a.nt > 128 || (a.nt & 31) || w.cin != w.cin_pad || w.phases != 1)
+      throw std::runtime_error("conv_tc: f16x3 split weights need fp16 operands, one column group of at most 128 columns and whole K blocks");
+    p.split_kbc = p.kblocks;
+    p.kblocks *= 2;
+    p.split2 = 1;
+    n_groups = 2;   // second accumulator for the cross terms, same weight rows
+  } else if (w.split) {
     if (a.f16 || a.gate || w.phase_cols || a.n_groups * a.nt > 256 || w.cin != w.cin_pad)
       throw std::runtime_error("conv_tc: split (fp32-emulation) weights need bf16 operands, whole K blocks and the persistent kernel");
     p.split_kbc = p.kblocks;
@@ -664,10 +707,10 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
   for (int g = 0; g < a.n_groups; ++g)
     if ((a.e[g].relu || a.e[g].out_split) && (a.nt & 31))
       throw std::runtime_error("conv_tc: relu / split outputs need 32-column tiles");
-  p.nt = a.nt; p.n_groups = a.n_groups; p.cout_rows = w.cout;
+  p.nt = a.nt; p.n_groups = n_groups; p.cout_rows = w.cout;
   p.phases = w.phases; p.ct_pad = w.ct_pad; p.out_mul = a.out_mul;
   p.gate = a.gate; p.f16 = a.f16;
-  p.e[0] = a.e[0]; p.e[1] = a.e[1];
+  p.e[0] = a.e[0]; p.e[1] = w.split == 2 ? a.e[0] : a.e[1];
   p.uttbias = a.uttbias; p.ldub = a.ldub;
   p.row_utt = a.row_utt; p.valid_div = a.valid_div < 1 ? 1 : a.valid_div;
   uint32_t cols = 32;
@@ -692,7 +735,7 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
   static const int persist_env = [] { const char* e = getenv("PIPER_B200_TC_PERSIST"); return e ? atoi(e) : 1; }();
   if (w.phase_cols && !(persist_env && a.n_groups * a.nt <= 256))
     throw std::runtime_error("conv_tc: merged polyphase weights need the persistent kernel");
-  if ((persist_env || w.split) && a.n_groups * a.nt <= 256) {
+  if ((persist_env || w.split) && n_groups * a.nt <= 256) {
     static int num_sms = 0;
     if (!num_sms) {
       int dev = 0;
@@ -706,9 +749,9 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
                                      (uint64_t)w.cin_pad * kmul, w.kb, a.nt, a.f16);
     p.window = 0;
     uint32_t pc = 32;
-    while ((int)pc < 2 * a.n_groups * a.nt) pc <<= 1;
+    while ((int)pc < 2 * n_groups * a.nt) pc <<= 1;
     p.tmem_cols = pc;
-    const int sb = TC_BM * w.kb * 2 + a.n_groups * a.nt * w.kb * 2;
+    const int sb = TC_BM * w.kb * 2 + n_groups * a.nt * w.kb * 2;
     constexpr int TBUF_BYTES = 2 * TCP_EG * 4 * 32 * 36 * 4;
     int st = (TC_SMEM_MAX - 2048 - TBUF_BYTES) / sb;
     if (st > TCP_MAX_STAGES) st = TCP_MAX_STAGES;
@@ -813,6 +856,34 @@ __global__ void split3_kernel(const float* __restrict__ src, int ldsrc, int64_t 
   *reinterpret_cast<uint2*>(o + 2 * cpad) = t2;
 }
 
+__global__ void pack_tc_weights_split2_kernel(const float* __restrict__ w, int ldw, int cin, int cout,
+                                              uint16_t* __restrict__ dst, int cout_total, int row_off, int cin_pad, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int ci = (int)(i % cin_pad);
+  const int co = (int)((i / cin_pad) % cout);
+  const int pt = (int)(i / ((int64_t)cin_pad * cout));
+  float v = 0.f;
+  if (ci < cin) v = w[((size_t)pt * cin + ci) * ldw + co];
+  uint16_t hi, lo;
+  split2h(v, hi, lo);
+  uint16_t* row = dst + ((size_t)pt * cout_total + row_off + co) * (size_t)(2 * cin_pad) + ci;
+  row[0] = hi; row[cin_pad] = lo;
+}
+
+__global__ void split2_kernel(const float* __restrict__ src, int ldsrc, int64_t R, int C4, uint16_t* __restrict__ dst, int cpad) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= R * C4) return;
+  const int64_t r = i / C4;
+  const int c = (int)(i - r * C4) * 4;
+  const float4 x = *reinterpret_cast<const float4*>(src + r * ldsrc + c);
+  uint2 t0, t1;
+  split2x4(x, t0, t1);
+  uint16_t* o = dst + r * (int64_t)(2 * cpad) + c;
+  *reinterpret_cast<uint2*>(o) = t0;
+  *reinterpret_cast<uint2*>(o + cpad) = t1;
+}
+
 __global__ void to_act16_kernel(const float* __restrict__ src, uint32_t* __restrict__ dst, int64_t n2, float slope,
                                 int f16) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -839,6 +910,23 @@ void launch_pack_tc_weights_split(Exec& ex, const float* w_f32, int ldw, int pha
   pack_tc_weights_split_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ex.st>>>(w_f32, ldw, cin, cout,
                                                                               static_cast<uint16_t*>(dst), cout_total,
                                                                               row_off, cin_pad, n);
+  ++ex.launches;
+}
+
+void launch_pack_tc_weights_split2(Exec& ex, const float* w_f32, int ldw, int phases_taps, int cin, int cout, void* dst,
+                                   int cout_total, int row_off, int cin_pad) {
+  const int64_t n = (int64_t)phases_taps * cout * cin_pad;
+  if (n <= 0) return;
+  pack_tc_weights_split2_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ex.st>>>(w_f32, ldw, cin, cout,
+                                                                               static_cast<uint16_t*>(dst), cout_total,
+                                                                               row_off, cin_pad, n);
+  ++ex.launches;
+}
+
+void launch_split2(Exec& ex, const float* src, int ldsrc, int64_t R, int C, void* dst, int cpad) {
+  const int64_t n = R * (C / 4);
+  if (n <= 0) return;
+  split2_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ex.st>>>(src, ldsrc, R, C / 4, static_cast<uint16_t*>(dst), cpad);
   ++ex.launches;
 }
 

@@ -34,6 +34,11 @@ struct TcW {
   // the six products with i + j <= 2 are accumulated in fp32, smallest first.  The weight rows then hold six
   // planes of cin_pad channels [B2 B1 B0 B1 B0 B0]; the activation operand is [rows][3 * cin_pad] = [A0 A1 A2] and
   // the kernel's producer reads planes [A0 A1 A2 A0 A1 A0] against them.
+  // split = 2 ("f16x3"): two fp16 planes x = hi + lo' * 2^-11 (hi = fp16(x), lo' = fp16((x - hi) * 2^11): 22-23 mantissa
+  // bits, the scaling keeps lo' out of the fp16 subnormals) and THREE products in two accumulators,
+  // D0 = A_hi B_hi and D1 = A_hi B_lo' + A_lo' B_hi, combined as D0 + 2^-11 D1 in the epilogue (the dropped lo lo term
+  // is below 2^-24 like the dropped bf16 terms).  Weight rows hold [B_hi | B_lo'], activations [A_hi | A_lo'];
+  // half the tensor work of bf16x6.  Inputs must stay inside the fp16 range (they are clamped to +-65504).
   int split = 0;
 };
 
@@ -93,6 +98,10 @@ void launch_pack_tc_weights_split(Exec& ex, const float* w_f32, int ldw, int pha
 void launch_fold_1x1(Exec& ex, const float* A, int lda, const float* ba, const float* B, int ldb, int n, int k, int cout,
                      float* out, int ldo, int row_off, float* bias_out);
 void launch_split3(Exec& ex, const float* src, int ldsrc, int64_t R, int C, void* dst, int cpad);
+// f16x3 helpers (TcW::split == 2): weights [phases*taps][cout][2 * cin_pad], activations [R][2 * cpad]
+void launch_pack_tc_weights_split2(Exec& ex, const float* w_f32, int ldw, int phases_taps, int cin, int cout,
+                                   void* dst, int cout_total, int row_off, int cin_pad);
+void launch_split2(Exec& ex, const float* src, int ldsrc, int64_t R, int C, void* dst, int cpad);
 // fp32 -> 16-bit copy of an activation tensor [R][C] (optional leaky-relu), used at stage boundaries
 void launch_to_act16(Exec& ex, const float* src, void* dst, int64_t n, float slope, int f16);
 

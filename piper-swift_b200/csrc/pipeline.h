@@ -92,7 +92,7 @@ struct TcVoice {
   void release();
 };
 TcW make_tcw(Exec& ex, std::vector<void*>& allocs, const ConvW& a, const ConvW* b, int f16);
-TcW make_tcw_split(Exec& ex, std::vector<void*>& allocs, const ConvW& a);   // bf16x6 fp32 emulation (conv_tc.h)
+TcW make_tcw_split(Exec& ex, std::vector<void*>& allocs, const ConvW& a, int mode);   // fp32 emulation: 1 = bf16x6, 2 = f16x3 (conv_tc.h)
 
 struct Context {
   int device = 0;

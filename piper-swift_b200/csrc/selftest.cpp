@@ -75,7 +75,8 @@ static void selftest_split(Context& c, int mode, int cin, int cout, int k, int d
   cw.cin = cin; cw.cout = cout; cw.k = k; cw.dil = dil; cw.ldw = ldw;
   cw.taps = k; cw.phases = 1; cw.ct_pad = 0; cw.pad_l = dil * (k - 1) / 2;
   std::vector<void*> allocs;
-  TcW tw = make_tcw_split(ex, allocs, cw);
+  const int smode = [] { const char* e = getenv("PIPER_B200_SELFTEST_SPLIT"); return e && atoi(e) == 1 ? 1 : 2; }();
+  TcW tw = make_tcw_split(ex, allocs, cw, smode);
   cudaEvent_t e0, e1, e2;
   CUDA_OK(cudaEventCreate(&e0)); CUDA_OK(cudaEventCreate(&e1)); CUDA_OK(cudaEventCreate(&e2));
   ConvArgs r;
@@ -86,13 +87,13 @@ static void selftest_split(Context& c, int mode, int cin, int cout, int k, int d
   r.R_in = rows; r.Q = rows; r.cin = cin; r.cout = cout; r.taps = k;
   r.tap_step = dil; r.in_off = -cw.pad_l;
   TcConvArgs a;
-  a.in = dxs.p; a.ldin = 3 * cin; a.R_in = rows; a.cin = cin;
+  a.in = dxs.p; a.ldin = (smode == 2 ? 2 : 3) * cin; a.R_in = rows; a.cin = cin;
   a.w = &tw; a.Q = rows;
   a.row_utt = dutt.as<int>(); a.valid_div = 1;
-  a.f16 = 0; a.tap_step = dil; a.in_off = -cw.pad_l;
+  a.f16 = smode == 2 ? 1 : 0; a.tap_step = dil; a.in_off = -cw.pad_l;
   a.n_groups = 1;
   a.nt = 32;
-  for (int nt : {256, 192, 128, 96, 64, 32}) if (cout % nt == 0) { a.nt = nt; break; }
+  for (int nt : {256, 192, 128, 96, 64, 32}) if ((smode != 2 || nt <= 128) && cout % nt == 0) { a.nt = nt; break; }
   if (const char* e = getenv("PIPER_B200_SELFTEST_NT")) { const int nt = atoi(e); if (nt >= 32 && cout % nt == 0) a.nt = nt; }
   a.n_tiles = cout / a.nt;
   a.e[0].bias = cw.b; a.e[0].out_f32 = dtc.as<float>(); a.e[0].ld_f32 = cout;
@@ -100,7 +101,8 @@ static void selftest_split(Context& c, int mode, int cin, int cout, int k, int d
     CUDA_OK(cudaEventRecord(e0, c.stream));
     launch_conv_f32(ex, r);
     CUDA_OK(cudaEventRecord(e1, c.stream));
-    launch_split3(ex, dx.as<float>(), cin, rows, cin, dxs.p, cin);
+    if (smode == 2) launch_split2(ex, dx.as<float>(), cin, rows, cin, dxs.p, cin);
+    else launch_split3(ex, dx.as<float>(), cin, rows, cin, dxs.p, cin);
     launch_conv_tc(ex, a);
     CUDA_OK(cudaEventRecord(e2, c.stream));
   }

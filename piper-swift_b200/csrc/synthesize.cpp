@@ -31,24 +31,31 @@ ConvArgs conv_args(const ConvW& w, const float* in, int ldin, float* out, int ld
   return a;
 }
 
-// a split (fp32-emulating) tensor-core convolution over the packed phoneme rows; `in` = [R][3 * cin] bf16
+// a split (fp32-emulating) tensor-core convolution over the packed phoneme rows; `in` = [R][3 * cin] bf16 (bf16x6)
+// or [R][2 * cin] fp16 (f16x3, which needs a second accumulator: at most 128 columns per tile)
 TcConvArgs split_args(const TcW& w, const void* in, int R, const int* row_utt) {
   TcConvArgs a;
-  a.in = in; a.ldin = 3 * w.cin; a.R_in = R; a.cin = w.cin;
+  const int planes = w.split == 2 ? 2 : 3;
+  a.in = in; a.ldin = planes * w.cin; a.R_in = R; a.cin = w.cin;
   a.w = &w; a.Q = R;
   a.row_utt = row_utt; a.valid_div = 1;
-  a.f16 = 0;
+  a.f16 = w.split == 2 ? 1 : 0;
   a.tap_step = w.dil; a.in_off = -w.pad_l;
   a.n_groups = 1;
   a.nt = 32;
   for (int nt : {256, 192, 128, 96, 64, 32})
-    if (w.cout % nt == 0) { a.nt = nt; break; }
+    if ((w.split != 2 || nt <= 128) && w.cout % nt == 0) { a.nt = nt; break; }
   a.n_tiles = w.cout / a.nt;
   a.e[0].bias = w.bias;
   return a;
 }
 
 // DDSConv: per layer depthwise conv + LN + GELU, 1x1 conv, LN + GELU, residual
+void launch_split_act(Exec& ex, int mode, const float* src, int ldsrc, int64_t R, int C, void* dst, int cpad) {
+  if (mode == 2) launch_split2(ex, src, ldsrc, R, C, dst, cpad);
+  else launch_split3(ex, src, ldsrc, R, C, dst, cpad);
+}
+
 void run_dds(Exec& ex, const std::vector<DDSLayerW>& layers, float* h, float* t1, float* t2, const int* row_utt,
              int R, int C) {
   for (const DDSLayerW& l : layers) {
@@ -248,14 +255,15 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
       // conv_tc.h) - same graph, same fp32 tensors between the kernels
       const EncLayerW& l = voice.enc[li];
       const TcEncLayer& t = tc.enc[li];
-      launch_split3(ex, x, H, Rp, H, xs, H);
+      const int sm = t.qkv.split, planes = sm == 2 ? 2 : 3;
+      launch_split_act(ex, sm, x, H, Rp, H, xs, H);
       {
         TcConvArgs a = split_args(t.qkv, xs, Rp, p_utt);
         a.e[0].out_f32 = qkv; a.e[0].ld_f32 = 3 * H;
         launch_conv_tc(ex, a);
       }
       launch_attention(ex, qkv, l.rel_k, l.rel_v, att, d_utt_start, d_utt_len, B, max_len, H, hp.n_heads, hp.window);
-      launch_split3(ex, att, H, Rp, H, atts, H);
+      launch_split_act(ex, sm, att, H, Rp, H, atts, H);
       {
         TcConvArgs a = split_args(t.o, atts, Rp, p_utt);
         a.e[0].out_f32 = y; a.e[0].ld_f32 = H;
@@ -264,11 +272,11 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
       LNArgs n1;
       n1.x = x; n1.y = y; n1.gamma = l.n1.gamma; n1.beta = l.n1.beta; n1.out = x; n1.row_utt = p_utt; n1.R = Rp; n1.C = H;
       launch_layernorm(ex, n1);
-      launch_split3(ex, x, H, Rp, H, xs, H);
+      launch_split_act(ex, sm, x, H, Rp, H, xs, H);
       {
         TcConvArgs a = split_args(t.ffn1, xs, Rp, p_utt);
         a.e[0].relu = 1;
-        a.e[0].out_split = mids; a.e[0].ld_split = 3 * hp.filter; a.e[0].split_c = hp.filter;
+        a.e[0].out_split = mids; a.e[0].ld_split = planes * hp.filter; a.e[0].split_c = hp.filter;
         launch_conv_tc(ex, a);
       }
       {
