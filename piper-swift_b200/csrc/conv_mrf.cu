@@ -1,10 +1,12 @@
-// Fused MRF stage (see conv_mrf.h).  Persistent kernel, one CTA per SM, 96 + 128*MRF_EG threads:
+// Fused MRF stage (see conv_mrf.h).  Persistent kernel, one CTA per SM, 160 + 128*MRF_EG threads:
 //   warp 0      : TMA producer - the 16-bit lrelu(x) window ((m+1)*128 rows, halo included, group-planar
 //                 without swizzle) and the weight taps (ring of C x C tiles; resident when they all fit)
-//   warps 1, 2 : tcgen05.mma issuers (warp 1 also owns the TMEM allocation).  Warp 1 issues conv1 of every
-//                 resblock (tile i into D_i, fresh), warp 2 issues conv2 (accumulating into S_i on top of
-//                 sum_r y1_r); tap shifts are 16-byte-granular descriptor offsets into the planar windows
-//   warps 3..   : MRF_EG epilogue warpgroups over (tile, 32-column half) units.  After conv1:
+//   warps 1..4 : tcgen05.mma issuers (warp 1 also owns the TMEM allocation).  Warps 1, 2 issue conv1 of every
+//                 resblock (tile i into D_i, fresh; even / odd tiles), warps 3, 4 issue conv2 (accumulating into
+//                 S_i on top of sum_r y1_r; even / odd tiles): one warp needs ~55+ cycles per small-N MMA plus a
+//                 fixed cost per tile, so a single stream left the tensor pipe waiting for the issuer (timeline,
+//                 tools/mrf_trace.py); tap shifts are 16-byte-granular descriptor offsets into the planar windows
+//   warps 5..   : MRF_EG epilogue warpgroups over (tile, 32-column half) units.  After conv1:
 //                 y1 = D + x + b1 (fp32), S += y1 (TMEM read-modify-write), lrelu(y1)*mask -> 16-bit ->
 //                 planar smem operand of conv2.  After the last resblock: out = (S + sum b2) / nk -> global.
 // A window of W = 128*m rows yields V = W - 2*HALO valid rows (HALO = max_r pad0_r + pad1_r):
@@ -45,12 +47,13 @@ struct MrfParams {
   float* out_f32;
   const float* post_w; int post_k; float post_slope; float* post_out;   // fused conv_post + tanh (C = 32 only)
   int f16, ring, resident;
+  int mma_split;              // 1: two issuing warps per convolution stream (even / odd tiles)
   uint32_t tmem_cols;
   uint32_t* trace;            // debug timeline of CTA 0 (PIPER_B200_MRF_TRACE), else null
 };
 
 template <int C, int MRF_EG>   // channels, epilogue warpgroups
-__global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __grid_constant__ CUtensorMap tmap_w,
+__global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __grid_constant__ CUtensorMap tmap_w,
                                                                 const MrfParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -129,10 +132,11 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_w);
     mbar_init(x_full, 1);
-    mbar_init(x_empty, 1 + 4 * MRF_EG);   // the last conv1's commit + every epilogue warp (they read the residual from X0)
+    // the last conv1's commit (of every conv1 issuer) + every epilogue warp (they read the residual from X0)
+    mbar_init(x_empty, (p.mma_split ? 2 : 1) + 4 * MRF_EG);
     for (int s = 0; s < p.ring; ++s) {
       mbar_init(&w_full[s], 1);
-      mbar_init(&w_empty[s], 1);
+      mbar_init(&w_empty[s], p.mma_split ? 2 : 1);
     }
     for (int i = 0; i < m; ++i) {
       mbar_init(&d_full[i], 1);
@@ -210,7 +214,7 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
         }
       }
     }
-  } else if (warp == 1 || warp == 2) {
+  } else if (warp <= 4) {
     // ===== MMA issuers: the whole warp runs the (warp-uniform) control flow, one elected lane issues =====
     const uint32_t idesc = make_idesc(C, p.f16);
     // descriptor address units are 16 bytes: one operand row = one unit
@@ -225,7 +229,10 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
     // barriers, and one warp alone cannot issue the small N = C MMAs fast enough (tools/micro/umma_bench.cu).
     // In streaming mode both walk the producer's ring order  c1(0); { c1(n+1), c2(n) }  and skip the
     // other stream's slots.
-    const int J = warp - 1;
+    const int J = (warp - 1) >> 1;          // stream: 0 = conv1, 1 = conv2
+    const int half = (warp - 1) & 1;        // tile parity this warp issues (mma_split), or all tiles (warp of half 0)
+    const int istep = p.mma_split ? 2 : 1;
+    const bool idle = (p.tap_outer && warp != 1) || (!p.mma_split && half == 1);
     uint32_t slot = 0, wph = 0;      // ring position of the next convolution in ring order (streaming mode)
     auto skip = [&](int k) {         // advance over a convolution of the other stream
       slot += (uint32_t)k;
@@ -240,12 +247,17 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
       const int dil = j ? p.d1[r] : p.d0[r];
       const uint32_t slot0 = p.resident ? (uint32_t)p.tap_base[r][j] : slot;
       const uint32_t wph0 = p.resident ? 0u : wph;
-      for (int i = 0; i < m; ++i) {
+      for (int i = half * (istep - 1); i < m; i += istep) {
         TRACE(1u + (uint32_t)j * 4u, n, (uint32_t)i);
         if (j == 0) {
           mbar_wait(&d_empty[i], (n & 1u) ^ 1u);           // epilogue of the previous pair drained D_i
-        } else {
-          if (i == 0) mbar_wait(&y_ready[0], n & 1u);      // conv2 operand rows of tiles i-1, i, i+1
+        } else {                                           // conv2 operand rows of tiles i-1, i, i+1
+          if (istep == 2) {
+            if (i > 0) mbar_wait(&y_ready[i - 1], n & 1u);
+            mbar_wait(&y_ready[i], n & 1u);
+          } else if (i == 0) {
+            mbar_wait(&y_ready[0], n & 1u);
+          }
           if (i + 1 < m) mbar_wait(&y_ready[i + 1], n & 1u);
         }
         tc_fence_after();
@@ -256,7 +268,7 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
         uint32_t a_lo = (j ? y1_lo : x0_lo) - (uint32_t)(((k - 1) / 2) * dil) + (uint32_t)(128 * i);
         uint32_t s = slot0, ph = wph0;
         for (int t = 0; t < k; ++t) {
-          if (first_use && i == 0) {
+          if (first_use && i < istep) {
             mbar_wait(&w_full[s], ph);
             tc_fence_after();
           }
@@ -321,8 +333,10 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
     };
 
     int it = 0, r = 0;
-    if (p.tap_outer) {
-      if (J == 0 && n_it > 0) {
+    if (idle) {
+      // nothing to issue: a conv stream with a single issuer, or the taps-outermost mode
+    } else if (p.tap_outer) {
+      if (n_it > 0) {
         mbar_wait(x_full, 0u);
         conv_to(0u, 0, 0);
         if (p.nk == 1 && elect_one()) umma_commit(x_empty);
@@ -369,7 +383,7 @@ __global__ void __launch_bounds__(96 + 128 * MRF_EG, 1) mrf_tc_kernel(const __gr
     // units g, g + MRF_EG, ...  Every thread owns one row and 32 columns: one 128-byte line of the fp32
     // residual, two TMEM loads of D, and two planes of the conv2 operand. =====
     constexpr int HALVES = C / 32;
-    const int group = (warp - 3) >> 2;
+    const int group = (warp - 5) >> 2;
     const int quarter = warp & 3;                        // TMEM lane quarter this warp may access
     const uint32_t lane_sel = (uint32_t)(quarter * 32) << 16;
     const float inv_nk = 1.0f / (float)p.nk;
@@ -711,6 +725,8 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   if (p.resident) ring = a.total_taps;
   p.ring = ring;
   p.tap_outer = (!p.resident && ring < kmax) ? 1 : 0;
+  static const int split_env = [] { const char* e = getenv("PIPER_B200_MRF_SPLIT"); return e ? atoi(e) : 1; }();
+  p.mma_split = (split_env && !p.tap_outer) ? 1 : 0;
   p.x_act = static_cast<const uint16_t*>(a.x_act); p.act_rows = a.act_rows; p.act_pad = a.act_pad;
   p.row_utt = a.row_utt; p.valid_div = a.valid_div < 1 ? 1 : a.valid_div;
   p.out_act = a.out_act; p.act_slope = a.act_slope; p.out_f32 = a.out_f32;
@@ -729,16 +745,16 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
 #else
   static const char* trace_path = nullptr;
 #endif
-  const size_t trace_words = (size_t)(96 + 128 * 5) / 32 * MRF_TRACE_EVENTS * 2;
+  const size_t trace_words = (size_t)(160 + 128 * 5) / 32 * MRF_TRACE_EVENTS * 2;
   if (trace_path) {
     if (cudaMalloc(&p.trace, trace_words * 4) != cudaSuccess) throw std::runtime_error("conv_mrf: trace buffer");
     cudaMemsetAsync(p.trace, 0, trace_words * 4, ex.st);
   }
   static const int eg_env = [] { const char* e = getenv("PIPER_B200_MRF_EG"); return e ? atoi(e) : 0; }();
   const int eg = eg_env >= 2 && eg_env <= 5 ? eg_env : 4;
-  const int threads = 96 + 128 * eg;
+  const int threads = 160 + 128 * eg;
   if (a.C == 128) {
-    mrf_tc_kernel<128, 4><<<grid, 96 + 128 * 4, smem, ex.st>>>(tw, p);
+    mrf_tc_kernel<128, 4><<<grid, 160 + 128 * 4, smem, ex.st>>>(tw, p);
   } else if (a.C == 32) {
     if (eg == 2) mrf_tc_kernel<32, 2><<<grid, threads, smem, ex.st>>>(tw, p);
     else if (eg == 3) mrf_tc_kernel<32, 3><<<grid, threads, smem, ex.st>>>(tw, p);
