@@ -132,6 +132,21 @@ void TcVoice::build(Exec& ex, const Voice& v, int f16_) {
         t.ffn2 = make_tcw_split(ex, allocs, l.ffn2, mode);
         enc.push_back(t);
       }
+    // stochastic duration predictor: its 1x1 convolutions in the f16x3 form (PIPER_B200_SDP_TC=0: CUDA cores)
+    static const int sdp_env = [] { const char* e = getenv("PIPER_B200_SDP_TC"); return e ? atoi(e) : 1; }();
+    sdp.clear();
+    if (ok && sdp_env && !enc.empty() && enc[0].qkv.split == 2) {
+      std::vector<const ConvW*> cs;
+      cs.push_back(&v.dp_pre);
+      for (const DDSLayerW& l : v.dp_dds) cs.push_back(&l.c1x1);
+      cs.push_back(&v.dp_proj);
+      for (const ConvFlowW& f : v.dp_flows)
+        for (const DDSLayerW& l : f.dds) cs.push_back(&l.c1x1);
+      bool fits = true;
+      for (const ConvW* c : cs) fits = fits && c->cin % 32 == 0 && c->cout % 32 == 0 && c->phases == 1 && c->taps == 1;
+      if (fits)
+        for (const ConvW* c : cs) sdp.push_back(make_tcw_split(ex, allocs, *c, 2));
+    }
   }
   for (const StageW& s : v.stages) {
     TcStage t;
@@ -218,6 +233,7 @@ void TcVoice::release() {
   flows.clear();
   stages.clear();
   enc.clear();
+  sdp.clear();
   built = false;
 }
 

@@ -81,6 +81,9 @@ struct LNArgs {
   const int* row_utt = nullptr;
   int R = 0, C = 0;
   int gelu = 0;
+  // optional second output: the f16x3 split operand of `out` (conv_tc.h, TcW::split == 2), [R][2 * C] fp16 planes
+  // [hi | lo'] - what the next tensor-core convolution reads (saves the separate split pass)
+  uint16_t* out_split2 = nullptr;
 };
 void launch_layernorm(Exec& ex, const LNArgs& a);
 
@@ -88,14 +91,16 @@ void launch_embed(Exec& ex, const int64_t* ids_packed, const float* emb, float* 
                   int n_vocab, float scale);
 
 // relative-position multi-head attention over qkv [R][3H] (q|k|v), per utterance
+// out_split2 != null: the head-dim-96 kernel writes the f16x3 split operand [R][2 * H] instead of fp32 `out`
+// (other head dims: fp32 `out`, the caller splits)
 void launch_attention(Exec& ex, const float* qkv, const float* rel_k, const float* rel_v, float* out,
                       const int* utt_start, const int* utt_len, int batch, int max_len, int H,
-                      int n_heads, int window);
+                      int n_heads, int window, uint16_t* out_split2 = nullptr, bool* wrote_split = nullptr);
 
 // depthwise conv (k taps, dilation d) + channel LayerNorm + GELU, DDSConv first half
 void launch_dds_sep_ln_gelu(Exec& ex, const float* x, const float* w_sep /*[k][C]*/, const float* b_sep,
                             const float* gamma, const float* beta, float* out, const int* row_utt,
-                            int R, int C, int k, int dil);
+                            int R, int C, int k, int dil, uint16_t* out_split2 = nullptr);   // split: [R][2 * C] instead of `out`
 
 // h[r][c] = w[c]*z[r] + b[c] + cond[r][c]   (ConvFlow.pre on one channel + DDSConv's `x + g`)
 void launch_convflow_pre(Exec& ex, const float* z, const float* w, const float* b, const float* cond,

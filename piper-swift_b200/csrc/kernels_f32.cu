@@ -4,6 +4,8 @@
 // implementation of the flow and HiFi-GAN stages (8a10-a12); the tensor-core versions of
 // the latter live in conv_tc.cu.  Each kernel names the ONNX ops / reference kernels it
 // replaces; none of them is a translation of the one-thread-per-output Metal kernels.
+#include <cuda_fp16.h>
+
 #include "kernels.h"
 
 #include <cstdlib>
@@ -26,6 +28,13 @@ __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
+}
+// f16x3 split of an fp32 value (conv_tc.h, TcW::split == 2): x = hi + lo' * 2^-11
+__device__ __forceinline__ void f32_split2(float x, uint16_t& hi, uint16_t& lo) {
+  x = fminf(fmaxf(x, -65504.f), 65504.f);
+  const __half h = __float2half_rn(x);
+  const __half l = __float2half_rn((x - __half2float(h)) * 2048.f);
+  hi = __half_as_ushort(h); lo = __half_as_ushort(l);
 }
 __device__ __forceinline__ float gelu_erf(float x) {
   // exact-erf GELU (ONNX Erf; the ORT-CPU target, not elementwise.metal:292-312's approximation)
@@ -443,7 +452,10 @@ __global__ void __launch_bounds__(256) layernorm_kernel(LNArgs a) {
   const size_t base = (size_t)warp * a.C;
   const bool valid = !a.row_utt || a.row_utt[warp] >= 0;
   if (!valid) {
-    for (int c = lane; c < a.C; c += 32) a.out[base + c] = 0.f;
+    for (int c = lane; c < a.C; c += 32) {
+      a.out[base + c] = 0.f;
+      if (a.out_split2) { a.out_split2[2 * base + c] = 0; a.out_split2[2 * base + a.C + c] = 0; }
+    }
     return;
   }
   float v[LN_MAXV];
@@ -478,6 +490,11 @@ __global__ void __launch_bounds__(256) layernorm_kernel(LNArgs a) {
       if (a.gelu) o = gelu_erf(o);
       if (a.res) o += a.res[base + c];
       a.out[base + c] = o;
+      if (a.out_split2) {
+        uint16_t hi, lo;
+        f32_split2(o, hi, lo);
+        a.out_split2[2 * base + c] = hi; a.out_split2[2 * base + a.C + c] = lo;
+      }
     }
   }
 }
@@ -639,7 +656,7 @@ constexpr int AT2_Q = 64, AT2_K = 64, AT2_D = 96, AT2_LD = 100, AT2_LDP = 68, AT
 __global__ void __launch_bounds__(256, 2) attention96_kernel(
     const float* __restrict__ qkv, const float* __restrict__ rel_k, const float* __restrict__ rel_v,
     float* __restrict__ out, const int* __restrict__ utt_start, const int* __restrict__ utt_len,
-    int H, int window) {
+    int H, int window, uint16_t* __restrict__ out_split2) {
   extern __shared__ __align__(16) float sm[];
   float* Qs = sm;                               // [64][100]  (scaled by 1/sqrt(96))
   float* Ks = Qs + AT2_Q * AT2_LD;              // [64][100]
@@ -792,6 +809,16 @@ __global__ void __launch_bounds__(256, 2) attention96_kernel(
   for (int r = 0; r < 4; ++r) {
     const int i = i0 + ty + 16 * r;
     if (i >= T) continue;
+    if (out_split2) {   // f16x3 split operand of the output projection instead of the fp32 tensor
+      uint16_t* sp = out_split2 + (size_t)(row0 + i) * 2 * H + head * AT2_D;
+#pragma unroll
+      for (int e = 0; e < 6; ++e) {
+        uint16_t hi, lo;
+        f32_split2(o[r][e] / lrun[r], hi, lo);
+        sp[tx + 16 * e] = hi; sp[H + tx + 16 * e] = lo;
+      }
+      continue;
+    }
     float* op = out + (size_t)(row0 + i) * H + head * AT2_D;
 #pragma unroll
     for (int e = 0; e < 6; ++e) op[tx + 16 * e] = o[r][e] / lrun[r];
@@ -800,7 +827,8 @@ __global__ void __launch_bounds__(256, 2) attention96_kernel(
 
 void launch_attention(Exec& ex, const float* qkv, const float* rel_k, const float* rel_v, float* out,
                       const int* utt_start, const int* utt_len, int batch, int max_len, int H,
-                      int n_heads, int window) {
+                      int n_heads, int window, uint16_t* out_split2, bool* wrote_split) {
+  if (wrote_split) *wrote_split = false;
   if (batch <= 0 || max_len <= 0) return;
   const int kc = H / n_heads;
   const int nrel = 2 * window + 1;
@@ -816,7 +844,8 @@ void launch_attention(Exec& ex, const float* qkv, const float* rel_k, const floa
       attr_set = true;
     }
     dim3 grid2((max_len + AT2_Q - 1) / AT2_Q, n_heads, batch);
-    attention96_kernel<<<grid2, 256, smem2, ex.st>>>(qkv, rel_k, rel_v, out, utt_start, utt_len, H, window);
+    attention96_kernel<<<grid2, 256, smem2, ex.st>>>(qkv, rel_k, rel_v, out, utt_start, utt_len, H, window, out_split2);
+    if (wrote_split) *wrote_split = out_split2 != nullptr;
     KLAUNCH(ex);
     return;
   }
@@ -833,13 +862,16 @@ void launch_attention(Exec& ex, const float* qkv, const float* rel_k, const floa
 __global__ void __launch_bounds__(256) dds_sep_ln_gelu_kernel(
     const float* __restrict__ x, const float* __restrict__ w_sep, const float* __restrict__ b_sep,
     const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ out,
-    const int* __restrict__ row_utt, int R, int C, int k, int dil) {
+    const int* __restrict__ row_utt, int R, int C, int k, int dil, uint16_t* __restrict__ out_split2) {
   const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (r >= R) return;
   const size_t base = (size_t)r * C;
   if (row_utt && row_utt[r] < 0) {
-    for (int c = lane; c < C; c += 32) out[base + c] = 0.f;
+    for (int c = lane; c < C; c += 32) {
+      if (out_split2) { out_split2[2 * base + c] = 0; out_split2[2 * base + C + c] = 0; }
+      else out[base + c] = 0.f;
+    }
     return;
   }
   const int pad = (k * dil - dil) / 2;
@@ -871,15 +903,25 @@ __global__ void __launch_bounds__(256) dds_sep_ln_gelu_kernel(
 #pragma unroll
   for (int i = 0; i < LN_MAXV; ++i) {
     const int c = lane + 32 * i;
-    if (c < C) out[base + c] = gelu_erf(v[i] / denom * gamma[c] + beta[c]);
+    if (c < C) {
+      const float o = gelu_erf(v[i] / denom * gamma[c] + beta[c]);
+      if (out_split2) {
+        uint16_t hi, lo;
+        f32_split2(o, hi, lo);
+        out_split2[2 * base + c] = hi; out_split2[2 * base + C + c] = lo;
+      } else {
+        out[base + c] = o;
+      }
+    }
   }
 }
 
 void launch_dds_sep_ln_gelu(Exec& ex, const float* x, const float* w_sep, const float* b_sep,
                             const float* gamma, const float* beta, float* out, const int* row_utt,
-                            int R, int C, int k, int dil) {
+                            int R, int C, int k, int dil, uint16_t* out_split2) {
   if (R <= 0) return;
-  dds_sep_ln_gelu_kernel<<<(R + 7) / 8, 256, 0, ex.st>>>(x, w_sep, b_sep, gamma, beta, out, row_utt, R, C, k, dil);
+  dds_sep_ln_gelu_kernel<<<(R + 7) / 8, 256, 0, ex.st>>>(x, w_sep, b_sep, gamma, beta, out, row_utt, R, C, k, dil,
+                                                         out_split2);
   KLAUNCH(ex);
 }
 

@@ -84,6 +84,9 @@ struct TcVoice {
   bool built = false;
   int f16 = 0;
   std::vector<TcEncLayer> enc;   // empty when PIPER_B200_FRONT_TC=0 or a shape does not fit
+  // duration predictor 1x1 convolutions in the f16x3 form (empty: CUDA-core kernels): dp_pre, dp_dds[*].c1x1, dp_proj,
+  // then dp_flows[f].dds[*].c1x1 in execution order
+  std::vector<TcW> sdp;
   std::vector<TcCoupling> flows;
   TcW dec_pre;
   std::vector<TcStage> stages;

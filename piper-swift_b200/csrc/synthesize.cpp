@@ -56,14 +56,25 @@ void launch_split_act(Exec& ex, int mode, const float* src, int ldsrc, int64_t R
   else launch_split3(ex, src, ldsrc, R, C, dst, cpad);
 }
 
+// tcw != null: the 1x1 convolutions run in the f16x3 tensor-core form (tcw[i] = layer i), the depthwise kernel
+// writes their split operand (t1s) directly; h_split != null: the last layer also emits the split of h
 void run_dds(Exec& ex, const std::vector<DDSLayerW>& layers, float* h, float* t1, float* t2, const int* row_utt,
-             int R, int C) {
-  for (const DDSLayerW& l : layers) {
-    launch_dds_sep_ln_gelu(ex, h, l.w_sep, l.b_sep, l.n1.gamma, l.n1.beta, t1, row_utt, R, C, l.k, l.dil);
-    launch_conv_f32(ex, conv_args(l.c1x1, t1, C, t2, C, R, row_utt));
+             int R, int C, const TcW* tcw = nullptr, uint16_t* t1s = nullptr, uint16_t* h_split = nullptr) {
+  for (size_t li = 0; li < layers.size(); ++li) {
+    const DDSLayerW& l = layers[li];
+    if (tcw) {
+      launch_dds_sep_ln_gelu(ex, h, l.w_sep, l.b_sep, l.n1.gamma, l.n1.beta, nullptr, row_utt, R, C, l.k, l.dil, t1s);
+      TcConvArgs a = split_args(tcw[li], t1s, R, row_utt);
+      a.e[0].out_f32 = t2; a.e[0].ld_f32 = C;
+      launch_conv_tc(ex, a);
+    } else {
+      launch_dds_sep_ln_gelu(ex, h, l.w_sep, l.b_sep, l.n1.gamma, l.n1.beta, t1, row_utt, R, C, l.k, l.dil);
+      launch_conv_f32(ex, conv_args(l.c1x1, t1, C, t2, C, R, row_utt));
+    }
     LNArgs n;
     n.x = t2; n.gamma = l.n2.gamma; n.beta = l.n2.beta; n.out = h; n.res = h; n.row_utt = row_utt;
     n.R = R; n.C = C; n.gelu = 1;
+    if (li + 1 == layers.size()) n.out_split2 = h_split;
     launch_layernorm(ex, n);
   }
 }
@@ -256,14 +267,18 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
       const EncLayerW& l = voice.enc[li];
       const TcEncLayer& t = tc.enc[li];
       const int sm = t.qkv.split, planes = sm == 2 ? 2 : 3;
-      launch_split_act(ex, sm, x, H, Rp, H, xs, H);
+      const bool fused_split = sm == 2;   // f16x3: LayerNorm / attention emit the split operand themselves
+      if (!fused_split || li == 0) launch_split_act(ex, sm, x, H, Rp, H, xs, H);
+      if (fused_split && li == 0) CUDA_OK(cudaMemsetAsync(atts, 0, (size_t)Rp * 2 * H * 2, stream));   // gap rows
       {
         TcConvArgs a = split_args(t.qkv, xs, Rp, p_utt);
         a.e[0].out_f32 = qkv; a.e[0].ld_f32 = 3 * H;
         launch_conv_tc(ex, a);
       }
-      launch_attention(ex, qkv, l.rel_k, l.rel_v, att, d_utt_start, d_utt_len, B, max_len, H, hp.n_heads, hp.window);
-      launch_split_act(ex, sm, att, H, Rp, H, atts, H);
+      bool att_split = false;
+      launch_attention(ex, qkv, l.rel_k, l.rel_v, att, d_utt_start, d_utt_len, B, max_len, H, hp.n_heads, hp.window,
+                       fused_split ? atts : nullptr, &att_split);
+      if (!att_split) launch_split_act(ex, sm, att, H, Rp, H, atts, H);
       {
         TcConvArgs a = split_args(t.o, atts, Rp, p_utt);
         a.e[0].out_f32 = y; a.e[0].ld_f32 = H;
@@ -271,8 +286,9 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
       }
       LNArgs n1;
       n1.x = x; n1.y = y; n1.gamma = l.n1.gamma; n1.beta = l.n1.beta; n1.out = x; n1.row_utt = p_utt; n1.R = Rp; n1.C = H;
+      if (fused_split) n1.out_split2 = xs;
       launch_layernorm(ex, n1);
-      launch_split_act(ex, sm, x, H, Rp, H, xs, H);
+      if (!fused_split) launch_split_act(ex, sm, x, H, Rp, H, xs, H);
       {
         TcConvArgs a = split_args(t.ffn1, xs, Rp, p_utt);
         a.e[0].relu = 1;
@@ -308,17 +324,35 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
 
     // ---- stochastic duration predictor, reverse ---------------------------------------------------
     {
-      ConvArgs a = conv_args(voice.dp_pre, x, H, dph, H, Rp, p_utt);
-      a.uttbias = cond_dp; a.ldub = H;
-      launch_conv_f32(ex, a);
-      run_dds(ex, voice.dp_dds, dph, t1, t2, p_utt, Rp, H);
-      launch_conv_f32(ex, conv_args(voice.dp_proj, dph, H, dpc, H, Rp, p_utt));
+      // f16x3 tensor-core form of the 1x1 convolutions (TcVoice::sdp): xs still holds the split of the encoder output
+      // (the last LayerNorm wrote it); atts serves as the depthwise kernel's split output, xs then as the split of dph
+      const bool sdp_tc = front_tc && !tc.sdp.empty();
+      const TcW* sw = sdp_tc ? tc.sdp.data() : nullptr;
+      const size_t nd = voice.dp_dds.size();
+      if (sdp_tc) {
+        TcConvArgs a = split_args(sw[0], xs, Rp, p_utt);
+        a.uttbias = cond_dp; a.ldub = H;
+        a.e[0].out_f32 = dph; a.e[0].ld_f32 = H;
+        launch_conv_tc(ex, a);
+        run_dds(ex, voice.dp_dds, dph, t1, t2, p_utt, Rp, H, sw + 1, atts, xs);
+        TcConvArgs b = split_args(sw[1 + nd], xs, Rp, p_utt);
+        b.e[0].out_f32 = dpc; b.e[0].ld_f32 = H;
+        launch_conv_tc(ex, b);
+      } else {
+        ConvArgs a = conv_args(voice.dp_pre, x, H, dph, H, Rp, p_utt);
+        a.uttbias = cond_dp; a.ldub = H;
+        launch_conv_f32(ex, a);
+        run_dds(ex, voice.dp_dds, dph, t1, t2, p_utt, Rp, H);
+        launch_conv_f32(ex, conv_args(voice.dp_proj, dph, H, dpc, H, Rp, p_utt));
+      }
+      size_t sdp_next = 2 + nd;
       CUDA_OK(cudaMemsetAsync(zdp, 0, (size_t)Rp * 2 * 4, stream));
       launch_noise_dp(ex, zdp, d_noise_dp, d_utt_start, d_utt_len, d_id_off, B, Rp, seed, noise_w);
       const float inv_sqrt_fc = 1.0f / std::sqrt((float)H);
       for (const ConvFlowW& f : voice.dp_flows) {
         launch_convflow_pre(ex, zdp + (size_t)(1 - f.target) * Rp, f.pre_w, f.pre_b, dpc, hh, p_utt, Rp, H);
-        run_dds(ex, f.dds, hh, t1, t2, p_utt, Rp, H);
+        run_dds(ex, f.dds, hh, t1, t2, p_utt, Rp, H, sdp_tc ? sw + sdp_next : nullptr, atts);
+        sdp_next += f.dds.size();
         launch_conv_f32(ex, conv_args(f.proj, hh, H, params, 32, Rp, p_utt));
         launch_spline_inverse(ex, zdp + (size_t)f.target * Rp, params, 32, p_utt, Rp, hp.dp_bins, 5.0f, inv_sqrt_fc);
       }
