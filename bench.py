@@ -195,6 +195,9 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
+        # keep stdout to the one JSON line: NCCL prints its version banner there at the VERSION / INFO levels
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     spec, utts, sids = workload(args, rank)
     mp, cp = synth_voice.write_voice(spec, VOICE_DIR) if rank == 0 or world == 1 else (None, None)

@@ -653,6 +653,62 @@ __global__ void __launch_bounds__(ATT_WARPS * 32) attention_kernel(
 // utterance are read ceil(T/64) times instead of ceil(T/8) times, and the inner loops are FMA-bound.
 constexpr int AT2_Q = 64, AT2_K = 64, AT2_D = 96, AT2_LD = 100, AT2_LDP = 68, AT2_MAXREL = 17;
 
+// S = Q K^T for the RM live query groups (rows ty + 16 r) and CM live key groups (keys tx + 16 c) of a tile: groups
+// that lie wholly beyond the utterance are not computed (their scores are masked anyway).  The FMA order of every
+// computed element is the same as in the full 4 x 4 form.
+template <int RM, int CM>
+__device__ __forceinline__ void att96_qk(const float* __restrict__ Qs, const float* __restrict__ Ks, int ty, int tx,
+                                         float (&sacc)[4][4]) {
+#pragma unroll 2
+  for (int d4 = 0; d4 < AT2_D / 4; ++d4) {
+    float4 q4[RM], k4[CM];
+#pragma unroll
+    for (int r = 0; r < RM; ++r) q4[r] = *reinterpret_cast<const float4*>(Qs + (ty + 16 * r) * AT2_LD + d4 * 4);
+#pragma unroll
+    for (int c = 0; c < CM; ++c) k4[c] = *reinterpret_cast<const float4*>(Ks + (tx + 16 * c) * AT2_LD + d4 * 4);
+#pragma unroll
+    for (int r = 0; r < RM; ++r)
+#pragma unroll
+      for (int c = 0; c < CM; ++c) {
+        sacc[r][c] = fmaf(q4[r].x, k4[c].x, sacc[r][c]);
+        sacc[r][c] = fmaf(q4[r].y, k4[c].y, sacc[r][c]);
+        sacc[r][c] = fmaf(q4[r].z, k4[c].z, sacc[r][c]);
+        sacc[r][c] = fmaf(q4[r].w, k4[c].w, sacc[r][c]);
+      }
+  }
+}
+template <int RM>
+__device__ __forceinline__ void att96_qk_c(const float* Qs, const float* Ks, int ty, int tx, int cmax, float (&sacc)[4][4]) {
+  switch (cmax) {
+    case 1: att96_qk<RM, 1>(Qs, Ks, ty, tx, sacc); break;
+    case 2: att96_qk<RM, 2>(Qs, Ks, ty, tx, sacc); break;
+    case 3: att96_qk<RM, 3>(Qs, Ks, ty, tx, sacc); break;
+    default: att96_qk<RM, 4>(Qs, Ks, ty, tx, sacc); break;
+  }
+}
+// O += P V for the RM live query groups
+template <int RM>
+__device__ __forceinline__ void att96_pv(const float* __restrict__ Ps, const float* __restrict__ Vs, int ty, int tx, int jn,
+                                         float (&o)[4][6]) {
+  for (int jj = 0; jj < jn; jj += 4) {           // rows jj..jj+3 beyond jn hold p = 0 and zero V
+    float4 p4[RM];
+#pragma unroll
+    for (int r = 0; r < RM; ++r) p4[r] = *reinterpret_cast<const float4*>(Ps + (ty + 16 * r) * AT2_LDP + jj);
+#pragma unroll
+    for (int e = 0; e < 6; ++e) {
+      const float v0 = Vs[(jj + 0) * AT2_D + tx + 16 * e], v1 = Vs[(jj + 1) * AT2_D + tx + 16 * e];
+      const float v2 = Vs[(jj + 2) * AT2_D + tx + 16 * e], v3 = Vs[(jj + 3) * AT2_D + tx + 16 * e];
+#pragma unroll
+      for (int r = 0; r < RM; ++r) {
+        o[r][e] = fmaf(p4[r].x, v0, o[r][e]);
+        o[r][e] = fmaf(p4[r].y, v1, o[r][e]);
+        o[r][e] = fmaf(p4[r].z, v2, o[r][e]);
+        o[r][e] = fmaf(p4[r].w, v3, o[r][e]);
+      }
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256, 2) attention96_kernel(
     const float* __restrict__ qkv, const float* __restrict__ rel_k, const float* __restrict__ rel_v,
     float* __restrict__ out, const int* __restrict__ utt_start, const int* __restrict__ utt_len,
@@ -695,6 +751,7 @@ __global__ void __launch_bounds__(256, 2) attention96_kernel(
     for (int d = 0; d < AT2_D; ++d) acc = fmaf(Qs[r * AT2_LD + d], RK[m * AT2_D + d], acc);
     QR[t] = acc;
   }
+  const int rmax = min(4, (T - i0 + 15) >> 4);     // live query groups of this CTA
   float mrun[4], lrun[4], o[4][6];
 #pragma unroll
   for (int r = 0; r < 4; ++r) {
@@ -722,26 +779,17 @@ __global__ void __launch_bounds__(256, 2) attention96_kernel(
     for (int r = 0; r < 4; ++r)
 #pragma unroll
       for (int c = 0; c < 4; ++c) sacc[r][c] = 0.f;
-#pragma unroll 2
-    for (int d4 = 0; d4 < AT2_D / 4; ++d4) {
-      float4 q4[4], k4[4];
-#pragma unroll
-      for (int r = 0; r < 4; ++r) q4[r] = *reinterpret_cast<const float4*>(Qs + (ty + 16 * r) * AT2_LD + d4 * 4);
-#pragma unroll
-      for (int c = 0; c < 4; ++c) k4[c] = *reinterpret_cast<const float4*>(Ks + (tx + 16 * c) * AT2_LD + d4 * 4);
-#pragma unroll
-      for (int r = 0; r < 4; ++r)
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          sacc[r][c] = fmaf(q4[r].x, k4[c].x, sacc[r][c]);
-          sacc[r][c] = fmaf(q4[r].y, k4[c].y, sacc[r][c]);
-          sacc[r][c] = fmaf(q4[r].z, k4[c].z, sacc[r][c]);
-          sacc[r][c] = fmaf(q4[r].w, k4[c].w, sacc[r][c]);
-        }
+    const int cmax = min(4, (T - j0 + 15) >> 4);   // live key groups of this tile
+    switch (rmax) {
+      case 1: att96_qk_c<1>(Qs, Ks, ty, tx, cmax, sacc); break;
+      case 2: att96_qk_c<2>(Qs, Ks, ty, tx, cmax, sacc); break;
+      case 3: att96_qk_c<3>(Qs, Ks, ty, tx, cmax, sacc); break;
+      default: att96_qk_c<4>(Qs, Ks, ty, tx, cmax, sacc); break;
     }
     // ---- relative-key band, mask, online softmax ----
 #pragma unroll
     for (int r = 0; r < 4; ++r) {
+      if (r >= rmax) continue;                   // CTA-uniform: the whole query group lies beyond the utterance
       const int i = i0 + ty + 16 * r;
       float mx = -FLT_MAX;
 #pragma unroll
@@ -775,26 +823,16 @@ __global__ void __launch_bounds__(256, 2) attention96_kernel(
     __syncthreads();
     // ---- O += P V ----
     const int jn = min(AT2_K, T - j0);
-    for (int jj = 0; jj < jn; jj += 4) {           // rows jj..jj+3 beyond jn hold p = 0 and zero V
-      float4 p4[4];
-#pragma unroll
-      for (int r = 0; r < 4; ++r) p4[r] = *reinterpret_cast<const float4*>(Ps + (ty + 16 * r) * AT2_LDP + jj);
-#pragma unroll
-      for (int e = 0; e < 6; ++e) {
-        const float v0 = Vs[(jj + 0) * AT2_D + tx + 16 * e], v1 = Vs[(jj + 1) * AT2_D + tx + 16 * e];
-        const float v2 = Vs[(jj + 2) * AT2_D + tx + 16 * e], v3 = Vs[(jj + 3) * AT2_D + tx + 16 * e];
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-          o[r][e] = fmaf(p4[r].x, v0, o[r][e]);
-          o[r][e] = fmaf(p4[r].y, v1, o[r][e]);
-          o[r][e] = fmaf(p4[r].z, v2, o[r][e]);
-          o[r][e] = fmaf(p4[r].w, v3, o[r][e]);
-        }
-      }
+    switch (rmax) {
+      case 1: att96_pv<1>(Ps, Vs, ty, tx, jn, o); break;
+      case 2: att96_pv<2>(Ps, Vs, ty, tx, jn, o); break;
+      case 3: att96_pv<3>(Ps, Vs, ty, tx, jn, o); break;
+      default: att96_pv<4>(Ps, Vs, ty, tx, jn, o); break;
     }
     // ---- relative-value band ----
 #pragma unroll
     for (int r = 0; r < 4; ++r) {
+      if (r >= rmax) continue;
       const int i = i0 + ty + 16 * r;
       for (int m = 0; m < nrel; ++m) {
         const int jl = i + m - window - j0;
