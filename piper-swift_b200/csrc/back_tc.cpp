@@ -221,6 +221,45 @@ void TcVoice::build(Exec& ex, const Voice& v, int f16_) {
         t.mrf = true;
       }
     }
+    {   // ResBlock1 stage (dilated conv -> lrelu -> plain conv, residual; three per resblock) as fused units
+      static const int rb1_env = [] { const char* e = getenv("PIPER_B200_RB1_FUSED"); return e ? atoi(e) : 1; }();
+      const int nk = (int)s.rbs.size();
+      const int U = nk ? (int)s.rbs[0].c1.size() : 0;
+      // PIPER_B200_RB1_ONLY_C=<channels>: debugging aid, fuse only the stage of that width
+      static const int only_c = [] { const char* e = getenv("PIPER_B200_RB1_ONLY_C"); return e ? atoi(e) : 0; }();
+      bool ok = rb1_env && !t.mrf && nk >= 1 && U >= 1 && (s.ch == 32 || s.ch == 64 || s.ch == 128) &&
+                (only_c == 0 || only_c == s.ch);
+      int taps = 0;
+      for (int j = 0; ok && j < nk; ++j) {
+        const ResBlockW& rb = s.rbs[j];
+        ok = (int)rb.c1.size() == U && (int)rb.c2.size() == U;
+        for (int u = 0; ok && u < U; ++u) {
+          const ConvW &a = rb.c1[u], &b = rb.c2[u];
+          const int k1 = a.k, dd0 = a.dil, dd1 = b.dil;
+          ok = a.k == b.k && a.cin == s.ch && a.cout == s.ch && b.cin == s.ch && b.cout == s.ch && a.phases == 1 &&
+               b.phases == 1 && a.pad_l == a.dil * (a.k - 1) / 2 && b.pad_l == b.dil * (b.k - 1) / 2 &&
+               mrf_tc_supported(s.ch, 1, &k1, &dd0, &dd1);
+          taps += 2 * a.k;
+        }
+      }
+      if (ok) {
+        const size_t tap_elems = (size_t)s.ch * s.ch;
+        CUDA_OK(cudaMalloc(&t.rb1_w, (size_t)taps * tap_elems * 2));
+        allocs.push_back(t.rb1_w);
+        int base = 0;
+        for (int j = 0; j < nk; ++j)
+          for (int u = 0; u < U; ++u) {
+            t.rb1_base.push_back(base);
+            for (const ConvW* cw : {&s.rbs[j].c1[u], &s.rbs[j].c2[u]}) {
+              launch_pack_tc_weights(ex, cw->w, cw->ldw, cw->taps, cw->cin, cw->cout,
+                                     static_cast<uint16_t*>(t.rb1_w) + (size_t)base * tap_elems, s.ch, 0, s.ch, f16);
+              base += cw->k;
+            }
+          }
+        t.rb1 = true;
+        t.rb1_units = U;
+      }
+    }
     stages.push_back(t);
   }
   CUDA_OK(cudaStreamSynchronize(ex.st));
@@ -276,7 +315,7 @@ size_t back_tc_bytes(const Context& ctx, int Rf, int batch) {
   bytes += (size_t)Rf * H * (4 * 2 + 2 * 4);       // h, skip fp32; zb, hb, actsb, skipb 16-bit
   bytes += (size_t)Rf * H * 2 * (size_t)std::max(0, v.hp.flow_wn_layers - 1);   // gated activations of every WN layer
   bytes += (size_t)Rf * P * (4 * 3 + 2 * 5);       // xu, yb, xs fp32; actA, actB, xub, ybb, tbb 16-bit
-  bytes += 128 * 1280 * 2 + 4096;                  // pad rows of the planar operand layout
+  bytes += 3 * (128 * 1280 * 2 + 4096);            // pad rows of the planar operand layouts
   bytes += (size_t)Rf * v.hp.hop * 4;              // packed audio
   bytes += 32 * 256;
   (void)batch;
@@ -390,8 +429,8 @@ float* run_decoder_tc(Context& ctx, Exec& ex, const DecoderIn& in) {
   float* xs = A.alloc<float>((size_t)Rf * P);
   uint16_t* act[2] = {A.alloc<uint16_t>((size_t)Rf * P), A.alloc<uint16_t>((size_t)Rf * P)};
   uint16_t* xub = A.alloc<uint16_t>((size_t)Rf * P + 128 * 1280);   // + pad rows of the planar layout
-  uint16_t* ybb = A.alloc<uint16_t>((size_t)Rf * P);
-  uint16_t* tbb = A.alloc<uint16_t>((size_t)Rf * P);
+  uint16_t* ybb = A.alloc<uint16_t>((size_t)Rf * P + 128 * 1280);   // also the ping / pong planar operands of ResBlock1 units
+  uint16_t* tbb = A.alloc<uint16_t>((size_t)Rf * P + 128 * 1280);
   float* audio = A.alloc<float>((size_t)Rf * v.hp.hop);
   if (!xu || !yb || !xs || !act[0] || !act[1] || !xub || !ybb || !tbb || !audio)
     throw std::runtime_error("capacity: back arena too small (decoder)");
@@ -415,7 +454,8 @@ float* run_decoder_tc(Context& ctx, Exec& ex, const DecoderIn& in) {
     const int C = s.ch;
     static const int mrf_env = [] { const char* e = getenv("PIPER_B200_MRF"); return e ? atoi(e) : 1; }();
     static const int c128_env = [] { const char* e = getenv("PIPER_B200_MRF_C128"); return e ? atoi(e) : 1; }();
-    const bool use_mrf = ts.mrf && mrf_env && (C < 128 || c128_env);
+    const bool use_rb1 = ts.rb1;
+    const bool use_mrf = (ts.mrf && mrf_env && (C < 128 || c128_env)) || use_rb1;   // both read the planar lrelu(x) operand
     // fused stages read lrelu(x) as a group-planar tensor [C/8][act_rows][8] with zero pad rows around the signal
     const int act_pad = 128;
     const int64_t act_rows = (int64_t)Rn + act_pad + 1152;
@@ -450,7 +490,42 @@ float* run_decoder_tc(Context& ctx, Exec& ex, const DecoderIn& in) {
       launch_conv_tc(ex, a);
     }
     uint16_t* xsb = act[cur ^ 1];
-    if (use_mrf) {   // whole MRF stage in one persistent kernel, intermediates on chip
+    if (use_rb1) {   // ResBlock1: one fused launch per (resblock, dilation) unit; the unit chain runs through 16-bit planar
+                     // operands (ping / pong), the cross-resblock mean accumulates in xs
+      uint16_t* pp[2] = {ybb, tbb};
+      for (int b = 0; b < 2; ++b) {
+        CUDA_OK(cudaMemset2DAsync(pp[b], (size_t)act_rows * 16, 0, (size_t)act_pad * 16, C / 8, ex.st));
+        CUDA_OK(cudaMemset2DAsync(pp[b] + ((size_t)act_pad + Rn) * 8, (size_t)act_rows * 16, 0, (size_t)1152 * 16, C / 8, ex.st));
+      }
+      const int Uu = ts.rb1_units;
+      for (int j = 0; j < nk; ++j) {
+        const uint16_t* src = xub;
+        for (int u = 0; u < Uu; ++u) {
+          const ConvW &c1 = s.rbs[j].c1[u], &c2 = s.rbs[j].c2[u];
+          MrfArgs a;
+          a.R = Rn; a.C = C; a.nk = 1; a.unit_mode = 1;
+          a.k[0] = c1.k; a.d0[0] = c1.dil; a.d1[0] = c2.dil;
+          a.tap_base[0][0] = 0; a.tap_base[0][1] = c1.k;            // this unit's 2k taps only
+          a.b1[0] = c1.b; a.b2[0] = c2.b;
+          a.w = static_cast<const uint16_t*>(ts.rb1_w) + (size_t)ts.rb1_base[j * Uu + u] * C * C;
+          a.total_taps = c1.k + c2.k;
+          a.x_act = src; a.act_rows = act_rows; a.act_pad = act_pad;
+          a.row_utt = in.frow_utt; a.valid_div = U;
+          a.f16 = f16;
+          if (u + 1 < Uu) {
+            a.out_planar = pp[u & 1]; a.out_rows = act_rows; a.out_pad = act_pad; a.act_slope = 0.1f;
+            src = pp[u & 1];
+          } else {
+            a.out_f32 = xs; a.accum = j > 0;
+            if (j == nk - 1) {
+              a.out_div = (float)nk;
+              if (!last_stage) { a.out_f32 = j > 0 ? xs : nullptr; a.out_act = xsb; a.act_slope = 0.1f; }
+            }
+          }
+          launch_mrf_tc(ex, a);
+        }
+      }
+    } else if (use_mrf) {   // whole MRF stage in one persistent kernel, intermediates on chip
       MrfArgs a;
       a.R = Rn; a.C = C; a.nk = nk;
       for (int j = 0; j < nk; ++j) {

@@ -48,11 +48,19 @@ struct MrfParams {
   const float* post_w; int post_k; float post_slope; float* post_out;   // fused conv_post + tanh (C = 32 only)
   int f16, ring, resident;
   int mma_split;              // 1: two issuing warps per convolution stream (even / odd tiles)
+  // ResBlock1 unit (nk = 1): out = x + conv2(lrelu(conv1(lrelu x) + b1)) + b2 - the residual does not enter the
+  // conv2 operand: Y1 = lrelu(D + b1), S starts from x
+  int unit_mode;
+  int accum;                  // stage output += previous contents of out_f32 (cross-resblock sum kept in HBM)
+  float out_div;              // != 0: stage output /= out_div (after accum)
+  uint16_t* out_planar; int64_t out_rows; int out_pad;   // optional group-planar 16-bit lrelu(out, act_slope), like x_act
   uint32_t tmem_cols;
   uint32_t* trace;            // debug timeline of CTA 0 (PIPER_B200_MRF_TRACE), else null
 };
 
-template <int C, int MRF_EG>   // channels, epilogue warpgroups
+// UNIT: ResBlock1 unit semantics (MrfParams::unit_mode) and the accumulate / planar stage outputs - a compile-time
+// switch so that the ResBlock2 instantiations keep their register allocation
+template <int C, int MRF_EG, bool UNIT = false>   // channels, epilogue warpgroups
 __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __grid_constant__ CUtensorMap tmap_w,
                                                                 const MrfParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -430,7 +438,7 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
             __syncwarp();
             tmem_ld16_async(dcol + (uint32_t)(hc * 16), t0);
             if (r > 0) tmem_ld16_async(scol + (uint32_t)(hc * 16), t2);
-            float d[16];
+            float d[16], xr[16];
             {   // x0 + b1 while the TMEM loads are in flight; x0 = min(v, 10 v) undoes lrelu(., 0.1)
               const uint32_t w[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
               const float4* b4 = reinterpret_cast<const float4*>(b1 + c0);
@@ -438,16 +446,26 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
               for (int q4 = 0; q4 < 4; ++q4) {
                 const float4 bb = b4[q4];
                 const float2 x01 = unpack2(w[2 * q4], p.f16), x23 = unpack2(w[2 * q4 + 1], p.f16);
-                d[4 * q4] = bb.x + fminf(x01.x, x01.x * 10.f);
-                d[4 * q4 + 1] = bb.y + fminf(x01.y, x01.y * 10.f);
-                d[4 * q4 + 2] = bb.z + fminf(x23.x, x23.x * 10.f);
-                d[4 * q4 + 3] = bb.w + fminf(x23.y, x23.y * 10.f);
+                if (UNIT) {
+                  xr[4 * q4] = fminf(x01.x, x01.x * 10.f);
+                  xr[4 * q4 + 1] = fminf(x01.y, x01.y * 10.f);
+                  xr[4 * q4 + 2] = fminf(x23.x, x23.x * 10.f);
+                  xr[4 * q4 + 3] = fminf(x23.y, x23.y * 10.f);
+                  d[4 * q4] = bb.x; d[4 * q4 + 1] = bb.y; d[4 * q4 + 2] = bb.z; d[4 * q4 + 3] = bb.w;
+                } else {
+                  d[4 * q4] = bb.x + fminf(x01.x, x01.x * 10.f);
+                  d[4 * q4 + 1] = bb.y + fminf(x01.y, x01.y * 10.f);
+                  d[4 * q4 + 2] = bb.z + fminf(x23.x, x23.x * 10.f);
+                  d[4 * q4 + 3] = bb.w + fminf(x23.y, x23.y * 10.f);
+                }
               }
             }
             tmem_wait_ld();
 #pragma unroll
             for (int e = 0; e < 16; ++e) d[e] += __uint_as_float(t0[e]);
-            if (r > 0) {
+            if (UNIT) {                       // ResBlock1 unit: the stream starts from x, conv2 accumulates onto it
+              tmem_st16(scol + (uint32_t)(hc * 16), xr);
+            } else if (r > 0) {
               float sv[16];
 #pragma unroll
               for (int e = 0; e < 16; ++e) sv[e] = __uint_as_float(t2[e]) + d[e];
@@ -599,6 +617,34 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
             s0[e] = valid ? (s0[e] + b2s[cb + e]) * inv_nk : 0.f;
             s1[e] = valid ? (s1[e] + b2s[cb + 16 + e]) * inv_nk : 0.f;
           }
+          if (UNIT && p.accum) {   // cross-resblock sum of a ResBlock1 stage lives in out_f32
+            const float4* a4 = reinterpret_cast<const float4*>(p.out_f32 + (size_t)grow * C + cb);
+#pragma unroll
+            for (int q4 = 0; q4 < 4; ++q4) {
+              const float4 a = a4[q4], b = a4[4 + q4];
+              s0[4 * q4] += a.x; s0[4 * q4 + 1] += a.y; s0[4 * q4 + 2] += a.z; s0[4 * q4 + 3] += a.w;
+              s1[4 * q4] += b.x; s1[4 * q4 + 1] += b.y; s1[4 * q4 + 2] += b.z; s1[4 * q4 + 3] += b.w;
+            }
+          }
+          if (UNIT && p.out_div != 0.f) {
+#pragma unroll
+            for (int e = 0; e < 16; ++e) { s0[e] = s0[e] / p.out_div; s1[e] = s1[e] / p.out_div; }
+          }
+          if (UNIT && !valid) {
+#pragma unroll
+            for (int e = 0; e < 16; ++e) { s0[e] = 0.f; s1[e] = 0.f; }
+          }
+          if (UNIT && p.out_planar) {   // operand of the next fused launch: planes cb/8 .. cb/8 + 3, one 16-byte piece per row each
+            uint16_t* pl = p.out_planar + ((size_t)(cb >> 3) * p.out_rows + (size_t)(p.out_pad + grow)) * 8;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              const float* v = g < 2 ? s0 + 8 * g : s1 + 8 * (g - 2);
+              uint32_t pk[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) pk[e] = pack2(lrelu(v[2 * e], p.act_slope), lrelu(v[2 * e + 1], p.act_slope), p.f16);
+              *reinterpret_cast<uint4*>(pl + (size_t)g * p.out_rows * 8) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            }
+          }
           if (p.out_f32) {
             float4* o4 = reinterpret_cast<float4*>(p.out_f32 + (size_t)grow * C + cb);
 #pragma unroll
@@ -667,7 +713,10 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
         cudaFuncSetAttribute(mrf_tc_kernel<64, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
         cudaFuncSetAttribute(mrf_tc_kernel<32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
         cudaFuncSetAttribute(mrf_tc_kernel<64, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
-        cudaFuncSetAttribute(mrf_tc_kernel<128, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess)
+        cudaFuncSetAttribute(mrf_tc_kernel<128, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
+        cudaFuncSetAttribute(mrf_tc_kernel<32, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
+        cudaFuncSetAttribute(mrf_tc_kernel<64, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
+        cudaFuncSetAttribute(mrf_tc_kernel<128, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess)
       throw std::runtime_error("cuda: cannot raise dynamic shared memory limit for mrf_tc_kernel");
   }
   MrfParams p{};
@@ -688,8 +737,8 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
     throw std::runtime_error("conv_mrf: planar operand needs zero pad rows around the signal");
   // window height: TMEM holds D and S for every tile (2*m*C columns <= 512); smem holds two operand
   // windows of (m+1)*128 rows plus at least kmax weight taps
-  int shift = 0;
-  for (int r = 0; r < a.nk; ++r) shift = std::max(shift, (a.k[r] - 1) / 2 * std::max(a.d0[r], a.d1[r]));
+  int shift = 0;   // conv2 shifts: guard rows of the conv2 operand window
+  for (int r = 0; r < a.nk; ++r) shift = std::max(shift, (a.k[r] - 1) / 2 * a.d1[r]);
   static const int g_env = [] { const char* e = getenv("PIPER_B200_MRF_G"); return e ? atoi(e) : 0; }();
   int G = (shift + 7) & ~7;
   if (g_env >= G && g_env <= MRF_G && g_env % 8 == 0) G = g_env;
@@ -698,10 +747,12 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   int shift_x = 0;
   for (int r = 0; r < a.nk; ++r) shift_x = std::max(shift_x, (a.k[r] - 1) / 2 * a.d0[r]);
   static const int gx_env = [] { const char* e = getenv("PIPER_B200_MRF_GX"); return e ? atoi(e) : 1; }();
-  const int GX = gx_env ? std::min(G, (shift_x + 7) & ~7) : G;
+  const int GX = gx_env ? ((shift_x + 7) & ~7) : std::max(G, (shift_x + 7) & ~7);
   p.GX = GX;
   // C = 128: a tap is 32 KB, the ring holds two of them and the taps-outermost issue order is used
-  const int need_ring = a.C > 64 ? 2 : kmax;
+  // ResBlock1 units whose 2k taps are not resident also take the taps-outermost order (a single issuing warp): with
+  // k = 11 a streamed ring would hold barely more than one convolution
+  const int need_ring = (a.C > 64 || a.unit_mode) ? 2 : kmax;
   int m = std::min(MRF_MAX_M, 512 / (2 * a.C));
   auto post_bytes = [&](int mm) { return post ? (7 * 32 + 2 * mm * 4 * 2 * 3 * 7) * 4 + 64 : 0; };
   auto fits = [&](int mm) {
@@ -724,12 +775,18 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   p.resident = a.total_taps <= ring ? 1 : 0;
   if (p.resident) ring = a.total_taps;
   p.ring = ring;
-  p.tap_outer = (!p.resident && ring < kmax) ? 1 : 0;
+  p.tap_outer = (!p.resident && (ring < kmax || a.unit_mode)) ? 1 : 0;
   static const int split_env = [] { const char* e = getenv("PIPER_B200_MRF_SPLIT"); return e ? atoi(e) : 1; }();
   p.mma_split = (split_env && !p.tap_outer) ? 1 : 0;
   p.x_act = static_cast<const uint16_t*>(a.x_act); p.act_rows = a.act_rows; p.act_pad = a.act_pad;
   p.row_utt = a.row_utt; p.valid_div = a.valid_div < 1 ? 1 : a.valid_div;
   p.out_act = a.out_act; p.act_slope = a.act_slope; p.out_f32 = a.out_f32;
+  if (a.unit_mode && a.nk != 1) throw std::runtime_error("conv_mrf: a ResBlock1 unit is one convolution pair");
+  if (!a.unit_mode && (a.accum || a.out_div != 0.f || a.out_planar))
+    throw std::runtime_error("conv_mrf: accum / out_div / out_planar belong to the ResBlock1 unit form");
+  if (a.accum && !a.out_f32) throw std::runtime_error("conv_mrf: accum needs out_f32");
+  p.unit_mode = a.unit_mode; p.accum = a.accum; p.out_div = a.out_div;
+  p.out_planar = static_cast<uint16_t*>(a.out_planar); p.out_rows = a.out_rows; p.out_pad = a.out_pad;
   p.post_w = a.post_w; p.post_k = a.post_k; p.post_slope = a.post_slope; p.post_out = a.post_out;
   p.f16 = a.f16;
   uint32_t cols = 32;
@@ -753,7 +810,11 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   static const int eg_env = [] { const char* e = getenv("PIPER_B200_MRF_EG"); return e ? atoi(e) : 0; }();
   const int eg = eg_env >= 2 && eg_env <= 5 ? eg_env : 4;
   const int threads = 160 + 128 * eg;
-  if (a.C == 128) {
+  if (a.unit_mode) {
+    if (a.C == 128) mrf_tc_kernel<128, 4, true><<<grid, 160 + 128 * 4, smem, ex.st>>>(tw, p);
+    else if (a.C == 64) mrf_tc_kernel<64, 4, true><<<grid, 160 + 128 * 4, smem, ex.st>>>(tw, p);
+    else mrf_tc_kernel<32, 4, true><<<grid, 160 + 128 * 4, smem, ex.st>>>(tw, p);
+  } else if (a.C == 128) {
     mrf_tc_kernel<128, 4><<<grid, 160 + 128 * 4, smem, ex.st>>>(tw, p);
   } else if (a.C == 32) {
     if (eg == 2) mrf_tc_kernel<32, 2><<<grid, threads, smem, ex.st>>>(tw, p);

@@ -45,6 +45,15 @@ struct MrfArgs {
   // is then never written.  post_w = fp32 [post_k][C].
   const float* post_w = nullptr; int post_k = 0; float post_slope = 0.01f;
   float* post_out = nullptr;     // fp32 [R]
+  // ResBlock1 unit (nk = 1, k[0] taps for both convolutions, d0 = dilation of conv1, d1 = 1):
+  //   out = x + conv2(lrelu(conv1(lrelu x) + b1)) + b2          (GraphExecutor.swift:2047-2069 chains, HiFi-GAN ResBlock1)
+  // x enters as the 16-bit lrelu(x) operand (like every fused stage); the next unit reads `out_planar`, the last unit of a
+  // resblock adds into / finishes the cross-resblock mean in out_f32 (accum, out_div)
+  int unit_mode = 0;
+  int accum = 0;                 // out += previous contents of out_f32
+  float out_div = 0.f;           // != 0: out /= out_div (after accum), then out_f32 / out_act / out_planar are written
+  void* out_planar = nullptr;    // optional 16-bit lrelu(out, act_slope) in the group-planar layout of x_act
+  int64_t out_rows = 0; int out_pad = 0;
   int f16 = 0;
 };
 

@@ -75,6 +75,12 @@ struct TcStage {
   void* mrf_w = nullptr;
   int mrf_taps = 0;
   int tap_base[MRF_MAX_RB][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}};
+  // ResBlock1 stage as fused units (conv_mrf.h, unit_mode): one launch per (resblock, dilation) pair of convolutions;
+  // rb1_base[j * units + u] = first tap of conv1, conv2 follows it
+  bool rb1 = false;
+  int rb1_units = 0;
+  void* rb1_w = nullptr;
+  std::vector<int> rb1_base;
 };
 // text-encoder convolutions as fp32-emulating tensor-core GEMMs (bf16x6 split operands, conv_tc.h)
 struct TcEncLayer {

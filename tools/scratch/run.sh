@@ -1,6 +1,8 @@
-python -m pytest tests -m gpu -x -q > gpurun_out/gpu_tests_v36.log 2>&1; tail -2 gpurun_out/gpu_tests_v36.log
-python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke_v36.log 2>&1; tail -1 gpurun_out/smoke_v36.log
-python bench.py > gpurun_out/bench_v36.json 2>gpurun_out/bench_v36.err
-python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_v36_reference.json 2>>gpurun_out/bench_v36.err
-ncu --metrics gpu__time_duration.sum --clock-control none -c 2000 --csv --log-file gpurun_out/launches_v36.csv python bench.py --steps 1 --warmup 1 --no-cpu > gpurun_out/ncu_v36.log 2>&1
-tail -c 400 gpurun_out/bench_v36.json
+timeout 300 python -m pytest tests -m gpu -x -q > gpurun_out/gpu_tests_v37.log 2>&1; tail -3 gpurun_out/gpu_tests_v37.log
+timeout 120 python tools/tc_parity_report.py > gpurun_out/tc_parity_v37.log 2>&1; grep -E "high|x_low" gpurun_out/tc_parity_v37.log
+timeout 60 python bench.py --voice high --batch 1 --t-lo 2000 --t-hi 2000 --no-cpu > gpurun_out/bench_v37_high.json 2>gpurun_out/bench_v37.err; tail -2 gpurun_out/bench_v37.err
+python -c "import json; d=json.loads(open('gpurun_out/bench_v37_high.json').read()); print('high', d['value'], d['ms_per_step'], d['stage_ms'], d['roofline']['by_class'])"
+timeout 60 python bench.py --voice high --batch 64 --t-lo 80 --t-hi 120 --no-cpu --steps 5 > gpurun_out/bench_v37_high_64.json 2>>gpurun_out/bench_v37.err
+python -c "import json; d=json.loads(open('gpurun_out/bench_v37_high_64.json').read()); print('high64', d['value'], d['ms_per_step'], d['stage_ms'], d['roofline']['by_class'])"
+timeout 200 python bench.py --no-cpu --steps 5 > gpurun_out/bench_v37.json 2>>gpurun_out/bench_v37.err
+python -c "import json; d=json.loads(open('gpurun_out/bench_v37.json').read()); print('medium', d['value'], d['ms_per_step'], d['roofline']['by_class']['mrf_tc_kernel'])"
