@@ -110,3 +110,21 @@ def test_tc_full_size_batch_properties():
     assert snr_db(np.concatenate(ref.audio), allv) >= 58.0
     again = r.synthesize_batch(utts, *S.FIXTURE_SCALES)
     assert all(np.array_equal(x, y) for x, y in zip(out.audio, again.audio))
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(120)
+@pytest.mark.parametrize("prec,min_snr", [("f16", 58.0), ("bf16", 40.0)])
+def test_tc_long_form_high_voice(prec, min_snr):
+    """BASELINE config 4 shape in the tensor-core modes: one long utterance of the ResBlock1 voice, so that every
+    fused ResBlock1 unit launch walks several windows per CTA (the 28-id parity cases fit in one); against the fp32
+    CUDA path (durations exact, audio SNR), and twice (idempotence)."""
+    ids = synthetic_utterances(1, 256, 600, 600, seed=11)[0]
+    ref = rt("high", "fp32").synthesize_batch([ids], *S.FIXTURE_SCALES)
+    r = rt("high", prec)
+    out = r.synthesize_batch([ids], *S.FIXTURE_SCALES)
+    assert np.array_equal(out.durations[0], ref.durations[0])
+    assert np.isfinite(out.audio[0]).all() and out.audio[0].shape == ref.audio[0].shape
+    assert snr_db(ref.audio[0], out.audio[0]) >= min_snr
+    again = r.synthesize_batch([ids], *S.FIXTURE_SCALES)
+    assert np.array_equal(out.audio[0], again.audio[0])
