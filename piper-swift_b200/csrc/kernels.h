@@ -95,7 +95,11 @@ void launch_embed(Exec& ex, const int64_t* ids_packed, const float* emb, float* 
 // (other head dims: fp32 `out`, the caller splits)
 void launch_attention(Exec& ex, const float* qkv, const float* rel_k, const float* rel_v, float* out,
                       const int* utt_start, const int* utt_len, int batch, int max_len, int H,
-                      int n_heads, int window, uint16_t* out_split2 = nullptr, bool* wrote_split = nullptr);
+                      int n_heads, int window, uint16_t* out_split2 = nullptr, bool* wrote_split = nullptr,
+                      float* scratch = nullptr);
+// bytes of `scratch` that launch_attention needs for `rows` packed rows when the longest utterance has max_len ids
+// (0 for short utterances: keys are split over several CTAs only from 512 ids on)
+size_t attention_scratch_bytes(int rows, int max_len, int H, int n_heads);
 
 // depthwise conv (k taps, dilation d) + channel LayerNorm + GELU, DDSConv first half
 void launch_dds_sep_ln_gelu(Exec& ex, const float* x, const float* w_sep /*[k][C]*/, const float* b_sep,

@@ -656,6 +656,13 @@ constexpr int AT2_Q = 64, AT2_K = 64, AT2_D = 96, AT2_LD = 100, AT2_LDP = 68, AT
 // S = Q K^T for the RM live query groups (rows ty + 16 r) and CM live key groups (keys tx + 16 c) of a tile: groups
 // that lie wholly beyond the utterance are not computed (their scores are masked anyway).  The FMA order of every
 // computed element is the same as in the full 4 x 4 form.
+// Long utterances: the keys of one (utterance, head, query tile) are split over several CTAs so that a single
+// 2000-id utterance fills the GPU (otherwise 64 CTAs); every CTA leaves its unnormalised output, running maximum and
+// sum per query row in `part` and attention96_merge_kernel combines them in split order.  The split count depends
+// on the utterance's own length only, so an utterance gives the same bits alone and inside a batch.
+constexpr int AT2_PW = AT2_D + 2;    // floats per (row, head, split) in the scratch buffer
+__host__ __device__ __forceinline__ int att96_splits(int T) { return T < 512 ? 1 : (T / 256 < 8 ? T / 256 : 8); }
+
 template <int RM, int CM>
 __device__ __forceinline__ void att96_qk(const float* __restrict__ Qs, const float* __restrict__ Ks, int ty, int tx,
                                          float (&sacc)[4][4]) {
@@ -712,7 +719,7 @@ __device__ __forceinline__ void att96_pv(const float* __restrict__ Ps, const flo
 __global__ void __launch_bounds__(256, 2) attention96_kernel(
     const float* __restrict__ qkv, const float* __restrict__ rel_k, const float* __restrict__ rel_v,
     float* __restrict__ out, const int* __restrict__ utt_start, const int* __restrict__ utt_len,
-    int H, int window, uint16_t* __restrict__ out_split2) {
+    int H, int window, uint16_t* __restrict__ out_split2, int smax, float* __restrict__ part) {
   extern __shared__ __align__(16) float sm[];
   float* Qs = sm;                               // [64][100]  (scaled by 1/sqrt(96))
   float* Ks = Qs + AT2_Q * AT2_LD;              // [64][100]
@@ -723,8 +730,12 @@ __global__ void __launch_bounds__(256, 2) attention96_kernel(
   float* QR = RV + AT2_MAXREL * AT2_D;          // [64][nrel]
   const int b = blockIdx.z, head = blockIdx.y;
   const int T = utt_len[b];
-  const int i0 = blockIdx.x * AT2_Q;
-  if (i0 >= T) return;
+  const int sp = (int)blockIdx.x % smax;        // key split handled by this CTA
+  const int i0 = ((int)blockIdx.x / smax) * AT2_Q;
+  const int S = smax > 1 ? att96_splits(T) : 1;   // smax == 1: no utterance of this call is long enough (or splitting is off)
+  if (i0 >= T || sp >= S) return;
+  const int n_kt = (T + AT2_K - 1) / AT2_K;
+  const int j_beg = (sp * n_kt / S) * AT2_K, j_end = min(T, ((sp + 1) * n_kt / S) * AT2_K);
   const int row0 = utt_start[b];
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const int nrel = 2 * window + 1;
@@ -759,7 +770,7 @@ __global__ void __launch_bounds__(256, 2) attention96_kernel(
 #pragma unroll
     for (int e = 0; e < 6; ++e) o[r][e] = 0.f;
   }
-  for (int j0 = 0; j0 < T; j0 += AT2_K) {
+  for (int j0 = j_beg; j0 < j_end; j0 += AT2_K) {
     __syncthreads();                             // previous tile's K, V, P fully consumed (and QR written)
     for (int f = tid; f < AT2_K * (AT2_D / 4); f += 256) {
       const int r = f / (AT2_D / 4), d4 = f - r * (AT2_D / 4);
@@ -847,6 +858,13 @@ __global__ void __launch_bounds__(256, 2) attention96_kernel(
   for (int r = 0; r < 4; ++r) {
     const int i = i0 + ty + 16 * r;
     if (i >= T) continue;
+    if (S > 1) {        // partial result of this key split
+      float* pp = part + (((size_t)(row0 + i) * gridDim.y + head) * smax + sp) * AT2_PW;
+#pragma unroll
+      for (int e = 0; e < 6; ++e) pp[tx + 16 * e] = o[r][e];
+      if (tx == 0) { pp[AT2_D] = mrun[r]; pp[AT2_D + 1] = lrun[r]; }
+      continue;
+    }
     if (out_split2) {   // f16x3 split operand of the output projection instead of the fp32 tensor
       uint16_t* sp = out_split2 + (size_t)(row0 + i) * 2 * H + head * AT2_D;
 #pragma unroll
@@ -863,9 +881,49 @@ __global__ void __launch_bounds__(256, 2) attention96_kernel(
   }
 }
 
+// one warp per (query row, head) of the utterances that were split
+__global__ void __launch_bounds__(256) attention96_merge_kernel(const float* __restrict__ part, float* __restrict__ out,
+                                                                uint16_t* __restrict__ out_split2,
+                                                                const int* __restrict__ utt_start,
+                                                                const int* __restrict__ utt_len, int H, int smax) {
+  const int b = blockIdx.z, head = blockIdx.y;
+  const int T = utt_len[b];
+  const int i = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  const int S = att96_splits(T);
+  if (i >= T || S == 1) return;
+  const size_t row = (size_t)utt_start[b] + i;
+  const float* pp = part + ((row * gridDim.y + head) * smax) * AT2_PW;
+  float M = -FLT_MAX;
+  for (int s = 0; s < S; ++s) M = fmaxf(M, pp[s * AT2_PW + AT2_D]);
+  float L = 0.f, acc[3] = {0.f, 0.f, 0.f};
+  for (int s = 0; s < S; ++s) {
+    const float w = expf(pp[s * AT2_PW + AT2_D] - M);
+    L += pp[s * AT2_PW + AT2_D + 1] * w;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) acc[c] = fmaf(pp[s * AT2_PW + lane + 32 * c], w, acc[c]);
+  }
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    const float v = acc[c] / L;
+    const int col = head * AT2_D + lane + 32 * c;
+    if (out_split2) {
+      uint16_t hi, lo;
+      f32_split2(v, hi, lo);
+      out_split2[row * 2 * H + col] = hi; out_split2[row * 2 * H + H + col] = lo;
+    } else {
+      out[row * H + col] = v;
+    }
+  }
+}
+
+size_t attention_scratch_bytes(int rows, int max_len, int H, int n_heads) {
+  const int smax = (H / n_heads == AT2_D) ? att96_splits(max_len) : 1;
+  return smax > 1 ? (size_t)rows * n_heads * smax * AT2_PW * sizeof(float) : 0;
+}
+
 void launch_attention(Exec& ex, const float* qkv, const float* rel_k, const float* rel_v, float* out,
                       const int* utt_start, const int* utt_len, int batch, int max_len, int H,
-                      int n_heads, int window, uint16_t* out_split2, bool* wrote_split) {
+                      int n_heads, int window, uint16_t* out_split2, bool* wrote_split, float* scratch) {
   if (wrote_split) *wrote_split = false;
   if (batch <= 0 || max_len <= 0) return;
   const int kc = H / n_heads;
@@ -881,10 +939,22 @@ void launch_attention(Exec& ex, const float* qkv, const float* rel_k, const floa
         throw std::runtime_error("cuda: cannot raise dynamic shared memory limit for attention96_kernel");
       attr_set = true;
     }
-    dim3 grid2((max_len + AT2_Q - 1) / AT2_Q, n_heads, batch);
-    attention96_kernel<<<grid2, 256, smem2, ex.st>>>(qkv, rel_k, rel_v, out, utt_start, utt_len, H, window, out_split2);
-    if (wrote_split) *wrote_split = out_split2 != nullptr;
+    static const int split_env = [] { const char* e = getenv("PIPER_B200_ATT_SPLIT"); return e ? atoi(e) : 1; }();
+    // key splits for long utterances (att96_splits): only with a scratch buffer; the split count per utterance is a
+    // function of its own length, the grid covers the longest one
+    const int smax = (scratch && split_env) ? att96_splits(max_len) : 1;
+    if (smax == 1 && att96_splits(max_len) > 1 && split_env)
+      throw std::runtime_error("attention: long utterances need the split scratch buffer");
+    dim3 grid2((max_len + AT2_Q - 1) / AT2_Q * smax, n_heads, batch);
+    attention96_kernel<<<grid2, 256, smem2, ex.st>>>(qkv, rel_k, rel_v, out, utt_start, utt_len, H, window, out_split2,
+                                                     smax, scratch);
     KLAUNCH(ex);
+    if (smax > 1) {
+      dim3 gm((max_len + 7) / 8, n_heads, batch);
+      attention96_merge_kernel<<<gm, 256, 0, ex.st>>>(scratch, out, out_split2, utt_start, utt_len, H, smax);
+      KLAUNCH(ex);
+    }
+    if (wrote_split) *wrote_split = out_split2 != nullptr;
     return;
   }
   dim3 grid((max_len + ATT_WARPS - 1) / ATT_WARPS, n_heads, batch);

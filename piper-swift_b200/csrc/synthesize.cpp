@@ -167,6 +167,8 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
     if (rq.noise_dp) fb += (size_t)n_ids * 2 * 4;
     const bool front_tc = use_tc && !tc.enc.empty();
     if (front_tc) fb += (size_t)Rp * 2 * 3 * (2 * H + hp.filter) + 3 * 256;   // split operands of x, att and the FFN mid
+    const size_t att_scratch_bytes = attention_scratch_bytes((int)Rp, max_len, H, hp.n_heads);
+    fb += att_scratch_bytes + 256;
     fb += 64 * 256;
     front.reserve(fb);
     front.reset();
@@ -194,6 +196,8 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
     float* t1 = F.alloc<float>((size_t)Rp * H);
     float* t2 = F.alloc<float>((size_t)Rp * H);
     float* params = F.alloc<float>((size_t)Rp * 32);
+    float* att_scratch = att_scratch_bytes ? F.alloc<float>(att_scratch_bytes / 4) : nullptr;
+    if (att_scratch_bytes && !att_scratch) throw std::runtime_error("capacity: front arena sizing bug (attention scratch)");
     float* zdp = F.alloc<float>((size_t)Rp * 2);
     float* logw = F.alloc<float>(Rp);
     int* dur = F.alloc<int>(Rp);
@@ -277,7 +281,7 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
       }
       bool att_split = false;
       launch_attention(ex, qkv, l.rel_k, l.rel_v, att, d_utt_start, d_utt_len, B, max_len, H, hp.n_heads, hp.window,
-                       fused_split ? atts : nullptr, &att_split);
+                       fused_split ? atts : nullptr, &att_split, att_scratch);
       if (!att_split) launch_split_act(ex, sm, att, H, Rp, H, atts, H);
       {
         TcConvArgs a = split_args(t.o, atts, Rp, p_utt);
@@ -307,7 +311,8 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
     for (size_t li = 0; !front_tc && li < voice.enc.size(); ++li) {
       const EncLayerW& l = voice.enc[li];
       launch_conv_f32(ex, conv_args(l.qkv, x, H, qkv, 3 * H, Rp, p_utt));
-      launch_attention(ex, qkv, l.rel_k, l.rel_v, att, d_utt_start, d_utt_len, B, max_len, H, hp.n_heads, hp.window);
+      launch_attention(ex, qkv, l.rel_k, l.rel_v, att, d_utt_start, d_utt_len, B, max_len, H, hp.n_heads, hp.window,
+                       nullptr, nullptr, att_scratch);
       launch_conv_f32(ex, conv_args(l.o, att, H, y, H, Rp, p_utt));
       LNArgs n1;
       n1.x = x; n1.y = y; n1.gamma = l.n1.gamma; n1.beta = l.n1.beta; n1.out = x; n1.row_utt = p_utt; n1.R = Rp; n1.C = H;
