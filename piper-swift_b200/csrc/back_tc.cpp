@@ -412,6 +412,7 @@ float* run_back_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep) 
   const FlowOut f = run_flow_tc(ctx, ex, in, z_keep);
   DecoderIn d;
   d.z = f.z; d.z16 = f.z16; d.frow_utt = in.frow_utt; d.rows = in.Rf; d.batch = in.batch; d.cond_dec = in.cond_dec;
+  d.chunks = in.chunks;
   return run_decoder_tc(ctx, ex, d);
 }
 
@@ -436,7 +437,7 @@ float* run_decoder_tc(Context& ctx, Exec& ex, const DecoderIn& in) {
     throw std::runtime_error("capacity: back arena too small (decoder)");
 
   int cur = 0;
-  bool post_fused = false;
+  bool post_fused = false, chunked = false;
   {
     TcConvArgs a = tc_args(tv.dec_pre, zb, H, Rf, in.frow_utt, 1, f16);
     a.uttbias = in.cond_dec; a.ldub = v.hp.dec_c0;
@@ -543,7 +544,24 @@ float* run_decoder_tc(Context& ctx, Exec& ex, const DecoderIn& in) {
       } else if (last_stage) a.out_f32 = xs;
       else { a.out_act = xsb; a.act_slope = 0.1f; }
       a.f16 = f16;
-      launch_mrf_tc(ex, a);
+      const AudioChunks* ch = in.chunks;
+      if (post_fused && ch && ch->frame_row.size() > 2 && ch->frame_row.front() == 0 && ch->frame_row.back() == Rf) {
+        // row ranges between utterance starts: the window origin, the validity table and the output move with the range,
+        // the planar operand keeps its plane stride; rows before a range start are gap rows (zero either way)
+        chunked = true;
+        for (size_t c = 0; c + 1 < ch->frame_row.size(); ++c) {
+          const int f0 = ch->frame_row[c], f1 = ch->frame_row[c + 1];
+          if (f1 <= f0) throw std::runtime_error("decoder: audio chunk boundaries are not ascending");
+          MrfArgs b = a;
+          b.R = (f1 - f0) * U;
+          b.act_pad = act_pad + f0 * U;
+          b.row_utt = in.frow_utt + f0;
+          b.post_out = audio + (size_t)f0 * U;
+          launch_mrf_tc(ex, b);
+          if (ch->done) ch->done((int)c, audio);
+        }
+      } else
+        launch_mrf_tc(ex, a);
     } else
     for (int j = 0; j < nk; ++j) {
       const TcResBlock& rb = ts.rbs[j];
@@ -581,6 +599,8 @@ float* run_decoder_tc(Context& ctx, Exec& ex, const DecoderIn& in) {
     R = Rn;
   }
   if (!post_fused) launch_conv_post_tanh(ex, xs, v.stages.back().ch, v.post_w, v.post_k, 0.01f, in.frow_utt, U, audio, R);
+  if (in.chunks && !chunked && in.chunks->done)   // this voice's last stage is not the fused form: everything is enqueued now
+    for (size_t c = 0; c + 1 < in.chunks->frame_row.size(); ++c) in.chunks->done((int)c, audio);
   return audio;
 }
 

@@ -53,6 +53,11 @@ void Context::init(int dev) {
   CUDA_OK(cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking));
   stream = own_stream;
   for (auto& e : ev) CUDA_OK(cudaEventCreate(&e));
+  int lo = 0, hi = 0;
+  CUDA_OK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+  CUDA_OK(cudaStreamCreateWithPriority(&copy_stream, cudaStreamNonBlocking, hi));   // its small gather blocks go ahead of the next range's CTAs
+  for (auto& e : ev_chunk) CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  CUDA_OK(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
 }
 
 void Context::destroy() {
@@ -69,8 +74,13 @@ void Context::destroy() {
   h_pcm.release();
   for (auto& e : ev)
     if (e) cudaEventDestroy(e);
+  for (auto& e : ev_chunk)
+    if (e) { cudaEventDestroy(e); e = nullptr; }
+  if (ev_join) cudaEventDestroy(ev_join);
+  ev_join = nullptr;
+  if (copy_stream) cudaStreamDestroy(copy_stream);
   if (own_stream) cudaStreamDestroy(own_stream);
-  own_stream = stream = nullptr;
+  own_stream = stream = copy_stream = nullptr;
 }
 
 void Context::finalize_voice() {

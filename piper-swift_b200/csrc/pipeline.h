@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <functional>
 #include <map>
 #include <string>
 #include <vector>
@@ -107,6 +108,9 @@ struct Context {
   int device = 0;
   cudaStream_t own_stream = nullptr;
   cudaStream_t stream = nullptr;
+  cudaStream_t copy_stream = nullptr;   // audio of finished row ranges goes to the host here while the generator's last stage runs
+  cudaEvent_t ev_chunk[8] = {};
+  cudaEvent_t ev_join = nullptr;
   Voice voice;
   TcVoice tc;
   PiperConfig config;
@@ -151,7 +155,15 @@ struct Context {
 };
 
 // fp32 CUDA-core implementation of flow + HiFi-GAN on packed rows (pipeline_back_f32.cpp)
+// The last generator stage can run as several launches over row ranges that begin at utterance starts (the rows before
+// such a boundary are zero gap rows, so every valid sample is bit-identical to the single launch); after each range is
+// enqueued the caller is told, and can gather and ship that range's audio on another stream while the next one computes.
+struct AudioChunks {
+  std::vector<int> frame_row;                          // ascending, [0] = 0, back() = rows; each one an utterance's first frame row
+  std::function<void(int chunk, float* packed)> done;  // ranges 0..chunk are enqueued on ex.st; packed = [rows * hop]
+};
 struct BackInputs {
+  const AudioChunks* chunks = nullptr;
   const float* zp = nullptr;        // [Rf][H] fp32, gap rows zero
   const int* frow_utt = nullptr;    // [Rf]
   int Rf = 0, batch = 0;
@@ -168,6 +180,7 @@ struct FlowOut {
   void* z16 = nullptr;        // [Rf][H] 16-bit (tensor-core back end) or null
 };
 struct DecoderIn {
+  const AudioChunks* chunks = nullptr;
   const float* z = nullptr;   // window start
   const void* z16 = nullptr;
   const int* frow_utt = nullptr;

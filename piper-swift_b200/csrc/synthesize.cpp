@@ -441,6 +441,7 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
       CUDA_OK(cudaMemcpyAsync(dump.logw.data(), logw, dump.logw.size() * 4, cudaMemcpyDeviceToHost, stream));
       CUDA_OK(cudaMemcpyAsync(dump.zp.data(), zp, dump.zp.size() * 4, cudaMemcpyDeviceToHost, stream));
     }
+    bool audio_shipped = false;
     BackInputs bi;
     bi.zp = zp; bi.frow_utt = frow_utt; bi.Rf = Rf; bi.batch = B;
     bi.cond_flow = cond_flow; bi.cond_dec = cond_dec;
@@ -454,8 +455,52 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
       sstate.z = fo.z; sstate.z16 = fo.z16; sstate.frow_utt = frow_utt; sstate.cond_dec = cond_dec;
       sstate.arena_mark = back.off;
     } else {
-      float* packed = use_tc ? run_back_tc(*this, ex, bi, z_keep) : run_back_f32(*this, ex, bi, z_keep);
-      launch_gather_audio(ex, packed, d_fstart, d_ylen, d_soff, B, hp.hop, dense, pcm, total_samples);
+      // Host-bound audio of a large batch leaves in row ranges: while the generator's last stage works on range c+1,
+      // range c is gathered and copied to pinned memory on the copy stream.  Ranges shrink towards the end
+      // (weights K, K-1, .. 1), so that the copy left exposed after the last launch is the smallest one.
+      static const int chunks_env = [] { const char* e = getenv("PIPER_B200_D2H_CHUNKS"); return e ? atoi(e) : 3; }();
+      AudioChunks chunks;
+      std::vector<int> chunk_utt;
+      if (use_tc && !keep_dev && !keep_stages && !want_pcm && chunks_env > 1 && B >= 4 * chunks_env &&
+          total_samples >= ((int64_t)1 << 22)) {
+        const int Kc = std::min(chunks_env, 8);
+        const double wsum = 0.5 * Kc * (Kc + 1);
+        chunks.frame_row.push_back(0);
+        chunk_utt.push_back(0);
+        double acc = 0;
+        for (int c = 0, b = 0; c + 1 < Kc; ++c) {
+          acc += (Kc - c) / wsum;
+          while (b < B && (double)h_fstart[b] < acc * (double)Rf) ++b;
+          if (b >= B) break;
+          if (b > chunk_utt.back()) { chunk_utt.push_back(b); chunks.frame_row.push_back((int)h_fstart[b]); }
+        }
+        chunk_utt.push_back(B);
+        chunks.frame_row.push_back(Rf);
+      }
+      if (chunks.frame_row.size() > 2) {
+        h_audio.reserve((size_t)total_samples * 4);   // before anything is enqueued: a growing pinned buffer synchronises
+        chunks.done = [&](int c, float* packed_audio) {
+          const int b0 = chunk_utt[(size_t)c], b1 = chunk_utt[(size_t)c + 1];
+          const int64_t s0 = sample_offsets[(size_t)b0], s1 = sample_offsets[(size_t)b1];
+          CUDA_OK(cudaEventRecord(ev_chunk[c], stream));
+          CUDA_OK(cudaStreamWaitEvent(copy_stream, ev_chunk[c], 0));
+          Exec exc;
+          exc.st = copy_stream;
+          launch_gather_audio(exc, packed_audio, d_fstart + b0, d_ylen + b0, d_soff + b0, b1 - b0, hp.hop, dense, nullptr,
+                              s1 - s0);
+          ex.launches += exc.launches;
+          CUDA_OK(cudaMemcpyAsync(static_cast<float*>(h_audio.p) + s0, dense + s0, (size_t)(s1 - s0) * 4,
+                                  cudaMemcpyDeviceToHost, copy_stream));
+        };
+        bi.chunks = &chunks;
+        run_back_tc(*this, ex, bi, z_keep);
+        CUDA_OK(cudaEventRecord(ev_join, copy_stream));
+        CUDA_OK(cudaStreamWaitEvent(stream, ev_join, 0));
+        audio_shipped = true;
+      } else {
+        float* packed = use_tc ? run_back_tc(*this, ex, bi, z_keep) : run_back_f32(*this, ex, bi, z_keep);
+        launch_gather_audio(ex, packed, d_fstart, d_ylen, d_soff, B, hp.hop, dense, pcm, total_samples);
+      }
     }
     CUDA_OK(cudaEventRecord(ev[4], stream));
     if (keep_stages) {
@@ -471,8 +516,10 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
       rs.audio = dense;
       rs.pcm16 = pcm;
     } else {
-      h_audio.reserve((size_t)total_samples * 4);
-      CUDA_OK(cudaMemcpyAsync(h_audio.p, dense, (size_t)total_samples * 4, cudaMemcpyDeviceToHost, stream));
+      if (!audio_shipped) {
+        h_audio.reserve((size_t)total_samples * 4);
+        CUDA_OK(cudaMemcpyAsync(h_audio.p, dense, (size_t)total_samples * 4, cudaMemcpyDeviceToHost, stream));
+      }
       d2h += (size_t)total_samples * 4;
       rs.audio = static_cast<const float*>(h_audio.p);
       if (want_pcm) {

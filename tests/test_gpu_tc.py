@@ -110,6 +110,10 @@ def test_tc_full_size_batch_properties():
     assert snr_db(np.concatenate(ref.audio), allv) >= 58.0
     again = r.synthesize_batch(utts, *S.FIXTURE_SCALES)
     assert all(np.array_equal(x, y) for x, y in zip(out.audio, again.audio))
+    # a batch this size leaves for the host in row ranges while the last generator stage is still running; a PCM16
+    # request takes the single-launch, single-copy path: the float audio of the two must be the same bits
+    whole = r.synthesize_batch(utts, *S.FIXTURE_SCALES, pcm16=True)
+    assert all(np.array_equal(x, y) for x, y in zip(out.audio, whole.audio))
 
 
 @pytest.mark.gpu

@@ -1,7 +1,4 @@
-timeout 400 python -m pytest tests -m gpu -x -q > gpurun_out/gpu_tests_v39.log 2>&1; tail -3 gpurun_out/gpu_tests_v39.log
-timeout 60 python bench.py --voice high --batch 1 --t-lo 2000 --t-hi 2000 --no-cpu > gpurun_out/bench_v39_high.json 2>gpurun_out/bench_v39.err; tail -2 gpurun_out/bench_v39.err
-python -c "import json; d=json.loads(open('gpurun_out/bench_v39_high.json').read()); print('high', d['value'], d['ms_per_step'], d['stage_ms'])"
-PIPER_B200_ATT_SPLIT=0 timeout 60 python bench.py --voice high --batch 1 --t-lo 2000 --t-hi 2000 --no-cpu > gpurun_out/bench_v39_high_nosplit.json 2>>gpurun_out/bench_v39.err
-python -c "import json; d=json.loads(open('gpurun_out/bench_v39_high_nosplit.json').read()); print('high ATT_SPLIT=0', d['value'], d['ms_per_step'], d['stage_ms']['front_ms'])"
-timeout 200 python bench.py --no-cpu --steps 5 > gpurun_out/bench_v39.json 2>>gpurun_out/bench_v39.err
-python -c "import json; d=json.loads(open('gpurun_out/bench_v39.json').read()); print('medium', d['value'], d['ms_per_step'], d['stage_ms']['front_ms'])"
+timeout 500 python -m pytest tests -m gpu -x -q > gpurun_out/gpu_tests_v40.log 2>&1; tail -3 gpurun_out/gpu_tests_v40.log
+timeout 200 python bench.py --steps 6 > gpurun_out/bench_v40.json 2>gpurun_out/bench_v40.err
+python -c "import json; d=json.loads(open('gpurun_out/bench_v40.json').read()); print('value', d['value'], d['ms_per_step'], 'e2e', d['e2e'], d.get('gpu_launches'), d['roofline'], d['cpu_baseline'])"
+timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 1 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 1 --impl reference --steps 2 --warmup 1 > gpurun_out/bench_v40_reference.json 2>>gpurun_out/bench_v40.err; cat gpurun_out/bench_v40_reference.json | cut -c1-400
