@@ -39,6 +39,7 @@ struct TcKernelParams {
   const float* uttbias; int ldub;
   const int* row_utt; int valid_div;
   uint32_t tmem_cols;
+  int dbg;                          // timing attribution probe (PIPER_B200_TC_DBG): 1 no residual load, 2 no fp32 store, 4 no 16-bit store, 8 no staging
 };
 
 }  // namespace
@@ -95,6 +96,7 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
   tc_fence_after();
   const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
   const int chunks = p.nt / 16;
+  if (p.dbg & 8) return;
   if (p.gate) {
     const TcEpi& e0 = p.e[0];
     const TcEpi& e1 = p.e[1];
@@ -204,6 +206,22 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
       const int g = f / cpg, c = f - g * cpg;
       const TcEpi& e = p.e[g];
       const bool planar = e.out_act && e.act_planar;      // only used by plain convolutions (no residual)
+      // Lean form for whole tiles of a plain convolution (every row of the warp's 32 inside the tensor, output row =
+      // input row): no per-row predicates, strides hoisted, and the residual loads go out before the accumulator is
+      // read so that their latency hides behind the TMEM load, bias add and staging.  The general form below runs
+      // ~1100 warp instructions per 32 x 32 chunk at one issue per ~9 cycles (ncu), which made every epilogue with
+      // fp32 / 16-bit outputs cost 5-14 us per row tile regardless of K.
+      const bool fast = !p.phase_cols && p.phases == 1 && p.out_mul == 1 && !planar && act_mask == 0xffffffffu;
+      float4 rr[8];
+      const size_t fcol = (size_t)e.col0 + (size_t)(ntile * p.nt + c * 32 + c4);
+      const size_t frow = (size_t)(row_base + sub);
+      const bool fres = fast && e.res && !(p.dbg & 1);
+      if (fres) {
+        const float* rp = e.res + frow * e.ld_res + fcol;
+        const size_t sr = (size_t)4 * e.ld_res;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) rr[it] = *reinterpret_cast<const float4*>(rp + it * sr);
+      }
       {
         float v[32];
         __syncwarp();
@@ -255,18 +273,83 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
           }
         }
         if (!e.out_f32 && !e.out_split && (planar || !e.out_act)) continue;
+        if (p.dbg & 16) continue;
         __syncwarp();                                     // the previous chunk's readers are done with tbuf
 #pragma unroll
         for (int i = 0; i < 8; ++i)
           *reinterpret_cast<float4*>(tbuf + lane * 36 + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
         __syncwarp();
+        if (fast) {
+          float4 x[8];
+#pragma unroll
+          for (int it = 0; it < 8; ++it) x[it] = *reinterpret_cast<const float4*>(tbuf + (it * 4 + sub) * 36 + c4);
+          if (fres) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) { x[it].x += rr[it].x; x[it].y += rr[it].y; x[it].z += rr[it].z; x[it].w += rr[it].w; }
+          }
+          float* of = e.out_f32 ? e.out_f32 + frow * e.ld_f32 + fcol : nullptr;
+          const size_t sf = (size_t)4 * e.ld_f32;
+          if (e.accum) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) rr[it] = *reinterpret_cast<const float4*>(of + it * sf);
+#pragma unroll
+            for (int it = 0; it < 8; ++it) { x[it].x += rr[it].x; x[it].y += rr[it].y; x[it].z += rr[it].z; x[it].w += rr[it].w; }
+          }
+          if (e.div != 0.f) {
+            const float d = e.div;
+#pragma unroll
+            for (int it = 0; it < 8; ++it) { x[it].x = x[it].x / d; x[it].y = x[it].y / d; x[it].z = x[it].z / d; x[it].w = x[it].w / d; }
+          }
+          if (valid_mask != 0xffffffffu) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it)
+              if (!((valid_mask >> (it * 4 + sub)) & 1u)) x[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+          if (of && !(p.dbg & 2)) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) *reinterpret_cast<float4*>(of + it * sf) = x[it];
+          }
+          if (e.out_split) {
+            uint16_t* sp = static_cast<uint16_t*>(e.out_split) + frow * e.ld_split + fcol;
+            const size_t ss = (size_t)4 * e.ld_split;
+            const size_t sc = (size_t)e.split_c;
+            if (p.split2) {
+#pragma unroll
+              for (int it = 0; it < 8; ++it) {
+                uint2 t0, t1;
+                split2x4(x[it], t0, t1);
+                *reinterpret_cast<uint2*>(sp + it * ss) = t0;
+                *reinterpret_cast<uint2*>(sp + it * ss + sc) = t1;
+              }
+            } else {
+#pragma unroll
+              for (int it = 0; it < 8; ++it) {
+                uint2 t0, t1, t2;
+                split3x4(x[it], t0, t1, t2);
+                *reinterpret_cast<uint2*>(sp + it * ss) = t0;
+                *reinterpret_cast<uint2*>(sp + it * ss + sc) = t1;
+                *reinterpret_cast<uint2*>(sp + it * ss + 2 * sc) = t2;
+              }
+            }
+          }
+          if (e.out_act && !(p.dbg & 4)) {
+            uint16_t* oa = static_cast<uint16_t*>(e.out_act) + frow * e.ld_act + fcol;
+            const size_t sa = (size_t)4 * e.ld_act;
+            const float sl = e.act_slope;
+#pragma unroll
+            for (int it = 0; it < 8; ++it)
+              *reinterpret_cast<uint2*>(oa + it * sa) = make_uint2(pack2(lrelu(x[it].x, sl), lrelu(x[it].y, sl), p.f16),
+                                                                   pack2(lrelu(x[it].z, sl), lrelu(x[it].w, sl), p.f16));
+          }
+          continue;
+        }
         // all global loads of the chunk are issued before the first use (8-16 independent 16-byte loads per
         // lane in flight): with only eight epilogue warps per SM the epilogue is latency-, not bandwidth-bound
-        float4 rr[8], aa[8];
+        float4 aa[8];
         const size_t orow0 = (size_t)(row_base + sub) * p.out_mul + ph_c;
         const size_t rstep = (size_t)4 * p.out_mul;
         float* of = e.out_f32 ? e.out_f32 + orow0 * e.ld_f32 + ocol + c4 : nullptr;
-        if (e.res) {
+        if (e.res && !(p.dbg & 1)) {
           const float* rp = e.res + orow0 * e.ld_res + ocol + c4;
 #pragma unroll
           for (int it = 0; it < 8; ++it)
@@ -282,11 +365,11 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
           const int row = it * 4 + sub;
           if (!((act_mask >> row) & 1u)) continue;
           float4 x = *reinterpret_cast<const float4*>(tbuf + row * 36 + c4);
-          if (e.res) { x.x += rr[it].x; x.y += rr[it].y; x.z += rr[it].z; x.w += rr[it].w; }
+          if (e.res && !(p.dbg & 1)) { x.x += rr[it].x; x.y += rr[it].y; x.z += rr[it].z; x.w += rr[it].w; }
           if (e.accum) { x.x += aa[it].x; x.y += aa[it].y; x.z += aa[it].z; x.w += aa[it].w; }
           if (e.div != 0.f) { x.x = x.x / e.div; x.y = x.y / e.div; x.z = x.z / e.div; x.w = x.w / e.div; }
           if (!((valid_mask >> row) & 1u)) x = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (of) *reinterpret_cast<float4*>(of + it * rstep * e.ld_f32) = x;
+          if (of && !(p.dbg & 2)) *reinterpret_cast<float4*>(of + it * rstep * e.ld_f32) = x;
           if (e.out_split) {
             uint16_t* sp = static_cast<uint16_t*>(e.out_split) + (orow0 + it * rstep) * e.ld_split + ocol + c4;
             uint2 t0, t1, t2;
@@ -301,7 +384,7 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
               *reinterpret_cast<uint2*>(sp + 2 * e.split_c) = t2;
             }
           }
-          if (e.out_act && !planar) {
+          if (e.out_act && !planar && !(p.dbg & 4)) {
             const uint32_t lo = pack2(lrelu(x.x, e.act_slope), lrelu(x.y, e.act_slope), p.f16);
             const uint32_t hi = pack2(lrelu(x.z, e.act_slope), lrelu(x.w, e.act_slope), p.f16);
             *reinterpret_cast<uint2*>(static_cast<uint16_t*>(e.out_act) + (orow0 + it * rstep) * e.ld_act + ocol + c4) =
@@ -687,6 +770,8 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
   if (a.nt % 16 || a.nt < 16 || a.nt > 256 || a.n_groups < 1 || a.n_groups > 2 || a.n_groups * a.nt > 512)
     throw std::runtime_error("conv_tc: bad column tiling");
   TcKernelParams p{};
+  static const int dbg_env = [] { const char* e = getenv("PIPER_B200_TC_DBG"); return e ? atoi(e) : 0; }();
+  p.dbg = dbg_env;
   p.Q = a.Q; p.taps = w.taps; p.tap_step = a.tap_step; p.in_off = a.in_off;
   p.kb = w.kb; p.kblocks = w.cin_pad / w.kb;
   const int kmul = w.split == 2 ? 2 : (w.split ? 6 : 1), amul = w.split == 2 ? 2 : (w.split ? 3 : 1);

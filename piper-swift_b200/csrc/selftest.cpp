@@ -250,13 +250,26 @@ int Context::selftest_conv(int mode, int cin, int cout, int k, int dil, int stri
       a.e[0].res = dres.as<float>(); a.e[0].ld_res = cout;
       a.e[0].out_act = dact.p; a.e[0].ld_act = cout;
     }
+    // timing probes: PIPER_B200_SELFTEST_NT overrides the column tile, PIPER_B200_SELFTEST_REPEAT launches the (idempotent)
+    // kernel n times and reports the mean
+    if (const char* e = getenv("PIPER_B200_SELFTEST_NT")) {
+      const int nt = atoi(e), width = mode == 0 || mode == 3 ? cout : H;
+      if (nt >= 16 && width % nt == 0) { a.nt = nt; a.n_tiles = width / nt; }
+    }
+    int repeat = 1;
+    if (const char* e = getenv("PIPER_B200_SELFTEST_REPEAT")) repeat = std::max(1, atoi(e));
     launch_conv_tc(ex, a);
+    if (repeat > 1) {
+      CUDA_OK(cudaEventRecord(e1, stream));
+      for (int i = 0; i < repeat; ++i) launch_conv_tc(ex, a);
+    }
     CUDA_OK(cudaEventRecord(e2, stream));
     CUDA_OK(cudaStreamSynchronize(stream));
     CUDA_OK(cudaGetLastError());
     float ms_ref = 0, ms_tc = 0;
     cudaEventElapsedTime(&ms_ref, e0, e1);
     cudaEventElapsedTime(&ms_tc, e1, e2);
+    ms_tc /= (float)repeat;
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
 
     // ---- compare ----------------------------------------------------------------------------------
