@@ -64,7 +64,9 @@ template <int C, int MRF_EG, bool UNIT = false>   // channels, epilogue warpgrou
 __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __grid_constant__ CUtensorMap tmap_w,
                                                                 const MrfParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // 1 KB alignment by pointer arithmetic on the shared array: an integer round-trip hides the address space from the
+  // compiler, which then emits generic LD / ST for every shared-memory access of the epilogues
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int m = p.m;
   // operand windows are group-planar without swizzle: [C/8 groups][(m+1)*128 rows][16 bytes]; a tap shift is
   // a 16-byte-granular descriptor offset (row-shifted descriptors into SWIZZLED tiles are ~100x slower

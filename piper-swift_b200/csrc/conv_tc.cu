@@ -26,6 +26,8 @@ using namespace tc;
 
 namespace {
 
+constexpr int TC_SBIAS = 1024;   // floats of bias staged in shared memory per column group (persistent kernel)
+
 struct TcKernelParams {
   int Q, taps, tap_step, in_off, kblocks, kb;
   int nt, n_groups, cout_rows;      // cout_rows = weight rows per (phase, tap)
@@ -79,12 +81,33 @@ __device__ __forceinline__ void split2x4(const float4& x, uint2& t0, uint2& t1) 
   t1 = make_uint2((uint32_t)b[0] | ((uint32_t)b[1] << 16), (uint32_t)b[2] | ((uint32_t)b[3] << 16));
 }
 
+// Explicit shared-space accesses for the epilogue's staging buffers: the dynamic shared-memory base is rounded up
+// through an integer cast, after which the compiler no longer knows the address space and emits generic LD / ST
+// (long-scoreboard latency on every staging access).
+__device__ __forceinline__ float4 lds128(uint32_t a) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t a, const float4& v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 lds128u(uint32_t a) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts128u(uint32_t a, const uint4& v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
 // Epilogue of one 128-row x (n_groups * nt) accumulator tile, run by the four warps of a warpgroup (TMEM lane
 // quarter = warp % 4): waits for `bar`, then bias / utterance bias / residual / accumulate / mask and the
 // fp32 and 16-bit stores, or the tanh * sigmoid gate.
 __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tmem_base, int m0, int ntile, int phase,
                                           int warp, int lane, uint64_t* bar, uint32_t bar_parity, float* tbuf,
-                                            int part, int nparts) {   // this warpgroup's share of the column chunks
+                                            int part, int nparts,     // this warpgroup's share of the column chunks
+                                            const float* sbias = nullptr) {   // bias staged in shared memory: [2][TC_SBIAS]
   const int quarter = warp & 3;
   const int q = m0 + quarter * 32 + lane;
   const bool active = q < p.Q;
@@ -96,6 +119,7 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
   tc_fence_after();
   const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
   const int chunks = p.nt / 16;
+  const uint32_t tbs = tbuf ? smem_u32(tbuf) : 0u, sbs = sbias ? smem_u32(sbias) : 0u;
   if (p.dbg & 8) return;
   if (p.gate) {
     const TcEpi& e0 = p.e[0];
@@ -111,7 +135,14 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
       // bias and per-utterance conditioning come in as 16-byte vectors; the gate uses the hardware tanh
       // (tanh.approx, rel. error ~2^-11 - the result is rounded to 16 bits right after):
       // tanh(a) * sigmoid(b) = tanh(a) * (0.5 + 0.5 tanh(b / 2))
-      if (e0.bias) {
+      if (e0.bias && sbias) {   // broadcast reads of the staged copy: the global form waited ~25 % of the epilogue on L1 misses
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 x = lds128(sbs + (uint32_t)(j + 4 * i) * 4u), y = lds128(sbs + (uint32_t)(TC_SBIAS + j + 4 * i) * 4u);
+          va[4 * i] += x.x; va[4 * i + 1] += x.y; va[4 * i + 2] += x.z; va[4 * i + 3] += x.w;
+          vb[4 * i] += y.x; vb[4 * i + 1] += y.y; vb[4 * i + 2] += y.z; vb[4 * i + 3] += y.w;
+        }
+      } else if (e0.bias) {
         const float4* b0 = reinterpret_cast<const float4*>(e0.bias + j);
         const float4* b1 = reinterpret_cast<const float4*>(e1.bias + j);
 #pragma unroll
@@ -163,14 +194,19 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
       // assembled in the warp's buffer as [plane][q][phase] and written with every lane storing an adjacent
       // 16-byte piece (512 contiguous bytes per instruction); the lane = row form touched 32 lines per store.
       const int Cp = p.phase_cols, ppt = p.nt / Cp, ph0 = ntile * ppt;
-      uint4* tb = reinterpret_cast<uint4*>(tbuf);
       const int pieces = 32 * ppt;                       // per plane
       for (int pp = 0; pp < Cp / 16; ++pp) {
         __syncwarp();
         for (int k = 0; k < ppt; ++k) {
           float v[16];
           tmem_ld16(lane_base + (uint32_t)(k * Cp + pp * 16), v);
-          if (em.bias) {
+          if (em.bias && sbias) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const float4 x = lds128(sbs + (uint32_t)(pp * 16 + 4 * i) * 4u);
+              v[4 * i] += x.x; v[4 * i + 1] += x.y; v[4 * i + 2] += x.z; v[4 * i + 3] += x.w;
+            }
+          } else if (em.bias) {
             const float4* b4 = reinterpret_cast<const float4*>(em.bias + pp * 16);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
@@ -183,8 +219,8 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
           for (int i = 0; i < 8; ++i)
             pk[i] = valid ? pack2(lrelu(v[2 * i], em.act_slope), lrelu(v[2 * i + 1], em.act_slope), p.f16) : 0u;
           const int slot = k ^ (lane & (ppt - 1));       // spreads the lanes' 16-byte stores over the banks
-          tb[lane * ppt + slot] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-          tb[pieces + lane * ppt + slot] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+          sts128u(tbs + (uint32_t)(lane * ppt + slot) * 16u, make_uint4(pk[0], pk[1], pk[2], pk[3]));
+          sts128u(tbs + (uint32_t)(pieces + lane * ppt + slot) * 16u, make_uint4(pk[4], pk[5], pk[6], pk[7]));
         }
         __syncwarp();
         for (int pl = 0; pl < 2; ++pl) {
@@ -195,15 +231,17 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
             if (!((act_mask >> qq) & 1u)) continue;
             const int k = sl ^ (qq & (ppt - 1));
             const size_t orow_r = (size_t)(row_base + qq) * p.out_mul + ph0 + k;
-            *reinterpret_cast<uint4*>(plane + orow_r * 8) = tb[pl * pieces + i];
+            *reinterpret_cast<uint4*>(plane + orow_r * 8) = lds128u(tbs + (uint32_t)(pl * pieces + i) * 16u);
           }
         }
       }
       return;
     }
     const int cpg = p.nt / 32, nunits = (p.split2 ? 1 : p.n_groups) * cpg;
-    for (int f = part * nunits / nparts; f < (part + 1) * nunits / nparts; ++f) {
-      const int g = f / cpg, c = f - g * cpg;
+    const int f_begin = part * nunits / nparts, f_end = (part + 1) * nunits / nparts;
+    int g = f_begin / cpg, c = f_begin - g * cpg - 1;
+    for (int f = f_begin; f < f_end; ++f) {
+      if (++c == cpg) { c = 0; ++g; }
       const TcEpi& e = p.e[g];
       const bool planar = e.out_act && e.act_planar;      // only used by plain convolutions (no residual)
       // Lean form for whole tiles of a plain convolution (every row of the warp's 32 inside the tensor, output row =
@@ -241,7 +279,13 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
         }
         const size_t ocol = (size_t)e.col0 + j;
         const int orow_c = active ? q * p.out_mul + ph_c : 0;
-        if (e.bias) {
+        if (e.bias && sbias) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 x = lds128(sbs + (uint32_t)(g * TC_SBIAS + j + 4 * i) * 4u);
+            v[4 * i] += x.x; v[4 * i + 1] += x.y; v[4 * i + 2] += x.z; v[4 * i + 3] += x.w;
+          }
+        } else if (e.bias) {
           const float4* b4 = reinterpret_cast<const float4*>(e.bias + j);
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
@@ -277,12 +321,12 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
         __syncwarp();                                     // the previous chunk's readers are done with tbuf
 #pragma unroll
         for (int i = 0; i < 8; ++i)
-          *reinterpret_cast<float4*>(tbuf + lane * 36 + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+          sts128(tbs + (uint32_t)(lane * 36 + 4 * i) * 4u, make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]));
         __syncwarp();
         if (fast) {
           float4 x[8];
 #pragma unroll
-          for (int it = 0; it < 8; ++it) x[it] = *reinterpret_cast<const float4*>(tbuf + (it * 4 + sub) * 36 + c4);
+          for (int it = 0; it < 8; ++it) x[it] = lds128(tbs + (uint32_t)((it * 4 + sub) * 36 + c4) * 4u);
           if (fres) {
 #pragma unroll
             for (int it = 0; it < 8; ++it) { x[it].x += rr[it].x; x[it].y += rr[it].y; x[it].z += rr[it].z; x[it].w += rr[it].w; }
@@ -364,7 +408,7 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
         for (int it = 0; it < 8; ++it) {
           const int row = it * 4 + sub;
           if (!((act_mask >> row) & 1u)) continue;
-          float4 x = *reinterpret_cast<const float4*>(tbuf + row * 36 + c4);
+          float4 x = lds128(tbs + (uint32_t)(row * 36 + c4) * 4u);
           if (e.res && !(p.dbg & 1)) { x.x += rr[it].x; x.y += rr[it].y; x.z += rr[it].z; x.w += rr[it].w; }
           if (e.accum) { x.x += aa[it].x; x.y += aa[it].y; x.z += aa[it].z; x.w += aa[it].w; }
           if (e.div != 0.f) { x.x = x.x / e.div; x.y = x.y / e.div; x.z = x.z / e.div; x.w = x.w / e.div; }
@@ -638,6 +682,13 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
   uint64_t* acc_empty = acc_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
   float* tbuf_base = reinterpret_cast<float*>(smem + (size_t)stages * stage_bytes + 512);   // one 32 x 36 float tile per epilogue warp
+  float* sbias = tbuf_base + 2 * TCP_EG * 4 * 32 * 36;                                      // [2][TC_SBIAS] bias of both column groups
+  const int bias_w = p.phase_cols ? p.phase_cols : n_tiles * p.nt;
+  const bool bias_staged = bias_w <= TC_SBIAS;
+  if (bias_staged)
+    for (int g = 0; g < 2 && g < p.n_groups; ++g)
+      if (p.e[g].bias)
+        for (int i = threadIdx.x; i < bias_w; i += TCP_THREADS) sbias[g * TC_SBIAS + i] = p.e[g].bias[i];
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
@@ -742,7 +793,7 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
       const int phase = t % p.phases, rest = t / p.phases;
       const int mt = rest % m_tiles, ntile = rest / m_tiles;
       tc_epilogue(p, tmem_base + group * acc_stride, mt * TC_BM, ntile, phase, warp, lane, &acc_full[group], (li >> 1) & 1u,
-                  tbuf_base + (warp - 2) * (32 * 36), (int)half, TCP_EG);
+                  tbuf_base + (warp - 2) * (32 * 36), (int)half, TCP_EG, bias_staged ? sbias : nullptr);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[group]);
@@ -838,13 +889,14 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
     p.tmem_cols = pc;
     const int sb = TC_BM * w.kb * 2 + n_groups * a.nt * w.kb * 2;
     constexpr int TBUF_BYTES = 2 * TCP_EG * 4 * 32 * 36 * 4;
-    int st = (TC_SMEM_MAX - 2048 - TBUF_BYTES) / sb;
+    constexpr int SBIAS_BYTES = 2 * TC_SBIAS * 4;
+    int st = (TC_SMEM_MAX - 2048 - TBUF_BYTES - SBIAS_BYTES) / sb;
     if (st > TCP_MAX_STAGES) st = TCP_MAX_STAGES;
     if (st < 2) throw std::runtime_error("conv_tc: tile does not fit in shared memory");
     const int m_tiles = (a.Q + TC_BM - 1) / TC_BM;
     const int total = m_tiles * a.n_tiles * w.phases;
     const int grid = total < num_sms ? total : num_sms;
-    const size_t smem = (size_t)st * sb + 1024 + 512 + TBUF_BYTES;
+    const size_t smem = (size_t)st * sb + 1024 + 512 + TBUF_BYTES + SBIAS_BYTES;
     double flops = 2.0 * a.Q * w.phases * w.taps * w.cin * (double)(a.n_groups * a.nt * a.n_tiles);
     if (w.phase_cols) {   // algorithmic work only: the zero blocks of the merged weights do not count
       int used = 0;
