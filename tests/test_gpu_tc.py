@@ -116,6 +116,23 @@ def test_tc_full_size_batch_properties():
     assert all(np.array_equal(x, y) for x, y in zip(out.audio, whole.audio))
 
 
+def test_tc_ragged_batch_leaves_in_row_ranges():
+    """Host-bound audio of a ragged batch (lengths 20..400 ids, multi-speaker voice) goes out in row ranges under the
+    last generator stage; the PCM16 request keeps the single launch + single copy: same float bits, same durations,
+    and PCM16 follows the WavFileWriter rule on those floats."""
+    utts = synthetic_utterances(48, 256, 20, 400, seed=5)
+    sids = [b % 4 for b in range(len(utts))]
+    r = rt("medium-multispeaker", "f16")
+    ranged = r.synthesize_batch(utts, *S.FIXTURE_SCALES, speaker_ids=sids)
+    whole = r.synthesize_batch(utts, *S.FIXTURE_SCALES, speaker_ids=sids, pcm16=True)
+    assert sum(len(a) for a in ranged.audio) >= 1 << 22           # large enough for the ranged path
+    assert np.array_equal(ranged.frame_lengths, whole.frame_lengths)
+    for a, b, d0, d1, pc in zip(ranged.audio, whole.audio, ranged.durations, whole.durations, whole.pcm16):
+        assert np.array_equal(d0, d1)
+        assert np.array_equal(a, b)
+        assert np.array_equal(pc, (np.clip(b, -1.0, 1.0) * np.float32(32767.0)).astype(np.int32).astype(np.int16))
+
+
 @pytest.mark.gpu
 @pytest.mark.timeout(120)
 @pytest.mark.parametrize("prec,min_snr", [("f16", 58.0), ("bf16", 40.0)])
