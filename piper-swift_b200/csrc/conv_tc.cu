@@ -184,7 +184,6 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
     // fp32 / 16-bit stores run with 8 lanes per row: every warp instruction touches 4 full 128-byte lines
     // instead of 32 lines (the lane = row form made the L1 tag stage the limit of every epilogue).
     const uint32_t act_mask = __ballot_sync(0xffffffffu, active);
-    const uint32_t valid_mask = __ballot_sync(0xffffffffu, valid);
     const int sub = lane >> 3, c4 = (lane & 7) * 4;
     const int row_base = m0 + quarter * 32;
     const TcEpi& em = p.e[0];
@@ -328,6 +327,9 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
         for (int i = 0; i < 8; ++i)
           sts128(tbs + (uint32_t)(lane * 36 + 4 * i) * 4u, make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]));
         __syncwarp();
+        // the row-validity vote waits for the row -> utterance load of this tile: taken here, after the first chunk's
+        // accumulator read and staging, not at the top of the tile where nothing could overlap that latency
+        const uint32_t valid_mask = __ballot_sync(0xffffffffu, valid);
         if (fast) {
           float4 x[8];
 #pragma unroll
