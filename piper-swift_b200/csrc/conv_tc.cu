@@ -41,6 +41,7 @@ struct TcKernelParams {
   const float* uttbias; int ldub;
   const int* row_utt; int valid_div;
   uint32_t tmem_cols;
+  int nbuf;                         // accumulator buffers in TMEM (persistent kernel): 2, or 4 when 4 tiles fit in 512 columns
   int dbg;                          // timing attribution probe (PIPER_B200_TC_DBG): 1 no residual load, 2 no fp32 store, 4 no 16-bit store, 8 no staging
 };
 
@@ -686,8 +687,8 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)stages * stage_bytes);
   uint64_t* empty = full + TCP_MAX_STAGES;
   uint64_t* acc_full = empty + TCP_MAX_STAGES;
-  uint64_t* acc_empty = acc_full + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  uint64_t* acc_empty = acc_full + 4;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 4);
   float* tbuf_base = reinterpret_cast<float*>(smem + (size_t)stages * stage_bytes + 512);   // one 32 x 36 float tile per epilogue warp
   float* sbias = tbuf_base + 2 * TCP_EG * 4 * 32 * 36;                                      // [2][TC_SBIAS] bias of both column groups
   const int bias_w = p.phase_cols ? p.phase_cols : n_tiles * p.nt;
@@ -705,7 +706,7 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
     }
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < 4; ++s) {
       mbar_init(&acc_full[s], 1);
       mbar_init(&acc_empty[s], 4 * TCP_EG);   // every warp of the warpgroups draining this buffer
     }
@@ -768,11 +769,15 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
     const uint32_t stage_lo = smem_u32(smem) >> 4;
     const uint32_t stage16 = (uint32_t)stage_bytes >> 4, a16 = (uint32_t)a_bytes >> 4, b16 = (uint32_t)b_bytes >> 4;
     int s = 0; uint32_t ph = 0, li = 0;
+    const uint32_t nbuf = (uint32_t)p.nbuf;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++li) {
       const int ntile_m = (t / p.phases) / m_tiles;
       const int n_it = __popc(p.tap_mask[ntile_m & 7]) * p.kblocks;
-      const uint32_t buf = li & 1u;
-      mbar_wait(&acc_empty[buf], ((li >> 1) & 1u) ^ 1u);     // the epilogue drained this accumulator buffer
+      // With four buffers each epilogue warpgroup owns two: the MMAs of its next tile run while it still drains the
+      // current one (with two, a group's MMA -> epilogue chain was serial, which small-K tiles cannot hide).
+      const uint32_t buf = nbuf == 4 ? (li & 3u) : (li & 1u);
+      const uint32_t use = nbuf == 4 ? (li >> 2) : (li >> 1);
+      mbar_wait(&acc_empty[buf], (use & 1u) ^ 1u);           // the epilogue drained this accumulator buffer
       tc_fence_after();
       const uint32_t acc = tmem_base + buf * acc_stride;
       for (int i = 0; i < n_it; ++i) {
@@ -799,11 +804,13 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
       if ((li & 1u) != group) continue;
       const int phase = t % p.phases, rest = t / p.phases;
       const int mt = rest % m_tiles, ntile = rest / m_tiles;
-      tc_epilogue(p, tmem_base + group * acc_stride, mt * TC_BM, ntile, phase, warp, lane, &acc_full[group], (li >> 1) & 1u,
+      const uint32_t buf = p.nbuf == 4 ? (li & 3u) : group;
+      const uint32_t use = p.nbuf == 4 ? (li >> 2) : (li >> 1);
+      tc_epilogue(p, tmem_base + buf * acc_stride, mt * TC_BM, ntile, phase, warp, lane, &acc_full[buf], use & 1u,
                   tbuf_base + (warp - 2) * (32 * 36), (int)half, TCP_EG, bias_staged ? sbias : nullptr);
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&acc_empty[group]);
+      if (lane == 0) mbar_arrive(&acc_empty[buf]);
     }
   }
   tc_fence_before();
@@ -891,8 +898,10 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
     const CUtensorMap tbp = make_map(w.w, (uint64_t)w.cin_pad * kmul, (uint64_t)w.phases * w.taps * w.cout,
                                      (uint64_t)w.cin_pad * kmul, w.kb, a.nt, a.f16);
     p.window = 0;
+    static const int nbuf_env = [] { const char* e = getenv("PIPER_B200_TC_NBUF"); return e ? atoi(e) : 4; }();
+    p.nbuf = (nbuf_env == 4 && 4 * n_groups * a.nt <= 512) ? 4 : 2;
     uint32_t pc = 32;
-    while ((int)pc < 2 * n_groups * a.nt) pc <<= 1;
+    while ((int)pc < p.nbuf * n_groups * a.nt) pc <<= 1;
     p.tmem_cols = pc;
     const int sb = TC_BM * w.kb * 2 + n_groups * a.nt * w.kb * 2;
     constexpr int TBUF_BYTES = 2 * TCP_EG * 4 * 32 * 36 * 4;
