@@ -43,6 +43,7 @@ struct MrfParams {
   const float* b2[MRF_MAX_RB];
   const uint16_t* x_act; int64_t act_rows; int act_pad;   // group-planar 16-bit lrelu(x): [C/8][act_rows][8]
   const int* row_utt; int valid_div;
+  int valid_shift;   // log2(valid_div) when it is a power of two (every stock voice), else -1: a shift instead of a ~20-instruction division per row lookup
   void* out_act; float act_slope;
   float* out_f32;
   const float* post_w; int post_k; float post_slope; float* post_out;   // fused conv_post + tanh (C = 32 only)
@@ -414,7 +415,7 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
           const uint32_t row_off = (uint32_t)((p.G + row_in_win) * 16);
           const uint32_t row_off_x = (uint32_t)((p.GX + row_in_win) * 16);
           int ru = 0;
-          if (inr && p.row_utt) ru = p.row_utt[grow / p.valid_div];
+          if (inr && p.row_utt) ru = p.row_utt[p.valid_shift >= 0 ? (grow >> p.valid_shift) : (grow / p.valid_div)];
           TRACE(10u, n, (uint32_t)u);
           if (n > 0) {   // conv2 of the previous pair must have finished with S_i and with Y1 rows of tiles i-1..i+1
             for (int ii = (i > 0 ? i - 1 : 0); ii <= (i + 1 < m ? i + 1 : m - 1); ++ii)
@@ -520,7 +521,7 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
             const int grow = w0 + row_in_win;
             const bool inr = grow >= 0 && grow < p.R;
             int ru = 0;
-            if (inr && p.row_utt) ru = p.row_utt[grow / p.valid_div];
+            if (inr && p.row_utt) ru = p.row_utt[p.valid_shift >= 0 ? (grow >> p.valid_shift) : (grow / p.valid_div)];
             TRACE(14u, nl, (uint32_t)i);
             mbar_wait(&s_full[i], nl & 1u);
             tc_fence_after();
@@ -595,7 +596,7 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
         const int grow = w0 + row_in_win;
         const bool owned = row_in_win >= p.halo && row_in_win < p.halo + p.V && grow >= 0 && grow < p.R;
         int ru = 0;
-        if (owned && p.row_utt) ru = p.row_utt[grow / p.valid_div];
+        if (owned && p.row_utt) ru = p.row_utt[p.valid_shift >= 0 ? (grow >> p.valid_shift) : (grow / p.valid_div)];
         TRACE(14u, nl, (uint32_t)u);
         mbar_wait(&s_full[i], nl & 1u);
         tc_fence_after();
@@ -782,6 +783,8 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   p.mma_split = (split_env && !p.tap_outer) ? 1 : 0;
   p.x_act = static_cast<const uint16_t*>(a.x_act); p.act_rows = a.act_rows; p.act_pad = a.act_pad;
   p.row_utt = a.row_utt; p.valid_div = a.valid_div < 1 ? 1 : a.valid_div;
+  p.valid_shift = -1;
+  if ((p.valid_div & (p.valid_div - 1)) == 0) { p.valid_shift = 0; while ((1 << p.valid_shift) < p.valid_div) ++p.valid_shift; }
   p.out_act = a.out_act; p.act_slope = a.act_slope; p.out_f32 = a.out_f32;
   if (a.unit_mode && a.nk != 1) throw std::runtime_error("conv_mrf: a ResBlock1 unit is one convolution pair");
   if (!a.unit_mode && (a.accum || a.out_div != 0.f || a.out_planar))
