@@ -1,3 +1,9 @@
 cd /root/repo
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 4 --master-addr 127.0.0.1 --master-port 29544 bench.py --gpus 4 --steps 10 --warmup 3 > gpurun_out/bench_v53_n4.json 2> gpurun_out/bench_v53_n4.err; cut -c1-260 gpurun_out/bench_v53_n4.json; grep -c . gpurun_out/bench_v53_n4.json
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 4 --master-addr 127.0.0.1 --master-port 29545 bench.py --gpus 4 --impl reference --steps 1 --warmup 1 > gpurun_out/bench_v53_n4_reference.json 2>> gpurun_out/bench_v53_n4.err; cut -c1-200 gpurun_out/bench_v53_n4_reference.json; grep -c . gpurun_out/bench_v53_n4_reference.json
+run() { env "$@" timeout 100 python bench.py --no-cpu --steps 5 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('$*', round(d['ms_per_step'],3), round(d['roofline']['by_class']['mrf_tc_kernel']['ms_per_step'],3))"; }
+run X=0
+run PIPER_B200_MRF_EG=3
+run PIPER_B200_MRF_EG=5
+for m in 2 3 4 5 6 7 8; do run PIPER_B200_MRF_M=$m; done
+for m in 2 3 4; do run PIPER_B200_MRF_M64=$m; done
+run PIPER_B200_MRF_SPLIT=0
+run X=0
