@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define PIPER_B200_ABI_VERSION 1
+#define PIPER_B200_ABI_VERSION 2
 
 /* status codes */
 #define PIPER_B200_OK 0
@@ -60,6 +60,8 @@ extern "C" {
                                             * without audio; the waveform is then decoded chunk by chunk with
                                             * piper_b200_stream_next (the incremental decode synthesizeStream intends,
                                             * PiperMetalRuntime.swift:82-121) */
+#define PIPER_B200_FLAG_PCM16_ONLY 64u      /* int16 PCM is the ONLY host output (WavFileWriter.swift:20-30 rule): result.audio is NULL,
+                                            * half the device->host bytes; a caller-owned output buffer then receives int16 */
 #define PIPER_B200_FLAG_PROFILE 16u        /* CUDA events around every GEMM-class kernel launch (PIPER_PROFILE, GraphExecutor.swift:163-175) */
 
 typedef struct piper_b200_ctx piper_b200_ctx;
@@ -157,6 +159,20 @@ int piper_b200_finalize(piper_b200_ctx* ctx);   /* recognise the VITS graph, rep
 int piper_b200_get_voice_info(const piper_b200_ctx* ctx, piper_b200_voice_info* out);
 int piper_b200_set_precision(piper_b200_ctx* ctx, int32_t precision);
 int piper_b200_set_stream(piper_b200_ctx* ctx, void* cuda_stream);   /* NULL -> the context's own stream */
+
+/* Caller-owned host output (the reference returns a fresh [Float] the caller owns, PiperMetalRuntime.swift:73-79;
+ * SURVEY 8b "written into a caller-provided buffer", 8e "shared pinned host arena"): the next synthesize calls write
+ * the concatenated float32 audio (int16 with PIPER_B200_FLAG_PCM16_ONLY) to `host` instead of the library's own pinned
+ * buffer and result.audio / result.pcm16 point into it.  The memory must be page-locked for the copies to be
+ * asynchronous: allocate it with piper_b200_host_alloc or pin an existing mapping (e.g. a /dev/shm arena shared by the
+ * ranks of one box) with piper_b200_host_register.  A result larger than `capacity_bytes` fails with
+ * PIPER_B200_ERR_CAPACITY (the message states the bytes needed) before any audio is written.  host == NULL restores
+ * the library-owned buffer.  Several contexts (one per GPU) may write disjoint ranges of one arena concurrently. */
+int piper_b200_set_output_buffer(piper_b200_ctx* ctx, void* host, size_t capacity_bytes);
+int piper_b200_host_alloc(size_t bytes, void** out);       /* page-locked, portable across the GPUs of the process */
+void piper_b200_host_free(void* p);
+int piper_b200_host_register(void* p, size_t bytes);       /* page-lock caller memory (cudaHostRegisterPortable) */
+int piper_b200_host_unregister(void* p);
 
 /* GraphExecutor.executeOutput (GraphExecutor.swift:156) for a ragged batch. */
 int piper_b200_synthesize(piper_b200_ctx* ctx, const piper_b200_request* req, piper_b200_result* res);

@@ -70,11 +70,82 @@ class VoiceParams:
         return h
 
 
+def canonicalize(inits: Dict[str, np.ndarray], nodes) -> Dict[str, np.ndarray]:
+    """Real Piper exports do not name every weight after its module: piper_train removes weight-norm from
+    `dec` only, and ONNX constant folding turns the flow's weight_g / weight_v pairs into initializers called
+    `onnx::Conv_NNNN`; `exp(-logs)` of the duration predictor's ElementwiseAffine is folded the same way
+    (`-logs` survives as `onnx::Exp_NNNN` or the whole factor as an anonymous Mul operand).  The reference never
+    needs names - it walks the nodes (GraphExecutor.swift:227-264) - so this restates what the graph says:
+    every Conv / ConvTranspose node's weight input is the `<module>.weight` of the module named by its bias
+    input (`<module>.bias`) or by its node name (`/flow/flows.0/enc/in_layers.0/Conv`).  Returns a copy of
+    `inits` with the canonical names added (and `dp.flows.0.inv_scale` when only the folded factor exists)."""
+    out = dict(inits)
+    for name in list(inits):          # unfolded weight-norm pairs: w = g * v / ||v|| over all axes but the first
+        if name.endswith(".weight_v"):
+            base = name[:-len(".weight_v")]
+            if base + ".weight" in out or base + ".weight_g" not in inits:
+                continue
+            v = np.asarray(inits[name], np.float64)
+            g = np.asarray(inits[base + ".weight_g"], np.float64).reshape(-1)
+            norm = np.sqrt((v.reshape(v.shape[0], -1) ** 2).sum(axis=1))
+            out[base + ".weight"] = (v * (g / norm).reshape((-1,) + (1,) * (v.ndim - 1))).astype(np.float32)
+    for n in nodes:
+        if n.op_type not in ("Conv", "ConvTranspose") or len(n.inputs) < 2:
+            continue
+        w_in = n.inputs[1]
+        b_in = n.inputs[2] if len(n.inputs) >= 3 else ""
+        if w_in.endswith(".weight") and w_in in inits:
+            continue
+        if b_in.endswith(".bias"):
+            mod = b_in[:-len(".bias")]
+        elif n.name.startswith("/") and n.name.rsplit("/", 1)[-1].startswith("Conv"):
+            mod = n.name[1:].rsplit("/", 1)[0].replace("/", ".")
+        else:
+            continue
+        if mod + ".weight" not in out and w_in in inits:
+            out[mod + ".weight"] = inits[w_in]
+    # The phoneme embedding: piper_train exports single-speaker voices with input_names = [input, input_lengths,
+    # scales, sid] but only three real inputs, so torch hands the spare name "sid" to the next graph input - the first
+    # parameter, enc_p.emb.weight.  A real single-speaker voice therefore has NO `enc_p.emb.weight`: its table is the
+    # initializer called `sid` (which is what ONNXParsingTests.swift:31 finds), read by the first node,
+    # Gather(sid, input) (ONNXParsingTests.swift:35).
+    if "enc_p.emb.weight" not in out:
+        for n in nodes:
+            if n.op_type == "Gather" and len(n.inputs) == 2 and n.inputs[1] == "input" and n.inputs[0] in inits:
+                out["enc_p.emb.weight"] = inits[n.inputs[0]]
+                break
+    if "dp.flows.0.logs" not in out:
+        consts = {}
+        for n in nodes:
+            if n.op_type == "Constant" and n.outputs and isinstance(n.attrs.get("value"), np.ndarray):
+                consts[n.outputs[0]] = n.attrs["value"]
+        by_out = {o: n for n in nodes for o in n.outputs}
+        diff = [n.outputs[0] for n in nodes if n.op_type == "Sub" and len(n.inputs) == 2 and n.inputs[1] == "dp.flows.0.m"]
+        for n in nodes:
+            if not diff or n.op_type != "Mul" or len(n.inputs) != 2 or diff[-1] not in n.inputs:
+                continue
+            other = n.inputs[1] if n.inputs[0] == diff[-1] else n.inputs[0]
+            src = by_out.get(other)
+            if src is not None and src.op_type == "Exp" and src.inputs[0] in inits:     # Exp(-logs): -logs survived
+                out["dp.flows.0.logs"] = -np.asarray(inits[src.inputs[0]], np.float32)
+                break
+            val = inits.get(other, consts.get(other))
+            if val is not None and np.asarray(val).size in (1, 2) and np.asarray(val).dtype == np.float32:
+                out["dp.flows.0.inv_scale"] = np.asarray(val, np.float32)
+                break
+    return out
+
+
 def derive_params(inits: Dict[str, np.ndarray], nodes) -> VoiceParams:
     attrs = {}
     for n in nodes:
         if n.op_type in ("Conv", "ConvTranspose") and len(n.inputs) >= 2:
             attrs[n.inputs[1]] = n.attrs
+            b_in = n.inputs[2] if len(n.inputs) >= 3 else ""
+            if b_in.endswith(".bias"):                         # canonical name of an anonymous weight (canonicalize)
+                attrs.setdefault(b_in[:-5] + ".weight", n.attrs)
+            elif n.name.startswith("/") and n.name.rsplit("/", 1)[-1].startswith("Conv"):
+                attrs.setdefault(n.name[1:].rsplit("/", 1)[0].replace("/", ".") + ".weight", n.attrs)
 
     def count(fmt):
         i = 0
@@ -221,7 +292,8 @@ class VitsOracle:
     def from_file(cls, path: str, dtype=torch.float32):
         from .onnx_reader import load_model
         m = load_model(path)
-        return cls(m.initializers, derive_params(m.initializers, m.nodes), dtype)
+        inits = canonicalize(m.initializers, m.nodes)
+        return cls(inits, derive_params(inits, m.nodes), dtype)
 
     # ---- helpers ------------------------------------------------------------------
     def _conv(self, x, name, dilation=1, padding=0, groups=1):
@@ -340,8 +412,10 @@ class VitsOracle:
         h = self._dds(h, "dp.convs")
         h = self._conv(h, "dp.proj")
         # flows = reversed([EA, CF, Flip, CF, Flip, ...]) with the second-to-last dropped
+        # (the dropped one is dp.flows.1; an exported graph no longer holds its weights, so it may be absent from the
+        # initializers already - its Flip, dp.flows.2, stays either way)
         seq = [("ea", 0)]
-        for i in p.dp_flow_ids:
+        for i in sorted(set(p.dp_flow_ids) | {1}):
             seq += [("cf", i), ("flip", None)]
         seq = list(reversed(seq))
         seq = seq[:-2] + [seq[-1]]
@@ -354,8 +428,11 @@ class VitsOracle:
                 z, bins = self._conv_flow_reverse(z, h, i)
                 self.last_bins.append(bins)
             else:
-                m, logs = self.w["dp.flows.0.m"], self.w["dp.flows.0.logs"]
-                z = (z - m) * torch.exp(-logs)
+                m = self.w["dp.flows.0.m"]
+                if "dp.flows.0.logs" in self.w:
+                    z = (z - m) * torch.exp(-self.w["dp.flows.0.logs"])
+                else:                               # the exporter folded exp(-logs) into a constant
+                    z = (z - m) * self.w["dp.flows.0.inv_scale"]
         return z[:, :1]
 
     # ---- length regulator: integer-exact part ----------------------------

@@ -120,8 +120,13 @@ int piper_b200_set_weight(piper_b200_ctx* ctx, const char* name, int32_t dtype, 
   return guarded(ctx, [&] {
     Context& c = ctx->c;
     if (c.voice.finalized) throw std::runtime_error("state: voice already finalized");
+    if (rank < 0 || rank > 8) throw std::runtime_error("onnx: tensor rank out of range for '" + std::string(name) + "'");
     int64_t n = 1;
-    for (int i = 0; i < rank; ++i) n *= dims[i];
+    for (int i = 0; i < rank; ++i) {   // no negative and no overflowing extents (a hostile caller must not wrap the byte check)
+      if (dims[i] < 0 || (dims[i] > 0 && n > ((int64_t)1 << 40) / dims[i]))
+        throw std::runtime_error("onnx: bad dims for '" + std::string(name) + "'");
+      n *= dims[i];
+    }
     if (dtype != PIPER_B200_DTYPE_F32) {
       // int64/int32/bool initializers (sid, shape constants) carry no weights on this path
       if (dtype == PIPER_B200_DTYPE_I64 || dtype == PIPER_B200_DTYPE_I32 || dtype == PIPER_B200_DTYPE_BOOL)
@@ -227,6 +232,78 @@ int piper_b200_set_stream(piper_b200_ctx* ctx, void* cuda_stream) {
     return PIPER_B200_ERR_INVALID_ARGUMENT;
   }
   ctx->c.stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->c.own_stream;
+  return PIPER_B200_OK;
+}
+
+int piper_b200_set_output_buffer(piper_b200_ctx* ctx, void* host, size_t capacity_bytes) {
+  if (!ctx || (host && capacity_bytes == 0)) {
+    g_error = "invalid argument: null context or empty buffer";
+    if (ctx) ctx->c.last_error = g_error;
+    return PIPER_B200_ERR_INVALID_ARGUMENT;
+  }
+  return guarded(ctx, [&] {
+    Context& c = ctx->c;
+    if (host) {   // pageable memory would turn every ranged copy into a synchronous staging copy: refuse it
+      if (cudaSetDevice(c.device) != cudaSuccess) throw std::runtime_error("cuda: cudaSetDevice failed");
+      cudaPointerAttributes at{};
+      const cudaError_t e = cudaPointerGetAttributes(&at, host);
+      if (e != cudaSuccess || at.type != cudaMemoryTypeHost) {
+        cudaGetLastError();
+        throw std::runtime_error("invalid argument: the output buffer is not page-locked (use piper_b200_host_alloc or "
+                                 "piper_b200_host_register)");
+      }
+    }
+    c.sstate.active = false;
+    c.out_host = host;
+    c.out_cap = host ? capacity_bytes : 0;
+    return PIPER_B200_OK;
+  });
+}
+
+int piper_b200_host_alloc(size_t bytes, void** out) {
+  if (!out || bytes == 0) {
+    g_error = "invalid argument: null out or zero bytes";
+    return PIPER_B200_ERR_INVALID_ARGUMENT;
+  }
+  *out = nullptr;
+  const cudaError_t e = cudaHostAlloc(out, bytes, cudaHostAllocPortable);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    g_error = std::string("cuda: cudaHostAlloc failed: ") + cudaGetErrorString(e);
+    return PIPER_B200_ERR_CUDA;
+  }
+  return PIPER_B200_OK;
+}
+
+void piper_b200_host_free(void* p) {
+  if (p && cudaFreeHost(p) != cudaSuccess) cudaGetLastError();
+}
+
+int piper_b200_host_register(void* p, size_t bytes) {
+  if (!p || bytes == 0) {
+    g_error = "invalid argument: null pointer or zero bytes";
+    return PIPER_B200_ERR_INVALID_ARGUMENT;
+  }
+  const cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    g_error = std::string("cuda: cudaHostRegister failed: ") + cudaGetErrorString(e);
+    return PIPER_B200_ERR_CUDA;
+  }
+  return PIPER_B200_OK;
+}
+
+int piper_b200_host_unregister(void* p) {
+  if (!p) {
+    g_error = "invalid argument: null pointer";
+    return PIPER_B200_ERR_INVALID_ARGUMENT;
+  }
+  const cudaError_t e = cudaHostUnregister(p);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    g_error = std::string("cuda: cudaHostUnregister failed: ") + cudaGetErrorString(e);
+    return PIPER_B200_ERR_CUDA;
+  }
   return PIPER_B200_OK;
 }
 
@@ -342,6 +419,7 @@ int piper_b200_random_normal(piper_b200_ctx* ctx, uint64_t seed, int64_t count, 
   return guarded(ctx, [&] {
     Context& c = ctx->c;
     if (cudaSetDevice(c.device) != cudaSuccess) throw std::runtime_error("cuda: cudaSetDevice failed");
+    c.invalidate_results();   // the arenas are about to be reused: a pending stream / device-resident result dies here
     c.back.reserve((size_t)count * 4 + 1024);
     c.back.reset();
     float* d = c.back.alloc<float>(count);
@@ -362,6 +440,7 @@ int piper_b200_selftest_conv(piper_b200_ctx* ctx, int32_t mode, int32_t cin, int
     if (ctx) ctx->c.last_error = g_error;
     return PIPER_B200_ERR_INVALID_ARGUMENT;
   }
+  ctx->c.invalidate_results();
   const int rc = ctx->c.selftest_conv(mode, cin, cout, k, dilation, stride, rows, precision, out4);
   if (rc != PIPER_B200_OK) g_error = ctx->c.last_error;
   return rc;

@@ -178,7 +178,7 @@ float* run_decoder_f32(Context& ctx, Exec& ex, const DecoderIn& in) {
     cur_i = (cur_i + 4) % 5;
     R = Rn;
   }
-  launch_conv_post_tanh(ex, cur, v.stages.back().ch, v.post_w, v.post_k, 0.01f, in.frow_utt, U, audio, R);
+  launch_conv_post_tanh(ex, cur, v.stages.back().ch, v.post_w, v.post_k, 0.01f, in.frow_utt, U, audio, R, v.post_b);
   return audio;
 }
 

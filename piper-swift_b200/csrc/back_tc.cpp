@@ -539,7 +539,7 @@ float* run_decoder_tc(Context& ctx, Exec& ex, const DecoderIn& in) {
       a.row_utt = in.frow_utt; a.valid_div = U;
       static const int post_env = [] { const char* e = getenv("PIPER_B200_MRF_POST"); return e ? atoi(e) : 1; }();
       if (last_stage && post_env && mrf_post_supported(C, v.post_k)) {   // conv_post + tanh as the stage kernel's epilogue
-        a.post_w = v.post_w; a.post_k = v.post_k; a.post_slope = 0.01f; a.post_out = audio;
+        a.post_w = v.post_w; a.post_k = v.post_k; a.post_slope = 0.01f; a.post_out = audio; a.post_bias = v.post_b;
         post_fused = true;
       } else if (last_stage) a.out_f32 = xs;
       else { a.out_act = xsb; a.act_slope = 0.1f; }
@@ -598,7 +598,7 @@ float* run_decoder_tc(Context& ctx, Exec& ex, const DecoderIn& in) {
     cur ^= 1;
     R = Rn;
   }
-  if (!post_fused) launch_conv_post_tanh(ex, xs, v.stages.back().ch, v.post_w, v.post_k, 0.01f, in.frow_utt, U, audio, R);
+  if (!post_fused) launch_conv_post_tanh(ex, xs, v.stages.back().ch, v.post_w, v.post_k, 0.01f, in.frow_utt, U, audio, R, v.post_b);
   if (in.chunks && !chunked && in.chunks->done)   // this voice's last stage is not the fused form: everything is enqueued now
     for (size_t c = 0; c + 1 < in.chunks->frame_row.size(); ++c) in.chunks->done((int)c, audio);
   return audio;

@@ -47,6 +47,7 @@ struct MrfParams {
   void* out_act; float act_slope;
   float* out_f32;
   const float* post_w; int post_k; float post_slope; float* post_out;   // fused conv_post + tanh (C = 32 only)
+  float post_bias;
   int f16, ring, resident;
   int mma_split;              // 1: two issuing warps per convolution stream (even / odd tiles)
   // ResBlock1 unit (nk = 1): out = x + conv2(lrelu(conv1(lrelu x) + b1)) + b2 - the residual does not enter the
@@ -585,7 +586,7 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
               else if (src > 31) v = blk + 1 < 4 * m ? sedge_w[(((blk + 1) * 2) * 3 + (src - 32)) * 7 + t] : 0.f;
               sum += v;
             }
-            if (owned) p.post_out[grow] = ((vmask >> ui) & 1u) ? tanhf(sum) : 0.f;
+            if (owned) p.post_out[grow] = ((vmask >> ui) & 1u) ? tanhf(sum + p.post_bias) : 0.f;
             TRACE(16u, nl, (uint32_t)i);
           }
         }
@@ -792,7 +793,7 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   if (a.accum && !a.out_f32) throw std::runtime_error("conv_mrf: accum needs out_f32");
   p.unit_mode = a.unit_mode; p.accum = a.accum; p.out_div = a.out_div;
   p.out_planar = static_cast<uint16_t*>(a.out_planar); p.out_rows = a.out_rows; p.out_pad = a.out_pad;
-  p.post_w = a.post_w; p.post_k = a.post_k; p.post_slope = a.post_slope; p.post_out = a.post_out;
+  p.post_w = a.post_w; p.post_k = a.post_k; p.post_slope = a.post_slope; p.post_out = a.post_out; p.post_bias = a.post_bias;
   p.f16 = a.f16;
   uint32_t cols = 32;
   while ((int)cols < 2 * m * a.C) cols <<= 1;

@@ -43,7 +43,7 @@ struct MrfArgs {
   // post_slope)) - the final LeakyRelu / Conv(C -> 1, k <= 7, no bias) / Tanh of the generator
   // (GraphExecutor.swift:2047-2069, 1739-1810, 2017) as the stage kernel's output epilogue; the stage output itself
   // is then never written.  post_w = fp32 [post_k][C].
-  const float* post_w = nullptr; int post_k = 0; float post_slope = 0.01f;
+  const float* post_w = nullptr; int post_k = 0; float post_slope = 0.01f; float post_bias = 0.f;
   float* post_out = nullptr;     // fp32 [R]
   // ResBlock1 unit (nk = 1, k[0] taps for both convolutions, d0 = dilation of conv1, d1 = 1):
   //   out = x + conv2(lrelu(conv1(lrelu x) + b1)) + b2          (GraphExecutor.swift:2047-2069 chains, HiFi-GAN ResBlock1)

@@ -120,8 +120,9 @@ void launch_noise_dp(Exec& ex, float* z /*[2][R]*/, const float* ext /*ragged [2
                      uint32_t seed, float noise_w);
 
 // durations: logw = (z0 - m)*exp(-logs); w = exp(logw)*length_scale; ceil; cumsum; y_len
-void launch_durations(Exec& ex, const float* z0, float ea_m, float ea_logs, float length_scale,
-                      const int* utt_start, const int* utt_len, int batch, float* logw_out,
+// (use_scale: exp(-logs) arrives as the constant `ea_scale` the exporter folded it into, ea_logs is unused)
+void launch_durations(Exec& ex, const float* z0, float ea_m, float ea_logs, float ea_scale, bool use_scale,
+                      float length_scale, const int* utt_start, const int* utt_len, int batch, float* logw_out,
                       int* dur /*[R]*/, int* cum /*[R]*/, int64_t* y_len /*[batch]*/);
 // logw given directly (parity entry point)
 void launch_durations_from_logw(Exec& ex, const float* logw, float length_scale, const int* utt_start,
@@ -144,7 +145,7 @@ void launch_wn_gate(Exec& ex, const float* xin /*[R][2H]*/, const float* cond /*
 
 // out[r] = tanh(sum_{tap,c} lrelu(in[r+tap-pad][c], slope) * w[tap][c]) and optional pcm16
 void launch_conv_post_tanh(Exec& ex, const float* in, int C, const float* w, int k, float slope,
-                           const int* row_utt, int valid_div, float* out, int R);
+                           const int* row_utt, int valid_div, float* out, int R, float bias = 0.f);
 
 // speaker conditioning: out[b][co] = bias[co] + sum_ci W[co][ci] * emb_g[sid[b]][ci]
 void launch_cond_gemv(Exec& ex, const float* emb_g, const int64_t* sids, const float* W, const float* bias,
@@ -154,6 +155,9 @@ void launch_cond_gemv(Exec& ex, const float* emb_g, const int64_t* sids, const f
 void launch_gather_audio(Exec& ex, const float* packed, const int64_t* fstart, const int64_t* y_len,
                          const int64_t* sample_off, int batch, int hop, float* dense, int16_t* pcm16,
                          int64_t total_samples);
+
+// int16 PCM of a sample range: Int(clamp(v, -1, 1) * 32767), truncation (WavFileWriter.swift:20-30)
+void launch_pcm16(Exec& ex, const float* src, int16_t* dst, int64_t n);
 
 void launch_pack_ids(Exec& ex, const int64_t* ids, const int64_t* id_off, const int* utt_start,
                      const int* utt_len, int batch, int64_t* ids_packed, int* row_utt, int n_vocab);

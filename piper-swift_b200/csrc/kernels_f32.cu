@@ -1233,7 +1233,8 @@ __device__ __forceinline__ int dur_from_w(float w) {
 
 template <bool FROM_LOGW>
 __global__ void __launch_bounds__(256) durations_kernel(const float* __restrict__ src, float ea_m,
-                                                        float ea_logs, float length_scale,
+                                                        float ea_logs, float ea_scale, int use_scale,
+                                                        float length_scale,
                                                         const int* __restrict__ utt_start,
                                                         const int* __restrict__ utt_len,
                                                         float* __restrict__ logw_out, int* __restrict__ dur,
@@ -1251,7 +1252,8 @@ __global__ void __launch_bounds__(256) durations_kernel(const float* __restrict_
     if (t < T) {
       float lw = src[r0 + t];
       if (!FROM_LOGW) {
-        lw = (lw - ea_m) * expf(-ea_logs);     // ElementwiseAffine reverse, channel 0
+        // ElementwiseAffine reverse, channel 0; use_scale: the export folded exp(-logs) into a constant
+        lw = (lw - ea_m) * (use_scale ? ea_scale : expf(-ea_logs));
         if (logw_out) logw_out[r0 + t] = lw;
       }
       const float w = expf(lw) * length_scale;   // x_mask == 1 inside the utterance
@@ -1276,18 +1278,18 @@ __global__ void __launch_bounds__(256) durations_kernel(const float* __restrict_
   if (threadIdx.x == 0) y_len[b] = carry_s < 1 ? 1 : carry_s;
 }
 
-void launch_durations(Exec& ex, const float* z0, float ea_m, float ea_logs, float length_scale,
-                      const int* utt_start, const int* utt_len, int batch, float* logw_out, int* dur,
+void launch_durations(Exec& ex, const float* z0, float ea_m, float ea_logs, float ea_scale, bool use_scale,
+                      float length_scale, const int* utt_start, const int* utt_len, int batch, float* logw_out, int* dur,
                       int* cum, int64_t* y_len) {
   if (batch <= 0) return;
-  durations_kernel<false><<<batch, 256, 0, ex.st>>>(z0, ea_m, ea_logs, length_scale, utt_start, utt_len,
+  durations_kernel<false><<<batch, 256, 0, ex.st>>>(z0, ea_m, ea_logs, ea_scale, use_scale ? 1 : 0, length_scale, utt_start, utt_len,
                                                     logw_out, dur, cum, y_len);
   KLAUNCH(ex);
 }
 void launch_durations_from_logw(Exec& ex, const float* logw, float length_scale, const int* utt_start,
                                 const int* utt_len, int batch, int* dur, int* cum, int64_t* y_len) {
   if (batch <= 0) return;
-  durations_kernel<true><<<batch, 256, 0, ex.st>>>(logw, 0.f, 0.f, length_scale, utt_start, utt_len,
+  durations_kernel<true><<<batch, 256, 0, ex.st>>>(logw, 0.f, 0.f, 1.f, 0, length_scale, utt_start, utt_len,
                                                    nullptr, dur, cum, y_len);
   KLAUNCH(ex);
 }
@@ -1414,12 +1416,13 @@ void launch_wn_gate(Exec& ex, const float* xin, const float* cond, int ldc, cons
   KLAUNCH(ex);
 }
 
-// conv_post (C -> 1 channel, no bias) with its preceding LeakyRelu and the final Tanh.
+// conv_post (C -> 1 channel; stock Piper has no bias, forks may: a scalar added before the Tanh) with its preceding
+// LeakyRelu and the final Tanh.
 constexpr int CP_ROWS = 128;
 __global__ void __launch_bounds__(CP_ROWS) conv_post_tanh_kernel(const float* __restrict__ in, int C,
                                                                    const float* __restrict__ w, int k, float slope,
                                                                    const int* __restrict__ row_utt, int valid_div,
-                                                                   float* __restrict__ out, int R) {
+                                                                   float* __restrict__ out, int R, float bias) {
   // a CTA stages CP_ROWS + k - 1 input rows (leaky-relu applied) in shared memory with coalesced
   // loads, then every thread reduces one output row over taps x channels (row stride C+1: no bank conflicts)
   extern __shared__ float sm[];
@@ -1454,7 +1457,7 @@ __global__ void __launch_bounds__(CP_ROWS) conv_post_tanh_kernel(const float* __
     const float* wp = ws + t * C;
     for (int c = 0; c < C; ++c) acc = fmaf(xr[c], wp[c], acc);
   }
-  out[r] = tanhf(acc);
+  out[r] = tanhf(acc + bias);
 }
 // Warp-per-row-block variant for k <= 7 and C = 32 * n (n <= 4): lane c owns channels c, c+32, ..; the taps'
 // weights sit in registers, input rows are read straight from global memory (one coalesced 128-byte load per
@@ -1465,7 +1468,7 @@ constexpr int CPW_ROWS = 32, CPW_MAXK = 7, CPW_MAXN = 4;
 template <int N>
 __global__ void __launch_bounds__(256) conv_post_tanh_warp_kernel(const float* __restrict__ in, const float* __restrict__ w,
                                                                   int k, float slope, const int* __restrict__ row_utt,
-                                                                  int valid_div, float* __restrict__ out, int R) {
+                                                                  int valid_div, float* __restrict__ out, int R, float bias) {
   constexpr int C = 32 * N;
   const int lane = threadIdx.x & 31;
   const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -1509,29 +1512,29 @@ __global__ void __launch_bounds__(256) conv_post_tanh_warp_kernel(const float* _
   const int64_t r = r0 + lane;
   if (r < R) {
     const bool valid = !row_utt || row_utt[r / valid_div] >= 0;
-    out[r] = valid ? tanhf(v[0]) : 0.f;
+    out[r] = valid ? tanhf(v[0] + bias) : 0.f;
   }
 }
 
 void launch_conv_post_tanh(Exec& ex, const float* in, int C, const float* w, int k, float slope,
-                           const int* row_utt, int valid_div, float* out, int R) {
+                           const int* row_utt, int valid_div, float* out, int R, float bias) {
   if (R <= 0) return;
   static const int cpw_env = [] { const char* e = getenv("PIPER_B200_CONV_POST_WARP"); return e ? atoi(e) : 1; }();
   if (cpw_env && k <= CPW_MAXK && (k & 1) && C % 32 == 0 && C / 32 <= CPW_MAXN) {
     const int warps = (R + CPW_ROWS - 1) / CPW_ROWS;
     const unsigned grid = (unsigned)((warps + 7) / 8);
     switch (C / 32) {
-      case 1: conv_post_tanh_warp_kernel<1><<<grid, 256, 0, ex.st>>>(in, w, k, slope, row_utt, valid_div, out, R); break;
-      case 2: conv_post_tanh_warp_kernel<2><<<grid, 256, 0, ex.st>>>(in, w, k, slope, row_utt, valid_div, out, R); break;
-      case 3: conv_post_tanh_warp_kernel<3><<<grid, 256, 0, ex.st>>>(in, w, k, slope, row_utt, valid_div, out, R); break;
-      default: conv_post_tanh_warp_kernel<4><<<grid, 256, 0, ex.st>>>(in, w, k, slope, row_utt, valid_div, out, R); break;
+      case 1: conv_post_tanh_warp_kernel<1><<<grid, 256, 0, ex.st>>>(in, w, k, slope, row_utt, valid_div, out, R, bias); break;
+      case 2: conv_post_tanh_warp_kernel<2><<<grid, 256, 0, ex.st>>>(in, w, k, slope, row_utt, valid_div, out, R, bias); break;
+      case 3: conv_post_tanh_warp_kernel<3><<<grid, 256, 0, ex.st>>>(in, w, k, slope, row_utt, valid_div, out, R, bias); break;
+      default: conv_post_tanh_warp_kernel<4><<<grid, 256, 0, ex.st>>>(in, w, k, slope, row_utt, valid_div, out, R, bias); break;
     }
     KLAUNCH(ex);
     return;
   }
   const size_t smem = sizeof(float) * ((size_t)k * C + (size_t)(CP_ROWS + k - 1) * (C + 1));
   conv_post_tanh_kernel<<<(R + CP_ROWS - 1) / CP_ROWS, CP_ROWS, smem, ex.st>>>(in, C, w, k, slope, row_utt,
-                                                                              valid_div, out, R);
+                                                                              valid_div, out, R, bias);
   KLAUNCH(ex);
 }
 
@@ -1573,6 +1576,16 @@ __global__ void gather_audio_kernel(const float* __restrict__ packed, const int6
     dense[o + i] = v;
     if (pcm16) pcm16[o + i] = (int16_t)(int)(fminf(fmaxf(v, -1.f), 1.f) * 32767.f);
   }
+}
+__global__ void pcm16_kernel(const float* __restrict__ src, int16_t* __restrict__ dst, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    dst[i] = (int16_t)(int)(fminf(fmaxf(src[i], -1.f), 1.f) * 32767.f);
+}
+void launch_pcm16(Exec& ex, const float* src, int16_t* dst, int64_t n) {
+  if (n <= 0) return;
+  int g = (int)((n + 1023) / 1024);
+  pcm16_kernel<<<g > 1184 ? 1184 : g, 256, 0, ex.st>>>(src, dst, n);
+  KLAUNCH(ex);
 }
 void launch_gather_audio(Exec& ex, const float* packed, const int64_t* fstart, const int64_t* y_len,
                          const int64_t* sample_off, int batch, int hop, float* dense, int16_t* pcm16,

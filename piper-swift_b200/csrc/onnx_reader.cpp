@@ -98,10 +98,21 @@ OnnxTensor read_tensor(Reader r) {
       default: r.skip(wt);
     }
   }
-  int64_t n = t.count();
+  // extents must be non-negative and their product must not overflow: the binders index f32 / i64 from dims
+  int64_t n = 1;
+  for (int64_t d : t.dims) {
+    if (d < 0 || (d > 0 && n > ((int64_t)1 << 40) / d))
+      throw std::runtime_error("onnx: bad dims for tensor '" + t.name + "'");
+    n *= d;
+  }
   auto check = [&](size_t elt) {
     if (raw && raw_n != size_t(n) * elt)
       throw std::runtime_error("onnx: raw_data size mismatch for '" + t.name + "'");
+  };
+  auto check_typed = [&](size_t have) {   // float_data / int64_data path: one value per element
+    if (have != size_t(n))
+      throw std::runtime_error("onnx: tensor '" + t.name + "' holds " + std::to_string(have) + " values for " +
+                               std::to_string(n) + " elements");
   };
   switch (t.dtype) {
     case 1:
@@ -110,6 +121,7 @@ OnnxTensor read_tensor(Reader r) {
         t.f32.resize(n);
         std::memcpy(t.f32.data(), raw, raw_n);   // little-endian host assumed (x86-64 / aarch64)
       } else {
+        check_typed(fdata.size());
         t.f32 = std::move(fdata);
       }
       break;
@@ -119,6 +131,7 @@ OnnxTensor read_tensor(Reader r) {
         t.i64.resize(n);
         std::memcpy(t.i64.data(), raw, raw_n);
       } else {
+        check_typed(idata.size());
         t.i64 = std::move(idata);
       }
       break;
@@ -132,6 +145,7 @@ OnnxTensor read_tensor(Reader r) {
           t.i64[i] = v;
         }
       } else {
+        check_typed(idata.size());
         t.i64 = std::move(idata);
       }
       t.dtype = 7;
@@ -142,6 +156,7 @@ OnnxTensor read_tensor(Reader r) {
         t.i64.resize(n);
         for (int64_t i = 0; i < n; ++i) t.i64[i] = raw[i] != 0;
       } else {
+        check_typed(idata.size());
         t.i64 = std::move(idata);
       }
       break;
@@ -162,10 +177,18 @@ OnnxAttr read_attr(Reader r) {
       case 2: a.f = r.f32(); break;
       case 3: a.i = int64_t(r.varint()); break;
       case 4: a.s = r.str(); break;
+      case 5:   // tensor-valued attribute: the value of a Constant node (a float / int64 tensor; other types are skipped)
+        try {
+          a.t = read_tensor(r.sub());
+          a.has_t = true;
+        } catch (const std::runtime_error&) {
+          a.has_t = false;
+        }
+        break;
       case 7: read_floats(r, wt, a.floats); break;
       case 8: read_ints(r, wt, a.ints); break;
       case 20: a.type = int32_t(r.varint()); break;
-      default: r.skip(wt);   // tensors (5), graphs, sparse tensors: not needed on this path
+      default: r.skip(wt);   // graphs, sparse tensors: not needed on this path
     }
   }
   return a;

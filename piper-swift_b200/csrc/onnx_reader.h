@@ -30,6 +30,8 @@ struct OnnxAttr {
   std::string s;
   std::vector<int64_t> ints;
   std::vector<float> floats;
+  bool has_t = false;                // attribute `t` (field 5): the value of a Constant node
+  OnnxTensor t;
 };
 
 struct OnnxNode {

@@ -116,6 +116,7 @@ int Context::length_regulate(const float* logw_h, const int64_t* lengths, int ba
   }
   try {
     CUDA_OK(cudaSetDevice(device));
+    invalidate_results();
     Exec ex;
     ex.st = stream;
     std::vector<int> us(batch), ul(batch);

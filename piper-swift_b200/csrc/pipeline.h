@@ -127,6 +127,8 @@ struct Context {
   StageDump dump;
   Prof prof;
   float* d_audio_dense = nullptr;   // inside `back`
+  void* out_host = nullptr;         // caller-owned page-locked output (piper_b200_set_output_buffer), else h_audio / h_pcm
+  size_t out_cap = 0;
 
   int gap_p = 0, gap_f = 0;         // zero rows between utterances (phoneme / frame level)
 
@@ -144,6 +146,9 @@ struct Context {
     int64_t chunk_frames = 0;
   } sstate;
   int stream_next(int64_t max_frames, piper_b200_result& rs, int32_t* is_final);
+  // every entry point that resets or regrows `front` / `back` ends a pending streamed utterance and a device-resident
+  // result: the next stream_next then reports ERR_STATE instead of decoding over reused memory
+  void invalidate_results() { sstate.active = false; d_audio_dense = nullptr; }
 
   void init(int dev);
   void destroy();

@@ -102,12 +102,22 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
   const bool ids_dev = rq.flags & PIPER_B200_FLAG_IDS_ON_DEVICE;
   const bool keep_dev = rq.flags & PIPER_B200_FLAG_KEEP_ON_DEVICE;
   const bool keep_stages = rq.flags & PIPER_B200_FLAG_KEEP_STAGES;
-  const bool want_pcm = rq.flags & PIPER_B200_FLAG_PCM16;
+  const bool pcm_only = rq.flags & PIPER_B200_FLAG_PCM16_ONLY;
+  const bool want_pcm = (rq.flags & PIPER_B200_FLAG_PCM16) || pcm_only;
   const bool stream_begin = rq.flags & PIPER_B200_FLAG_STREAM;
   sstate.active = false;
-  if (stream_begin && (rq.batch != 1 || keep_dev || keep_stages)) {
-    last_error = "invalid argument: PIPER_B200_FLAG_STREAM needs batch == 1 and host output";
+  d_audio_dense = nullptr;
+  if (stream_begin && (rq.batch != 1 || keep_dev || keep_stages || pcm_only)) {
+    last_error = "invalid argument: PIPER_B200_FLAG_STREAM needs batch == 1 and float host output";
     return PIPER_B200_ERR_INVALID_ARGUMENT;
+  }
+  if (pcm_only && (keep_dev || keep_stages)) {
+    last_error = "invalid argument: PIPER_B200_FLAG_PCM16_ONLY is a host-output mode";
+    return PIPER_B200_ERR_INVALID_ARGUMENT;
+  }
+  if (rq.batch > 65535) {   // the batch index is a grid dimension of the per-utterance kernels
+    last_error = "capacity: at most 65535 utterances per call (got " + std::to_string(rq.batch) + ")";
+    return PIPER_B200_ERR_CAPACITY;
   }
   const float noise_scale = std::isnan(rq.noise_scale) ? config.noise_scale : rq.noise_scale;
   const float length_scale = std::isnan(rq.length_scale) ? config.length_scale : rq.length_scale;
@@ -364,7 +374,8 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
     }
 
     // ---- length regulator ----------------------------------------------------------------------
-    launch_durations(ex, zdp + (size_t)voice.dp_logw_channel * Rp, voice.ea_m, voice.ea_logs, length_scale,
+    launch_durations(ex, zdp + (size_t)voice.dp_logw_channel * Rp, voice.ea_m, voice.ea_logs, voice.ea_scale, voice.ea_has_scale,
+                     length_scale,
                      d_utt_start, d_utt_len, B, logw, dur, cum, d_ylen);
     launch_frame_layout(ex, d_ylen, B, gap_f, d_fstart);
     h_meta.reserve((size_t)(2 * B + 2) * 8 + (size_t)Rp * 4);
@@ -397,6 +408,13 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
       sample_offsets[b + 1] = sample_offsets[b] + h_ylen[b] * hp.hop;
     }
     const int64_t total_samples = sample_offsets[B];
+    // host destination of the audio: the caller's buffer (piper_b200_set_output_buffer) or the library's pinned one
+    const size_t out_bytes = (size_t)total_samples * (pcm_only ? 2 : 4);
+    if (out_host && !keep_dev && !stream_begin && out_bytes > out_cap) {
+      last_error = "capacity: the output buffer holds " + std::to_string(out_cap) + " bytes, this result needs " +
+                   std::to_string(out_bytes);
+      return PIPER_B200_ERR_CAPACITY;
+    }
     durations.resize(n_ids);
     for (int b = 0; b < B; ++b)
       std::memcpy(durations.data() + id_off[b], h_dur + utt_start[b], (size_t)utt_len[b] * 4);
@@ -461,7 +479,7 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
       static const int chunks_env = [] { const char* e = getenv("PIPER_B200_D2H_CHUNKS"); return e ? atoi(e) : 3; }();
       AudioChunks chunks;
       std::vector<int> chunk_utt;
-      if (use_tc && !keep_dev && !keep_stages && !want_pcm && chunks_env > 1 && B >= 4 * chunks_env &&
+      if (use_tc && !keep_dev && !keep_stages && (!want_pcm || pcm_only) && chunks_env > 1 && B >= 4 * chunks_env &&
           total_samples >= ((int64_t)1 << 22)) {
         const int Kc = std::min(chunks_env, 8);
         const double wsum = 0.5 * Kc * (Kc + 1);
@@ -478,19 +496,29 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
         chunks.frame_row.push_back(Rf);
       }
       if (chunks.frame_row.size() > 2) {
-        h_audio.reserve((size_t)total_samples * 4);   // before anything is enqueued: a growing pinned buffer synchronises
-        chunks.done = [&](int c, float* packed_audio) {
+        // before anything is enqueued: a growing pinned buffer synchronises
+        char* dst_host = static_cast<char*>(out_host);
+        if (!dst_host) {
+          PinnedBuf& hb = pcm_only ? h_pcm : h_audio;
+          hb.reserve(out_bytes);
+          dst_host = static_cast<char*>(hb.p);
+        }
+        chunks.done = [&, dst_host](int c, float* packed_audio) {
           const int b0 = chunk_utt[(size_t)c], b1 = chunk_utt[(size_t)c + 1];
           const int64_t s0 = sample_offsets[(size_t)b0], s1 = sample_offsets[(size_t)b1];
           CUDA_OK(cudaEventRecord(ev_chunk[c], stream));
           CUDA_OK(cudaStreamWaitEvent(copy_stream, ev_chunk[c], 0));
           Exec exc;
           exc.st = copy_stream;
-          launch_gather_audio(exc, packed_audio, d_fstart + b0, d_ylen + b0, d_soff + b0, b1 - b0, hp.hop, dense, nullptr,
+          launch_gather_audio(exc, packed_audio, d_fstart + b0, d_ylen + b0, d_soff + b0, b1 - b0, hp.hop, dense, pcm,
                               s1 - s0);
           ex.launches += exc.launches;
-          CUDA_OK(cudaMemcpyAsync(static_cast<float*>(h_audio.p) + s0, dense + s0, (size_t)(s1 - s0) * 4,
-                                  cudaMemcpyDeviceToHost, copy_stream));
+          if (pcm_only)
+            CUDA_OK(cudaMemcpyAsync(dst_host + (size_t)s0 * 2, pcm + s0, (size_t)(s1 - s0) * 2, cudaMemcpyDeviceToHost,
+                                    copy_stream));
+          else
+            CUDA_OK(cudaMemcpyAsync(dst_host + (size_t)s0 * 4, dense + s0, (size_t)(s1 - s0) * 4, cudaMemcpyDeviceToHost,
+                                    copy_stream));
         };
         bi.chunks = &chunks;
         run_back_tc(*this, ex, bi, z_keep);
@@ -515,13 +543,18 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
     } else if (keep_dev) {
       rs.audio = dense;
       rs.pcm16 = pcm;
+    } else if (pcm_only) {
+      void* dst = out_host;
+      if (!dst) { h_pcm.reserve(out_bytes); dst = h_pcm.p; }
+      if (!audio_shipped) CUDA_OK(cudaMemcpyAsync(dst, pcm, out_bytes, cudaMemcpyDeviceToHost, stream));
+      d2h += out_bytes;
+      rs.pcm16 = static_cast<const int16_t*>(dst);
     } else {
-      if (!audio_shipped) {
-        h_audio.reserve((size_t)total_samples * 4);
-        CUDA_OK(cudaMemcpyAsync(h_audio.p, dense, (size_t)total_samples * 4, cudaMemcpyDeviceToHost, stream));
-      }
-      d2h += (size_t)total_samples * 4;
-      rs.audio = static_cast<const float*>(h_audio.p);
+      void* dst = out_host;
+      if (!dst) { h_audio.reserve(out_bytes); dst = h_audio.p; }
+      if (!audio_shipped) CUDA_OK(cudaMemcpyAsync(dst, dense, out_bytes, cudaMemcpyDeviceToHost, stream));
+      d2h += out_bytes;
+      rs.audio = static_cast<const float*>(dst);
       if (want_pcm) {
         h_pcm.reserve((size_t)total_samples * 2);
         CUDA_OK(cudaMemcpyAsync(h_pcm.p, pcm, (size_t)total_samples * 2, cudaMemcpyDeviceToHost, stream));
@@ -600,11 +633,19 @@ int Context::stream_next(int64_t max_frames, piper_b200_result& rs, int32_t* is_
     const float* src = packed + (size_t)(sstate.f0 + n0 - w0) * hp.hop;
     h_audio.reserve((size_t)n_samples * 4);
     CUDA_OK(cudaMemcpyAsync(h_audio.p, src, (size_t)n_samples * 4, cudaMemcpyDeviceToHost, stream));
+    if (sstate.want_pcm) {   // PCM16 of the chunk with the same rule as the one-shot call (WavFileWriter.swift:20-30)
+      int16_t* d_pcm = back.alloc<int16_t>((size_t)n_samples);
+      if (!d_pcm) throw std::runtime_error("capacity: back arena too small (stream pcm16)");
+      launch_pcm16(ex, src, d_pcm, n_samples);
+      h_pcm.reserve((size_t)n_samples * 2);
+      CUDA_OK(cudaMemcpyAsync(h_pcm.p, d_pcm, (size_t)n_samples * 2, cudaMemcpyDeviceToHost, stream));
+    }
     CUDA_OK(cudaEventRecord(ev[5], stream));
     CUDA_OK(cudaStreamSynchronize(stream));
     CUDA_OK(cudaGetLastError());
     rs = piper_b200_result{};
     rs.audio = static_cast<const float*>(h_audio.p);
+    if (sstate.want_pcm) rs.pcm16 = static_cast<const int16_t*>(h_pcm.p);
     sstate.chunk_offsets[0] = 0; sstate.chunk_offsets[1] = n_samples;
     sstate.chunk_frames = n1 - n0;
     rs.sample_offsets = sstate.chunk_offsets;
@@ -617,7 +658,7 @@ int Context::stream_next(int64_t max_frames, piper_b200_result& rs, int32_t* is_
     timings = piper_b200_timings{};
     timings.gpu_ms = timings.decoder_ms = ms_between(ev[0], ev[5]);
     timings.kernel_launches = ex.launches;
-    timings.d2h_bytes = n_samples * 4;
+    timings.d2h_bytes = n_samples * (sstate.want_pcm ? 6 : 4);
     timings.wall_ms = std::chrono::duration<double, std::milli>(clk::now() - t_wall0).count();
     return PIPER_B200_OK;
   } catch (const std::exception& e) {

@@ -64,6 +64,10 @@ struct Binder {
     const int cout = co_count < 0 ? cout_all - co_begin : co_count;
     const ConvAttr a = attr(p + ".weight");
     if (a.group != 1) throw std::runtime_error("unsupported: grouped conv '" + p + "' on the dense path");
+    if (cout_all <= 0 || cin <= 0 || k <= 0 || w.f32.size() != (size_t)cout_all * cin * k || co_begin < 0 || cout <= 0 ||
+        co_begin + cout > cout_all)
+      throw std::runtime_error("unsupported: '" + p + ".weight' holds " + std::to_string(w.f32.size()) +
+                               " values for dims " + std::to_string(cout_all) + "x" + std::to_string(cin) + "x" + std::to_string(k));
     ConvW o;
     o.cin = cin; o.cout = cout; o.k = k; o.taps = k; o.dil = a.dilation;
     o.ldw = round_up(cout, 64);
@@ -81,6 +85,7 @@ struct Binder {
     std::vector<float> b(o.ldw, 0.f);
     if (has(p + ".bias")) {
       const HostTensor& bt = get(p + ".bias");
+      if ((int)bt.f32.size() != cout_all) throw std::runtime_error("unsupported: '" + p + ".bias' does not match the weight");
       for (int co = 0; co < cout; ++co)
         b[co] = sign * bt.f32[co_begin + (rev_out ? cout - 1 - co : co)];
     }
@@ -97,7 +102,7 @@ struct Binder {
     for (int s = 0; s < 3; ++s) {
       const HostTensor& w = get(p + names[s] + ".weight");
       const HostTensor& bt = get(p + names[s] + ".bias");
-      if ((int)w.f32.size() != H * H) throw std::runtime_error("unsupported: attention conv shape in " + p);
+      if ((int)w.f32.size() != H * H || (int)bt.f32.size() != H) throw std::runtime_error("unsupported: attention conv shape in " + p);
       for (int co = 0; co < H; ++co) {
         b[s * H + co] = bt.f32[co];
         for (int ci = 0; ci < H; ++ci) pk[(size_t)ci * o.ldw + s * H + co] = w.f32[(size_t)co * H + ci];
@@ -112,7 +117,10 @@ struct Binder {
   // out[q*u+ph] = sum_j in[q + (ph+p)/u - j] * W[:, :, (ph+p)%u + j*u]
   ConvW conv_transpose(const std::string& p, int stride_fallback) {
     const HostTensor& w = get(p + ".weight");
+    if (w.dims.size() != 3) throw std::runtime_error("unsupported: '" + p + ".weight' is not rank 3");
     const int cin = (int)w.dims[0], cout = (int)w.dims[1], k = (int)w.dims[2];
+    if (cin <= 0 || cout <= 0 || k <= 0 || w.f32.size() != (size_t)cin * cout * k)
+      throw std::runtime_error("unsupported: '" + p + ".weight' element count does not match its dims");
     const ConvAttr a = attr(p + ".weight");
     const int u = v.conv_attrs.count(p + ".weight") ? a.stride : stride_fallback;
     if (u <= 0 || k % u != 0)
@@ -133,6 +141,7 @@ struct Binder {
     std::vector<float> b(o.ldw, 0.f);
     if (has(p + ".bias")) {
       const HostTensor& bt = get(p + ".bias");
+      if ((int)bt.f32.size() != cout) throw std::runtime_error("unsupported: '" + p + ".bias' does not match the weight");
       for (int co = 0; co < cout; ++co) b[co] = bt.f32[co];
     }
     o.b = upload(b);
@@ -145,6 +154,8 @@ struct Binder {
       DDSLayerW l;
       const std::string sp = p + ".convs_sep." + std::to_string(i);
       const HostTensor& w = get(sp + ".weight");   // [C][1][k]
+      if (w.dims.size() != 3 || w.dims[2] <= 0 || w.f32.size() != (size_t)C * (size_t)w.dims[2])
+        throw std::runtime_error("unsupported: depthwise weight '" + sp + ".weight' shape");
       l.k = (int)w.dims[2];
       const ConvAttr a = attr(sp + ".weight");
       l.dil = v.conv_attrs.count(sp + ".weight") ? a.dilation : (int)std::lround(std::pow((double)l.k, i));
@@ -172,6 +183,11 @@ void Voice::add_onnx(const OnnxModel& m) {
     h.f32 = t.f32;
     tensors[t.name] = std::move(h);
   }
+  // float values of Constant nodes, by output name (an export without constant folding keeps scalars there)
+  std::map<std::string, const OnnxTensor*> constants;
+  for (const auto& n : m.nodes)
+    if (n.op_type == "Constant" && !n.outputs.empty())
+      if (auto x = n.attr("value"); x && x->has_t && x->t.dtype == 1) constants[n.outputs[0]] = &x->t;
   for (const auto& n : m.nodes) {
     if ((n.op_type != "Conv" && n.op_type != "ConvTranspose") || n.inputs.size() < 2) continue;
     ConvAttr a;
@@ -183,6 +199,130 @@ void Voice::add_onnx(const OnnxModel& m) {
       a.pad_end = (int)x->ints[1];
     }
     conv_attrs[n.inputs[1]] = a;
+    ConvNodeRef r;
+    r.node_name = n.name;
+    r.weight_input = n.inputs[1];
+    if (n.inputs.size() >= 3) r.bias_input = n.inputs[2];
+    r.attr = a;
+    conv_nodes.push_back(std::move(r));
+  }
+  // The phoneme embedding of a real single-speaker export is NOT called enc_p.emb.weight: piper_train passes
+  // input_names = [input, input_lengths, scales, sid] with three real inputs, so the exporter gives the spare name
+  // "sid" to the first parameter - the embedding table (that is the `sid` initializer ONNXParsingTests.swift:31
+  // finds; the first node is Gather(sid, input), :35).  Bind the table through that Gather.
+  if (!tensors.count("enc_p.emb.weight"))
+    for (const auto& n : m.nodes)
+      if (n.op_type == "Gather" && n.inputs.size() == 2 && n.inputs[1] == "input") {
+        auto it = tensors.find(n.inputs[0]);
+        if (it != tensors.end() && it->second.dims.size() == 2) {
+          tensors["enc_p.emb.weight"] = it->second;
+          folded_sources.insert(n.inputs[0]);
+        }
+        break;
+      }
+  // ElementwiseAffine of the duration predictor, reverse: (z - m) * exp(-logs).  Constant folding replaces exp(-logs) by
+  // an anonymous constant and drops `dp.flows.0.logs`: follow Sub(., dp.flows.0.m) to the Mul that scales it.
+  if (!tensors.count("dp.flows.0.logs") && !tensors.count("dp.flows.0.inv_scale")) {
+    std::string diff;
+    for (const auto& n : m.nodes)
+      if (n.op_type == "Sub" && n.inputs.size() == 2 && n.inputs[1] == "dp.flows.0.m" && !n.outputs.empty())
+        diff = n.outputs[0];
+    for (const auto& n : m.nodes) {
+      if (diff.empty() || n.op_type != "Mul" || n.inputs.size() != 2) continue;
+      const std::string* other = n.inputs[0] == diff ? &n.inputs[1] : (n.inputs[1] == diff ? &n.inputs[0] : nullptr);
+      if (!other) continue;
+      // (a) only the negation was folded: Mul(diff, Exp(onnx::Exp_NNNN)) with the initializer holding -logs
+      bool found = false;
+      for (const auto& e : m.nodes)
+        if (e.op_type == "Exp" && e.inputs.size() == 1 && !e.outputs.empty() && e.outputs[0] == *other) {
+          auto it = tensors.find(e.inputs[0]);
+          if (it != tensors.end() && !it->second.f32.empty()) {
+            HostTensor lg = it->second;
+            for (float& v : lg.f32) v = -v;
+            tensors["dp.flows.0.logs"] = std::move(lg);
+            folded_sources.insert(e.inputs[0]);
+            found = true;
+          }
+        }
+      if (found) break;
+      // (b) the whole factor exp(-logs) was folded into an initializer / Constant
+      HostTensor h;
+      if (auto it = tensors.find(*other); it != tensors.end()) h = it->second;
+      else if (auto ct = constants.find(*other); ct != constants.end()) { h.dims = ct->second->dims; h.f32 = ct->second->f32; }
+      if (h.f32.size() == 2 || h.f32.size() == 1) {   // one scale per z channel ([2,1]); a mask has T entries
+        tensors["dp.flows.0.inv_scale"] = std::move(h);
+        break;
+      }
+    }
+  }
+}
+
+namespace {
+// "/flow/flows.0/enc/in_layers.0/Conv" (also ".../Conv_1", ".../ConvTranspose") -> "flow.flows.0.enc.in_layers.0"
+std::string module_of_node_name(const std::string& name) {
+  if (name.empty() || name[0] != '/') return "";
+  const size_t cut = name.rfind('/');
+  if (cut == 0 || cut == std::string::npos || name.compare(cut + 1, 4, "Conv") != 0) return "";
+  std::string s = name.substr(1, cut - 1);
+  for (char& c : s)
+    if (c == '/') c = '.';
+  return s;
+}
+bool ends_with(const std::string& s, const char* suf) {
+  const size_t n = std::strlen(suf);
+  return s.size() >= n && s.compare(s.size() - n, n, suf) == 0;
+}
+}  // namespace
+
+void Voice::resolve_conv_nodes() {
+  // (1) weight-norm pairs kept as parameters (export without constant folding, or route B passing the raw state
+  //     dict): w = g * v / ||v||, the norm over every axis but the first (torch.nn.utils.weight_norm, dim = 0)
+  std::vector<std::string> pairs;
+  for (const auto& kv : tensors)
+    if (ends_with(kv.first, ".weight_v")) pairs.push_back(kv.first.substr(0, kv.first.size() - 9));
+  for (const std::string& p : pairs) {
+    if (tensors.count(p + ".weight") || !tensors.count(p + ".weight_g")) continue;
+    const HostTensor& v = tensors[p + ".weight_v"];
+    const HostTensor& g = tensors[p + ".weight_g"];
+    if (v.dims.empty() || v.dims[0] <= 0 || (int64_t)g.f32.size() != v.dims[0] || v.f32.size() % (size_t)v.dims[0])
+      throw std::runtime_error("unsupported: weight_g / weight_v shapes of '" + p + "' do not match");
+    const size_t rows = (size_t)v.dims[0], inner = v.f32.size() / rows;
+    HostTensor w;
+    w.dims = v.dims;
+    w.f32.resize(v.f32.size());
+    for (size_t r = 0; r < rows; ++r) {
+      double ss = 0.0;
+      for (size_t i = 0; i < inner; ++i) ss += (double)v.f32[r * inner + i] * (double)v.f32[r * inner + i];
+      const double sc = (double)g.f32[r] / std::sqrt(ss);
+      for (size_t i = 0; i < inner; ++i) w.f32[r * inner + i] = (float)((double)v.f32[r * inner + i] * sc);
+    }
+    tensors[p + ".weight"] = std::move(w);
+    folded_sources.insert(p + ".weight_v");
+    folded_sources.insert(p + ".weight_g");
+  }
+  // (2) anonymous folded weights: the literal `<module>.weight` initializer is the first choice, else whatever
+  //     initializer the module's Conv node reads; the module path comes from the named bias input or the node name
+  for (const ConvNodeRef& r : conv_nodes) {
+    std::string mod;
+    if (ends_with(r.weight_input, ".weight") && tensors.count(r.weight_input)) mod = r.weight_input.substr(0, r.weight_input.size() - 7);
+    else if (ends_with(r.bias_input, ".bias")) mod = r.bias_input.substr(0, r.bias_input.size() - 5);
+    else mod = module_of_node_name(r.node_name);
+    if (mod.empty()) continue;
+    conv_attrs[mod + ".weight"] = r.attr;
+    if (!tensors.count(mod + ".weight")) {
+      auto it = tensors.find(r.weight_input);
+      if (it != tensors.end()) {
+        tensors[mod + ".weight"] = it->second;
+        folded_sources.insert(r.weight_input);
+      }
+    }
+    if (!r.bias_input.empty() && !tensors.count(mod + ".bias")) {
+      auto it = tensors.find(r.bias_input);
+      if (it != tensors.end()) {
+        tensors[mod + ".bias"] = it->second;
+        folded_sources.insert(r.bias_input);
+      }
+    }
   }
 }
 
@@ -194,6 +334,7 @@ void Voice::release() {
 
 void Voice::finalize() {
   if (finalized) return;
+  resolve_conv_nodes();
   Binder B(*this);
   auto count = [&](const std::string& pre, const std::string& post) {
     int i = 0;
@@ -240,7 +381,8 @@ void Voice::finalize() {
   hp.gin = B.has("emb_g.weight") ? (int)B.get("emb_g.weight").dims[1] : 0;
   hp.n_speakers = hp.gin ? (int)B.get("emb_g.weight").dims[0] : 1;
   hp.n_params = 0;
-  for (auto& kv : tensors) hp.n_params += (int64_t)kv.second.f32.size();
+  for (auto& kv : tensors)   // aliases made by resolve_conv_nodes() count once, under their canonical name
+    if (!folded_sources.count(kv.first)) hp.n_params += (int64_t)kv.second.f32.size();
 
   // ---- text encoder ---------------------------------------------------------------------------
   emb = B.upload(embt.f32);
@@ -272,8 +414,13 @@ void Voice::finalize() {
   }
   {
     struct Step { int kind; int id; };   // 0 EA, 1 ConvFlow, 2 Flip
+    // forward order [EA 0, ConvFlow 1, Flip 2, ConvFlow 3, Flip 4, ...]; reverse drops ConvFlow 1 ("a useless vflow") but
+    // keeps its Flip.  An exported graph no longer holds dp.flows.1's weights (unused -> not exported), the synthetic
+    // state dict does: put 1 in the sequence either way so that exactly that one is dropped.
     std::vector<Step> seq{{0, 0}};
-    for (int id : hp.dp_flow_ids) {
+    std::vector<int> cf_ids = hp.dp_flow_ids;
+    if (cf_ids.empty() || cf_ids[0] != 1) cf_ids.insert(cf_ids.begin(), 1);
+    for (int id : cf_ids) {
       seq.push_back({1, id});
       seq.push_back({2, 0});
     }
@@ -294,9 +441,17 @@ void Voice::finalize() {
         dp_flows.push_back(f);
       } else {
         const HostTensor& m = B.get("dp.flows.0.m");
-        const HostTensor& lg = B.get("dp.flows.0.logs");
+        if (m.f32.empty()) throw std::runtime_error("unsupported: dp.flows.0.m is empty");
         ea_m = m.f32[0];
-        ea_logs = lg.f32[0];
+        if (B.has("dp.flows.0.logs")) {
+          const HostTensor& lg = B.get("dp.flows.0.logs");
+          if (lg.f32.empty()) throw std::runtime_error("unsupported: dp.flows.0.logs is empty");
+          ea_logs = lg.f32[0];
+        } else {   // exp(-logs) folded into a constant by the exporter (add_onnx located it)
+          const HostTensor& sc = B.get("dp.flows.0.inv_scale");
+          ea_scale = sc.f32[0];
+          ea_has_scale = true;
+        }
         dp_logw_channel = L0;
       }
     }
@@ -382,11 +537,17 @@ void Voice::finalize() {
     const HostTensor& w = B.get("dec.conv_post.weight");   // [1][C][k]
     const int C = (int)w.dims[1];
     post_k = (int)w.dims[2];
-    if (C != stages.back().ch || C % 4 != 0) throw std::runtime_error("unsupported: dec.conv_post channel count");
+    if (w.dims.size() != 3 || w.dims[0] != 1 || w.f32.size() != (size_t)w.dims[1] * (size_t)w.dims[2] ||
+        C != stages.back().ch || C % 4 != 0) throw std::runtime_error("unsupported: dec.conv_post channel count");
     std::vector<float> pk((size_t)post_k * C);
     for (int c = 0; c < C; ++c)
       for (int t = 0; t < post_k; ++t) pk[(size_t)t * C + c] = w.f32[(size_t)c * post_k + t];
     post_w = B.upload(pk);
+    if (B.has("dec.conv_post.bias")) {
+      const HostTensor& bt = B.get("dec.conv_post.bias");
+      if (bt.f32.size() != 1) throw std::runtime_error("unsupported: dec.conv_post.bias must hold one value");
+      post_b = bt.f32[0];
+    }
     hp.dec_flops_per_frame += rows * 2.0 * C * post_k;
   }
   // algorithmic FLOP tables

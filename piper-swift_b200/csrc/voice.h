@@ -8,6 +8,7 @@
 
 #include <cstdint>
 #include <map>
+#include <set>
 #include <string>
 #include <vector>
 
@@ -22,6 +23,16 @@ struct ConvAttr {
 struct HostTensor {
   std::vector<int64_t> dims;
   std::vector<float> f32;
+};
+
+// One Conv / ConvTranspose node of the graph: what ties an initializer to its module when the initializer itself is
+// anonymous.  A real Piper export removes weight-norm only from `dec` (HiFi-GAN); the flow's WN convolutions keep
+// weight_g / weight_v, which ONNX constant folding turns into initializers called `onnx::Conv_NNNN` - only the node
+// name (`/flow/flows.0/enc/in_layers.0/Conv`) and the bias input (`flow.flows.0.enc.in_layers.0.bias`) still carry the
+// module path.  The reference never needs names (it interprets node by node, GraphExecutor.swift:227-264).
+struct ConvNodeRef {
+  std::string node_name, weight_input, bias_input;
+  ConvAttr attr;
 };
 
 // fp32 SIMT conv weights: [phases][taps][cin][ldw] (+ bias[ldw]); see kernels.h ConvArgs
@@ -96,6 +107,8 @@ struct Voice {
   // host-side staging (route A fills it from the ONNX file, route B from set_weight calls)
   std::map<std::string, HostTensor> tensors;
   std::map<std::string, ConvAttr> conv_attrs;
+  std::vector<ConvNodeRef> conv_nodes;   // resolved by finalize(): canonical `<module>.weight` / `.bias` aliases
+  std::set<std::string> folded_sources;  // initializers that live on under a canonical alias (not counted twice)
   bool finalized = false;
 
   // device weights
@@ -110,6 +123,8 @@ struct Voice {
   std::vector<ConvFlowW> dp_flows;   // execution order
   int dp_logw_channel = 0;           // which physical z channel holds logw after the flips
   float ea_m = 0.f, ea_logs = 0.f;
+  float ea_scale = 0.f;              // exp(-logs) when the export folded it into a constant (ea_has_scale), else unused
+  bool ea_has_scale = false;
   std::vector<CouplingW> flows;      // execution order
   ConvW dec_pre;
   float* dec_cond_w = nullptr;
@@ -117,10 +132,12 @@ struct Voice {
   std::vector<StageW> stages;
   float* post_w = nullptr;           // [k][C]
   int post_k = 7;
+  float post_b = 0.f;                // dec.conv_post.bias (stock Piper: bias=False -> 0)
 
   std::vector<void*> allocs;
 
   void add_onnx(const OnnxModel& m);   // copies initializers + conv attributes
+  void resolve_conv_nodes();           // anonymous conv weights -> `<module>.weight`; weight_g / weight_v pairs folded
   void finalize();                     // throws std::runtime_error on an unrecognised graph
   void release();
   ~Voice() { release(); }

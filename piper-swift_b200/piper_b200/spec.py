@@ -79,6 +79,10 @@ MEDIUM_MULTISPEAKER = VoiceSpec(name="medium-multispeaker", n_speakers=904, gin=
 # fp32 conv kernels and the 96-wide tensor-core tiles.
 X_LOW = VoiceSpec(name="x_low", sample_rate=16000, hidden=96, filter_channels=384)
 
+# the `low` quality tier: the medium architecture trained on 16 kHz audio (piper_train --quality low keeps the default
+# hidden 192 / ResBlock2 / (8, 8, 4) generator; only audio.sample_rate differs; VOICES.md:10-159 lists the tier)
+LOW = VoiceSpec(name="low", sample_rate=16000)
+
 # reduced-size variant used only to keep CPU unit tests fast (same structure, fewer channels)
 TINY = VoiceSpec(
     name="tiny",
@@ -93,9 +97,21 @@ TINY = VoiceSpec(
     rb_dilations=((1, 2), (2, 3)),
 )
 
-SPECS = {s.name: s for s in (MEDIUM, HIGH, MEDIUM_MULTISPEAKER, X_LOW, TINY)}
+SPECS = {s.name: s for s in (MEDIUM, HIGH, MEDIUM_MULTISPEAKER, LOW, X_LOW, TINY)}
 
 # fixture of the reference: bench/fixtures/test_summary.json:8,16-18 and SmokeTests.swift:15-16
 FIXTURE_IDS = [1, 20, 0, 120, 0, 61, 0, 24, 0, 59, 0, 100, 0, 2]
 FIXTURE_SCALES = (0.667, 1.0, 0.8)   # noise_scale, length_scale, noise_w
 DEFAULT_SEED = 1234                  # PiperMetalRuntime.swift:15, benchmark_onnxruntime.py:39
+
+# The 50 ONNX op types of a Piper voice graph = the cases of the reference's executor switch
+# (Sources/PiperMetal/Execution/GraphExecutor.swift:591-2663; anything else throws
+# ExecutionError.unsupportedOp, :2661-2662).  tests/test_real_export_cpu.py checks that the upstream network restated
+# in oracle/vits_modules.py, exported by torch's own ONNX exporter, uses exactly these (plus `Constant`, which the
+# exporter of the voices' era wrote as initializers).
+REFERENCE_GRAPH_OPS = (
+    "Add", "And", "Cast", "Ceil", "Clip", "Concat", "ConstantOfShape", "Conv", "ConvTranspose", "CumSum", "Div",
+    "Equal", "Erf", "Exp", "Expand", "Gather", "GatherElements", "GatherND", "GreaterOrEqual", "LeakyRelu", "Less",
+    "LessOrEqual", "MatMul", "Mul", "Neg", "NonZero", "Not", "Pad", "Pow", "RandomNormalLike", "Range", "ReduceMax",
+    "ReduceMean", "ReduceSum", "Relu", "Reshape", "ScatterND", "Shape", "Sigmoid", "Slice", "Softmax", "Softplus",
+    "Split", "Sqrt", "Squeeze", "Sub", "Tanh", "Transpose", "Unsqueeze", "Where")
