@@ -139,6 +139,7 @@ int piper_b200_abi_version(void);
 const char* piper_b200_last_error(const piper_b200_ctx* ctx);   /* ctx may be NULL */
 
 /* MetalContext.init (MetalContext.swift:11-32): device + stream + kernel module */
+int piper_b200_device_count(int* count);   /* the reference has one MTLDevice (MetalContext.swift:12); a B200 box has up to 8 */
 int piper_b200_create(int device, piper_b200_ctx** out);
 void piper_b200_destroy(piper_b200_ctx* ctx);
 

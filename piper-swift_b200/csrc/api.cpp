@@ -51,6 +51,22 @@ const char* piper_b200_last_error(const piper_b200_ctx* ctx) {
   return ctx ? ctx->c.last_error.c_str() : g_error.c_str();
 }
 
+int piper_b200_device_count(int* count) {
+  if (!count) {
+    g_error = "invalid argument: count is null";
+    return PIPER_B200_ERR_INVALID_ARGUMENT;
+  }
+  *count = 0;
+  const cudaError_t e = cudaGetDeviceCount(count);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    *count = 0;
+    g_error = std::string("cuda: ") + cudaGetErrorString(e);
+    return PIPER_B200_ERR_CUDA;
+  }
+  return PIPER_B200_OK;
+}
+
 int piper_b200_create(int device, piper_b200_ctx** out) {
   if (!out) {
     g_error = "invalid argument: out is null";

@@ -26,6 +26,8 @@ LIB_PATH = os.path.join(os.path.dirname(_HERE), "libpiper_b200.so")
 OK = 0
 PRECISION = {"fp32": 0, "bf16": 1, "f16": 2}
 FLAG_IDS_ON_DEVICE, FLAG_KEEP_ON_DEVICE, FLAG_KEEP_STAGES, FLAG_PCM16, FLAG_PROFILE, FLAG_STREAM = 1, 2, 4, 8, 16, 32
+FLAG_PCM16_ONLY = 64
+ABI_VERSION = 2
 ERR_NAMES = {1: "invalid_argument", 2: "io", 3: "decode", 4: "unsupported", 5: "cuda", 6: "state", 7: "capacity"}
 
 
@@ -88,6 +90,7 @@ def load_library(path: str = LIB_PATH):
     sig = {
         "piper_b200_abi_version": (C.c_int, []),
         "piper_b200_last_error": (C.c_char_p, [P]),
+        "piper_b200_device_count": (C.c_int, [C.POINTER(C.c_int)]),
         "piper_b200_create": (C.c_int, [C.c_int, C.POINTER(P)]),
         "piper_b200_destroy": (None, [P]),
         "piper_b200_load_voice": (C.c_int, [P, C.c_char_p, C.c_char_p]),
@@ -98,6 +101,11 @@ def load_library(path: str = LIB_PATH):
         "piper_b200_get_voice_info": (C.c_int, [P, C.POINTER(VoiceInfo)]),
         "piper_b200_set_precision": (C.c_int, [P, C.c_int32]),
         "piper_b200_set_stream": (C.c_int, [P, P]),
+        "piper_b200_set_output_buffer": (C.c_int, [P, P, C.c_size_t]),
+        "piper_b200_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(P)]),
+        "piper_b200_host_free": (None, [P]),
+        "piper_b200_host_register": (C.c_int, [P, C.c_size_t]),
+        "piper_b200_host_unregister": (C.c_int, [P]),
         "piper_b200_synthesize": (C.c_int, [P, C.POINTER(Request), C.POINTER(Result)]),
         "piper_b200_get_timings": (C.c_int, [P, C.POINTER(Timings)]),
         "piper_b200_stream_next": (C.c_int, [P, C.c_int64, C.POINTER(Result), C.POINTER(C.c_int32)]),
@@ -123,8 +131,56 @@ EXPORTED_SYMBOLS = [
     "piper_b200_finalize", "piper_b200_get_voice_info", "piper_b200_set_precision", "piper_b200_set_stream",
     "piper_b200_synthesize", "piper_b200_get_timings", "piper_b200_get_stage", "piper_b200_length_regulate",
     "piper_b200_random_normal", "piper_b200_selftest_conv", "piper_b200_ipa_to_ids", "piper_b200_config_ipa_to_ids",
-    "piper_b200_stream_next",
+    "piper_b200_stream_next", "piper_b200_device_count", "piper_b200_set_output_buffer", "piper_b200_host_alloc",
+    "piper_b200_host_free", "piper_b200_host_register", "piper_b200_host_unregister",
 ]
+
+
+def device_count() -> int:
+    """GPUs visible to the process (the reference has one MTLDevice, MetalContext.swift:11-19)."""
+    lib = load_library()
+    n = C.c_int(0)
+    rc = lib.piper_b200_device_count(C.byref(n))
+    if rc != OK:
+        raise PiperB200Error(rc, lib.piper_b200_last_error(None).decode())
+    return int(n.value)
+
+
+class HostArena:
+    """Page-locked host memory that one or several contexts write their audio into (piper_b200_set_output_buffer):
+    allocated by the library (portable across the GPUs of the process), or an existing mapping - e.g. a /dev/shm
+    file shared by the ranks of one box - pinned in place."""
+
+    def __init__(self, nbytes: int, mapping=None):
+        self._lib = load_library()
+        self.nbytes = int(nbytes)
+        self._owned = mapping is None
+        self._mapping = mapping
+        if mapping is None:
+            p = C.c_void_p()
+            rc = self._lib.piper_b200_host_alloc(self.nbytes, C.byref(p))
+            if rc != OK:
+                raise PiperB200Error(rc, self._lib.piper_b200_last_error(None).decode())
+            self.ptr = int(p.value)
+        else:
+            self.ptr = C.addressof(C.c_char.from_buffer(mapping))
+            rc = self._lib.piper_b200_host_register(C.c_void_p(self.ptr), self.nbytes)
+            if rc != OK:
+                raise PiperB200Error(rc, self._lib.piper_b200_last_error(None).decode())
+
+    def close(self):
+        if getattr(self, "ptr", 0):
+            if self._owned:
+                self._lib.piper_b200_host_free(C.c_void_p(self.ptr))
+            else:
+                self._lib.piper_b200_host_unregister(C.c_void_p(self.ptr))
+            self.ptr = 0
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def config_ipa_to_ids(config_path: str, ipa: str) -> List[int]:
@@ -221,6 +277,12 @@ class PiperCUDARuntime:
     def set_stream(self, cuda_stream_ptr: Optional[int]):
         self._check(self._lib.piper_b200_set_stream(self._ctx, C.c_void_p(cuda_stream_ptr or 0)))
 
+    def set_output_buffer(self, ptr: Optional[int], nbytes: int = 0):
+        """Caller-owned page-locked destination of the audio (HostArena); None restores the library's own buffer.
+        Results then are views into that memory: they stay valid until the caller reuses it."""
+        self._check(self._lib.piper_b200_set_output_buffer(self._ctx, C.c_void_p(ptr or 0), nbytes if ptr else 0))
+        self._out_ptr = ptr or None
+
     @property
     def sample_rate(self) -> int:
         return int(self.info.sample_rate)
@@ -291,17 +353,18 @@ class PiperCUDARuntime:
                          noise_dp: Optional[Sequence[np.ndarray]] = None,
                          noise_main: Optional[Sequence[np.ndarray]] = None,
                          seed: Optional[int] = None, keep_stages: bool = False, pcm16: bool = False,
-                         copy: bool = True) -> BatchResult:
+                         copy: bool = True, pcm16_only: bool = False) -> BatchResult:
         B = len(utterances)
         lengths = np.array([len(u) for u in utterances], dtype=np.int64)
         ids = np.concatenate([np.asarray(u, dtype=np.int64) for u in utterances]) if B else np.zeros(0, np.int64)
         return self.synthesize_packed(ids, lengths, noise_scale, length_scale, noise_w, speaker_ids, noise_dp,
-                                      noise_main, seed, keep_stages, pcm16, copy)
+                                      noise_main, seed, keep_stages, pcm16, copy, pcm16_only=pcm16_only)
 
     def synthesize_packed(self, ids: np.ndarray, lengths: np.ndarray, noise_scale=None, length_scale=None,
                           noise_w=None, speaker_ids=None, noise_dp=None, noise_main=None, seed=None,
                           keep_stages=False, pcm16=False, copy=True, ids_device_ptr: Optional[int] = None,
-                          keep_on_device: bool = False, profile: bool = False, stream: bool = False) -> BatchResult:
+                          keep_on_device: bool = False, profile: bool = False, stream: bool = False,
+                          pcm16_only: bool = False) -> BatchResult:
         B = int(len(lengths))
         lengths = np.ascontiguousarray(lengths, dtype=np.int64)
         rq = Request()
@@ -340,6 +403,7 @@ class PiperCUDARuntime:
         rq.seed = self.options.seed if seed is None else seed
         rq.flags = ((FLAG_KEEP_STAGES if keep_stages else 0) | (FLAG_PCM16 if pcm16 else 0) |
                     (FLAG_PROFILE if profile else 0) | (FLAG_STREAM if stream else 0) |
+                    (FLAG_PCM16_ONLY if pcm16_only else 0) |
                     (FLAG_IDS_ON_DEVICE if ids_device_ptr is not None else 0) |
                     (FLAG_KEEP_ON_DEVICE if keep_on_device else 0))
         rs = Result()
@@ -357,8 +421,15 @@ class PiperCUDARuntime:
         if stream:      # audio follows through piper_b200_stream_next
             return out
         total = int(rs.total_samples)
+        own = getattr(self, "_out_ptr", None) is None      # a caller-owned buffer is the caller's to keep: no copy
+        if pcm16_only:      # int16 is the only host output (half the device->host bytes)
+            p = np.ctypeslib.as_array(C.cast(rs.pcm16, C.POINTER(C.c_int16)), shape=(total,))
+            if copy and own:
+                p = p.copy()
+            out.pcm16 = [p[offs[b]:offs[b + 1]] for b in range(B)]
+            return out
         flat = np.ctypeslib.as_array(C.cast(rs.audio, C.POINTER(C.c_float)), shape=(total,))
-        if copy:
+        if copy and own:
             flat = flat.copy()
         out.audio = [flat[offs[b]:offs[b + 1]] for b in range(B)]
         if pcm16:

@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol():
     for s in syms:
         assert hasattr(lib, s), f"{s} declared in include/piper_b200.h but not exported"
     assert sorted(runtime.EXPORTED_SYMBOLS) == syms
-    assert lib.piper_b200_abi_version() == 1
+    assert lib.piper_b200_abi_version() == runtime.ABI_VERSION == 2
 
 
 def test_struct_sizes_match_header():
