@@ -65,3 +65,139 @@ def test_world_size_2_gloo_gather():
         for i in s_:
             expect[i] = 3 * lens[i] + r
     assert got == expect
+
+
+# ---- the product's multi-GPU drivers, host logic only (fake one-"GPU" runtimes; the real ones: tests/test_gpu_pool.py) ----
+import ctypes as C
+from types import SimpleNamespace
+
+from piper_b200 import sharding
+
+HOP = 4
+
+
+class _Short(RuntimeError):
+    code = 7
+
+
+class FakeRuntime:
+    """Stands in for PiperCUDARuntime behind ShardedSynthesizer / PiperCUDAPool: 3 frames per id (+1 for odd speakers),
+    sample s of an utterance = sum(ids) + s, written to the caller-owned output buffer like the C ABI does."""
+
+    def __init__(self, *a, **k):
+        self.ptr, self.cap = None, 0
+        self.info = SimpleNamespace(hop=HOP, sample_rate=22050)
+
+    def set_output_buffer(self, ptr, nbytes=0):
+        self.ptr, self.cap = ptr, nbytes
+
+    def close(self):
+        pass
+
+    @staticmethod
+    def expected(u, sid=0):
+        frames = 3 * len(u) + (sid % 2)
+        return (np.arange(frames * HOP, dtype=np.float32) + np.float32(sum(u))), frames
+
+    def synthesize_batch(self, utts, ns=None, ls=None, nw=None, speaker_ids=None, seed=None, copy=False,
+                         pcm16_only=False):
+        sids = speaker_ids or [0] * len(utts)
+        audio = [self.expected(u, s) for u, s in zip(utts, sids)]
+        total = sum(a.size for a, _ in audio)
+        if total * 4 > self.cap:
+            raise _Short(f"[capacity] the output buffer holds {self.cap} bytes, this result needs {total * 4}")
+        buf = np.frombuffer((C.c_char * (total * 4)).from_address(self.ptr), dtype=np.float32)
+        out, at = [], 0
+        for a, _ in audio:
+            buf[at:at + a.size] = a
+            out.append(buf[at:at + a.size])
+            at += a.size
+        return SimpleNamespace(audio=out, pcm16=None, frame_lengths=np.array([f for _, f in audio], np.int64),
+                               durations=[np.full(len(u), 3, np.int32) for u in utts], total_samples=total,
+                               total_frames=sum(f for _, f in audio))
+
+
+def _sharded_worker(rank, world, port, utts, sids, bytes_per_id, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    syn = sharding.ShardedSynthesizer(FakeRuntime(), HOP, bytes_per_id=bytes_per_id, pin=False, tag=f"test{port}")
+    ok = True
+    for _ in range(2):                       # second call reuses the arena
+        res = syn.synthesize_batch(utts, speaker_ids=sids)
+        if rank == 0:
+            for i, u in enumerate(utts):
+                exp, frames = FakeRuntime.expected(u, sids[i])
+                ok = ok and res.frame_lengths[i] == frames and np.array_equal(res.audio[i], exp)
+            ok = ok and res.total_samples == sum(a.size for a in res.audio)
+            ok = ok and sorted(i for s in syn.last_shards for i in s) == list(range(len(utts)))
+    dist.barrier()
+    if rank == 0:
+        q.put(bool(ok))
+    del res
+    syn.close()
+    dist.destroy_process_group()
+
+
+def _run_sharded(bytes_per_id):
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    utts = synthetic_utterances(13, 64, 5, 30)
+    sids = list(range(13))
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_sharded_worker, args=(r, 2, port, utts, sids, bytes_per_id, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    ok = q.get(timeout=120)
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    assert ok
+
+
+def test_sharded_synthesizer_world_size_2_gloo():
+    """every utterance comes back in the original order with its own audio, out of one /dev/shm arena"""
+    _run_sharded(bytes_per_id=8 * HOP * 4)
+
+
+def test_sharded_synthesizer_grows_a_short_arena():
+    """a region that is too small is reported by the runtime (ERR_CAPACITY), agreed on by all ranks, and retried"""
+    _run_sharded(bytes_per_id=HOP * 4)          # 1 frame per id reserved, 3 needed
+
+
+def test_region_layout_is_disjoint_and_aligned():
+    lens = [7, 3, 9, 1, 4]
+    sh = shard_utterances(lens, 3)
+    offs, caps = sharding.region_layout(sh, lens, 100)
+    for r in range(3):
+        assert offs[r] % 4096 == 0 and caps[r] % 4096 == 0
+        assert caps[r] >= 100 * sum(lens[i] for i in sh[r])
+        if r:
+            assert offs[r] == offs[r - 1] + caps[r - 1]
+
+
+class _PlainArena:                              # pinned allocation replaced by plain memory (no CUDA here)
+    def __init__(self, nbytes):
+        self.buf = (C.c_char * nbytes)()
+        self.ptr, self.nbytes = C.addressof(self.buf), nbytes
+
+    def close(self):
+        pass
+
+
+def test_pool_gathers_in_original_order():
+    """PiperCUDAPool over three fake devices: same contract, threads instead of ranks"""
+    pool = sharding.PiperCUDAPool("m", "c", devices=[0, 1, 2], runtime_factory=FakeRuntime, bytes_per_id=HOP * 4,
+                                  arena_factory=_PlainArena)
+    utts = synthetic_utterances(20, 64, 5, 30)
+    sids = list(range(20))
+    res = pool.synthesize_batch(utts, speaker_ids=sids)
+    for i, u in enumerate(utts):
+        exp, frames = FakeRuntime.expected(u, sids[i])
+        assert res.frame_lengths[i] == frames and np.array_equal(res.audio[i], exp)
+        assert res.rank_of[i] == next(r for r, s in enumerate(pool.last_shards) if i in s)
+    assert pool._bytes_per_id > HOP * 4          # the short first estimate was grown
+    pool.close()
