@@ -203,6 +203,20 @@ int piper_b200_length_regulate(piper_b200_ctx* ctx, const float* logw, const int
                                int32_t batch, float length_scale, int32_t* durations,
                                int64_t* frame_lengths, int32_t* frame_index, int64_t frame_capacity);
 
+/* The same durations / frame counts for callers that must not allocate (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  NO counterpart in the reference.
+ * Calls no cudaMalloc / cudaFree or allocating routine: every device buffer lives in one file-scope
+ * `static __device__` array of PIPER_B200_NOALLOC_MAX_IDS / _MAX_BATCH capacity (about 0.8 MB, held by every GPU that
+ * loads the library until the process exits); larger inputs return PIPER_B200_ERR_CAPACITY.  All calls on a GPU share
+ * that array (it keeps the last call's contents; the call clears what it needs): calls that overlap on one GPU race,
+ * the caller serialises them.  logw, lengths, durations, frame_lengths are host memory as in
+ * piper_b200_length_regulate; no frame_index output. */
+#define PIPER_B200_NOALLOC_MAX_IDS 65536    /* phoneme ids over the whole batch */
+#define PIPER_B200_NOALLOC_MAX_BATCH 1024   /* utterances per call */
+int piper_b200_length_regulate_noalloc(piper_b200_ctx* ctx, const float* logw, const int64_t* lengths,
+                                       int32_t batch, float length_scale, int32_t* durations,
+                                       int64_t* frame_lengths);
+
 /* IPA text -> phoneme ids with the voice's phoneme_id_map: BOS "^", id + blank "_" per Unicode scalar,
  * EOS "$" (ESpeakPhonemizer.phonemeIDs, Sources/PiperCLI/ESpeakPhonemizer.swift:73-100; idsFromIPA,
  * PiperCLI.swift:115-136).  Host-only table lookup, needs a voice loaded from files (route A).

@@ -111,6 +111,7 @@ def load_library(path: str = LIB_PATH):
         "piper_b200_stream_next": (C.c_int, [P, C.c_int64, C.POINTER(Result), C.POINTER(C.c_int32)]),
         "piper_b200_get_stage": (C.c_int, [P, C.c_char_p, C.c_int32, P, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
         "piper_b200_length_regulate": (C.c_int, [P, P, P, C.c_int32, C.c_float, P, P, P, C.c_int64]),
+        "piper_b200_length_regulate_noalloc": (C.c_int, [P, P, P, C.c_int32, C.c_float, P, P]),
         "piper_b200_random_normal": (C.c_int, [P, C.c_uint64, C.c_int64, P]),
         "piper_b200_selftest_conv": (C.c_int, [P] + [C.c_int32] * 8 + [C.POINTER(C.c_float)]),
         "piper_b200_ipa_to_ids": (C.c_int, [P, C.c_char_p, C.POINTER(C.c_int64), C.c_int64, C.POINTER(C.c_int64)]),
@@ -133,7 +134,9 @@ EXPORTED_SYMBOLS = [
     "piper_b200_random_normal", "piper_b200_selftest_conv", "piper_b200_ipa_to_ids", "piper_b200_config_ipa_to_ids",
     "piper_b200_stream_next", "piper_b200_device_count", "piper_b200_set_output_buffer", "piper_b200_host_alloc",
     "piper_b200_host_free", "piper_b200_host_register", "piper_b200_host_unregister",
+    "piper_b200_length_regulate_noalloc",
 ]
+NOALLOC_MAX_IDS, NOALLOC_MAX_BATCH = 65536, 1024
 
 
 def device_count() -> int:
@@ -462,6 +465,20 @@ class PiperCUDARuntime:
                                                          idx.ctypes.data, cap))
         off = np.concatenate([[0], np.cumsum(lengths)])
         return ([dur[off[b]:off[b + 1]] for b in range(B)], fl, [idx[b, :fl[b]] for b in range(B)])
+
+    def length_regulate_noalloc(self, logw: Sequence[np.ndarray], length_scale: float):
+        """piper_b200_length_regulate_noalloc: (durations per utterance, frame_lengths) out of the library's fixed
+        device scratch array - no allocation on the device side; at most NOALLOC_MAX_IDS ids / NOALLOC_MAX_BATCH
+        utterances.  Calls on one GPU must not overlap."""
+        B = len(logw)
+        lengths = np.array([len(l) for l in logw], dtype=np.int64)
+        flat = np.ascontiguousarray(np.concatenate([np.asarray(l, np.float32) for l in logw]))
+        dur = np.zeros(int(lengths.sum()), np.int32)
+        fl = np.zeros(B, np.int64)
+        self._check(self._lib.piper_b200_length_regulate_noalloc(self._ctx, flat.ctypes.data, lengths.ctypes.data, B,
+                                                                 length_scale, dur.ctypes.data, fl.ctypes.data))
+        off = np.concatenate([[0], np.cumsum(lengths)])
+        return [dur[off[b]:off[b + 1]] for b in range(B)], fl
 
     def random_normal(self, count: int, seed: int = 1234) -> np.ndarray:
         out = np.zeros(count, np.float32)
