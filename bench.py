@@ -327,8 +327,11 @@ def main():
             ms_e, acc = timed(step_e2e, steps)
             samples_e = all_sum(sum(a[0] for a in acc))
             tm_e = acc[-1][1]
+            last = acc[-1][2]
+            if getattr(last, "audio", None):     # views into the pinned result buffer, which later legs reuse: copy
+                last.audio = [np.array(a) for a in last.audio]      # (after the timed region)
             out.update(e2e_ms=ms_e, e2e_value=samples_e / sr / (ms_e / 1000.0), e2e_ms_per_step=ms_e / steps,
-                       h2d=all_sum(tm_e["h2d_bytes"]), d2h=all_sum(tm_e["d2h_bytes"]), last=acc[-1][2])
+                       h2d=all_sum(tm_e["h2d_bytes"]), d2h=all_sum(tm_e["d2h_bytes"]), last=last)
             if sharded:
                 rt.set_output_buffer(None)
         return out

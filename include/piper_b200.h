@@ -153,6 +153,17 @@ int piper_b200_set_weight(piper_b200_ctx* ctx, const char* name, int32_t dtype, 
                           int32_t rank, const void* data, size_t bytes);
 int piper_b200_set_conv_attr(piper_b200_ctx* ctx, const char* weight_name, int32_t stride,
                              int32_t dilation, int32_t group, int32_t pad_begin, int32_t pad_end);
+/* Route B, graph side: one call per node of ONNXGraph.nodes (ONNXIR.swift:68-84; only Conv, ConvTranspose, Gather, Sub,
+ * Mul and Exp nodes are kept, the others are ignored, so a host may simply pass them all).  Real piper_train exports do not
+ * name every weight after its module (weight-normed flow convolutions become `onnx::Conv_NNNN`, the embedding table of a
+ * single-speaker voice is the initializer called `sid`, exp(-logs) of the duration predictor is folded): the binder
+ * follows these nodes exactly like route A does, which is what the reference's node-by-node interpreter gets for free
+ * (GraphExecutor.swift:227-264).  stride / dilation / group / pads = the Conv attributes (first spatial axis; <= 0 or
+ * pad_begin < 0: ONNX default).  The float value of a Constant node is passed with piper_b200_set_weight under the
+ * node's OUTPUT name. */
+int piper_b200_add_node(piper_b200_ctx* ctx, const char* op_type, const char* name, const char* const* inputs,
+                        int32_t n_inputs, const char* const* outputs, int32_t n_outputs, int32_t stride, int32_t dilation,
+                        int32_t group, int32_t pad_begin, int32_t pad_end);
 int piper_b200_set_config(piper_b200_ctx* ctx, int32_t sample_rate, int32_t num_speakers,
                           float noise_scale, float length_scale, float noise_w);
 int piper_b200_finalize(piper_b200_ctx* ctx);   /* recognise the VITS graph, repack to kernel layouts */

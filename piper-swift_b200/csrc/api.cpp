@@ -175,6 +175,29 @@ int piper_b200_set_conv_attr(piper_b200_ctx* ctx, const char* weight_name, int32
   });
 }
 
+int piper_b200_add_node(piper_b200_ctx* ctx, const char* op_type, const char* name, const char* const* inputs,
+                        int32_t n_inputs, const char* const* outputs, int32_t n_outputs, int32_t stride, int32_t dilation,
+                        int32_t group, int32_t pad_begin, int32_t pad_end) {
+  if (!ctx || !op_type || n_inputs < 0 || n_outputs < 0 || (n_inputs && !inputs) || (n_outputs && !outputs)) {
+    g_error = "invalid argument: null pointer";
+    return PIPER_B200_ERR_INVALID_ARGUMENT;
+  }
+  return guarded(ctx, [&] {
+    if (ctx->c.voice.finalized) throw std::runtime_error("state: voice already finalized");
+    piper::GraphNodeRef g;
+    g.op_type = op_type;
+    g.name = name ? name : "";
+    for (int i = 0; i < n_inputs; ++i) g.inputs.push_back(inputs[i] ? inputs[i] : "");
+    for (int i = 0; i < n_outputs; ++i) g.outputs.push_back(outputs[i] ? outputs[i] : "");
+    g.attr.stride = stride > 0 ? stride : 1;
+    g.attr.dilation = dilation > 0 ? dilation : 1;
+    g.attr.group = group > 0 ? group : 1;
+    g.attr.pad_begin = pad_begin; g.attr.pad_end = pad_end;
+    ctx->c.voice.add_node(std::move(g));
+    return PIPER_B200_OK;
+  });
+}
+
 int piper_b200_set_config(piper_b200_ctx* ctx, int32_t sample_rate, int32_t num_speakers, float noise_scale,
                           float length_scale, float noise_w) {
   if (!ctx) {

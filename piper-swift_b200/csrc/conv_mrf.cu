@@ -704,7 +704,8 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
     throw std::runtime_error("conv_mrf: fused conv_post needs C = 32 and an odd kernel of at most 7 taps");
   if (!mrf_tc_supported(a.C, a.nk, a.k, a.d0, a.d1)) throw std::runtime_error("conv_mrf: unsupported stage shape");
   static int num_sms = 0;
-  if (!num_sms) {
+  static PerDeviceOnce once;
+  once.run([&] {
     int dev = 0;
     cudaGetDevice(&dev);
     if (cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || num_sms <= 0)
@@ -722,7 +723,7 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
         cudaFuncSetAttribute(mrf_tc_kernel<64, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
         cudaFuncSetAttribute(mrf_tc_kernel<128, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess)
       throw std::runtime_error("cuda: cannot raise dynamic shared memory limit for mrf_tc_kernel");
-  }
+  });
   MrfParams p{};
   p.R = a.R; p.C = a.C; p.nk = a.nk;
   int halo = 0, kmax = 0;

@@ -887,14 +887,15 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
     throw std::runtime_error("conv_tc: merged polyphase weights need the persistent kernel");
   if ((persist_env || w.split) && n_groups * a.nt <= 256) {
     static int num_sms = 0;
-    if (!num_sms) {
+    static PerDeviceOnce once;
+    once.run([&] {
       int dev = 0;
       cudaGetDevice(&dev);
       if (cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || num_sms <= 0)
         throw std::runtime_error("cuda: cannot query the SM count");
       if (cudaFuncSetAttribute(conv_tc_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess)
         throw std::runtime_error("cuda: cannot raise dynamic shared memory limit for conv_tc_persist_kernel");
-    }
+    });
     const CUtensorMap tbp = make_map(w.w, (uint64_t)w.cin_pad * kmul, (uint64_t)w.phases * w.taps * w.cout,
                                      (uint64_t)w.cin_pad * kmul, w.kb, a.nt, a.f16);
     p.window = 0;
@@ -942,12 +943,11 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
   if (stages > n_it) stages = n_it < 2 ? 2 : n_it;
   const size_t smem = (size_t)a_ring + (size_t)stages * stage_bytes + 1024 + 256;
   if (smem > (size_t)TC_SMEM_MAX) throw std::runtime_error("conv_tc: tile does not fit in shared memory");
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce once_tile;
+  once_tile.run([&] {
     if (cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess)
       throw std::runtime_error("cuda: cannot raise dynamic shared memory limit for conv_tc_kernel");
-    attr_set = true;
-  }
+  });
   CUtensorMap tans = ta;
   if (p.window == 2) tans = make_map_ns(a.in, (uint64_t)a.cin, (uint64_t)a.R_in, (uint64_t)a.ldin, 2 * TC_BM, w.kb / 8, a.f16);
   dim3 grid((a.Q + TC_BM - 1) / TC_BM, a.n_tiles, w.phases);

@@ -7,9 +7,28 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cstdint>
+#include <mutex>
 #include <vector>
 
 namespace piper {
+
+// One-time set-up PER DEVICE at a launch site: cudaFuncSetAttribute (the raised dynamic shared-memory limit) belongs to
+// the device that is current when it is called, so a process driving several GPUs (PiperCUDAPool: one context per
+// device, one host thread each) must repeat it on each of them.  `static PerDeviceOnce once; once.run([&] {...});`
+struct PerDeviceOnce {
+  std::mutex mu;
+  uint64_t done = 0;
+  template <typename F>
+  void run(F&& f) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const uint64_t bit = 1ull << (dev & 63);
+    std::lock_guard<std::mutex> lk(mu);
+    if (done & bit) return;
+    f();
+    done |= bit;
+  }
+};
 
 // optional per-kernel-class device timing (PIPER_B200_FLAG_PROFILE): CUDA events around every launch of
 // the three GEMM-class kernels, summed after the call's final synchronisation

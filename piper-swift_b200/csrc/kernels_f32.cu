@@ -933,12 +933,11 @@ void launch_attention(Exec& ex, const float* qkv, const float* rel_k, const floa
   if (at2_env && kc == AT2_D && nrel <= AT2_MAXREL && H % 4 == 0) {
     const size_t smem2 = sizeof(float) * (AT2_Q * AT2_LD + AT2_K * AT2_LD + AT2_K * AT2_D + AT2_Q * AT2_LDP +
                                           2 * AT2_MAXREL * AT2_D + AT2_Q * AT2_MAXREL);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce once;
+    once.run([&] {
       if (cudaFuncSetAttribute(attention96_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2) != cudaSuccess)
         throw std::runtime_error("cuda: cannot raise dynamic shared memory limit for attention96_kernel");
-      attr_set = true;
-    }
+    });
     static const int split_env = [] { const char* e = getenv("PIPER_B200_ATT_SPLIT"); return e ? atoi(e) : 1; }();
     // key splits for long utterances (att96_splits): only with a scratch buffer; the split count per utterance is a
     // function of its own length, the grid covers the longest one

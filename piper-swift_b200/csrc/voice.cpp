@@ -183,27 +183,51 @@ void Voice::add_onnx(const OnnxModel& m) {
     h.f32 = t.f32;
     tensors[t.name] = std::move(h);
   }
-  // float values of Constant nodes, by output name (an export without constant folding keeps scalars there)
-  std::map<std::string, const OnnxTensor*> constants;
-  for (const auto& n : m.nodes)
-    if (n.op_type == "Constant" && !n.outputs.empty())
-      if (auto x = n.attr("value"); x && x->has_t && x->t.dtype == 1) constants[n.outputs[0]] = &x->t;
   for (const auto& n : m.nodes) {
-    if ((n.op_type != "Conv" && n.op_type != "ConvTranspose") || n.inputs.size() < 2) continue;
-    ConvAttr a;
-    if (auto x = n.attr("strides"); x && !x->ints.empty()) a.stride = (int)x->ints[0];
-    if (auto x = n.attr("dilations"); x && !x->ints.empty()) a.dilation = (int)x->ints[0];
-    if (auto x = n.attr("group")) a.group = (int)x->i;
-    if (auto x = n.attr("pads"); x && x->ints.size() >= 2) {
-      a.pad_begin = (int)x->ints[0];
-      a.pad_end = (int)x->ints[1];
+    // float values of Constant nodes live under their output name (an export without constant folding keeps scalars there)
+    if (n.op_type == "Constant" && !n.outputs.empty()) {
+      if (auto x = n.attr("value"); x && x->has_t && x->t.dtype == 1 && !tensors.count(n.outputs[0])) {
+        HostTensor h;
+        h.dims = x->t.dims;
+        h.f32 = x->t.f32;
+        tensors[n.outputs[0]] = std::move(h);
+        folded_sources.insert(n.outputs[0]);
+      }
+      continue;
     }
-    conv_attrs[n.inputs[1]] = a;
+    GraphNodeRef g;
+    g.op_type = n.op_type; g.name = n.name; g.inputs = n.inputs; g.outputs = n.outputs;
+    if (auto x = n.attr("strides"); x && !x->ints.empty()) g.attr.stride = (int)x->ints[0];
+    if (auto x = n.attr("dilations"); x && !x->ints.empty()) g.attr.dilation = (int)x->ints[0];
+    if (auto x = n.attr("group")) g.attr.group = (int)x->i;
+    if (auto x = n.attr("pads"); x && x->ints.size() >= 2) {
+      g.attr.pad_begin = (int)x->ints[0];
+      g.attr.pad_end = (int)x->ints[1];
+    }
+    add_node(std::move(g));
+  }
+}
+
+// Route A (add_onnx) and route B (piper_b200_add_node) both end here: only the node kinds the binder needs are kept
+void Voice::add_node(GraphNodeRef g) {
+  static const char* kept[] = {"Conv", "ConvTranspose", "Gather", "Sub", "Mul", "Exp"};
+  for (const char* k : kept)
+    if (g.op_type == k) {
+      nodes.push_back(std::move(g));
+      return;
+    }
+}
+
+// What the graph says about initializers that are not named after their module (real piper_train exports)
+void Voice::resolve_graph() {
+  for (const GraphNodeRef& n : nodes) {
+    if ((n.op_type != "Conv" && n.op_type != "ConvTranspose") || n.inputs.size() < 2) continue;
+    conv_attrs[n.inputs[1]] = n.attr;
     ConvNodeRef r;
     r.node_name = n.name;
     r.weight_input = n.inputs[1];
     if (n.inputs.size() >= 3) r.bias_input = n.inputs[2];
-    r.attr = a;
+    r.attr = n.attr;
     conv_nodes.push_back(std::move(r));
   }
   // The phoneme embedding of a real single-speaker export is NOT called enc_p.emb.weight: piper_train passes
@@ -211,7 +235,7 @@ void Voice::add_onnx(const OnnxModel& m) {
   // "sid" to the first parameter - the embedding table (that is the `sid` initializer ONNXParsingTests.swift:31
   // finds; the first node is Gather(sid, input), :35).  Bind the table through that Gather.
   if (!tensors.count("enc_p.emb.weight"))
-    for (const auto& n : m.nodes)
+    for (const GraphNodeRef& n : nodes)
       if (n.op_type == "Gather" && n.inputs.size() == 2 && n.inputs[1] == "input") {
         auto it = tensors.find(n.inputs[0]);
         if (it != tensors.end() && it->second.dims.size() == 2) {
@@ -220,20 +244,20 @@ void Voice::add_onnx(const OnnxModel& m) {
         }
         break;
       }
-  // ElementwiseAffine of the duration predictor, reverse: (z - m) * exp(-logs).  Constant folding replaces exp(-logs) by
-  // an anonymous constant and drops `dp.flows.0.logs`: follow Sub(., dp.flows.0.m) to the Mul that scales it.
+  // ElementwiseAffine of the duration predictor, reverse: (z - m) * exp(-logs).  Constant folding replaces -logs (or the
+  // whole factor) by an anonymous constant and drops `dp.flows.0.logs`: follow Sub(., dp.flows.0.m) to the Mul that scales it.
   if (!tensors.count("dp.flows.0.logs") && !tensors.count("dp.flows.0.inv_scale")) {
     std::string diff;
-    for (const auto& n : m.nodes)
+    for (const GraphNodeRef& n : nodes)
       if (n.op_type == "Sub" && n.inputs.size() == 2 && n.inputs[1] == "dp.flows.0.m" && !n.outputs.empty())
         diff = n.outputs[0];
-    for (const auto& n : m.nodes) {
+    for (const GraphNodeRef& n : nodes) {
       if (diff.empty() || n.op_type != "Mul" || n.inputs.size() != 2) continue;
       const std::string* other = n.inputs[0] == diff ? &n.inputs[1] : (n.inputs[1] == diff ? &n.inputs[0] : nullptr);
       if (!other) continue;
       // (a) only the negation was folded: Mul(diff, Exp(onnx::Exp_NNNN)) with the initializer holding -logs
       bool found = false;
-      for (const auto& e : m.nodes)
+      for (const GraphNodeRef& e : nodes)
         if (e.op_type == "Exp" && e.inputs.size() == 1 && !e.outputs.empty() && e.outputs[0] == *other) {
           auto it = tensors.find(e.inputs[0]);
           if (it != tensors.end() && !it->second.f32.empty()) {
@@ -246,10 +270,9 @@ void Voice::add_onnx(const OnnxModel& m) {
         }
       if (found) break;
       // (b) the whole factor exp(-logs) was folded into an initializer / Constant
-      HostTensor h;
-      if (auto it = tensors.find(*other); it != tensors.end()) h = it->second;
-      else if (auto ct = constants.find(*other); ct != constants.end()) { h.dims = ct->second->dims; h.f32 = ct->second->f32; }
-      if (h.f32.size() == 2 || h.f32.size() == 1) {   // one scale per z channel ([2,1]); a mask has T entries
+      auto it = tensors.find(*other);
+      if (it != tensors.end() && (it->second.f32.size() == 2 || it->second.f32.size() == 1)) {   // a mask has T entries
+        HostTensor h = it->second;
         tensors["dp.flows.0.inv_scale"] = std::move(h);
         break;
       }
@@ -334,6 +357,7 @@ void Voice::release() {
 
 void Voice::finalize() {
   if (finalized) return;
+  resolve_graph();
   resolve_conv_nodes();
   Binder B(*this);
   auto count = [&](const std::string& pre, const std::string& post) {

@@ -35,6 +35,14 @@ struct ConvNodeRef {
   ConvAttr attr;
 };
 
+// A graph node as the binder needs it (route A copies it out of the parsed file, route B receives it through
+// piper_b200_add_node): names only, plus the Conv / ConvTranspose attributes.
+struct GraphNodeRef {
+  std::string op_type, name;
+  std::vector<std::string> inputs, outputs;
+  ConvAttr attr;
+};
+
 // fp32 SIMT conv weights: [phases][taps][cin][ldw] (+ bias[ldw]); see kernels.h ConvArgs
 struct ConvW {
   float* w = nullptr;
@@ -107,6 +115,7 @@ struct Voice {
   // host-side staging (route A fills it from the ONNX file, route B from set_weight calls)
   std::map<std::string, HostTensor> tensors;
   std::map<std::string, ConvAttr> conv_attrs;
+  std::vector<GraphNodeRef> nodes;       // Conv / ConvTranspose / Gather / Sub / Mul / Exp nodes of the graph
   std::vector<ConvNodeRef> conv_nodes;   // resolved by finalize(): canonical `<module>.weight` / `.bias` aliases
   std::set<std::string> folded_sources;  // initializers that live on under a canonical alias (not counted twice)
   bool finalized = false;
@@ -136,7 +145,9 @@ struct Voice {
 
   std::vector<void*> allocs;
 
-  void add_onnx(const OnnxModel& m);   // copies initializers + conv attributes
+  void add_onnx(const OnnxModel& m);   // copies initializers + the graph nodes the binder needs
+  void add_node(GraphNodeRef g);
+  void resolve_graph();                // conv attributes, the `sid`-named embedding table, the folded ElementwiseAffine scale
   void resolve_conv_nodes();           // anonymous conv weights -> `<module>.weight`; weight_g / weight_v pairs folded
   void finalize();                     // throws std::runtime_error on an unrecognised graph
   void release();

@@ -96,6 +96,8 @@ def load_library(path: str = LIB_PATH):
         "piper_b200_load_voice": (C.c_int, [P, C.c_char_p, C.c_char_p]),
         "piper_b200_set_weight": (C.c_int, [P, C.c_char_p, C.c_int32, C.POINTER(C.c_int64), C.c_int32, P, C.c_size_t]),
         "piper_b200_set_conv_attr": (C.c_int, [P, C.c_char_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32]),
+        "piper_b200_add_node": (C.c_int, [P, C.c_char_p, C.c_char_p, C.POINTER(C.c_char_p), C.c_int32, C.POINTER(C.c_char_p),
+                                          C.c_int32] + [C.c_int32] * 5),
         "piper_b200_set_config": (C.c_int, [P, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_float]),
         "piper_b200_finalize": (C.c_int, [P]),
         "piper_b200_get_voice_info": (C.c_int, [P, C.POINTER(VoiceInfo)]),
@@ -134,7 +136,7 @@ EXPORTED_SYMBOLS = [
     "piper_b200_random_normal", "piper_b200_selftest_conv", "piper_b200_ipa_to_ids", "piper_b200_config_ipa_to_ids",
     "piper_b200_stream_next", "piper_b200_device_count", "piper_b200_set_output_buffer", "piper_b200_host_alloc",
     "piper_b200_host_free", "piper_b200_host_register", "piper_b200_host_unregister",
-    "piper_b200_length_regulate_noalloc",
+    "piper_b200_length_regulate_noalloc", "piper_b200_add_node",
 ]
 NOALLOC_MAX_IDS, NOALLOC_MAX_BATCH = 65536, 1024
 
@@ -256,6 +258,60 @@ class PiperCUDARuntime:
             self.close()
             raise
         self.model_path, self.config_path = model_path, config_path
+
+    @classmethod
+    def from_parsed(cls, initializers, nodes, sample_rate: int, num_speakers: int = 1, noise_scale: float = 0.667,
+                    length_scale: float = 1.0, noise_w: float = 0.8, options: Optional[Options] = None):
+        """init(model:config:options:) (PiperMetalRuntime.swift:54-59), route B of the C ABI: the host has already
+        parsed the model (Swift: PiperONNX's ONNXModel; here any reader) and pushes it - every initializer with
+        piper_b200_set_weight, every graph node with piper_b200_add_node, the config scalars with piper_b200_set_config -
+        then piper_b200_finalize binds and repacks.  `initializers`: name -> ndarray; `nodes`: objects with op_type, name,
+        inputs, outputs and an `attrs` dict (strides / dilations / group / pads / value)."""
+        self = cls.__new__(cls)
+        self.options = options or Options()
+        self._lib = load_library()
+        self._ctx = C.c_void_p()
+        rc = self._lib.piper_b200_create(self.options.device, C.byref(self._ctx))
+        if rc != OK:
+            raise PiperB200Error(rc, self._lib.piper_b200_last_error(None).decode())
+        dtypes = {np.dtype(np.float32): 1, np.dtype(np.int32): 6, np.dtype(np.int64): 7, np.dtype(np.bool_): 9}
+
+        def push(name, arr):
+            arr = np.ascontiguousarray(arr)
+            if arr.dtype not in dtypes:
+                return
+            dims = (C.c_int64 * max(arr.ndim, 1))(*arr.shape)
+            self._check(self._lib.piper_b200_set_weight(self._ctx, name.encode(), dtypes[arr.dtype], dims, arr.ndim,
+                                                        arr.ctypes.data, arr.nbytes))
+        try:
+            for name, arr in initializers.items():
+                push(name, arr)
+            for n in nodes:
+                at = getattr(n, "attrs", {}) or {}
+                if n.op_type == "Constant":       # its float value travels as a weight under the node's output name
+                    v = at.get("value")
+                    if isinstance(v, np.ndarray) and v.dtype == np.float32 and n.outputs:
+                        push(n.outputs[0], v)
+                    continue
+                ins = (C.c_char_p * max(len(n.inputs), 1))(*[i.encode() for i in n.inputs])
+                outs = (C.c_char_p * max(len(n.outputs), 1))(*[o.encode() for o in n.outputs])
+                pads = at.get("pads") or [-1, -1]
+                self._check(self._lib.piper_b200_add_node(
+                    self._ctx, n.op_type.encode(), (n.name or "").encode(), ins, len(n.inputs), outs, len(n.outputs),
+                    int((at.get("strides") or [1])[0]), int((at.get("dilations") or [1])[0]), int(at.get("group") or 1),
+                    int(pads[0]), int(pads[1] if len(pads) > 1 else pads[0])))
+            self._check(self._lib.piper_b200_set_config(self._ctx, sample_rate, num_speakers, noise_scale, length_scale,
+                                                        noise_w))
+            self._check(self._lib.piper_b200_finalize(self._ctx))
+            self.set_precision(self.options.precision)
+            info = VoiceInfo()
+            self._check(self._lib.piper_b200_get_voice_info(self._ctx, C.byref(info)))
+            self.info = info
+        except Exception:
+            self.close()
+            raise
+        self.model_path = self.config_path = None
+        return self
 
     # ---- plumbing ---------------------------------------------------------------------
     def _check(self, rc: int):

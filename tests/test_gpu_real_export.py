@@ -34,3 +34,27 @@ def test_real_export_loads_and_matches_the_oracle(name, precision, snr_min, abs_
     assert np.abs(plain.audio[0] - r.audio[0]).max() <= abs_max
     assert int(rt.info.num_symbols) == spec.n_vocab and int(rt.info.hidden) == spec.hidden
     rt.close()
+
+
+@pytest.mark.parametrize("which", ["plain", "torch-export"])
+def test_route_b_equals_route_a(which):
+    """init(model:config:options:) (PiperMetalRuntime.swift:54-59) through the C ABI's route B - set_weight per
+    initializer, add_node per graph node, set_config, finalize - must give the same bits as route A
+    (piper_b200_load_voice on the same file).  The parser on the host side here is the oracle's pure-Python ONNX reader,
+    standing in for the reference's PiperONNX."""
+    from oracle.onnx_reader import load_model
+    name = "medium"
+    path = voice_files(name)[0] if which == "plain" else exported(name)
+    m = load_model(path)
+    ids = fixture_ids(2)
+    ns, ls, nw = S.FIXTURE_SCALES
+    a = PiperCUDARuntime(path, voice_files(name)[1], Options(precision="f16"))
+    b = PiperCUDARuntime.from_parsed(m.initializers, m.nodes, sample_rate=S.SPECS[name].sample_rate,
+                                     options=Options(precision="f16"))
+    ra, rb = a.synthesize_batch([ids], ns, ls, nw), b.synthesize_batch([ids], ns, ls, nw)
+    assert np.array_equal(ra.durations[0], rb.durations[0])
+    assert np.array_equal(ra.audio[0], rb.audio[0])
+    assert int(a.info.n_params) == int(b.info.n_params) and int(b.info.num_symbols) == S.SPECS[name].n_vocab
+    assert np.array_equal(b.synthesize(ids), a.synthesize(ids))       # config defaults arrived (set_config)
+    a.close()
+    b.close()
