@@ -5,11 +5,18 @@
 // NOT BUILT in this repository's image (no Swift toolchain); see INTEGRATION.md.
 import PackageDescription
 
+// PiperCore / PiperONNX are the reference's own modules (audio types, PiperConfig, ONNXModel): either add the two
+// targets below to the reference's Package.swift, or build this package beside a checkout of it.
 let package = Package(
     name: "PiperCUDA",
     products: [.library(name: "PiperCUDA", targets: ["PiperCUDA"])],
+    dependencies: [.package(name: "PiperSwift", path: "../../piper-swift")],
     targets: [
         .systemLibrary(name: "CPiperB200", path: "Sources/CPiperB200"),
-        .target(name: "PiperCUDA", dependencies: ["CPiperB200"], path: "Sources/PiperCUDA"),
+        .target(name: "PiperCUDA",
+                dependencies: ["CPiperB200",
+                               .product(name: "PiperCore", package: "PiperSwift"),
+                               .product(name: "PiperONNX", package: "PiperSwift")],
+                path: "Sources/PiperCUDA"),
     ]
 )
