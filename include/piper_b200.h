@@ -250,6 +250,18 @@ int piper_b200_random_normal(piper_b200_ctx* ctx, uint64_t seed, int64_t count, 
 int piper_b200_selftest_conv(piper_b200_ctx* ctx, int32_t mode, int32_t cin, int32_t cout, int32_t k,
                              int32_t dilation, int32_t stride, int32_t rows, int32_t precision, float* out4);
 
+/* Op-level known-answer hook: ONE Conv (transposed = 0; odd k, stride 1, "same" padding dilation*(k-1)/2) or
+ * ConvTranspose (transposed = 1; k a multiple of stride, padding (k-stride)/2, rows*stride output rows) node on
+ * caller-supplied host operands - the reference's conv1d_f32 / convtranspose1d_f32 kernels
+ * (Sources/PiperMetal/Kernels/conv1d.metal:28-71, 97-142; dispatch GraphExecutor.swift:1739-1860).  x is
+ * [rows][cin] (time-major), w the ONNX initializer layout (Conv [cout][cin][k], ConvTranspose [cin][cout][k]), bias
+ * [cout] or NULL, out [rows*stride][cout].  precision FP32 runs the CUDA-core kernel, F16 / BF16 the tcgen05 kernel on
+ * the 16-bit rounding of x and w with fp32 accumulation (cin % 32 == 0, cout % 16 == 0).  The parity tests compare it
+ * with torch.nn.functional.conv1d / conv_transpose1d. */
+int piper_b200_conv1d(piper_b200_ctx* ctx, int32_t transposed, const float* x, int64_t rows, const float* w,
+                      const float* bias, int32_t cin, int32_t cout, int32_t k, int32_t dilation, int32_t stride,
+                      int32_t precision, float* out);
+
 #ifdef __cplusplus
 }
 #endif

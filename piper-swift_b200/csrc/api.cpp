@@ -485,4 +485,17 @@ int piper_b200_selftest_conv(piper_b200_ctx* ctx, int32_t mode, int32_t cin, int
   return rc;
 }
 
+int piper_b200_conv1d(piper_b200_ctx* ctx, int32_t transposed, const float* x, int64_t rows, const float* w, const float* bias,
+                      int32_t cin, int32_t cout, int32_t k, int32_t dilation, int32_t stride, int32_t precision, float* out) {
+  if (!ctx || !x || !w || !out || cin <= 0 || cout <= 0 || k <= 0 || dilation <= 0 || stride <= 0 || rows <= 0) {
+    g_error = "invalid argument";
+    if (ctx) ctx->c.last_error = g_error;
+    return PIPER_B200_ERR_INVALID_ARGUMENT;
+  }
+  ctx->c.invalidate_results();
+  const int rc = ctx->c.conv1d_op(transposed, x, rows, w, bias, cin, cout, k, dilation, stride, precision, out);
+  if (rc != PIPER_B200_OK) g_error = ctx->c.last_error;
+  return rc;
+}
+
 }  // extern "C"

@@ -6,8 +6,13 @@
 // epilogue of the in_layer convolution, res|skip is one GEMM with two column groups, and
 // every producer also emits the 16-bit (leaky-relu'd) operand copy its consumer reads.
 // Residual streams, skip sums and the cross-resblock mean stay in fp32.
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
 #include <algorithm>
 #include <cstdlib>
+#include <cstring>
+#include <vector>
 #include <stdexcept>
 
 #include "conv_tc.h"
@@ -209,15 +214,35 @@ void TcVoice::build(Exec& ex, const Voice& v, int f16_) {
         for (int j = 0; j < nk; ++j)
           for (int c = 0; c < 2; ++c) { t.tap_base[j][c] = taps; taps += kk[j]; }
         const size_t tap_elems = (size_t)s.ch * s.ch;
-        CUDA_OK(cudaMalloc(&t.mrf_w, (size_t)taps * tap_elems * 2));
+        // last stage: conv_post joins the stage's taps (conv_mrf.h, post_tap_base) - tap t is a C x C matrix whose cout
+        // row 0 holds post_w[t][:], the other rows are zero
+        const bool last = &s == &v.stages.back();
+        const int post_taps = (last && mrf_post_supported(s.ch, v.post_k) && v.post_w) ? v.post_k : 0;
+        CUDA_OK(cudaMalloc(&t.mrf_w, (size_t)(taps + post_taps) * tap_elems * 2));
         allocs.push_back(t.mrf_w);
+        if (post_taps) {
+          std::vector<float> pw((size_t)post_taps * s.ch);
+          CUDA_OK(cudaMemcpy(pw.data(), v.post_w, pw.size() * 4, cudaMemcpyDeviceToHost));
+          std::vector<uint16_t> h((size_t)post_taps * tap_elems, 0);
+          for (int tt = 0; tt < post_taps; ++tt)
+            for (int c = 0; c < s.ch; ++c) {
+              const float x = pw[(size_t)tt * s.ch + c];
+              uint16_t b;
+              if (f16) { const __half hv = __float2half_rn(x); std::memcpy(&b, &hv, 2); }
+              else { const __nv_bfloat16 hv = __float2bfloat16_rn(x); std::memcpy(&b, &hv, 2); }
+              h[(size_t)tt * tap_elems + c] = b;
+            }
+          CUDA_OK(cudaMemcpy(static_cast<uint16_t*>(t.mrf_w) + (size_t)taps * tap_elems, h.data(), h.size() * 2,
+                             cudaMemcpyHostToDevice));
+          t.post_tap_base = taps;
+        }
         for (int j = 0; j < nk; ++j)
           for (int c = 0; c < 2; ++c) {
             const ConvW& cw = s.rbs[j].c1[c];
             launch_pack_tc_weights(ex, cw.w, cw.ldw, cw.taps, cw.cin, cw.cout,
                                    static_cast<uint16_t*>(t.mrf_w) + (size_t)t.tap_base[j][c] * tap_elems, s.ch, 0, s.ch, f16);
           }
-        t.mrf_taps = taps;
+        t.mrf_taps = taps + post_taps;
         t.mrf = true;
       }
     }
@@ -540,6 +565,7 @@ float* run_decoder_tc(Context& ctx, Exec& ex, const DecoderIn& in) {
       static const int post_env = [] { const char* e = getenv("PIPER_B200_MRF_POST"); return e ? atoi(e) : 1; }();
       if (last_stage && post_env && mrf_post_supported(C, v.post_k)) {   // conv_post + tanh as the stage kernel's epilogue
         a.post_w = v.post_w; a.post_k = v.post_k; a.post_slope = 0.01f; a.post_out = audio; a.post_bias = v.post_b;
+        a.post_tap_base = ts.post_tap_base;
         post_fused = true;
       } else if (last_stage) a.out_f32 = xs;
       else { a.out_act = xsb; a.act_slope = 0.1f; }

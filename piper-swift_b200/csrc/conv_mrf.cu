@@ -30,15 +30,16 @@ namespace {
 
 constexpr int MRF_G = 64;          // upper bound of the guard rows on both sides of the operand windows (p.G >= largest tap shift)
 constexpr int MRF_MAX_M = 8;
-constexpr int MRF_MAX_RING = 32;
+constexpr int MRF_MAX_RING = 40;   // >= the 30 + 7 resident taps of a 32-channel stage with its conv_post taps
 constexpr uint32_t MRF_TRACE_EVENTS = 4096;
 
 struct MrfParams {
   int R, C, nk, m, V, halo, n_windows, G;   // G: guard rows actually used (multiple of 8, <= MRF_G)
   int GX;                                   // guard rows of the lrelu(x) window (conv1 shifts only; <= G)
   int tap_outer;                            // weight ring shorter than a convolution: one issuing warp, taps outermost
-  int k[MRF_MAX_RB], d0[MRF_MAX_RB], d1[MRF_MAX_RB];
-  int tap_base[MRF_MAX_RB][2];
+  // entry nk of k / d1 / tap_base[.][1] describes the conv_post pseudo pair (post_tc)
+  int k[MRF_MAX_RB + 1], d0[MRF_MAX_RB + 1], d1[MRF_MAX_RB + 1];
+  int tap_base[MRF_MAX_RB + 1][2];
   const float* b1[MRF_MAX_RB];
   const float* b2[MRF_MAX_RB];
   const uint16_t* x_act; int64_t act_rows; int act_pad;   // group-planar 16-bit lrelu(x): [C/8][act_rows][8]
@@ -48,6 +49,10 @@ struct MrfParams {
   float* out_f32;
   const float* post_w; int post_k; float post_slope; float* post_out;   // fused conv_post + tanh (C = 32 only)
   float post_bias;
+  // conv_post on the tensor cores (resident weights only): after the last resblock the epilogue writes lrelu(out) as one
+  // more 16-bit operand window, the conv2 stream runs the post_k taps (a C x C tap whose row 0 holds the post weights)
+  // into S_i, and the output step reads column 0
+  int post_tc;
   int f16, ring, resident;
   int mma_split;              // 1: two issuing warps per convolution stream (even / odd tiles)
   // ResBlock1 unit (nk = 1): out = x + conv2(lrelu(conv1(lrelu x) + b1)) + b2 - the residual does not enter the
@@ -148,7 +153,9 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
     mbar_init(x_empty, (p.mma_split ? 2 : 1) + 4 * MRF_EG);
     for (int s = 0; s < p.ring; ++s) {
       mbar_init(&w_full[s], 1);
-      mbar_init(&w_empty[s], p.mma_split ? 2 : 1);
+      // every issuing warp arrives once per slot and lap: the owners of the tap (the stream's one or two warps) through
+      // the commit of their MMAs, the warps of the OTHER stream after observing the tap's arrival (skip() below)
+      mbar_init(&w_empty[s], p.tap_outer ? 1 : (p.mma_split ? 4 : 2));
     }
     for (int i = 0; i < m; ++i) {
       mbar_init(&d_full[i], 1);
@@ -167,6 +174,13 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
   const uint32_t d_col = 0, s_col = (uint32_t)(m * C);
+#ifdef PIPER_MBAR_WATCHDOG
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    printf("mrf_tc_kernel<%d> m %d nk %d ring %d resident %d tap_outer %d split %d unit %d: barriers x_full @%u x_empty +8 w_full +16 "
+           "w_empty +%d d_full +%d d_empty +%d y_ready +%d s_full +%d e_ready +%d\n", C, m, p.nk, p.ring, p.resident, p.tap_outer,
+           p.mma_split, p.unit_mode, smem_u32(bars), 16 + 8 * MRF_MAX_RING, 16 + 16 * MRF_MAX_RING, 16 + 16 * MRF_MAX_RING + 8 * MRF_MAX_M,
+           16 + 16 * MRF_MAX_RING + 16 * MRF_MAX_M, 16 + 16 * MRF_MAX_RING + 24 * MRF_MAX_M, 16 + 16 * MRF_MAX_RING + 32 * MRF_MAX_M);
+#endif
 
   // Convolution pairs are numbered n = it*nk + r over the windows this CTA owns.  The issue order is
   //   conv1(0);  then for n = 0,1,..:  conv2(n) and conv1(n+1)
@@ -193,7 +207,9 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
       };
       auto load_w = [&](int r, int j) {
         for (int t = 0; t < p.k[r]; ++t) {
+          TRACE(22u, (uint32_t)(r * 2 + j), (uint32_t)t);
           mbar_wait(&w_empty[slot], wph ^ 1u);
+          TRACE(23u, (uint32_t)(r * 2 + j), (uint32_t)t);
           mbar_expect_tx(&w_full[slot], (uint32_t)tap_bytes);
 #pragma unroll
           for (int kh = 0; kh < KH; ++kh)
@@ -246,20 +262,41 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
     const int istep = p.mma_split ? 2 : 1;
     const bool idle = (p.tap_outer && warp != 1) || (!p.mma_split && half == 1);
     uint32_t slot = 0, wph = 0;      // ring position of the next convolution in ring order (streaming mode)
-    auto skip = [&](int k) {         // advance over a convolution of the other stream
+    auto advance = [&](int k) {
       slot += (uint32_t)k;
       while (slot >= ring) { slot -= ring; wph ^= 1u; }
+    };
+    // A convolution of the OTHER stream.  Its ring slots are not simply stepped over: this warp waits for every tap to
+    // land and then arrives on the slot's w_empty like an owner would.  An mbarrier parity wait only tells "phase L
+    // done" from "phase L - 1 done"; a warp that steps over a whole lap of a slot (the other stream's convolution
+    // covered it) and then waits for lap L + 1 of that slot with the parity of L + 1 = parity of L - 1 passes as soon
+    // as it arrives, on weights of the wrong convolution, and its release then corrupts the producer's w_empty count -
+    // the round-1 hang of the k = 11 ResBlock1 units (ring 11..14 < 2k; tools/hang_repro.py, mbarrier watchdog:
+    // producers stuck on w_empty of the third lap).  Observing every slot in every lap keeps each issuing warp within
+    // one phase of every w_full barrier, and a slot cannot be refilled before all issuing warps have passed it, so
+    // no barrier can run two phases ahead of a waiter either.
+    auto skip = [&](int k) {
+      for (int t = 0; t < k; ++t) {
+        mbar_wait(&w_full[slot], wph);
+        if (lane == 0) mbar_arrive(&w_empty[slot]);
+        if (++slot == ring) { slot = 0; wph ^= 1u; }
+      }
+      __syncwarp();
     };
     // K step ks of a weight tap: 32 bytes further inside the swizzled rows, next sub-tile after KB channels
     auto b_step = [&](int ks) { return (uint32_t)((ks / (KB / 16)) * (sub_bytes >> 4) + 2 * (ks % (KB / 16))); };
 
     // one convolution over all tiles: per tile k taps x KS tcgen05 K steps, then the commit for the epilogue
-    auto conv = [&](uint32_t n, int r, int j, bool first_use) {
+    auto conv = [&](uint32_t n, int r, int j, bool first_use, bool fresh = false) {
       const int k = p.k[r];
       const int dil = j ? p.d1[r] : p.d0[r];
       const uint32_t slot0 = p.resident ? (uint32_t)p.tap_base[r][j] : slot;
       const uint32_t wph0 = p.resident ? 0u : wph;
-      for (int i = half * (istep - 1); i < m; i += istep) {
+      // streamed ring: a tap's slot goes back to the producer with the MMAs of this warp's LAST tile (not after the whole
+      // convolution), so that the next convolution's taps are on their way while the last tile is still being issued
+      const int i_first = half * (istep - 1);
+      const int i_last = i_first < m ? i_first + ((m - 1 - i_first) / istep) * istep : -1;
+      for (int i = i_first; i < m; i += istep) {
         TRACE(1u + (uint32_t)j * 4u, n, (uint32_t)i);
         if (j == 0) {
           mbar_wait(&d_empty[i], (n & 1u) ^ 1u);           // epilogue of the previous pair drained D_i
@@ -289,7 +326,8 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
 #pragma unroll
             for (int ks = 0; ks < KS; ++ks)   // K step of 16 channels = two planes of A, 32 bytes of B
               umma_f16(acc, a_hi | (uint64_t)(a_lo + (uint32_t)ks * 2u * plane16), b_hi | (uint64_t)(b_lo + b_step(ks)),
-                       idesc, (j == 1 || t > 0 || ks > 0) ? 1u : 0u);
+                       idesc, ((j == 1 && !fresh) || t > 0 || ks > 0) ? 1u : 0u);
+            if (!p.resident && i == i_last) umma_commit(&w_empty[s]);
           }
           a_lo += (uint32_t)dil;
           if (++s == ring) { s = 0; ph ^= 1u; }
@@ -297,13 +335,17 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
         if (elect_one()) umma_commit(j ? &s_full[i] : &d_full[i]);
         TRACE(3u + (uint32_t)j * 4u, n, (uint32_t)i);
       }
-      if (!p.resident) {   // hand the ring slots back to the producer once every tile has used them
-        uint32_t s = slot;
-        for (int t = 0; t < k; ++t) {
-          if (elect_one()) umma_commit(&w_empty[s]);
-          if (++s == ring) s = 0;
+      if (!p.resident) {
+        if (i_last < 0) {   // a warp without tiles (m = 1, odd warp) still owes its arrival on every slot
+          uint32_t s = slot, ph = wph;
+          for (int t = 0; t < k; ++t) {
+            mbar_wait(&w_full[s], ph);
+            if (lane == 0) mbar_arrive(&w_empty[s]);
+            if (++s == ring) { s = 0; ph ^= 1u; }
+          }
+          __syncwarp();
         }
-        skip(k);
+        advance(k);
       }
     };
 
@@ -313,19 +355,23 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
     auto conv_to = [&](uint32_t n, int r, int j) {
       const int k = p.k[r];
       const int dil = j ? p.d1[r] : p.d0[r];
+      TRACE(1u + (uint32_t)j * 4u, n, 0u);
       for (int i = 0; i < m; ++i) {
         if (j == 0) mbar_wait(&d_empty[i], (n & 1u) ^ 1u);
         else mbar_wait(&y_ready[i], n & 1u);
       }
       tc_fence_after();
+      TRACE(2u + (uint32_t)j * 4u, n, 0u);
       const uint64_t a_hi = j ? a_hi_y : a_hi_x;
       const uint32_t plane16 = j ? plane16_y : plane16_x;
       const uint32_t a_base = (j ? y1_lo : x0_lo) - (uint32_t)(((k - 1) / 2) * dil);
       for (int t = 0; t < k; ++t) {
+        TRACE(24u, n, (uint32_t)(t * 2 + j));
         mbar_wait(&w_full[slot], wph);
         tc_fence_after();
+        TRACE(25u, n, (uint32_t)(t * 2 + j));
         const uint32_t b_lo = wr_lo + slot * tap16;
-        if (elect_one()) {
+        if (elect_one()) {   // (warp-uniform tile loops with one election per tile measured 4 % slower here)
           for (int i = 0; i < m; ++i) {
             const uint32_t acc = tmem_base + (j ? s_col : d_col) + (uint32_t)(i * C);
             const uint32_t a_lo = a_base + (uint32_t)(t * dil + 128 * i);
@@ -342,6 +388,7 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
       if (elect_one())
         for (int i = 0; i < m; ++i) umma_commit(j ? &s_full[i] : &d_full[i]);
       __syncwarp();
+      TRACE(3u + (uint32_t)j * 4u, n, 0u);
     };
 
     int it = 0, r = 0;
@@ -380,6 +427,12 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
         if (!p.resident) skip(p.k[r]);                       // c2(n) belongs to the other stream
         it = it1; r = r1;
       }
+    } else if (p.post_tc) {
+      // resident weights: conv2 of every pair, then the conv_post pseudo pair (index nk) of the window, fresh into S_i;
+      // the y_ready / s_full phases count nk + 1 steps per window
+      uint32_t n2 = 0;
+      for (int itw = 0; itw < n_it; ++itw)
+        for (int rr = 0; rr <= p.nk; ++rr, ++n2) conv(n2, rr, 1, itw == 0, rr == p.nk);
     } else {
       if (!p.resident && n_it > 0) skip(p.k[0]);             // c1(0)
       for (uint32_t n = 0; n < n_total; ++n) {
@@ -400,11 +453,12 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
     const uint32_t lane_sel = (uint32_t)(quarter * 32) << 16;
     const float inv_nk = 1.0f / (float)p.nk;
     const int units = m * HALVES;
-    uint32_t n = 0;
+    uint32_t n = 0;    // pair counter of the conv1 side (d_full / d_empty phases)
+    uint32_t n2 = 0;   // step counter of the conv2 side (y_ready / s_full phases): nk per window, nk + 1 with post_tc
     for (int it = 0; it < n_it; ++it) {
       const int w0 = ((int)blockIdx.x + it * (int)gridDim.x) * p.V - p.halo;
       mbar_wait(x_full, (uint32_t)it & 1u);   // the epilogue reads the window itself (residual)
-      for (int r = 0; r < p.nk; ++r, ++n) {
+      for (int r = 0; r < p.nk; ++r, ++n, ++n2) {
         const float* b1 = sbias + r * C;
         for (int u = group; u < units; u += MRF_EG) {
           const int i = u / HALVES, cb = (u % HALVES) * 32;
@@ -418,9 +472,9 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
           int ru = 0;
           if (inr && p.row_utt) ru = p.row_utt[p.valid_shift >= 0 ? (grow >> p.valid_shift) : (grow / p.valid_div)];
           TRACE(10u, n, (uint32_t)u);
-          if (n > 0) {   // conv2 of the previous pair must have finished with S_i and with Y1 rows of tiles i-1..i+1
+          if (n2 > 0) {   // conv2 of the previous step must have finished with S_i and with Y1 rows of tiles i-1..i+1
             for (int ii = (i > 0 ? i - 1 : 0); ii <= (i + 1 < m ? i + 1 : m - 1); ++ii)
-              mbar_wait(&s_full[ii], (n - 1u) & 1u);
+              mbar_wait(&s_full[ii], (n2 - 1u) & 1u);
           }
           TRACE(11u, n, (uint32_t)u);
           mbar_wait(&d_full[i], n & 1u);
@@ -442,6 +496,53 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
             __syncwarp();
             tmem_ld16_async(dcol + (uint32_t)(hc * 16), t0);
             if (r > 0) tmem_ld16_async(scol + (uint32_t)(hc * 16), t2);
+#ifndef PIPER_MRF_EPI_SCALAR
+            if (!UNIT) {
+              // packed form (FADD2 / FMUL2 on fp32 pairs, the leaky relu of the operand in the 16-bit type): the 16
+              // epilogue warps are bound by issue slots, this is ~40 % fewer instructions per chunk than the scalar form
+              uint64_t d2[8];
+              {
+                const uint32_t w[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
+                const ulonglong2* b2 = reinterpret_cast<const ulonglong2*>(b1 + c0);
+                const uint64_t ten = f2pack(10.f, 10.f);
+#pragma unroll
+                for (int q4 = 0; q4 < 4; ++q4) {
+                  const ulonglong2 bb = b2[q4];
+                  const float2 x01 = unpack2(w[2 * q4], p.f16), x23 = unpack2(w[2 * q4 + 1], p.f16);
+                  const float2 t01 = f2unpack(f2mul(f2pack(x01.x, x01.y), ten)), t23 = f2unpack(f2mul(f2pack(x23.x, x23.y), ten));
+                  d2[2 * q4] = f2add(bb.x, f2pack(fminf(x01.x, t01.x), fminf(x01.y, t01.y)));
+                  d2[2 * q4 + 1] = f2add(bb.y, f2pack(fminf(x23.x, t23.x), fminf(x23.y, t23.y)));
+                }
+              }
+              tmem_wait_ld();
+              float dv[16];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) {
+                d2[e] = f2add(d2[e], f2pack(__uint_as_float(t0[2 * e]), __uint_as_float(t0[2 * e + 1])));
+                const float2 v = f2unpack(d2[e]);
+                dv[2 * e] = v.x; dv[2 * e + 1] = v.y;
+              }
+              if (r > 0) {
+                float sv[16];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                  const float2 v = f2unpack(f2add(d2[e], f2pack(__uint_as_float(t2[2 * e]), __uint_as_float(t2[2 * e + 1]))));
+                  sv[2 * e] = v.x; sv[2 * e + 1] = v.y;
+                }
+                tmem_st16(scol + (uint32_t)(hc * 16), sv);
+              } else {
+                tmem_st16(scol + (uint32_t)(hc * 16), dv);
+              }
+              const uint32_t vm = valid ? 0xffffffffu : 0u;
+              uint32_t pk[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) pk[e] = lrelu_pack2(dv[2 * e], dv[2 * e + 1], 0.1f, p.f16) & vm;
+              uint8_t* y = Y1 + (size_t)(c0 >> 3) * plane_bytes + row_off;   // planes c0/8 and c0/8 + 1
+              *reinterpret_cast<uint4*>(y) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+              *reinterpret_cast<uint4*>(y + plane_bytes) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+              continue;
+            }
+#endif
             float d[16], xr[16];
             {   // x0 + b1 while the TMEM loads are in flight; x0 = min(v, 10 v) undoes lrelu(., 0.1)
               const uint32_t w[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
@@ -501,8 +602,77 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
         }
       }
       // ---- stage output: (S + sum_r b2_r) / nk over the window's valid rows ----
-      const uint32_t nl = n - 1u;
       const float* b2s = sbias + p.nk * C;
+      if (C == 32 && p.post_out && p.post_tc) {
+        // conv_post + tanh with the taps on the tensor cores.  Step 1 (per unit = tile): v = lrelu((S + sum b2) / nk,
+        // post_slope) * mask -> 16-bit -> the conv2 operand window (what a conv1 epilogue does with y1); the conv2
+        // stream then runs the post taps over it, fresh into S_i.  Step 2: column 0 of S_i is the pre-tanh sample.
+        // The accumulation order of a sample (taps, K steps) does not depend on its row's position in the window.
+        constexpr int MAXU = (MRF_MAX_M + MRF_EG - 1) / MRF_EG;
+        uint32_t vmask = 0u;
+#pragma unroll
+        for (int ui = 0; ui < MAXU; ++ui) {
+          const int i = group + ui * MRF_EG;
+          if (i < units) {
+            const int row_in_win = 128 * i + quarter * 32 + lane;
+            const int grow = w0 + row_in_win;
+            const bool inr = grow >= 0 && grow < p.R;
+            int ru = 0;
+            if (inr && p.row_utt) ru = p.row_utt[p.valid_shift >= 0 ? (grow >> p.valid_shift) : (grow / p.valid_div)];
+            TRACE(14u, n2, (uint32_t)i);
+            for (int ii = (i > 0 ? i - 1 : 0); ii <= (i + 1 < m ? i + 1 : m - 1); ++ii)
+              mbar_wait(&s_full[ii], (n2 - 1u) & 1u);
+            tc_fence_after();
+            TRACE(15u, n2, (uint32_t)i);
+            asm volatile("" : "+r"(ru));
+            const bool valid = inr && ru >= 0;
+            vmask |= (valid ? 1u : 0u) << ui;
+            const uint32_t scol = tmem_base + lane_sel + s_col + (uint32_t)(i * C);
+            uint32_t t0[16], t1[16];
+            __syncwarp();
+            tmem_ld16_async(scol, t0);
+            tmem_ld16_async(scol + 16u, t1);
+            tmem_wait_ld();
+            uint32_t pk[16];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const float a0 = lrelu((__uint_as_float(t0[2 * e]) + b2s[2 * e]) * inv_nk, p.post_slope);
+              const float a1 = lrelu((__uint_as_float(t0[2 * e + 1]) + b2s[2 * e + 1]) * inv_nk, p.post_slope);
+              const float c0 = lrelu((__uint_as_float(t1[2 * e]) + b2s[16 + 2 * e]) * inv_nk, p.post_slope);
+              const float c1 = lrelu((__uint_as_float(t1[2 * e + 1]) + b2s[16 + 2 * e + 1]) * inv_nk, p.post_slope);
+              pk[e] = valid ? pack2(a0, a1, p.f16) : 0u;
+              pk[8 + e] = valid ? pack2(c0, c1, p.f16) : 0u;
+            }
+            uint8_t* y = Y1 + (size_t)((p.G + row_in_win) * 16);
+#pragma unroll
+            for (int g = 0; g < 4; ++g)
+              *reinterpret_cast<uint4*>(y + (size_t)g * plane_bytes) = make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
+            fence_proxy_async();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&y_ready[i]);
+            TRACE(16u, n2, (uint32_t)i);
+          }
+        }
+#pragma unroll
+        for (int ui = 0; ui < MAXU; ++ui) {
+          const int i = group + ui * MRF_EG;
+          if (i < units) {
+            const int row_in_win = 128 * i + quarter * 32 + lane;
+            const int grow = w0 + row_in_win;
+            const bool owned = row_in_win >= p.halo && row_in_win < p.halo + p.V && grow >= 0 && grow < p.R;
+            mbar_wait(&s_full[i], n2 & 1u);
+            tc_fence_after();
+            __syncwarp();
+            const float sum = tmem_ld1(tmem_base + lane_sel + s_col + (uint32_t)(i * C));
+            if (owned) p.post_out[grow] = ((vmask >> ui) & 1u) ? tanhf(sum + p.post_bias) : 0.f;
+            tc_fence_before();
+          }
+        }
+        ++n2;
+        continue;
+      }
+      const uint32_t nl = n2 - 1u;
       if (C == 32 && p.post_out) {
         // Fused conv_post + tanh.  Every thread owns one row with all 32 channels: it forms the seven per-tap channel
         // sums q_t = sum_c w[t][c] * lrelu(out[row][c]); audio[r] = tanh(sum_t q_t[r + t - 3]) then needs the q of the
@@ -757,7 +927,8 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   // C = 128: a tap is 32 KB, the ring holds two of them and the taps-outermost issue order is used
   // ResBlock1 units whose 2k taps are not resident also take the taps-outermost order (a single issuing warp): with
   // k = 11 a streamed ring would hold barely more than one convolution
-  const int need_ring = (a.C > 64 || a.unit_mode) ? 2 : kmax;
+  static const int unit_stream_env0 = [] { const char* e = getenv("PIPER_B200_MRF_UNIT_STREAM"); return e ? atoi(e) : 1; }();
+  const int need_ring = (a.C > 64 || (a.unit_mode && !unit_stream_env0)) ? 2 : kmax;
   int m = std::min(MRF_MAX_M, 512 / (2 * a.C));
   auto post_bytes = [&](int mm) { return post ? (7 * 32 + 2 * mm * 4 * 2 * 3 * 7) * 4 + 64 : 0; };
   auto fits = [&](int mm) {
@@ -780,7 +951,11 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   p.resident = a.total_taps <= ring ? 1 : 0;
   if (p.resident) ring = a.total_taps;
   p.ring = ring;
-  p.tap_outer = (!p.resident && (ring < kmax || a.unit_mode)) ? 1 : 0;
+  // ResBlock1 units take the streamed-ring order with two issuing warps per stream whenever a whole convolution fits in
+  // the ring (the form that hung in round 1 until the issuing warps observed every slot, see skip() in the kernel);
+  // PIPER_B200_MRF_UNIT_STREAM=0 restores the taps-outermost single-issuer order for them
+  static const int unit_stream_env = [] { const char* e = getenv("PIPER_B200_MRF_UNIT_STREAM"); return e ? atoi(e) : 1; }();
+  p.tap_outer = (!p.resident && (ring < kmax || (a.unit_mode && !unit_stream_env))) ? 1 : 0;
   static const int split_env = [] { const char* e = getenv("PIPER_B200_MRF_SPLIT"); return e ? atoi(e) : 1; }();
   p.mma_split = (split_env && !p.tap_outer) ? 1 : 0;
   p.x_act = static_cast<const uint16_t*>(a.x_act); p.act_rows = a.act_rows; p.act_pad = a.act_pad;
@@ -795,6 +970,13 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   p.unit_mode = a.unit_mode; p.accum = a.accum; p.out_div = a.out_div;
   p.out_planar = static_cast<uint16_t*>(a.out_planar); p.out_rows = a.out_rows; p.out_pad = a.out_pad;
   p.post_w = a.post_w; p.post_k = a.post_k; p.post_slope = a.post_slope; p.post_out = a.post_out; p.post_bias = a.post_bias;
+  static const int post_tc_env = [] { const char* e = getenv("PIPER_B200_MRF_POST_TC"); return e ? atoi(e) : 1; }();
+  p.post_tc = (post && a.post_tap_base >= 0 && p.resident && !a.unit_mode && a.nk < MRF_MAX_RB + 1 && post_tc_env) ? 1 : 0;
+  if (p.post_tc) {
+    p.k[a.nk] = a.post_k; p.d0[a.nk] = 1; p.d1[a.nk] = 1;
+    p.tap_base[a.nk][0] = a.post_tap_base; p.tap_base[a.nk][1] = a.post_tap_base;
+    if ((a.post_k - 1) / 2 > G) throw std::runtime_error("conv_mrf: conv_post taps exceed the guard rows");
+  }
   p.f16 = a.f16;
   uint32_t cols = 32;
   while ((int)cols < 2 * m * a.C) cols <<= 1;

@@ -45,6 +45,10 @@ struct MrfArgs {
   // is then never written.  post_w = fp32 [post_k][C].
   const float* post_w = nullptr; int post_k = 0; float post_slope = 0.01f; float post_bias = 0.f;
   float* post_out = nullptr;     // fp32 [R]
+  // >= 0: `w` also holds post_k taps from this tap index on, each a C x C tap whose cout row 0 is post_w[t][:] in 16 bits
+  // and whose other rows are zero: conv_post then runs on the tensor cores as one more convolution of the stage
+  // (lrelu(out) as a 16-bit operand, fp32 accumulation) when all taps are resident in shared memory
+  int post_tap_base = -1;
   // ResBlock1 unit (nk = 1, k[0] taps for both convolutions, d0 = dilation of conv1, d1 = 1):
   //   out = x + conv2(lrelu(conv1(lrelu x) + b1)) + b2          (GraphExecutor.swift:2047-2069 chains, HiFi-GAN ResBlock1)
   // x enters as the 16-bit lrelu(x) operand (like every fused stage); the next unit reads `out_planar`, the last unit of a

@@ -195,6 +195,57 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
       // 16-byte piece (512 contiguous bytes per instruction); the lane = row form touched 32 lines per store.
       const int Cp = p.phase_cols, ppt = p.nt / Cp, ph0 = ntile * ppt;
       const int pieces = 32 * ppt;                       // per plane
+#ifndef PIPER_TC_UPS_SCALAR
+      if (sbias && em.bias) {
+        // batched form: the TMEM loads of all phases of a 16-column slice are issued back to back and waited for once
+        // (the one-load-one-wait form left the eight epilogue warps idle for a TMEM round trip per phase), bias added as
+        // packed fp32 pairs, leaky relu taken in the 16-bit type
+        const uint32_t vm = valid ? 0xffffffffu : 0u;
+        for (int pp = 0; pp < Cp / 16; ++pp) {
+          uint64_t b2[8];
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 x = lds128(sbs + (uint32_t)(pp * 16 + 4 * i) * 4u);
+            b2[2 * i] = f2pack(x.x, x.y); b2[2 * i + 1] = f2pack(x.z, x.w);
+          }
+          for (int k0 = 0; k0 < ppt; k0 += 2) {   // two phases per round trip (four would spill at 166 registers)
+            uint32_t t[2][16];
+            tmem_ld16_async(lane_base + (uint32_t)(k0 * Cp + pp * 16), t[0]);
+            if (k0 + 1 < ppt) tmem_ld16_async(lane_base + (uint32_t)((k0 + 1) * Cp + pp * 16), t[1]);
+            tmem_wait_ld();
+#pragma unroll
+            for (int kk = 0; kk < 2; ++kk) {
+              const int k = k0 + kk;
+              if (k < ppt) {
+                uint32_t pk[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                  const float2 v = f2unpack(f2add(f2pack(__uint_as_float(t[kk][2 * i]), __uint_as_float(t[kk][2 * i + 1])), b2[i]));
+                  pk[i] = lrelu_pack2(v.x, v.y, em.act_slope, p.f16) & vm;
+                }
+                const int slot = k ^ (lane & (ppt - 1));       // spreads the lanes' 16-byte stores over the banks
+                sts128u(tbs + (uint32_t)(lane * ppt + slot) * 16u, make_uint4(pk[0], pk[1], pk[2], pk[3]));
+                sts128u(tbs + (uint32_t)(pieces + lane * ppt + slot) * 16u, make_uint4(pk[4], pk[5], pk[6], pk[7]));
+              }
+            }
+          }
+          __syncwarp();
+          for (int pl = 0; pl < 2; ++pl) {
+            uint16_t* plane = static_cast<uint16_t*>(em.out_act) +
+                              ((size_t)(em.col0 / 8 + pp * 2 + pl) * em.act_rows + em.act_pad) * 8;
+            for (int i = lane; i < pieces; i += 32) {
+              const int qq = i / ppt, sl = i - qq * ppt;
+              if (!((act_mask >> qq) & 1u)) continue;
+              const int k = sl ^ (qq & (ppt - 1));
+              const size_t orow_r = (size_t)(row_base + qq) * p.out_mul + ph0 + k;
+              *reinterpret_cast<uint4*>(plane + orow_r * 8) = lds128u(tbs + (uint32_t)(pl * pieces + i) * 16u);
+            }
+          }
+        }
+        return;
+      }
+#endif
       for (int pp = 0; pp < Cp / 16; ++pp) {
         __syncwarp();
         for (int k = 0; k < ppt; ++k) {

@@ -75,6 +75,7 @@ struct TcStage {
   bool mrf = false;
   void* mrf_w = nullptr;
   int mrf_taps = 0;
+  int post_tap_base = -1;   // last stage: first of the conv_post taps appended to mrf_w (-1: none)
   int tap_base[MRF_MAX_RB][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}};
   // ResBlock1 stage as fused units (conv_mrf.h, unit_mode): one launch per (resblock, dilation) pair of convolutions;
   // rb1_base[j * units + u] = first tap of conv1, conv2 follows it
@@ -155,6 +156,8 @@ struct Context {
   void finalize_voice();            // voice.finalize() + derived layout constants
   int synthesize(const piper_b200_request& rq, piper_b200_result& rs);
   int selftest_conv(int mode, int cin, int cout, int k, int dil, int stride, int rows, int prec, float* out4);
+  int conv1d_op(int transposed, const float* x, int64_t rows, const float* w, const float* bias, int cin, int cout, int k, int dil,
+                int stride, int prec, float* out);
   int length_regulate(const float* logw, const int64_t* lengths, int batch, float length_scale,
                       int32_t* durations, int64_t* frame_lengths, int32_t* frame_index, int64_t frame_capacity);
 };

@@ -321,4 +321,94 @@ int Context::selftest_conv(int mode, int cin, int cout, int k, int dil, int stri
   }
 }
 
+// Op-level known-answer hook behind piper_b200_conv1d: ONE Conv / ConvTranspose node on caller-supplied operands in the
+// ONNX layouts (Conv W [cout][cin][k], ConvTranspose W [cin][cout][k]; "same" padding dil*(k-1)/2 resp. (k-stride)/2,
+// the only forms a Piper-VITS graph holds), so that a test can set the product kernels against
+// torch.nn.functional.conv1d / conv_transpose1d.  fp32 -> conv_f32_*_kernel, f16 / bf16 -> conv_tc_persist_kernel
+// (tcgen05) on the 16-bit rounding of x and W with fp32 accumulation.  Reference kernels: conv1d_f32
+// (conv1d.metal:28-71), convtranspose1d_f32 (conv1d.metal:97-142).
+int Context::conv1d_op(int transposed, const float* x, int64_t rows64, const float* w, const float* bias, int cin, int cout, int k,
+                       int dil, int stride, int prec, float* out) {
+  try {
+    CUDA_OK(cudaSetDevice(device));
+    if (rows64 <= 0 || rows64 > (1 << 24)) throw std::runtime_error("invalid argument: rows");
+    const int rows = (int)rows64;
+    const bool ct = transposed != 0;
+    if (ct && (stride < 1 || k % stride || dil != 1)) throw std::runtime_error("invalid argument: ConvTranspose needs k % stride == 0, dilation 1");
+    if (!ct && (stride != 1 || (k & 1) == 0)) throw std::runtime_error("invalid argument: Conv needs stride 1 and an odd kernel");
+    const bool use_tc = prec != PIPER_B200_PRECISION_FP32;
+    if (use_tc && (cin % 32 || cout % 16)) throw std::runtime_error("invalid argument: tensor-core conv needs cin % 32 == 0, cout % 16 == 0");
+    const int f16 = prec == PIPER_B200_PRECISION_F16;
+    Exec ex;
+    ex.st = stream;
+    const int phases = ct ? stride : 1, taps = ct ? k / stride : k;
+    const int ldw = (cout + 63) / 64 * 64;
+    const int pad = ct ? (k - stride) / 2 : 0;
+    std::vector<float> pk((size_t)phases * taps * cin * ldw, 0.f), hb(ldw, 0.f);
+    if (ct) {   // same repack as Binder::conv_transpose (voice.cpp): phase ph, tap j <- kernel position (ph + pad) % u + j * u
+      for (int ph = 0; ph < phases; ++ph) {
+        const int kk0 = (ph + pad) % stride;
+        for (int j = 0; j < taps; ++j)
+          for (int ci = 0; ci < cin; ++ci)
+            for (int co = 0; co < cout; ++co)
+              pk[(((size_t)ph * taps + j) * cin + ci) * ldw + co] = w[((size_t)ci * cout + co) * k + kk0 + j * stride];
+      }
+    } else {
+      for (int co = 0; co < cout; ++co)
+        for (int ci = 0; ci < cin; ++ci)
+          for (int t = 0; t < k; ++t) pk[((size_t)t * cin + ci) * ldw + co] = w[((size_t)co * cin + ci) * k + t];
+    }
+    for (int co = 0; co < cout && bias; ++co) hb[co] = bias[co];
+    const int Rout = rows * phases;
+    DevBuf dw(pk.size() * 4), db(hb.size() * 4), dx((size_t)rows * cin * 4), dx16((size_t)rows * cin * 2), dutt((size_t)rows * 4);
+    DevBuf dout((size_t)Rout * cout * 4);
+    CUDA_OK(cudaMemcpy(dw.p, pk.data(), pk.size() * 4, cudaMemcpyHostToDevice));
+    CUDA_OK(cudaMemcpy(db.p, hb.data(), hb.size() * 4, cudaMemcpyHostToDevice));
+    CUDA_OK(cudaMemcpy(dx.p, x, (size_t)rows * cin * 4, cudaMemcpyHostToDevice));
+    ConvW cw;
+    cw.w = dw.as<float>(); cw.b = db.as<float>();
+    cw.cin = cin; cw.cout = cout; cw.k = k; cw.dil = dil; cw.ldw = ldw;
+    cw.taps = taps; cw.phases = phases; cw.ct_pad = pad; cw.pad_l = dil * (k - 1) / 2;
+    std::vector<void*> allocs;
+    if (!use_tc) {
+      ConvArgs r;
+      r.in = dx.as<float>(); r.ldin = cin;
+      r.w = cw.w; r.ldw = ldw; r.bias = cw.b;
+      r.out = dout.as<float>(); r.ldout = cout;
+      r.row_utt = dutt.as<int>(); r.valid_div = phases;   // all rows belong to utterance 0 (DevBuf zero-fills)
+      r.R_in = rows; r.Q = rows; r.cin = cin; r.cout = cout; r.taps = taps;
+      if (ct) { r.tap_step = -1; r.out_mul = stride; r.phases = phases; r.ct_pad = pad; }
+      else { r.tap_step = dil; r.in_off = -cw.pad_l; }
+      launch_conv_f32(ex, r);
+    } else {
+      launch_to_act16(ex, dx.as<float>(), dx16.p, (int64_t)rows * cin, 1.f, f16);
+      TcW tw = make_tcw(ex, allocs, cw, nullptr, f16);
+      TcConvArgs a;
+      a.in = dx16.p; a.ldin = cin; a.R_in = rows; a.cin = cin;
+      a.w = &tw; a.Q = rows;
+      a.row_utt = dutt.as<int>(); a.valid_div = phases;
+      a.f16 = f16;
+      if (ct) { a.tap_step = -1; a.out_mul = stride; }
+      else { a.tap_step = dil; a.in_off = -cw.pad_l; }
+      a.n_groups = 1;
+      a.nt = 16;
+      for (int nt : {128, 96, 64, 48, 32, 16}) if (cout % nt == 0) { a.nt = nt; break; }
+      a.n_tiles = cout / a.nt;
+      a.e[0].bias = cw.b;
+      a.e[0].out_f32 = dout.as<float>(); a.e[0].ld_f32 = cout;
+      launch_conv_tc(ex, a);
+    }
+    CUDA_OK(cudaStreamSynchronize(stream));
+    CUDA_OK(cudaGetLastError());
+    CUDA_OK(cudaMemcpy(out, dout.p, (size_t)Rout * cout * 4, cudaMemcpyDeviceToHost));
+    for (void* p : allocs) cudaFree(p);
+    return PIPER_B200_OK;
+  } catch (const std::exception& e) {
+    last_error = e.what();
+    cudaGetLastError();
+    if (last_error.rfind("invalid", 0) == 0) return PIPER_B200_ERR_INVALID_ARGUMENT;
+    return last_error.rfind("unsupported", 0) == 0 ? PIPER_B200_ERR_UNSUPPORTED : PIPER_B200_ERR_CUDA;
+  }
+}
+
 }  // namespace piper

@@ -584,7 +584,12 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
     timings.d2h_bytes = (int64_t)d2h;
     timings.dec_flops = hp.dec_flops_per_frame * (double)total_frames;
     timings.flow_flops = hp.flow_flops_per_frame * (double)total_frames;
+    // PIPER_B200_PROF_DUMP=1 (with PIPER_B200_FLAG_PROFILE): one stderr line per profiled launch, in launch order
+    static const bool prof_dump = [] { const char* e = getenv("PIPER_B200_PROF_DUMP"); return e && atoi(e) != 0; }();
     for (const Prof::Span& sp : prof.spans) {
+      if (prof_dump)
+        fprintf(stderr, "prof cls %d ms %.4f gflop %.3f tflops %.1f\n", sp.cls, ms_between(sp.a, sp.b), sp.flops * 1e-9,
+                sp.flops * 1e-9 / std::max(ms_between(sp.a, sp.b), 1e-6));
       timings.class_ms[sp.cls] += ms_between(sp.a, sp.b);
       timings.class_flops[sp.cls] += sp.flops;
       timings.class_launches[sp.cls] += 1;

@@ -1,6 +1,7 @@
 // Shared device helpers for the tcgen05 / TMEM / TMA kernels (conv_tc.cu, conv_mrf.cu): PTX
 // wrappers, shared-memory matrix descriptors, instruction descriptors, tensor-map encoding.
 #pragma once
+#include <cstdio>
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
@@ -41,6 +42,29 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   const uint32_t addr = smem_u32(bar);
+#ifdef PIPER_MBAR_WATCHDOG
+  // diagnostic build (make trace): a wait that lasts ~2 s names itself and traps instead of hanging the box.
+  // The barrier is identified by its shared-memory address; the kernels print the base of their barrier block once.
+  const long long t0 = clock64();
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred P1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, P1;\n\t"
+        "}\n"
+        : "=r"(ok)
+        : "r"(addr), "r"(parity)
+        : "memory");
+    if (ok) break;
+    if (clock64() - t0 > 4000000000LL) {
+      printf("mbar watchdog: block %d thread %d (warp %d) waits on barrier @%u parity %u\n", (int)blockIdx.x, (int)threadIdx.x,
+             (int)(threadIdx.x >> 5), addr, parity);
+      __trap();
+    }
+  }
+#else
   asm volatile(
       "{\n\t"
       ".reg .pred P1;\n\t"
@@ -52,6 +76,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "}\n" ::"r"(addr),
       "r"(parity)
       : "memory");
+#endif
 }
 __device__ __forceinline__ void fence_barrier_init() {
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -106,6 +131,17 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint6
       "}\n" ::"r"(tmem_d),
       "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
+}
+// one fp32 column of the warp's 32 lanes
+__device__ __forceinline__ float tmem_ld1(uint32_t taddr) {
+  uint32_t r;
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];\n\t"
+      "tcgen05.wait::ld.sync.aligned;"
+      : "=r"(r)
+      : "r"(taddr)
+      : "memory");
+  return __uint_as_float(r);
 }
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
   uint32_t r[16];
@@ -169,6 +205,40 @@ __device__ __forceinline__ uint32_t pack2(float a, float b, int f16) {
   return *reinterpret_cast<const uint32_t*>(&h);
 }
 __device__ __forceinline__ float lrelu(float v, float s) { return v >= 0.f ? v : v * s; }
+// Packed fp32 pairs (FADD2 / FMUL2, one issue slot for two IEEE operations - same rounding as the scalar forms) for the
+// epilogues of the fused stage kernel, which are bound by issue slots
+__device__ __forceinline__ uint64_t f2pack(float a, float b) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ float2 f2unpack(uint64_t v) {
+  float2 r;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v));
+  return r;
+}
+__device__ __forceinline__ uint64_t f2add(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t f2mul(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+// lrelu(., s) of a pair rounded to the 16-bit operand type, taken in that type: max(h, s h) with h = round16(v)
+// (0 < s < 1; against round16(max(v, s v)) the negative side is rounded twice, 2^-11 / 2^-8 relative at most)
+__device__ __forceinline__ uint32_t lrelu_pack2(float a, float b, float s, int f16) {
+  if (f16) {
+    __half2 h = __floats2half2_rn(a, b);
+    h = __hmax2(h, __hmul2(h, __float2half2_rn(s)));
+    return *reinterpret_cast<const uint32_t*>(&h);
+  }
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  h = __hmax2(h, __hmul2(h, __float2bfloat162_rn(s)));
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
 __device__ __forceinline__ float2 unpack2(uint32_t u, int f16) {
   if (f16) return __half22float2(*reinterpret_cast<const __half2*>(&u));
   return make_float2(__uint_as_float(u << 16), __uint_as_float(u & 0xFFFF0000u));   // bf16 = upper half of an fp32

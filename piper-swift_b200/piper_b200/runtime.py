@@ -21,7 +21,8 @@ from typing import Iterator, List, Optional, Sequence
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "libpiper_b200.so")
+# PIPER_B200_LIB: a diagnostic build of the same library (e.g. `make trace`); there is no non-CUDA alternative
+LIB_PATH = os.environ.get("PIPER_B200_LIB") or os.path.join(os.path.dirname(_HERE), "libpiper_b200.so")
 
 OK = 0
 PRECISION = {"fp32": 0, "bf16": 1, "f16": 2}
@@ -116,6 +117,7 @@ def load_library(path: str = LIB_PATH):
         "piper_b200_length_regulate_noalloc": (C.c_int, [P, P, P, C.c_int32, C.c_float, P, P]),
         "piper_b200_random_normal": (C.c_int, [P, C.c_uint64, C.c_int64, P]),
         "piper_b200_selftest_conv": (C.c_int, [P] + [C.c_int32] * 8 + [C.POINTER(C.c_float)]),
+        "piper_b200_conv1d": (C.c_int, [P, C.c_int32, P, C.c_int64, P, P] + [C.c_int32] * 6 + [P]),
         "piper_b200_ipa_to_ids": (C.c_int, [P, C.c_char_p, C.POINTER(C.c_int64), C.c_int64, C.POINTER(C.c_int64)]),
         "piper_b200_config_ipa_to_ids": (C.c_int, [C.c_char_p, C.c_char_p, C.POINTER(C.c_int64), C.c_int64,
                                                    C.POINTER(C.c_int64)]),
@@ -136,7 +138,7 @@ EXPORTED_SYMBOLS = [
     "piper_b200_random_normal", "piper_b200_selftest_conv", "piper_b200_ipa_to_ids", "piper_b200_config_ipa_to_ids",
     "piper_b200_stream_next", "piper_b200_device_count", "piper_b200_set_output_buffer", "piper_b200_host_alloc",
     "piper_b200_host_free", "piper_b200_host_register", "piper_b200_host_unregister",
-    "piper_b200_length_regulate_noalloc", "piper_b200_add_node",
+    "piper_b200_length_regulate_noalloc", "piper_b200_add_node", "piper_b200_conv1d",
 ]
 NOALLOC_MAX_IDS, NOALLOC_MAX_BATCH = 65536, 1024
 
@@ -539,6 +541,23 @@ class PiperCUDARuntime:
     def random_normal(self, count: int, seed: int = 1234) -> np.ndarray:
         out = np.zeros(count, np.float32)
         self._check(self._lib.piper_b200_random_normal(self._ctx, seed, count, out.ctypes.data))
+        return out
+
+    def conv1d(self, x: np.ndarray, w: np.ndarray, bias: Optional[np.ndarray] = None, dilation: int = 1, stride: int = 1,
+               transposed: bool = False, precision: str = "fp32") -> np.ndarray:
+        """piper_b200_conv1d: one Conv / ConvTranspose node on caller-supplied operands.  x [rows][cin] time-major, w in
+        the ONNX layout (Conv [cout][cin][k], ConvTranspose [cin][cout][k]); returns [rows*stride][cout]."""
+        x = np.ascontiguousarray(x, np.float32)
+        w = np.ascontiguousarray(w, np.float32)
+        rows, cin = x.shape
+        cout = w.shape[1] if transposed else w.shape[0]
+        assert (w.shape[0] if transposed else w.shape[1]) == cin
+        k = w.shape[2]
+        b = None if bias is None else np.ascontiguousarray(bias, np.float32)
+        out = np.empty((rows * (stride if transposed else 1), cout), np.float32)
+        self._check(self._lib.piper_b200_conv1d(self._ctx, 1 if transposed else 0, x.ctypes.data, rows, w.ctypes.data,
+                                                None if b is None else b.ctypes.data, cin, cout, k, dilation, stride,
+                                                PRECISION[precision], out.ctypes.data))
         return out
 
     def selftest_conv(self, mode: int, cin: int, cout: int, k: int = 1, dilation: int = 1, stride: int = 1,

@@ -48,6 +48,45 @@ def test_tcgen05_conv_matches_fp32_kernel(case, prec):
     assert r["max_abs_diff"] <= tol, r
 
 
+KAT = [  # transposed, cin, cout, k, dil, stride, rows  - the node shapes of the medium / high generator, flow, encoder
+    (0, 192, 256, 7, 1, 1, 515), (0, 192, 384, 5, 1, 1, 700), (0, 192, 192, 1, 1, 1, 300), (0, 192, 768, 3, 1, 1, 260),
+    (0, 128, 128, 3, 1, 1, 1000), (0, 64, 64, 5, 6, 1, 2100), (0, 32, 32, 7, 12, 1, 4000), (0, 256, 256, 11, 5, 1, 900),
+    (0, 32, 32, 3, 1, 1, 1), (0, 64, 64, 7, 3, 1, 129),
+    (1, 256, 128, 16, 1, 8, 300), (1, 128, 64, 16, 1, 8, 777), (1, 64, 32, 8, 1, 4, 1500), (1, 512, 256, 16, 1, 8, 100),
+    (1, 128, 64, 4, 1, 2, 500),
+]
+
+
+@pytest.mark.parametrize("prec", ["fp32", "f16", "bf16"])
+@pytest.mark.parametrize("case", KAT, ids=lambda c: "%s_%dto%d_k%d_d%d_s%d_r%d" % (("ct" if c[0] else "conv",) + c[1:]))
+def test_conv_kernels_against_torch(case, prec):
+    """Per-op known-answer test: the product's convolution kernels - conv_f32_*_kernel in fp32,
+    conv_tc_persist_kernel (tcgen05) in f16 / bf16 - through piper_b200_conv1d on seeded random operands against
+    torch.nn.functional.conv1d / conv_transpose1d on the CPU.  In the 16-bit modes torch sees the same rounded operands
+    in float64, so what is left is fp32 accumulation order: tolerance 2e-5 * sqrt(cin*k) (observed ~1e-6)."""
+    import torch
+    import torch.nn.functional as F
+    tr, cin, cout, k, dil, stride, rows = case
+    g = torch.Generator().manual_seed(1000 + cin + 7 * cout + 31 * k + rows)
+    x = torch.randn(rows, cin, generator=g)
+    w = torch.randn((cin, cout, k) if tr else (cout, cin, k), generator=g) / float(np.sqrt(cin * k / (stride if tr else 1)))
+    b = torch.randn(cout, generator=g) * 0.1
+    if prec != "fp32":
+        dt = torch.float16 if prec == "f16" else torch.bfloat16
+        x, w = x.to(dt).float(), w.to(dt).float()
+    xt = x.t().unsqueeze(0).double()
+    if tr:
+        ref = F.conv_transpose1d(xt, w.double(), b.double(), stride=stride, padding=(k - stride) // 2)
+    else:
+        ref = F.conv1d(xt, w.double(), b.double(), dilation=dil, padding=dil * (k - 1) // 2)
+    ref = ref[0].t().numpy()
+    out = rt("tiny", "fp32").conv1d(x.numpy(), w.numpy(), b.numpy(), dilation=dil, stride=stride, transposed=bool(tr),
+                                    precision=prec)
+    assert out.shape == ref.shape
+    tol = 2e-5 * float(np.sqrt(cin * k)) * max(1.0, float(np.abs(ref).max()))
+    assert float(np.abs(out - ref).max()) <= tol, (float(np.abs(out - ref).max()), tol)
+
+
 def test_selftest_rejects_bad_shapes():
     with pytest.raises(PiperB200Error):
         rt("tiny", "fp32").selftest_conv(0, 24, 64, 3, 1, 1, 100, precision="bf16")    # cin not a multiple of 32

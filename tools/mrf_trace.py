@@ -37,8 +37,15 @@ def dur(w, a, b):
     return tot / max(cnt, 1), cnt
 span = out[-1][0] - out[0][0]
 print("total span cycles", span)
-for name, w, a, b in [("mma conv1 wait", 1, 1, 2), ("mma conv1 issue", 1, 2, 3), ("mma conv2 wait", 2, 5, 6), ("mma conv2 issue", 2, 6, 7),
-                      ("epi g0 s wait", 3, 10, 11), ("epi g0 d wait", 3, 11, 12), ("epi g0 work", 3, 12, 13), ("epi g0 out wait", 3, 14, 15),
-                      ("epi g0 out work", 3, 15, 16), ("prod x wait", 0, 20, 21)]:
-    d, c = dur(w, a, b)
-    print("%-18s avg %8.0f cycles x %5d = %5.1f%% of span" % (name, d, c, 100.0 * d * c / span))
+# warps: 0 producer, 1/2 conv1 issuers (even/odd tiles), 3/4 conv2 issuers, 5.. epilogue (group g = warps 5+4g .. 8+4g)
+warps = sorted(by_w)
+PAIRS = [("c1 wait", 1, 2), ("c1 issue", 2, 3), ("c2 wait", 5, 6), ("c2 issue", 6, 7), ("w_full wait", 24, 25),
+         ("x wait", 20, 21), ("w_empty wait", 22, 23), ("ep s wait", 10, 11), ("ep d wait", 11, 12), ("ep work", 12, 13),
+         ("out wait", 14, 15), ("out work", 15, 16)]
+for w in warps:
+    if w > 9 and w != warps[-1]:
+        continue
+    for name, a_, b_ in PAIRS:
+        d, c = dur(w, a_, b_)
+        if c:
+            print("warp %2d %-14s avg %8.0f cycles x %5d = %5.1f%% of span" % (w, name, d, c, 100.0 * d * c / span))
