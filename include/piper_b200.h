@@ -62,6 +62,10 @@ extern "C" {
                                             * PiperMetalRuntime.swift:82-121) */
 #define PIPER_B200_FLAG_PCM16_ONLY 64u      /* int16 PCM is the ONLY host output (WavFileWriter.swift:20-30 rule): result.audio is NULL,
                                             * half the device->host bytes; a caller-owned output buffer then receives int16 */
+#define PIPER_B200_FLAG_GENERIC 128u        /* run the graph node by node through the generic op executor (the reference's
+                                            * GraphExecutor.executeNode, GraphExecutor.swift:591-2663) instead of the fused pipeline;
+                                            * implied for a graph the fused pipeline does not recognise.  Route A only, float host
+                                            * audio only; durations are not reported (read them with piper_b200_run_graph) */
 #define PIPER_B200_FLAG_PROFILE 16u        /* CUDA events around every GEMM-class kernel launch (PIPER_PROFILE, GraphExecutor.swift:163-175) */
 
 typedef struct piper_b200_ctx piper_b200_ctx;
@@ -249,6 +253,17 @@ int piper_b200_random_normal(piper_b200_ctx* ctx, uint64_t seed, int64_t count, 
  * out4 = {max |tc - fp32|, max |fp32|, tc kernel ms, fp32 kernel ms}. */
 int piper_b200_selftest_conv(piper_b200_ctx* ctx, int32_t mode, int32_t cin, int32_t cout, int32_t k,
                              int32_t dilation, int32_t stride, int32_t rows, int32_t precision, float* out4);
+
+/* The generic op executor, one utterance: runs every node of the loaded graph (route A) as plain CUDA kernels and copies
+ * the value called `value_name` (NULL = the graph output) to `out` - the reference's
+ * GraphExecutor.execute(inputs:maxNodeIndex:overrides:) / executeOutput (GraphExecutor.swift:75-152, 156-327) over
+ * executeNode (:591-2663), 50 op types (csrc/graph_exec.cu).  scales3 = {noise_scale, length_scale, noise_w} (the
+ * `scales` feed), speaker_id feeds `sid` when the graph has that input.  dtype = ONNX data_type of the value (1 float32,
+ * 7 int64, 9 bool = one byte), dims8 / rank its shape; out may be NULL to query the shape only.  An op outside the set
+ * returns PIPER_B200_ERR_UNSUPPORTED (ExecutionError.unsupportedOp). */
+int piper_b200_run_graph(piper_b200_ctx* ctx, const int64_t* phoneme_ids, int64_t n_ids, int64_t speaker_id,
+                         const float* scales3, uint64_t seed, const char* value_name, void* out, size_t out_capacity_bytes,
+                         int32_t* dtype, int64_t* dims8, int32_t* rank);
 
 /* Op-level known-answer hook: ONE Conv (transposed = 0; odd k, stride 1, "same" padding dilation*(k-1)/2) or
  * ConvTranspose (transposed = 1; k a multiple of stride, padding (k-stride)/2, rows*stride output rows) node on

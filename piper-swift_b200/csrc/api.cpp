@@ -1,5 +1,6 @@
 // C ABI (include/piper_b200.h).  No exception leaves this file.
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <stdexcept>
 
@@ -107,7 +108,8 @@ int piper_b200_load_voice(piper_b200_ctx* ctx, const char* model_path, const cha
   return guarded(ctx, [&] {
     Context& c = ctx->c;
     if (c.voice.finalized) throw std::runtime_error("state: a voice is already loaded in this context");
-    piper::OnnxModel m = piper::load_onnx(model_path);
+    std::shared_ptr<piper::OnnxModel> mp = std::make_shared<piper::OnnxModel>(piper::load_onnx(model_path));
+    const piper::OnnxModel& m = *mp;
     // the graph signature the reference's loader test pins (ONNXParsingTests.swift:22-27)
     auto has = [](const std::vector<std::string>& v, const char* n) {
       for (auto& s : v)
@@ -119,10 +121,24 @@ int piper_b200_load_voice(piper_b200_ctx* ctx, const char* model_path, const cha
       throw std::runtime_error("unsupported: graph signature is not input/input_lengths/scales -> output");
     c.config = piper::PiperConfig::load(config_path);
     c.have_config = true;
-    c.voice.add_onnx(m);
-    c.finalize_voice();
-    if (c.config.num_speakers > 1 && c.voice.hp.gin == 0)
-      throw std::runtime_error("unsupported: config says multi-speaker but the graph has no emb_g.weight");
+    c.onnx = mp;
+    c.gexec.reset();
+    c.generic_only = false;
+    try {
+      c.voice.add_onnx(m);
+      c.finalize_voice();
+      if (c.config.num_speakers > 1 && c.voice.hp.gin == 0)
+        throw std::runtime_error("unsupported: config says multi-speaker but the graph has no emb_g.weight");
+    } catch (const std::exception& e) {
+      // Not the Piper-VITS pattern the fused pipeline binds: like the reference, which interprets any graph of its ops
+      // node by node (GraphExecutor.swift:591-2663), the context falls back to the generic op executor.  A graph with an
+      // op outside that set fails there, at the first synthesize, with PIPER_B200_ERR_UNSUPPORTED.
+      const std::string msg = e.what();
+      if (msg.rfind("unsupported", 0) != 0) throw;
+      c.voice = piper::Voice();
+      c.generic_only = true;
+      c.generic_reason = msg;
+    }
     return PIPER_B200_OK;
   });
 }
@@ -231,6 +247,15 @@ int piper_b200_get_voice_info(const piper_b200_ctx* ctx, piper_b200_voice_info* 
     return PIPER_B200_ERR_INVALID_ARGUMENT;
   }
   const Context& c = ctx->c;
+  if (c.generic_only) {   // an unrecognised graph: only what the config says is known
+    std::memset(out, 0, sizeof(*out));
+    out->sample_rate = c.config.sample_rate;
+    out->num_speakers = c.config.num_speakers;
+    out->noise_scale = c.config.noise_scale;
+    out->length_scale = c.config.length_scale;
+    out->noise_w = c.config.noise_w;
+    return PIPER_B200_OK;
+  }
   if (!c.voice.finalized) {
     g_error = "state: voice not finalized";
     return PIPER_B200_ERR_STATE;
@@ -351,7 +376,10 @@ int piper_b200_synthesize(piper_b200_ctx* ctx, const piper_b200_request* req, pi
     g_error = "invalid argument: null pointer";
     return PIPER_B200_ERR_INVALID_ARGUMENT;
   }
-  return guarded(ctx, [&] { return ctx->c.synthesize(*req, *res); });
+  return guarded(ctx, [&] {
+    if (ctx->c.generic_only || (req->flags & PIPER_B200_FLAG_GENERIC)) return ctx->c.synthesize_generic(*req, *res);
+    return ctx->c.synthesize(*req, *res);
+  });
 }
 
 int piper_b200_stream_next(piper_b200_ctx* ctx, int64_t max_frames, piper_b200_result* res, int32_t* is_final) {
@@ -496,6 +524,19 @@ int piper_b200_conv1d(piper_b200_ctx* ctx, int32_t transposed, const float* x, i
   const int rc = ctx->c.conv1d_op(transposed, x, rows, w, bias, cin, cout, k, dilation, stride, precision, out);
   if (rc != PIPER_B200_OK) g_error = ctx->c.last_error;
   return rc;
+}
+
+int piper_b200_run_graph(piper_b200_ctx* ctx, const int64_t* phoneme_ids, int64_t n_ids, int64_t speaker_id, const float* scales3,
+                         uint64_t seed, const char* value_name, void* out, size_t out_capacity_bytes, int32_t* dtype, int64_t* dims8,
+                         int32_t* rank) {
+  if (!ctx || !phoneme_ids || n_ids <= 0 || !scales3) {
+    g_error = "invalid argument: null context, ids or scales";
+    if (ctx) ctx->c.last_error = g_error;
+    return PIPER_B200_ERR_INVALID_ARGUMENT;
+  }
+  return guarded(ctx, [&] {
+    return ctx->c.run_graph(phoneme_ids, n_ids, speaker_id, scales3, seed, value_name, out, out_capacity_bytes, dtype, dims8, rank);
+  });
 }
 
 }  // extern "C"

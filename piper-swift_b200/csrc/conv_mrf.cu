@@ -634,14 +634,22 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
             tmem_ld16_async(scol + 16u, t1);
             tmem_wait_ld();
             uint32_t pk[16];
+            {
+              const uint64_t inv2 = f2pack(inv_nk, inv_nk);
+              const uint32_t vm = valid ? 0xffffffffu : 0u;
+              const ulonglong2* bq = reinterpret_cast<const ulonglong2*>(b2s);
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              const float a0 = lrelu((__uint_as_float(t0[2 * e]) + b2s[2 * e]) * inv_nk, p.post_slope);
-              const float a1 = lrelu((__uint_as_float(t0[2 * e + 1]) + b2s[2 * e + 1]) * inv_nk, p.post_slope);
-              const float c0 = lrelu((__uint_as_float(t1[2 * e]) + b2s[16 + 2 * e]) * inv_nk, p.post_slope);
-              const float c1 = lrelu((__uint_as_float(t1[2 * e + 1]) + b2s[16 + 2 * e + 1]) * inv_nk, p.post_slope);
-              pk[e] = valid ? pack2(a0, a1, p.f16) : 0u;
-              pk[8 + e] = valid ? pack2(c0, c1, p.f16) : 0u;
+              for (int q4 = 0; q4 < 4; ++q4) {
+                const ulonglong2 ba = bq[q4], bc = bq[4 + q4];
+                const float2 a01 = f2unpack(f2mul(f2add(f2pack(__uint_as_float(t0[4 * q4]), __uint_as_float(t0[4 * q4 + 1])), ba.x), inv2));
+                const float2 a23 = f2unpack(f2mul(f2add(f2pack(__uint_as_float(t0[4 * q4 + 2]), __uint_as_float(t0[4 * q4 + 3])), ba.y), inv2));
+                const float2 c01 = f2unpack(f2mul(f2add(f2pack(__uint_as_float(t1[4 * q4]), __uint_as_float(t1[4 * q4 + 1])), bc.x), inv2));
+                const float2 c23 = f2unpack(f2mul(f2add(f2pack(__uint_as_float(t1[4 * q4 + 2]), __uint_as_float(t1[4 * q4 + 3])), bc.y), inv2));
+                pk[2 * q4] = lrelu_pack2(a01.x, a01.y, p.post_slope, p.f16) & vm;
+                pk[2 * q4 + 1] = lrelu_pack2(a23.x, a23.y, p.post_slope, p.f16) & vm;
+                pk[8 + 2 * q4] = lrelu_pack2(c01.x, c01.y, p.post_slope, p.f16) & vm;
+                pk[8 + 2 * q4 + 1] = lrelu_pack2(c23.x, c23.y, p.post_slope, p.f16) & vm;
+              }
             }
             uint8_t* y = Y1 + (size_t)((p.G + row_in_win) * 16);
 #pragma unroll
@@ -785,7 +793,29 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
 #pragma unroll
           for (int e = 0; e < 16; ++e) { s0[e] = __uint_as_float(t0[e]); s1[e] = __uint_as_float(t1[e]); }
         }
-        if (owned) {
+        if (!UNIT && owned && p.out_act && !p.out_f32) {
+          // ResBlock2 stage whose only output is the next ConvTranspose's 16-bit operand: packed fp32 pairs, leaky
+          // relu in the 16-bit type
+          const uint64_t inv2 = f2pack(inv_nk, inv_nk);
+          const uint32_t vm = valid ? 0xffffffffu : 0u;
+          const ulonglong2* bq = reinterpret_cast<const ulonglong2*>(b2s + cb);
+          uint32_t pk[16];
+#pragma unroll
+          for (int q4 = 0; q4 < 4; ++q4) {
+            const ulonglong2 ba = bq[q4], bc = bq[4 + q4];
+            const float2 a01 = f2unpack(f2mul(f2add(f2pack(s0[4 * q4], s0[4 * q4 + 1]), ba.x), inv2));
+            const float2 a23 = f2unpack(f2mul(f2add(f2pack(s0[4 * q4 + 2], s0[4 * q4 + 3]), ba.y), inv2));
+            const float2 c01 = f2unpack(f2mul(f2add(f2pack(s1[4 * q4], s1[4 * q4 + 1]), bc.x), inv2));
+            const float2 c23 = f2unpack(f2mul(f2add(f2pack(s1[4 * q4 + 2], s1[4 * q4 + 3]), bc.y), inv2));
+            pk[2 * q4] = lrelu_pack2(a01.x, a01.y, p.act_slope, p.f16) & vm;
+            pk[2 * q4 + 1] = lrelu_pack2(a23.x, a23.y, p.act_slope, p.f16) & vm;
+            pk[8 + 2 * q4] = lrelu_pack2(c01.x, c01.y, p.act_slope, p.f16) & vm;
+            pk[8 + 2 * q4 + 1] = lrelu_pack2(c23.x, c23.y, p.act_slope, p.f16) & vm;
+          }
+          uint4* dst = reinterpret_cast<uint4*>(static_cast<uint16_t*>(p.out_act) + (size_t)grow * C + cb);
+#pragma unroll
+          for (int g = 0; g < 4; ++g) dst[g] = make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
+        } else if (owned) {
 #pragma unroll
           for (int e = 0; e < 16; ++e) {
             s0[e] = valid ? (s0[e] + b2s[cb + e]) * inv_nk : 0.f;

@@ -722,7 +722,15 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
 // warpgroups, one per TMEM buffer) overlaps the TMA/MMA main loop of tile i+1 inside the same CTA.
 constexpr int TCP_MAX_STAGES = 8;
 constexpr int TCP_EG = 1;                      // epilogue warpgroups per TMEM buffer (column split); 2 starves registers
-constexpr int TCP_THREADS = 64 + 2 * TCP_EG * 128;   // producer, MMA issuer, epilogue warpgroups
+// epilogue warpgroups taking tiles round robin.  The epilogues are latency-bound per warp, so a third group was tried
+// (-DPIPER_TC_NG=3): 14 warps put four on one SM sub-partition (16384 registers each), i.e. at most 128 registers per
+// thread instead of 168 - a 144-register build fails to launch ("too many resources") although 448 x 144 < 65536, and the
+// 128-register build (104 bytes of spills) did not finish the GPU suite inside the call's time limit.  Two groups stay.
+#ifndef PIPER_TC_NG
+#define PIPER_TC_NG 2
+#endif
+constexpr int TCP_NG = PIPER_TC_NG;
+constexpr int TCP_THREADS = 64 + TCP_NG * TCP_EG * 128;   // producer, MMA issuer, epilogue warpgroups
 
 __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const __grid_constant__ CUtensorMap tmap_a,
                                                                          const __grid_constant__ CUtensorMap tmap_b,
@@ -741,7 +749,7 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
   uint64_t* acc_empty = acc_full + 4;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 4);
   float* tbuf_base = reinterpret_cast<float*>(smem + (size_t)stages * stage_bytes + 512);   // one 32 x 36 float tile per epilogue warp
-  float* sbias = tbuf_base + 2 * TCP_EG * 4 * 32 * 36;                                      // [2][TC_SBIAS] bias of both column groups
+  float* sbias = tbuf_base + TCP_NG * TCP_EG * 4 * 32 * 36;                                      // [2][TC_SBIAS] bias of both column groups
   const int bias_w = p.phase_cols ? p.phase_cols : n_tiles * p.nt;
   const bool bias_staged = bias_w <= TC_SBIAS;
   if (bias_staged)
@@ -849,13 +857,20 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
     }
   } else {
     // ===== epilogue: four warpgroups = (TMEM buffer, i.e. every other tile) x (half of the column chunks) =====
-    const uint32_t group = ((uint32_t)(warp - 2) >> 2) & 1u, half = (uint32_t)(warp - 2) >> 3;
-    uint32_t li = 0;
+    const uint32_t group = ((uint32_t)(warp - 2) >> 2) % (uint32_t)TCP_NG, half = (uint32_t)(warp - 2) / (4u * TCP_NG);
+    // With two accumulator buffers only two groups take tiles: a third would wait on a buffer's acc_full barrier at
+    // every third use, and a parity wait that skips two phases passes early (same hazard as conv_mrf.cu's weight ring).
+    // With four buffers a group skips one use per visit, and that use has completed before the group's own previous
+    // tile did (MMAs retire in issue order), so the wait is sound.
+    const uint32_t ng_eff = p.nbuf == 4 ? (uint32_t)TCP_NG : 2u;
+    uint32_t li = 0, turn = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++li) {
-      if ((li & 1u) != group) continue;
+      const bool mine = turn == group;
+      if (++turn == ng_eff) turn = 0;
+      if (!mine) continue;
       const int phase = t % p.phases, rest = t / p.phases;
       const int mt = rest % m_tiles, ntile = rest / m_tiles;
-      const uint32_t buf = p.nbuf == 4 ? (li & 3u) : group;
+      const uint32_t buf = p.nbuf == 4 ? (li & 3u) : (li & 1u);
       const uint32_t use = p.nbuf == 4 ? (li >> 2) : (li >> 1);
       tc_epilogue(p, tmem_base + buf * acc_stride, mt * TC_BM, ntile, phase, warp, lane, &acc_full[buf], use & 1u,
                   tbuf_base + (warp - 2) * (32 * 36), (int)half, TCP_EG, bias_staged ? sbias : nullptr);
@@ -956,9 +971,9 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
     while ((int)pc < p.nbuf * n_groups * a.nt) pc <<= 1;
     p.tmem_cols = pc;
     const int sb = TC_BM * w.kb * 2 + n_groups * a.nt * w.kb * 2;
-    constexpr int TBUF_BYTES = 2 * TCP_EG * 4 * 32 * 36 * 4;
+    constexpr int TBUF_BYTES = TCP_NG * TCP_EG * 4 * 32 * 36 * 4;
     constexpr int SBIAS_BYTES = 2 * TC_SBIAS * 4;
-    int st = (TC_SMEM_MAX - 2048 - TBUF_BYTES - SBIAS_BYTES) / sb;
+    int st = (TC_SMEM_MAX - 3072 - TBUF_BYTES - SBIAS_BYTES) / sb;   // 1 KB static + alignment slack + barriers
     if (st > TCP_MAX_STAGES) st = TCP_MAX_STAGES;
     if (st < 2) throw std::runtime_error("conv_tc: tile does not fit in shared memory");
     const int m_tiles = (a.Q + TC_BM - 1) / TC_BM;
@@ -973,6 +988,14 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
     }
     ProfScope ps(ex, Prof::CONV_TC, flops);
     conv_tc_persist_kernel<<<grid, TCP_THREADS, smem, ex.st>>>(ta, tbp, p, st, m_tiles, a.n_tiles, total);
+    if (const cudaError_t le = cudaPeekAtLastError(); le != cudaSuccess) {
+      cudaFuncAttributes fa{};
+      cudaFuncGetAttributes(&fa, conv_tc_persist_kernel);
+      throw std::runtime_error(std::string("cuda: conv_tc_persist_kernel launch failed: ") + cudaGetErrorString(le) + " (threads " +
+                               std::to_string(TCP_THREADS) + ", dynamic smem " + std::to_string(smem) + ", static smem " +
+                               std::to_string(fa.sharedSizeBytes) + ", registers " + std::to_string(fa.numRegs) + ", stages " +
+                               std::to_string(st) + ", stage bytes " + std::to_string(sb) + ")");
+    }
     ++ex.launches;
     return;
   }

@@ -16,6 +16,9 @@
 #include "conv_tc.h"
 #include "kernels.h"
 #include "piper_config.h"
+#include <memory>
+
+#include "graph_exec.h"
 #include "voice.h"
 
 namespace piper {
@@ -132,6 +135,17 @@ struct Context {
   size_t out_cap = 0;
 
   int gap_p = 0, gap_f = 0;         // zero rows between utterances (phoneme / frame level)
+
+  // generic ONNX-op executor (graph_exec.h): the parsed model of route A is kept; a graph the fused pipeline
+  // does not recognise runs through it (generic_only), a recognised one on request (PIPER_B200_FLAG_GENERIC)
+  std::shared_ptr<OnnxModel> onnx;
+  std::unique_ptr<GraphExec> gexec;
+  bool generic_only = false;
+  std::string generic_reason;
+  std::vector<float> generic_audio;
+  int synthesize_generic(const piper_b200_request& rq, piper_b200_result& rs);
+  int run_graph(const int64_t* ids, int64_t n_ids, int64_t sid, const float* scales3, uint64_t seed, const char* value_name, void* out,
+                size_t cap_bytes, int32_t* dtype, int64_t* dims8, int32_t* rank);
 
   // incremental decoding (PIPER_B200_FLAG_STREAM + piper_b200_stream_next): the flow output stays in `back`
   struct StreamState {

@@ -27,6 +27,7 @@ LIB_PATH = os.environ.get("PIPER_B200_LIB") or os.path.join(os.path.dirname(_HER
 OK = 0
 PRECISION = {"fp32": 0, "bf16": 1, "f16": 2}
 FLAG_IDS_ON_DEVICE, FLAG_KEEP_ON_DEVICE, FLAG_KEEP_STAGES, FLAG_PCM16, FLAG_PROFILE, FLAG_STREAM = 1, 2, 4, 8, 16, 32
+FLAG_GENERIC = 128
 FLAG_PCM16_ONLY = 64
 ABI_VERSION = 2
 ERR_NAMES = {1: "invalid_argument", 2: "io", 3: "decode", 4: "unsupported", 5: "cuda", 6: "state", 7: "capacity"}
@@ -117,6 +118,8 @@ def load_library(path: str = LIB_PATH):
         "piper_b200_length_regulate_noalloc": (C.c_int, [P, P, P, C.c_int32, C.c_float, P, P]),
         "piper_b200_random_normal": (C.c_int, [P, C.c_uint64, C.c_int64, P]),
         "piper_b200_selftest_conv": (C.c_int, [P] + [C.c_int32] * 8 + [C.POINTER(C.c_float)]),
+        "piper_b200_run_graph": (C.c_int, [P, P, C.c_int64, C.c_int64, P, C.c_uint64, C.c_char_p, P, C.c_size_t,
+                                           C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
         "piper_b200_conv1d": (C.c_int, [P, C.c_int32, P, C.c_int64, P, P] + [C.c_int32] * 6 + [P]),
         "piper_b200_ipa_to_ids": (C.c_int, [P, C.c_char_p, C.POINTER(C.c_int64), C.c_int64, C.POINTER(C.c_int64)]),
         "piper_b200_config_ipa_to_ids": (C.c_int, [C.c_char_p, C.c_char_p, C.POINTER(C.c_int64), C.c_int64,
@@ -138,7 +141,7 @@ EXPORTED_SYMBOLS = [
     "piper_b200_random_normal", "piper_b200_selftest_conv", "piper_b200_ipa_to_ids", "piper_b200_config_ipa_to_ids",
     "piper_b200_stream_next", "piper_b200_device_count", "piper_b200_set_output_buffer", "piper_b200_host_alloc",
     "piper_b200_host_free", "piper_b200_host_register", "piper_b200_host_unregister",
-    "piper_b200_length_regulate_noalloc", "piper_b200_add_node", "piper_b200_conv1d",
+    "piper_b200_length_regulate_noalloc", "piper_b200_add_node", "piper_b200_conv1d", "piper_b200_run_graph",
 ]
 NOALLOC_MAX_IDS, NOALLOC_MAX_BATCH = 65536, 1024
 
@@ -414,18 +417,19 @@ class PiperCUDARuntime:
                          noise_dp: Optional[Sequence[np.ndarray]] = None,
                          noise_main: Optional[Sequence[np.ndarray]] = None,
                          seed: Optional[int] = None, keep_stages: bool = False, pcm16: bool = False,
-                         copy: bool = True, pcm16_only: bool = False) -> BatchResult:
+                         copy: bool = True, pcm16_only: bool = False, generic: bool = False) -> BatchResult:
         B = len(utterances)
         lengths = np.array([len(u) for u in utterances], dtype=np.int64)
         ids = np.concatenate([np.asarray(u, dtype=np.int64) for u in utterances]) if B else np.zeros(0, np.int64)
         return self.synthesize_packed(ids, lengths, noise_scale, length_scale, noise_w, speaker_ids, noise_dp,
-                                      noise_main, seed, keep_stages, pcm16, copy, pcm16_only=pcm16_only)
+                                      noise_main, seed, keep_stages, pcm16, copy, pcm16_only=pcm16_only, generic=generic)
 
     def synthesize_packed(self, ids: np.ndarray, lengths: np.ndarray, noise_scale=None, length_scale=None,
                           noise_w=None, speaker_ids=None, noise_dp=None, noise_main=None, seed=None,
                           keep_stages=False, pcm16=False, copy=True, ids_device_ptr: Optional[int] = None,
                           keep_on_device: bool = False, profile: bool = False, stream: bool = False,
-                          pcm16_only: bool = False) -> BatchResult:
+                          pcm16_only: bool = False, generic: bool = False) -> BatchResult:
+        """generic=True: PIPER_B200_FLAG_GENERIC - the graph runs node by node through the generic op executor."""
         B = int(len(lengths))
         lengths = np.ascontiguousarray(lengths, dtype=np.int64)
         rq = Request()
@@ -464,7 +468,7 @@ class PiperCUDARuntime:
         rq.seed = self.options.seed if seed is None else seed
         rq.flags = ((FLAG_KEEP_STAGES if keep_stages else 0) | (FLAG_PCM16 if pcm16 else 0) |
                     (FLAG_PROFILE if profile else 0) | (FLAG_STREAM if stream else 0) |
-                    (FLAG_PCM16_ONLY if pcm16_only else 0) |
+                    (FLAG_PCM16_ONLY if pcm16_only else 0) | (FLAG_GENERIC if generic else 0) |
                     (FLAG_IDS_ON_DEVICE if ids_device_ptr is not None else 0) |
                     (FLAG_KEEP_ON_DEVICE if keep_on_device else 0))
         rs = Result()
@@ -541,6 +545,24 @@ class PiperCUDARuntime:
     def random_normal(self, count: int, seed: int = 1234) -> np.ndarray:
         out = np.zeros(count, np.float32)
         self._check(self._lib.piper_b200_random_normal(self._ctx, seed, count, out.ctypes.data))
+        return out
+
+    def run_graph(self, phoneme_ids: Sequence[int], noise_scale: float, length_scale: float, noise_w: float,
+                  value_name: Optional[str] = None, speaker_id: int = 0, seed: Optional[int] = None) -> np.ndarray:
+        """piper_b200_run_graph: the generic op executor on one utterance; returns the named value (default: the graph
+        output) as float32 / int64 / bool - GraphExecutor.execute(inputs:maxNodeIndex:) (GraphExecutor.swift:75-152)."""
+        ids = np.ascontiguousarray(phoneme_ids, np.int64)
+        scales = np.array([noise_scale, length_scale, noise_w], np.float32)
+        dt, rank = C.c_int32(0), C.c_int32(0)
+        dims = (C.c_int64 * 8)()
+        name = value_name.encode() if value_name else None
+        sd = self.options.seed if seed is None else seed
+        self._check(self._lib.piper_b200_run_graph(self._ctx, ids.ctypes.data, len(ids), speaker_id, scales.ctypes.data, sd, name,
+                                                   None, 0, C.byref(dt), dims, C.byref(rank)))
+        shape = tuple(int(dims[i]) for i in range(rank.value))
+        out = np.empty(shape, {1: np.float32, 7: np.int64, 9: np.bool_}[dt.value])
+        self._check(self._lib.piper_b200_run_graph(self._ctx, ids.ctypes.data, len(ids), speaker_id, scales.ctypes.data, sd, name,
+                                                   out.ctypes.data, out.nbytes, C.byref(dt), dims, C.byref(rank)))
         return out
 
     def conv1d(self, x: np.ndarray, w: np.ndarray, bias: Optional[np.ndarray] = None, dilation: int = 1, stride: int = 1,
