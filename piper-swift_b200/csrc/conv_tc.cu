@@ -128,8 +128,19 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
     for (int c = part * chunks / nparts; c < (part + 1) * chunks / nparts; ++c) {
       float va[16], vb[16];
       __syncwarp();
+#ifndef PIPER_TC_EPI_SYNC_LD
+      {
+        uint32_t ta_[16], tb_[16];
+        tmem_ld16_async(lane_base + (uint32_t)(c * 16), ta_);
+        tmem_ld16_async(lane_base + (uint32_t)(p.nt + c * 16), tb_);
+        tmem_wait_ld();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) { va[i] = __uint_as_float(ta_[i]); vb[i] = __uint_as_float(tb_[i]); }
+      }
+#else
       tmem_ld16(lane_base + (uint32_t)(c * 16), va);
       tmem_ld16(lane_base + (uint32_t)(p.nt + c * 16), vb);
+#endif
       if (!active) continue;
       const int j = ntile * p.nt + c * 16;
       uint32_t pk[8];
@@ -319,6 +330,25 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
       {
         float v[32];
         __syncwarp();
+#ifndef PIPER_TC_EPI_SYNC_LD
+        {   // all TMEM loads of the chunk in flight at once, one wait (two to four round trips per chunk otherwise)
+          uint32_t tv[32];
+          tmem_ld16_async(lane_base + (uint32_t)(g * p.nt + c * 32), tv);
+          tmem_ld16_async(lane_base + (uint32_t)(g * p.nt + c * 32 + 16), tv + 16);
+          if (p.split2) {   // f16x3: the cross terms sit in the second accumulator, scaled by 2^11
+            uint32_t tw[32];
+            tmem_ld16_async(lane_base + (uint32_t)(p.nt + c * 32), tw);
+            tmem_ld16_async(lane_base + (uint32_t)(p.nt + c * 32 + 16), tw + 16);
+            tmem_wait_ld();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = fmaf(__uint_as_float(tw[i]), 1.0f / 2048.f, __uint_as_float(tv[i]));
+          } else {
+            tmem_wait_ld();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(tv[i]);
+          }
+        }
+#else
         tmem_ld16(lane_base + (uint32_t)(g * p.nt + c * 32), v);
         tmem_ld16(lane_base + (uint32_t)(g * p.nt + c * 32 + 16), v + 16);
         if (p.split2) {   // f16x3: the cross terms sit in the second accumulator, scaled by 2^11
@@ -328,6 +358,7 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
 #pragma unroll
           for (int i = 0; i < 32; ++i) v[i] = fmaf(w[i], 1.0f / 2048.f, v[i]);
         }
+#endif
         int j = ntile * p.nt + c * 32, ph_c = p.phases > 1 ? phase : 0;
         if (p.phase_cols) {   // merged polyphase weights: the chunk's columns are channels j % phase_cols of phase j / phase_cols
           ph_c = j / p.phase_cols;
@@ -337,9 +368,11 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
         const int orow_c = active ? q * p.out_mul + ph_c : 0;
         if (e.bias && sbias) {
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
+          for (int i = 0; i < 8; ++i) {   // packed fp32 pairs (FADD2): same rounding, half the issue slots
             const float4 x = lds128(sbs + (uint32_t)(g * TC_SBIAS + j + 4 * i) * 4u);
-            v[4 * i] += x.x; v[4 * i + 1] += x.y; v[4 * i + 2] += x.z; v[4 * i + 3] += x.w;
+            const float2 a = f2unpack(f2add(f2pack(v[4 * i], v[4 * i + 1]), f2pack(x.x, x.y)));
+            const float2 b = f2unpack(f2add(f2pack(v[4 * i + 2], v[4 * i + 3]), f2pack(x.z, x.w)));
+            v[4 * i] = a.x; v[4 * i + 1] = a.y; v[4 * i + 2] = b.x; v[4 * i + 3] = b.y;
           }
         } else if (e.bias) {
           const float4* b4 = reinterpret_cast<const float4*>(e.bias + j);
@@ -388,7 +421,11 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
           for (int it = 0; it < 8; ++it) x[it] = lds128(tbs + (uint32_t)((it * 4 + sub) * 36 + c4) * 4u);
           if (fres) {
 #pragma unroll
-            for (int it = 0; it < 8; ++it) { x[it].x += rr[it].x; x[it].y += rr[it].y; x[it].z += rr[it].z; x[it].w += rr[it].w; }
+            for (int it = 0; it < 8; ++it) {
+              const float2 a = f2unpack(f2add(f2pack(x[it].x, x[it].y), f2pack(rr[it].x, rr[it].y)));
+              const float2 b = f2unpack(f2add(f2pack(x[it].z, x[it].w), f2pack(rr[it].z, rr[it].w)));
+              x[it] = make_float4(a.x, a.y, b.x, b.y);
+            }
           }
           float* of = e.out_f32 ? e.out_f32 + frow * e.ld_f32 + fcol : nullptr;
           const size_t sf = (size_t)4 * e.ld_f32;
