@@ -719,7 +719,7 @@ __device__ __forceinline__ void att96_pv(const float* __restrict__ Ps, const flo
 __global__ void __launch_bounds__(256, 2) attention96_kernel(
     const float* __restrict__ qkv, const float* __restrict__ rel_k, const float* __restrict__ rel_v,
     float* __restrict__ out, const int* __restrict__ utt_start, const int* __restrict__ utt_len,
-    int H, int window, uint16_t* __restrict__ out_split2, int smax, float* __restrict__ part) {
+    int H, int window, uint16_t* __restrict__ out_split2, int smax, float* __restrict__ part, int skip_upto) {
   extern __shared__ __align__(16) float sm[];
   float* Qs = sm;                               // [64][100]  (scaled by 1/sqrt(96))
   float* Ks = Qs + AT2_Q * AT2_LD;              // [64][100]
@@ -730,6 +730,7 @@ __global__ void __launch_bounds__(256, 2) attention96_kernel(
   float* QR = RV + AT2_MAXREL * AT2_D;          // [64][nrel]
   const int b = blockIdx.z, head = blockIdx.y;
   const int T = utt_len[b];
+  if (T <= skip_upto) return;                   // short utterances were taken by attention_tc_kernel
   const int sp = (int)blockIdx.x % smax;        // key split handled by this CTA
   const int i0 = ((int)blockIdx.x / smax) * AT2_Q;
   const int S = smax > 1 ? att96_splits(T) : 1;   // smax == 1: no utterance of this call is long enough (or splitting is off)
@@ -923,7 +924,7 @@ size_t attention_scratch_bytes(int rows, int max_len, int H, int n_heads) {
 
 void launch_attention(Exec& ex, const float* qkv, const float* rel_k, const float* rel_v, float* out,
                       const int* utt_start, const int* utt_len, int batch, int max_len, int H,
-                      int n_heads, int window, uint16_t* out_split2, bool* wrote_split, float* scratch) {
+                      int n_heads, int window, uint16_t* out_split2, bool* wrote_split, float* scratch, int skip_upto) {
   if (wrote_split) *wrote_split = false;
   if (batch <= 0 || max_len <= 0) return;
   const int kc = H / n_heads;
@@ -946,7 +947,7 @@ void launch_attention(Exec& ex, const float* qkv, const float* rel_k, const floa
       throw std::runtime_error("attention: long utterances need the split scratch buffer");
     dim3 grid2((max_len + AT2_Q - 1) / AT2_Q * smax, n_heads, batch);
     attention96_kernel<<<grid2, 256, smem2, ex.st>>>(qkv, rel_k, rel_v, out, utt_start, utt_len, H, window, out_split2,
-                                                     smax, scratch);
+                                                     smax, scratch, skip_upto);
     KLAUNCH(ex);
     if (smax > 1) {
       dim3 gm((max_len + 7) / 8, n_heads, batch);

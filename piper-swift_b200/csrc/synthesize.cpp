@@ -177,6 +177,10 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
     if (rq.noise_dp) fb += (size_t)n_ids * 2 * 4;
     const bool front_tc = use_tc && !tc.enc.empty();
     if (front_tc) fb += (size_t)Rp * 2 * 3 * (2 * H + hp.filter) + 3 * 256;   // split operands of x, att and the FFN mid
+    // attention on the tensor cores (attention_tc.cu): the qkv convolution also writes its output as f16x3 split planes
+    static const int att_tc_env = [] { const char* e = getenv("PIPER_B200_ATT_TC"); return e ? atoi(e) : 1; }();
+    const bool att_tc = front_tc && att_tc_env && tc.enc[0].qkv.split == 2 && attention_tc_supported(H, hp.n_heads, hp.window);
+    if (att_tc) fb += (size_t)Rp * 6 * H * 2 + 256;
     const size_t att_scratch_bytes = attention_scratch_bytes((int)Rp, max_len, H, hp.n_heads);
     fb += att_scratch_bytes + 256;
     fb += 64 * 256;
@@ -199,6 +203,8 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
     uint16_t* xs = front_tc ? F.alloc<uint16_t>((size_t)Rp * 3 * H) : nullptr;
     uint16_t* atts = front_tc ? F.alloc<uint16_t>((size_t)Rp * 3 * H) : nullptr;
     uint16_t* mids = front_tc ? F.alloc<uint16_t>((size_t)Rp * 3 * hp.filter) : nullptr;
+    uint16_t* qkvs = att_tc ? F.alloc<uint16_t>((size_t)Rp * 6 * H) : nullptr;
+    if (att_tc && !qkvs) throw std::runtime_error("capacity: front arena sizing bug (qkv split planes)");
     if (front_tc && (!xs || !atts || !mids)) throw std::runtime_error("capacity: front arena sizing bug (split operands)");
     float* dph = F.alloc<float>((size_t)Rp * H);
     float* dpc = F.alloc<float>((size_t)Rp * H);
@@ -287,9 +293,17 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
       {
         TcConvArgs a = split_args(t.qkv, xs, Rp, p_utt);
         a.e[0].out_f32 = qkv; a.e[0].ld_f32 = 3 * H;
+        if (att_tc) { a.e[0].out_split = qkvs; a.e[0].ld_split = 6 * H; a.e[0].split_c = 3 * H; }
         launch_conv_tc(ex, a);
       }
       bool att_split = false;
+      if (att_tc) {   // utterances of at most 128 ids on the tensor cores, longer ones through the CUDA-core kernel
+        launch_attention_tc(ex, qkv, qkvs, l.rel_k, l.rel_v, nullptr, atts, d_utt_start, d_utt_len, B, Rp, H, hp.n_heads, hp.window);
+        att_split = true;
+        if (max_len > 128)
+          launch_attention(ex, qkv, l.rel_k, l.rel_v, att, d_utt_start, d_utt_len, B, max_len, H, hp.n_heads, hp.window, atts,
+                           &att_split, att_scratch, 128);
+      } else
       launch_attention(ex, qkv, l.rel_k, l.rel_v, att, d_utt_start, d_utt_len, B, max_len, H, hp.n_heads, hp.window,
                        fused_split ? atts : nullptr, &att_split, att_scratch);
       if (!att_split) launch_split_act(ex, sm, att, H, Rp, H, atts, H);
