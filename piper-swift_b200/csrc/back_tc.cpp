@@ -135,6 +135,23 @@ void TcVoice::build(Exec& ex, const Voice& v, int f16_) {
         t.o = make_tcw_split(ex, allocs, l.o, mode);
         t.ffn1 = make_tcw_split(ex, allocs, l.ffn1, mode);
         t.ffn2 = make_tcw_split(ex, allocs, l.ffn2, mode);
+        const int kc = v.hp.hidden / std::max(v.hp.n_heads, 1), nrel = 2 * v.hp.window + 1;
+        if (mode == 2 && kc == 96 && nrel <= 16) {   // relative-key table for the tensor-core attention
+          std::vector<float> rk((size_t)nrel * kc);
+          CUDA_OK(cudaMemcpy(rk.data(), l.rel_k, rk.size() * 4, cudaMemcpyDeviceToHost));
+          std::vector<uint16_t> h((size_t)16 * 2 * kc, 0);
+          for (int m = 0; m < nrel; ++m)
+            for (int d = 0; d < kc; ++d) {
+              const float x = std::min(std::max(rk[(size_t)m * kc + d], -65504.f), 65504.f);
+              const __half hi = __float2half_rn(x);
+              const __half lo = __float2half_rn((x - __half2float(hi)) * 2048.f);
+              std::memcpy(&h[(size_t)m * 2 * kc + d], &hi, 2);
+              std::memcpy(&h[(size_t)m * 2 * kc + kc + d], &lo, 2);
+            }
+          CUDA_OK(cudaMalloc(&t.relk16, h.size() * 2));
+          allocs.push_back(t.relk16);
+          CUDA_OK(cudaMemcpy(t.relk16, h.data(), h.size() * 2, cudaMemcpyHostToDevice));
+        }
         enc.push_back(t);
       }
     // stochastic duration predictor: its 1x1 convolutions in the f16x3 form (PIPER_B200_SDP_TC=0: CUDA cores)

@@ -117,10 +117,11 @@ void launch_attention(Exec& ex, const float* qkv, const float* rel_k, const floa
                       int n_heads, int window, uint16_t* out_split2 = nullptr, bool* wrote_split = nullptr,
                       float* scratch = nullptr, int skip_upto = 0);   // skip_upto: utterances of at most this many ids are left alone
 // The same attention layer on the tensor cores (attention_tc.cu) for utterances of at most 128 ids and head dimension 96:
-// q / k / v come as the f16x3 split planes [rows][2][3H] the qkv convolution writes beside its fp32 output; longer
-// utterances are skipped (launch_attention with skip_upto = 128 takes them).
+// q / k / v come as the f16x3 split planes [rows][2][3H] the qkv convolution writes beside its fp32 output, the
+// relative-key table as split planes [16][2][96] (TcEncLayer::relk16); longer utterances are skipped (launch_attention
+// with skip_upto = 128 takes them).
 bool attention_tc_supported(int H, int n_heads, int window);
-void launch_attention_tc(Exec& ex, const float* qkv, const uint16_t* qkvs, const float* rel_k, const float* rel_v, float* out,
+void launch_attention_tc(Exec& ex, const uint16_t* qkvs, const void* relk16, const float* rel_v, float* out,
                          uint16_t* out_split2, const int* utt_start, const int* utt_len, int batch, int rows, int H, int n_heads,
                          int window);
 // bytes of `scratch` that launch_attention needs for `rows` packed rows when the longest utterance has max_len ids

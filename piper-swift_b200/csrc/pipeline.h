@@ -90,6 +90,7 @@ struct TcStage {
 // text-encoder convolutions as fp32-emulating tensor-core GEMMs (bf16x6 split operands, conv_tc.h)
 struct TcEncLayer {
   TcW qkv, o, ffn1, ffn2;
+  void* relk16 = nullptr;   // emb_rel_k as f16x3 split planes [16 rows][2][96] (rows beyond 2w+1 zero) for attention_tc.cu
 };
 struct TcVoice {
   bool built = false;

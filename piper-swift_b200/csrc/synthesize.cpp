@@ -179,7 +179,8 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
     if (front_tc) fb += (size_t)Rp * 2 * 3 * (2 * H + hp.filter) + 3 * 256;   // split operands of x, att and the FFN mid
     // attention on the tensor cores (attention_tc.cu): the qkv convolution also writes its output as f16x3 split planes
     static const int att_tc_env = [] { const char* e = getenv("PIPER_B200_ATT_TC"); return e ? atoi(e) : 1; }();
-    const bool att_tc = front_tc && att_tc_env && tc.enc[0].qkv.split == 2 && attention_tc_supported(H, hp.n_heads, hp.window);
+    const bool att_tc = front_tc && att_tc_env && tc.enc[0].qkv.split == 2 && tc.enc[0].relk16 &&
+                        attention_tc_supported(H, hp.n_heads, hp.window);
     if (att_tc) fb += (size_t)Rp * 6 * H * 2 + 256;
     const size_t att_scratch_bytes = attention_scratch_bytes((int)Rp, max_len, H, hp.n_heads);
     fb += att_scratch_bytes + 256;
@@ -298,7 +299,7 @@ int Context::synthesize(const piper_b200_request& rq, piper_b200_result& rs) {
       }
       bool att_split = false;
       if (att_tc) {   // utterances of at most 128 ids on the tensor cores, longer ones through the CUDA-core kernel
-        launch_attention_tc(ex, qkv, qkvs, l.rel_k, l.rel_v, nullptr, atts, d_utt_start, d_utt_len, B, Rp, H, hp.n_heads, hp.window);
+        launch_attention_tc(ex, qkvs, t.relk16, l.rel_v, nullptr, atts, d_utt_start, d_utt_len, B, Rp, H, hp.n_heads, hp.window);
         att_split = true;
         if (max_len > 128)
           launch_attention(ex, qkv, l.rel_k, l.rel_v, att, d_utt_start, d_utt_len, B, max_len, H, hp.n_heads, hp.window, atts,
