@@ -53,8 +53,9 @@ __device__ __forceinline__ uint32_t sw128_off(int row, int j, int sub_bytes) {
 
 __global__ void __launch_bounds__(2 * ATC_T, 1) attention_tc_kernel(const __grid_constant__ CUtensorMap tmap,
                                                                   const __grid_constant__ CUtensorMap tmap_rk, const AttTcParams p) {
+  PDL_TRIGGER();
   const int head = blockIdx.x, b = blockIdx.y;
-  const int T = p.utt_len[b];
+  const int T = p.utt_len[b];   // written by a copy long before the preceding kernel
   if (T > ATC_T || T <= 0) return;     // long utterances: attention96_kernel (launched with skip_short)
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -88,6 +89,7 @@ __global__ void __launch_bounds__(2 * ATC_T, 1) attention_tc_kernel(const __grid
     mbar_init(s_full, 1);
     mbar_init(o_full, 1);
     fence_barrier_init();
+    PDL_WAIT();   // the qkv convolution's output is read from here on
     // Q and K planes of this head (2 planes x 3 blocks of 32 channels, 128 rows from the utterance start) and rel_k: requested
     // at once, so that the loads run under the TMEM allocation and the rest of the set-up
     mbar_expect_tx(full, 12u * ATC_QK_BLOCK + 6u * ATC_RK_BLOCK);
@@ -107,6 +109,7 @@ __global__ void __launch_bounds__(2 * ATC_T, 1) attention_tc_kernel(const __grid
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  PDL_WAIT();
   TR();   // 1: setup done
   const uint32_t s0_col = 0, s1_col = 128, o0_col = 256, o1_col = 352, r0_col = 448, r1_col = 464;
 
@@ -399,7 +402,7 @@ void launch_attention_tc(Exec& ex, const uint16_t* qkvs, const void* relk16, con
     if (cudaMalloc(&p.trace, 16 * sizeof(long long)) != cudaSuccess) throw std::runtime_error("attention_tc: trace buffer");
     cudaMemsetAsync(p.trace, 0, 16 * sizeof(long long), ex.st);
   }
-  attention_tc_kernel<<<grid, 2 * ATC_T, smem, ex.st>>>(tm, trk, p);
+  launch_pdl(attention_tc_kernel, grid, dim3(2 * ATC_T), smem, ex.st, tm, trk, p);
   ++ex.launches;
   if (trace_env) {   // debug only: phase boundaries of CTA (0, 0) in cycles since its start
     long long h[16];

@@ -600,6 +600,7 @@ float* run_decoder_tc(Context& ctx, Exec& ex, const DecoderIn& in) {
           b.act_pad = act_pad + f0 * U;
           b.row_utt = in.frow_utt + f0;
           b.post_out = audio + (size_t)f0 * U;
+          b.no_pdl = 1;
           launch_mrf_tc(ex, b);
           if (ch->done) ch->done((int)c, audio);
         }

@@ -70,6 +70,7 @@ struct MrfParams {
 template <int C, int MRF_EG, bool UNIT = false>   // channels, epilogue warpgroups
 __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __grid_constant__ CUtensorMap tmap_w,
                                                                 const MrfParams p) {
+  PDL_TRIGGER();   // the next kernel may be staged; PDL_WAIT() below, after the set-up that touches constants only
   extern __shared__ uint8_t smem_raw[];
   // 1 KB alignment by pointer arithmetic on the shared array: an integer round-trip hides the address space from the
   // compiler, which then emits generic LD / ST for every shared-memory access of the epilogues
@@ -174,6 +175,7 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
   const uint32_t d_col = 0, s_col = (uint32_t)(m * C);
+  PDL_WAIT();      // the operand window, the validity table and (unit form) the accumulated output are read from here on
 #ifdef PIPER_MBAR_WATCHDOG
   if (blockIdx.x == 0 && threadIdx.x == 0)
     printf("mrf_tc_kernel<%d> m %d nk %d ring %d resident %d tap_outer %d split %d unit %d: barriers x_full @%u x_empty +8 w_full +16 "
@@ -318,8 +320,10 @@ __global__ void __launch_bounds__(160 + 128 * MRF_EG, 1) mrf_tc_kernel(const __g
         uint32_t s = slot0, ph = wph0;
         for (int t = 0; t < k; ++t) {
           if (first_use && i < istep) {
+            TRACE(24u, n, (uint32_t)(t * 2 + j));
             mbar_wait(&w_full[s], ph);
             tc_fence_after();
+            TRACE(25u, n, (uint32_t)(t * 2 + j));
           }
           const uint32_t b_lo = wr_lo + s * tap16;
           if (elect_one()) {
@@ -1029,22 +1033,28 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
   static const int eg_env = [] { const char* e = getenv("PIPER_B200_MRF_EG"); return e ? atoi(e) : 0; }();
   const int eg = eg_env >= 2 && eg_env <= 5 ? eg_env : 4;
   const int threads = 160 + 128 * eg;
+  // plain launch on request (no_pdl): the row-range launches of the last stage must not be staged early - their CTAs would
+  // take the SMs the instant the previous range retires, ahead of the copy stream's gather kernel that waits for that range
+  auto L = [&](auto kernel, int nthreads) {
+    if (a.no_pdl) kernel<<<grid, nthreads, smem, ex.st>>>(tw, p);
+    else launch_pdl(kernel, dim3(grid), dim3(nthreads), smem, ex.st, tw, p);
+  };
   if (a.unit_mode) {
-    if (a.C == 128) mrf_tc_kernel<128, 4, true><<<grid, 160 + 128 * 4, smem, ex.st>>>(tw, p);
-    else if (a.C == 64) mrf_tc_kernel<64, 4, true><<<grid, 160 + 128 * 4, smem, ex.st>>>(tw, p);
-    else mrf_tc_kernel<32, 4, true><<<grid, 160 + 128 * 4, smem, ex.st>>>(tw, p);
+    if (a.C == 128) L(mrf_tc_kernel<128, 4, true>, 160 + 128 * 4);
+    else if (a.C == 64) L(mrf_tc_kernel<64, 4, true>, 160 + 128 * 4);
+    else L(mrf_tc_kernel<32, 4, true>, 160 + 128 * 4);
   } else if (a.C == 128) {
-    mrf_tc_kernel<128, 4><<<grid, 160 + 128 * 4, smem, ex.st>>>(tw, p);
+    L(mrf_tc_kernel<128, 4>, 160 + 128 * 4);
   } else if (a.C == 32) {
-    if (eg == 2) mrf_tc_kernel<32, 2><<<grid, threads, smem, ex.st>>>(tw, p);
-    else if (eg == 3) mrf_tc_kernel<32, 3><<<grid, threads, smem, ex.st>>>(tw, p);
-    else if (eg == 4) mrf_tc_kernel<32, 4><<<grid, threads, smem, ex.st>>>(tw, p);
-    else mrf_tc_kernel<32, 5><<<grid, threads, smem, ex.st>>>(tw, p);
+    if (eg == 2) L(mrf_tc_kernel<32, 2>, threads);
+    else if (eg == 3) L(mrf_tc_kernel<32, 3>, threads);
+    else if (eg == 4) L(mrf_tc_kernel<32, 4>, threads);
+    else L(mrf_tc_kernel<32, 5>, threads);
   } else {
-    if (eg == 2) mrf_tc_kernel<64, 2><<<grid, threads, smem, ex.st>>>(tw, p);
-    else if (eg == 3) mrf_tc_kernel<64, 3><<<grid, threads, smem, ex.st>>>(tw, p);
-    else if (eg == 4) mrf_tc_kernel<64, 4><<<grid, threads, smem, ex.st>>>(tw, p);
-    else mrf_tc_kernel<64, 5><<<grid, threads, smem, ex.st>>>(tw, p);
+    if (eg == 2) L(mrf_tc_kernel<64, 2>, threads);
+    else if (eg == 3) L(mrf_tc_kernel<64, 3>, threads);
+    else if (eg == 4) L(mrf_tc_kernel<64, 4>, threads);
+    else L(mrf_tc_kernel<64, 5>, threads);
   }
   ++ex.launches;
   if (trace_path) {   // debug only: dump "C m warp tag n i clock" lines, one file per stage width

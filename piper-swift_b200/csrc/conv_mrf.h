@@ -59,6 +59,7 @@ struct MrfArgs {
   void* out_planar = nullptr;    // optional 16-bit lrelu(out, act_slope) in the group-planar layout of x_act
   int64_t out_rows = 0; int out_pad = 0;
   int f16 = 0;
+  int no_pdl = 0;                // 1: plain stream-ordered launch instead of a programmatic dependent launch (kernels.h)
 };
 
 bool mrf_tc_supported(int C, int nk, const int* k, const int* d0, const int* d1);

@@ -774,6 +774,7 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
                                                                          const TcKernelParams p, const int stages,
                                                                          const int m_tiles, const int n_tiles,
                                                                          const int total_tiles) {
+  PDL_TRIGGER();   // the next kernel of the stream may be staged; this one waits for its predecessor after the set-up (PDL_WAIT below)
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int row_bytes = p.kb * 2;
@@ -816,6 +817,7 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
   const uint32_t acc_stride = (uint32_t)(p.n_groups * p.nt);
+  PDL_WAIT();      // everything above touched constants only (bias, tensor maps); activations are read from here on
 
   if (warp == 0) {
     // ===== TMA producer =====
@@ -1024,7 +1026,7 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
       flops = 2.0 * a.Q * w.cin * (double)w.phase_cols * used;
     }
     ProfScope ps(ex, Prof::CONV_TC, flops);
-    conv_tc_persist_kernel<<<grid, TCP_THREADS, smem, ex.st>>>(ta, tbp, p, st, m_tiles, a.n_tiles, total);
+    launch_pdl(conv_tc_persist_kernel, dim3(grid), dim3(TCP_THREADS), smem, ex.st, ta, tbp, p, st, m_tiles, a.n_tiles, total);
     if (const cudaError_t le = cudaPeekAtLastError(); le != cudaSuccess) {
       cudaFuncAttributes fa{};
       cudaFuncGetAttributes(&fa, conv_tc_persist_kernel);

@@ -6,6 +6,8 @@
 // of the layout.  Rows outside [0,R) are never read (guarded).
 #pragma once
 #include <cuda_runtime.h>
+
+#include <utility>
 #include <cstdint>
 #include <mutex>
 #include <vector>
@@ -55,6 +57,35 @@ struct Exec {
   int64_t launches = 0;
   Prof* prof = nullptr;
 };
+
+// ---- programmatic dependent launch (PDL) ---------------------------------------------------------------------------------
+// A synthesize call is ~145 dependent launches; at small batches (one utterance, or 32 per GPU in the 8-GPU strong-scaling
+// case) the step is the sum of launch gaps and kernel prologues, not of work.  Kernels launched through launch_pdl carry
+// cudaLaunchAttributeProgrammaticStreamSerialization: their CTAs may be scheduled while the preceding kernel of the stream
+// still runs, execute their prologue (barrier init, TMEM allocation, tensor-map prefetch, constant staging), and block in
+// PDL_WAIT() until the predecessor has completed and its writes are visible.  PDL_TRIGGER() at the top of a kernel tells
+// the scheduler that the NEXT kernel may be staged.  Rules: a kernel launched through launch_pdl MUST execute PDL_WAIT()
+// before its first read of anything an earlier kernel wrote (and before its first write of anything an earlier kernel
+// reads); plain <<<>>> launches stay fully ordered.  PIPER_B200_PDL=0 turns the attribute off (plain launches).
+#if defined(__CUDACC__)
+#define PDL_WAIT() asm volatile("griddepcontrol.wait;" ::: "memory")
+#define PDL_TRIGGER() asm volatile("griddepcontrol.launch_dependents;" ::: "memory")
+#endif
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cudaLaunchKernelEx(&cfg, kernel, KArgs(std::forward<Args>(args))...);
+}
 
 struct ProfScope {
   Exec& ex; cudaEvent_t b = nullptr;

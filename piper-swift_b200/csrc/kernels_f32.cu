@@ -18,6 +18,8 @@
 namespace piper {
 
 #define KLAUNCH(ex) (++(ex).launches)
+// simple kernels: the next kernel may be staged at once, this one starts its work when its predecessor is complete
+#define PDL_ENTER() do { PDL_TRIGGER(); PDL_WAIT(); } while (0)
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
@@ -51,6 +53,7 @@ __device__ __forceinline__ float gelu_erf(float x) {
 constexpr int CBM = 64, CBN = 64, CBK = 16;
 
 __global__ void __launch_bounds__(256) conv_f32_kernel(ConvArgs a) {
+  PDL_ENTER();
   __shared__ __align__(16) float As[CBK][CBM];
   __shared__ __align__(16) float Bs[CBK][CBN];
   const int tid = threadIdx.x;
@@ -144,6 +147,7 @@ constexpr int LBM = 128, LBK = 16;
 
 template <int BN>   // 128 or 64 output columns per CTA
 __global__ void __launch_bounds__(256, 2) conv_f32_big_kernel(ConvArgs a) {
+  PDL_ENTER();
   constexpr int NJ = BN / 16;                          // columns per thread (8 or 4)
   __shared__ __align__(16) float As[2][LBK][LBM];
   __shared__ __align__(16) float Bs[2][LBK][BN];
@@ -273,6 +277,7 @@ __global__ void __launch_bounds__(256, 2) conv_f32_big_kernel(ConvArgs a) {
 constexpr int WBM = 96, WBN = 192, WBK = 16;
 
 __global__ void __launch_bounds__(256, 2) conv_f32_w192_kernel(ConvArgs a) {
+  PDL_ENTER();
   __shared__ __align__(16) float As[2][WBK][WBM];
   __shared__ __align__(16) float Bs[2][WBK][WBN];
   const int tid = threadIdx.x;
@@ -417,7 +422,7 @@ void launch_conv_f32(Exec& ex, const ConvArgs& a) {
   if (w192_env && a.Q >= 4096 && a.cout % WBN == 0 && a.cin % 4 == 0 && a.ldw % 4 == 0) {
     dim3 grid((a.Q + WBM - 1) / WBM, a.cout / WBN, a.phases);
     ProfScope ps(ex, Prof::CONV_F32, 2.0 * a.Q * a.phases * a.taps * a.cin * a.cout);
-    conv_f32_w192_kernel<<<grid, 256, 0, ex.st>>>(a);
+    launch_pdl(conv_f32_w192_kernel, grid, dim3(256), 0, ex.st, a);
     KLAUNCH(ex);
     return;
   }
@@ -426,14 +431,14 @@ void launch_conv_f32(Exec& ex, const ConvArgs& a) {
     const int bn = wide ? 128 : 64;
     dim3 grid((a.Q + LBM - 1) / LBM, (a.cout + bn - 1) / bn, a.phases);
     ProfScope ps(ex, Prof::CONV_F32, 2.0 * a.Q * a.phases * a.taps * a.cin * a.cout);
-    if (wide) conv_f32_big_kernel<128><<<grid, 256, 0, ex.st>>>(a);
-    else conv_f32_big_kernel<64><<<grid, 256, 0, ex.st>>>(a);
+    if (wide) launch_pdl(conv_f32_big_kernel<128>, grid, dim3(256), 0, ex.st, a);
+    else launch_pdl(conv_f32_big_kernel<64>, grid, dim3(256), 0, ex.st, a);
     KLAUNCH(ex);
     return;
   }
   dim3 grid((a.Q + CBM - 1) / CBM, (a.cout + CBN - 1) / CBN, a.phases);
   ProfScope ps(ex, Prof::CONV_F32, 2.0 * a.Q * a.phases * a.taps * a.cin * a.cout);
-  conv_f32_kernel<<<grid, 256, 0, ex.st>>>(a);
+  launch_pdl(conv_f32_kernel, grid, dim3(256), 0, ex.st, a);
   KLAUNCH(ex);
 }
 
@@ -446,6 +451,7 @@ void launch_conv_f32(Exec& ex, const ConvArgs& a) {
 constexpr int LN_MAXV = 8;   // channels <= 256
 
 __global__ void __launch_bounds__(256) layernorm_kernel(LNArgs a) {
+  PDL_ENTER();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= a.R) return;
@@ -502,7 +508,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(LNArgs a) {
 void launch_layernorm(Exec& ex, const LNArgs& a) {
   if (a.R <= 0) return;
   const int warps_per_block = 8;
-  layernorm_kernel<<<(a.R + warps_per_block - 1) / warps_per_block, 256, 0, ex.st>>>(a);
+  launch_pdl(layernorm_kernel, dim3((a.R + warps_per_block - 1) / warps_per_block), dim3(256), 0, ex.st, a);
   KLAUNCH(ex);
 }
 
@@ -513,6 +519,7 @@ void launch_layernorm(Exec& ex, const LNArgs& a) {
 // ------------------------------------------------------------------------------------------
 __global__ void embed_kernel(const int64_t* __restrict__ ids, const float* __restrict__ emb,
                              float* __restrict__ x, int R, int H, int n_vocab, float scale) {
+  PDL_ENTER();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (int64_t)R * H) return;
   const int r = (int)(i / H), c = (int)(i % H);
@@ -526,7 +533,7 @@ void launch_embed(Exec& ex, const int64_t* ids_packed, const float* emb, float* 
                   int n_vocab, float scale) {
   const int64_t n = (int64_t)R * H;
   if (n <= 0) return;
-  embed_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ex.st>>>(ids_packed, emb, x, R, H, n_vocab, scale);
+  launch_pdl(embed_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, ex.st, ids_packed, emb, x, R, H, n_vocab, scale);
   KLAUNCH(ex);
 }
 
@@ -971,6 +978,7 @@ __global__ void __launch_bounds__(256) dds_sep_ln_gelu_kernel(
     const float* __restrict__ x, const float* __restrict__ w_sep, const float* __restrict__ b_sep,
     const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ out,
     const int* __restrict__ row_utt, int R, int C, int k, int dil, uint16_t* __restrict__ out_split2) {
+  PDL_ENTER();
   const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (r >= R) return;
@@ -1028,8 +1036,8 @@ void launch_dds_sep_ln_gelu(Exec& ex, const float* x, const float* w_sep, const 
                             const float* gamma, const float* beta, float* out, const int* row_utt,
                             int R, int C, int k, int dil, uint16_t* out_split2) {
   if (R <= 0) return;
-  dds_sep_ln_gelu_kernel<<<(R + 7) / 8, 256, 0, ex.st>>>(x, w_sep, b_sep, gamma, beta, out, row_utt, R, C, k, dil,
-                                                         out_split2);
+  launch_pdl(dds_sep_ln_gelu_kernel, dim3((R + 7) / 8), dim3(256), 0, ex.st, x, w_sep, b_sep, gamma, beta, out, row_utt, R, C, k, dil,
+             out_split2);
   KLAUNCH(ex);
 }
 
@@ -1037,6 +1045,7 @@ void launch_dds_sep_ln_gelu(Exec& ex, const float* x, const float* w_sep, const 
 __global__ void convflow_pre_kernel(const float* __restrict__ z, const float* __restrict__ w,
                                     const float* __restrict__ b, const float* __restrict__ cond,
                                     float* __restrict__ h, const int* __restrict__ row_utt, int R, int C) {
+  PDL_ENTER();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (int64_t)R * C) return;
   const int r = (int)(i / C), c = (int)(i % C);
@@ -1049,7 +1058,7 @@ void launch_convflow_pre(Exec& ex, const float* z, const float* w, const float* 
                          float* h, const int* row_utt, int R, int C) {
   const int64_t n = (int64_t)R * C;
   if (n <= 0) return;
-  convflow_pre_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ex.st>>>(z, w, b, cond, h, row_utt, R, C);
+  launch_pdl(convflow_pre_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, ex.st, z, w, b, cond, h, row_utt, R, C);
   KLAUNCH(ex);
 }
 
@@ -1066,6 +1075,7 @@ constexpr int SPL_MAXB = 16;
 __global__ void spline_inverse_kernel(float* __restrict__ zt, const float* __restrict__ params, int ldp,
                                       const int* __restrict__ row_utt, int R, int nb, float tb,
                                       float inv_sqrt_fc) {
+  PDL_ENTER();
   const int r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= R) return;
   if (row_utt && row_utt[r] < 0) {
@@ -1151,8 +1161,8 @@ __global__ void spline_inverse_kernel(float* __restrict__ zt, const float* __res
 void launch_spline_inverse(Exec& ex, float* z_target, const float* params, int ldp, const int* row_utt,
                            int R, int bins, float tail_bound, float inv_sqrt_filter) {
   if (R <= 0) return;
-  spline_inverse_kernel<<<(R + 127) / 128, 128, 0, ex.st>>>(z_target, params, ldp, row_utt, R, bins,
-                                                           tail_bound, inv_sqrt_filter);
+  launch_pdl(spline_inverse_kernel, dim3((R + 127) / 128), dim3(128), 0, ex.st, z_target, params, ldp, row_utt, R, bins, tail_bound,
+             inv_sqrt_filter);
   KLAUNCH(ex);
 }
 
@@ -1360,6 +1370,7 @@ __global__ void expand_prior_kernel(const float* __restrict__ stats, const int* 
                                     const int64_t* __restrict__ y_len, const float* __restrict__ ext,
                                     int64_t ext_stride, uint32_t seed, float noise_scale,
                                     float* __restrict__ zp, int Rf, int H) {
+  PDL_ENTER();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (int64_t)Rf * H) return;
   const int r = (int)(i / H), c = (int)(i % H);
@@ -1385,8 +1396,8 @@ void launch_expand_prior(Exec& ex, const float* stats, const int* frow_utt, cons
                          int64_t ext_stride, uint32_t seed, float noise_scale, float* zp, int Rf, int H) {
   const int64_t n = (int64_t)Rf * H;
   if (n <= 0) return;
-  expand_prior_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ex.st>>>(
-      stats, frow_utt, frow_src, fstart, y_len, ext_noise, ext_stride, seed, noise_scale, zp, Rf, H);
+  launch_pdl(expand_prior_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, ex.st, stats, frow_utt, frow_src, fstart, y_len,
+             ext_noise, ext_stride, seed, noise_scale, zp, Rf, H);
   KLAUNCH(ex);
 }
 
@@ -1618,4 +1629,11 @@ void launch_pack_ids(Exec& ex, const int64_t* ids, const int64_t* id_off, const 
   KLAUNCH(ex);
 }
 
+}  // namespace piper
+
+namespace piper {
+bool pdl_enabled() {
+  static const bool on = [] { const char* e = getenv("PIPER_B200_PDL"); return !e || atoi(e) != 0; }();
+  return on;
+}
 }  // namespace piper

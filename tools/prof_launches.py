@@ -31,7 +31,9 @@ from piper_b200.synth_voice import synthetic_utterances            # noqa: E402
 
 mp, cp = voice_files("medium")
 rt = PiperCUDARuntime(mp, cp, Options(precision="f16"))
-utts = synthetic_utterances(256, 256)
+# PROF_UTTS / PROF_IDS: batch size and ids per utterance (default: config 3; PROF_UTTS=1 PROF_IDS=14 = config 1)
+n_utts, n_ids = int(os.environ.get("PROF_UTTS", "256")), int(os.environ.get("PROF_IDS", "0"))
+utts = synthetic_utterances(n_utts, 256) if not n_ids else synthetic_utterances(n_utts, 256, n_ids, n_ids)
 import numpy as np
 ids = np.concatenate([np.asarray(u, np.int64) for u in utts]); lengths = np.array([len(u) for u in utts], np.int64)
 for i in range(3):
