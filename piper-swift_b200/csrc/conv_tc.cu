@@ -42,6 +42,7 @@ struct TcKernelParams {
   const int* row_utt; int valid_div;
   uint32_t tmem_cols;
   int nbuf;                         // accumulator buffers in TMEM (persistent kernel): 2, or 4 when 4 tiles fit in 512 columns
+  long long* trace;                 // debug (PIPER_B200_TC_TRACE=1): clock64 of CTA 0 at its phase boundaries
   int dbg;                          // timing attribution probe (PIPER_B200_TC_DBG): 1 no residual load, 2 no fp32 store, 4 no 16-bit store, 8 no staging
 };
 
@@ -775,6 +776,8 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
                                                                          const int m_tiles, const int n_tiles,
                                                                          const int total_tiles) {
   PDL_TRIGGER();   // the next kernel of the stream may be staged; this one waits for its predecessor after the set-up (PDL_WAIT below)
+  auto TR = [&](int slot) { if (p.trace && blockIdx.x == 0) p.trace[slot] = clock64(); };
+  if (threadIdx.x == 0) TR(0);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int row_bytes = p.kb * 2;
@@ -817,7 +820,9 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
   const uint32_t acc_stride = (uint32_t)(p.n_groups * p.nt);
+  if (threadIdx.x == 0) TR(1);
   PDL_WAIT();      // everything above touched constants only (bias, tensor maps); activations are read from here on
+  if (threadIdx.x == 0) TR(2);
 
   if (warp == 0) {
     // ===== TMA producer =====
@@ -881,6 +886,7 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
       for (int i = 0; i < n_it; ++i) {
         mbar_wait(&full[s], ph);
         tc_fence_after();
+        if (li == 0 && i == 0 && lane == 0) TR(3);
         const uint32_t al = stage_lo + (uint32_t)s * stage16, bl = al + a16;
         const int g0 = (p.split2 && 2 * i >= n_it) ? 1 : 0;   // f16x3: the A_lo' half of the K loop feeds D1 only
         if (elect_one()) {
@@ -893,6 +899,7 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
         if (++s == stages) { s = 0; ph ^= 1u; }
       }
       if (elect_one()) umma_commit(&acc_full[buf]);
+      if (li == 0 && lane == 0) TR(4);
     }
   } else {
     // ===== epilogue: four warpgroups = (TMEM buffer, i.e. every other tile) x (half of the column chunks) =====
@@ -916,11 +923,13 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
+      if (li == 0 && warp == 2 && lane == 0) TR(5);
     }
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, p.tmem_cols);
+  if (threadIdx.x == 32) TR(6);
 }
 
 }  // namespace
@@ -1026,7 +1035,20 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
       flops = 2.0 * a.Q * w.cin * (double)w.phase_cols * used;
     }
     ProfScope ps(ex, Prof::CONV_TC, flops);
+    static const bool trace_env = [] { const char* e = getenv("PIPER_B200_TC_TRACE"); return e && atoi(e) != 0; }();
+    if (trace_env) {
+      if (cudaMalloc(&p.trace, 8 * sizeof(long long)) != cudaSuccess) throw std::runtime_error("conv_tc: trace buffer");
+      cudaMemsetAsync(p.trace, 0, 8 * sizeof(long long), ex.st);
+    }
     launch_pdl(conv_tc_persist_kernel, dim3(grid), dim3(TCP_THREADS), smem, ex.st, ta, tbp, p, st, m_tiles, a.n_tiles, total);
+    if (trace_env) {   // debug only: CTA 0's phase boundaries in cycles since its start
+      long long h[8];
+      cudaStreamSynchronize(ex.st);
+      cudaMemcpy(h, p.trace, sizeof(h), cudaMemcpyDeviceToHost);
+      cudaFree(p.trace);
+      fprintf(stderr, "conv_tc trace Q %d cin %d nt %d tiles %d grid %d stages %d: setup %lld pdl_wait %lld first_full %lld mma_done %lld epi_done %lld exit %lld\n",
+              a.Q, w.cin, a.nt, total, grid, st, h[1] - h[0], h[2] - h[0], h[3] - h[0], h[4] - h[0], h[5] - h[0], h[6] - h[0]);
+    }
     if (const cudaError_t le = cudaPeekAtLastError(); le != cudaSuccess) {
       cudaFuncAttributes fa{};
       cudaFuncGetAttributes(&fa, conv_tc_persist_kernel);

@@ -45,6 +45,15 @@ TcConvArgs split_args(const TcW& w, const void* in, int R, const int* row_utt) {
   a.nt = 32;
   for (int nt : {256, 192, 128, 96, 64, 32})
     if ((w.split != 2 || nt <= 128) && w.cout % nt == 0) { a.nt = nt; break; }
+  // Small calls (one utterance, or the 32 utterances per GPU of the 8-GPU strong-scaling case): with the widest column tile
+  // a launch has fewer tiles than SMs and its duration is one CTA's chain (set-up, weight stream through one SM, an
+  // epilogue of nt / 32 chunks).  Narrower tiles spread the weights and the epilogue over more SMs; the accumulation
+  // order of an output element does not depend on the tile width, so results are bit-identical.
+  {
+    const int m_tiles = (R + 127) / 128;
+    for (int nt : {96, 64, 32})
+      if (nt < a.nt && m_tiles * (w.cout / a.nt) * 2 <= 148 && w.cout % nt == 0) a.nt = nt;
+  }
   a.n_tiles = w.cout / a.nt;
   a.e[0].bias = w.bias;
   return a;
