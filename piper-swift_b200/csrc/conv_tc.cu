@@ -37,6 +37,7 @@ struct TcKernelParams {
   uint32_t tap_mask[8];             // per column tile: taps to run (merged polyphase weights are zero elsewhere)
   int split_kbc;                    // bf16x6 fp32 emulation: K blocks per operand plane (0 = off)
   int split2;                       // f16x3 fp32 emulation (two planes, two accumulators; uses split_kbc too)
+  int sp1;                          // f16x3 in one pass: a stage holds A_hi, A_lo', B_hi, B_lo' of one K block
   TcEpi e[2];
   const float* uttbias; int ldub;
   const int* row_utt; int valid_div;
@@ -783,7 +784,8 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
   const int row_bytes = p.kb * 2;
   const int a_bytes = TC_BM * row_bytes;
   const int b_bytes = p.nt * row_bytes;
-  const int stage_bytes = a_bytes + p.n_groups * b_bytes;
+  const int a_tiles = p.sp1 ? 2 : 1;
+  const int stage_bytes = a_tiles * a_bytes + p.n_groups * b_bytes;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)stages * stage_bytes);
   uint64_t* empty = full + TCP_MAX_STAGES;
   uint64_t* acc_full = empty + TCP_MAX_STAGES;
@@ -839,7 +841,7 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
         // accumulated before the first large one (the tensor core aligns addends to the largest exponent and
         // drops what falls below its accumulator width)
         const int kb_inner = p.split_kbc ? p.split_kbc : p.kblocks;
-        const int n_outer = p.split2 ? 2 : (p.split_kbc ? 6 : 1);
+        const int n_outer = p.sp1 ? 1 : (p.split2 ? 2 : (p.split_kbc ? 6 : 1));
         for (int pl = 0; pl < n_outer; ++pl) {
           // bf16x6: A planes {0,1,2,0,1,0} against weight planes 0..5; f16x3: A_hi against (B_hi -> D0, B_lo' -> D1),
           // then A_lo' against B_hi -> D1 only
@@ -851,6 +853,17 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
             for (int kbi = 0; kbi < kb_inner; ++kbi) {
               mbar_wait(&empty[s], ph ^ 1u);
               uint8_t* st = smem + (size_t)s * stage_bytes;
+              if (p.sp1) {
+                // one pass: both activation planes and both weight planes of this K block (A_hi, B_hi and B_lo' are
+                // fetched once instead of twice; the K chain of a tile is half as long)
+                mbar_expect_tx(&full[s], (uint32_t)(2 * a_bytes + 2 * b_bytes));
+                for (int h = 0; h < 2; ++h) {
+                  tma_load_2d(&tmap_a, &full[s], st + h * a_bytes, (h * kb_inner + kbi) * p.kb, arow);
+                  tma_load_2d(&tmap_b, &full[s], st + 2 * a_bytes + h * b_bytes, (h * kb_inner + kbi) * p.kb, wrow + p.e[0].row0);
+                }
+                if (++s == stages) { s = 0; ph ^= 1u; }
+                continue;
+              }
               const int g0 = (p.split2 && pl == 1) ? 1 : 0;
               mbar_expect_tx(&full[s], (uint32_t)(a_bytes + (p.n_groups - g0) * b_bytes));
               tma_load_2d(&tmap_a, &full[s], st, (a_plane * kb_inner + kbi) * p.kb, arow);
@@ -867,6 +880,8 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
   } else if (warp == 1) {
     // ===== MMA issuer: warp-uniform control flow, one elected lane issues =====
     const uint32_t idesc = make_idesc(p.nt, p.f16);
+    const bool merge2 = p.n_groups == 2 && 2 * p.nt <= 256;
+    const uint32_t idesc2 = make_idesc(2 * p.nt, p.f16);
     const int ksteps = p.kb / 16;
     const uint64_t d_hi = make_smem_desc(0, p.kb);
     const uint32_t stage_lo = smem_u32(smem) >> 4;
@@ -887,9 +902,28 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
         mbar_wait(&full[s], ph);
         tc_fence_after();
         if (li == 0 && i == 0 && lane == 0) TR(3);
-        const uint32_t al = stage_lo + (uint32_t)s * stage16, bl = al + a16;
-        const int g0 = (p.split2 && 2 * i >= n_it) ? 1 : 0;   // f16x3: the A_lo' half of the K loop feeds D1 only
+        const uint32_t al = stage_lo + (uint32_t)s * stage16, bl = al + (p.sp1 ? 2u : 1u) * a16;
+        const int g0 = (p.split2 && !p.sp1 && 2 * i >= n_it) ? 1 : 0;   // f16x3 in two passes: the A_lo' half of the K loop feeds D1 only
         if (elect_one()) {
+          if (p.sp1) {
+            // A_hi x [B_hi ; B_lo'] -> D0 | D1 (adjacent weight tiles, adjacent accumulators: one N = 2 nt instruction),
+            // then A_lo' x B_hi -> D1
+            for (int k = 0; k < ksteps; ++k) {
+              umma_f16(acc, d_hi | (uint64_t)(al + 2u * (uint32_t)k), d_hi | (uint64_t)(bl + 2u * (uint32_t)k), idesc2,
+                       (i == 0 && k == 0) ? 0u : 1u);
+              umma_f16(acc + (uint32_t)p.nt, d_hi | (uint64_t)(al + a16 + 2u * (uint32_t)k),
+                       d_hi | (uint64_t)(bl + 2u * (uint32_t)k), idesc, 1u);
+            }
+          } else
+#ifndef PIPER_TC_NO_GROUP_MERGE
+          if (merge2 && g0 == 0) {
+            // Both groups read the same A tile, their B tiles are adjacent in the stage and their accumulators adjacent
+            // in TMEM: one N = 2*nt instruction fetches A once instead of twice (an N=96 MMA is operand-fetch bound).
+            for (int k = 0; k < ksteps; ++k)
+              umma_f16(acc, d_hi | (uint64_t)(al + 2u * (uint32_t)k), d_hi | (uint64_t)(bl + 2u * (uint32_t)k), idesc2,
+                       (i == 0 && k == 0) ? 0u : 1u);
+          } else
+#endif
           for (int g = g0; g < p.n_groups; ++g)
             for (int k = 0; k < ksteps; ++k)
               umma_f16(acc + (uint32_t)(g * p.nt), d_hi | (uint64_t)(al + 2u * (uint32_t)k),
@@ -958,8 +992,10 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
   if (w.split == 2) {
     if (!a.f16 || a.gate || w.phase_cols || a.n_groups != 1 || a.nt > 128 || (a.nt & 31) || w.cin != w.cin_pad || w.phases != 1)
       throw std::runtime_error("conv_tc: f16x3 split weights need fp16 operands, one column group of at most 128 columns and whole K blocks");
+    static const int sp1_env = [] { const char* e = getenv("PIPER_B200_SPLIT_1PASS"); return e ? atoi(e) : 1; }();
     p.split_kbc = p.kblocks;
-    p.kblocks *= 2;
+    p.sp1 = sp1_env ? 1 : 0;
+    if (!p.sp1) p.kblocks *= 2;
     p.split2 = 1;
     n_groups = 2;   // second accumulator for the cross terms, same weight rows
   } else if (w.split) {
@@ -1018,7 +1054,7 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
     uint32_t pc = 32;
     while ((int)pc < p.nbuf * n_groups * a.nt) pc <<= 1;
     p.tmem_cols = pc;
-    const int sb = TC_BM * w.kb * 2 + n_groups * a.nt * w.kb * 2;
+    const int sb = (p.sp1 ? 2 : 1) * TC_BM * w.kb * 2 + n_groups * a.nt * w.kb * 2;
     constexpr int TBUF_BYTES = TCP_NG * TCP_EG * 4 * 32 * 36 * 4;
     constexpr int SBIAS_BYTES = 2 * TC_SBIAS * 4;
     int st = (TC_SMEM_MAX - 3072 - TBUF_BYTES - SBIAS_BYTES) / sb;   // 1 KB static + alignment slack + barriers

@@ -1,0 +1,14 @@
+# GPU suite on the default build, then bench --no-cpu of: default, PIPER_B200_SPLIT_1PASS=0, libpiper_b200_variant.so
+cd /root/repo
+TAG=${1:-ab3}
+timeout 500 python -m pytest tests -m gpu -x -q --timeout 120 > gpurun_out/gpu_tests_$TAG.log 2>&1; tail -3 gpurun_out/gpu_tests_$TAG.log
+run() {  # name, env...
+  local name=$1; shift
+  echo "== $name"
+  env "$@" timeout 240 python bench.py --no-cpu > gpurun_out/bench_${TAG}_$name.json 2> gpurun_out/bench_${TAG}_$name.err
+  python tools/bench_brief.py gpurun_out/bench_${TAG}_$name.json | head -9
+}
+run default X=1
+run twopass PIPER_B200_SPLIT_1PASS=0
+run nomerge PIPER_B200_LIB=piper-swift_b200/libpiper_b200_variant.so
+run default2 X=1
