@@ -358,6 +358,7 @@ size_t back_tc_bytes(const Context& ctx, int Rf, int batch) {
   bytes += (size_t)Rf * H * 2 * (size_t)std::max(0, v.hp.flow_wn_layers - 1);   // gated activations of every WN layer
   bytes += (size_t)Rf * P * (4 * 3 + 2 * 5);       // xu, yb, xs fp32; actA, actB, xub, ybb, tbb 16-bit
   bytes += 3 * (128 * 1280 * 2 + 4096);            // pad rows of the planar operand layouts
+  bytes += (size_t)H * 2 * 256;                    // pad rows of the flow's group-planar residual copy
   bytes += (size_t)Rf * v.hp.hop * 4;              // packed audio
   bytes += 32 * 256;
   (void)batch;
@@ -375,7 +376,20 @@ FlowOut run_flow_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep)
   float* h = A.alloc<float>((size_t)Rf * H);
   float* skip = A.alloc<float>((size_t)Rf * H);
   uint16_t* zb = A.alloc<uint16_t>((size_t)Rf * H);
-  uint16_t* hb = A.alloc<uint16_t>((size_t)Rf * H);
+  // The 16-bit copy of the WN residual stream is group-planar [H / 8][hb_rows][8] when every in_layer can take its
+  // operand as a row window (conv_tc.h, TcConvArgs::in_planar): a k = 5 in_layer then fetches each row once instead
+  // of once per tap (-31 % L2 -> SM bytes).  Off by default: the launch time did not change (DESIGN.md section 10 -
+  // those launches are bound by the MMA / epilogue interplay inside the SM, not by operand bytes).
+  static const int flow_win_env = [] { const char* e = getenv("PIPER_B200_FLOW_WINDOW"); return e ? atoi(e) : 0; }();
+  bool hb_planar = flow_win_env != 0 && H % 64 == 0 && !tv.flows.empty();
+  for (const TcCoupling& t : tv.flows)
+    for (const TcW& w : t.in_layers)
+      if (w.taps < 2 || w.kb != 64 || w.split || w.cin != w.cin_pad || w.cin != H || (w.taps - 1) * w.dil > 64 || w.pad_l > 8 ||
+          w.phases != 1)
+        hb_planar = false;
+  const int hb_pad = 8;
+  const int64_t hb_rows = hb_planar ? (int64_t)Rf + hb_pad + 248 : Rf;
+  uint16_t* hb = A.alloc<uint16_t>((size_t)hb_rows * H);
   const bool noskip = !tv.flows.empty() && tv.flows[0].post_fused.w != nullptr;
   const int LA = noskip ? L : 1;                       // the skip-free form keeps the gated activations of every layer
   uint16_t* actsb = A.alloc<uint16_t>((size_t)Rf * H * LA);
@@ -383,6 +397,14 @@ FlowOut run_flow_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep)
   if (!h || !skip || !zb || !hb || !actsb || !skipb) throw std::runtime_error("capacity: back arena too small (flow)");
 
   // ---- flow ------------------------------------------------------------------------------
+  if (hb_planar) {   // zero rows around the signal: taps of the first / last row tile read them
+    CUDA_OK(cudaMemset2DAsync(hb, (size_t)hb_rows * 16, 0, (size_t)hb_pad * 16, H / 8, ex.st));
+    CUDA_OK(cudaMemset2DAsync(hb + ((size_t)hb_pad + Rf) * 8, (size_t)hb_rows * 16, 0, (size_t)248 * 16, H / 8, ex.st));
+  }
+  auto hb_out = [&](TcEpi& e) {
+    e.out_act = hb; e.ld_act = H;
+    if (hb_planar) { e.act_planar = 1; e.act_rows = hb_rows; e.act_pad = hb_pad; }
+  };
   launch_to_act16(ex, z, zb, (int64_t)Rf * H, 1.f, f16);
   for (size_t f = 0; f < v.flows.size(); ++f) {
     const CouplingW& c = v.flows[f];
@@ -391,12 +413,13 @@ FlowOut run_flow_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep)
     {
       TcConvArgs a = tc_args(t.pre, zb + c.in_off, H, Rf, in.frow_utt, 1, f16);
       a.e[0].out_f32 = h; a.e[0].ld_f32 = H;
-      a.e[0].out_act = hb; a.e[0].ld_act = H;
+      hb_out(a.e[0]);
       launch_conv_tc(ex, a);
     }
     for (int l = 0; l < L; ++l) {
       {   // in_layer + (cond) + tanh*sigmoid gate
         TcConvArgs a = tc_args(t.in_layers[l], hb, H, Rf, in.frow_utt, 1, f16);
+        if (hb_planar) { a.in_planar = hb; a.in_rows = hb_rows; a.in_pad = hb_pad; }
         a.gate = 1; a.n_groups = 2;
         a.nt = pick_nt(H);
         a.n_tiles = H / a.nt;
@@ -413,7 +436,7 @@ FlowOut run_flow_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep)
         if (l < L - 1) {
           TcConvArgs a = tc_args(t.res[l], actsb + l * H, H * LA, Rf, in.frow_utt, 1, f16);
           a.e[0].out_f32 = h; a.e[0].ld_f32 = H; a.e[0].res = h; a.e[0].ld_res = H;
-          a.e[0].out_act = hb; a.e[0].ld_act = H;
+          hb_out(a.e[0]);
           launch_conv_tc(ex, a);
         }
       } else {   // res | skip
@@ -424,7 +447,7 @@ FlowOut run_flow_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep)
           a.n_groups = 2;
           a.e[0].row0 = 0; a.e[0].bias = c.res[l].b;
           a.e[0].out_f32 = h; a.e[0].ld_f32 = H; a.e[0].res = h; a.e[0].ld_res = H;   // x = (x + res_acts) * mask
-          a.e[0].out_act = hb; a.e[0].ld_act = H;
+          hb_out(a.e[0]);
           a.e[1].row0 = H; a.e[1].bias = c.skip[l].b;
           a.e[1].out_f32 = skip; a.e[1].ld_f32 = H; a.e[1].accum = l > 0;             // output += skip_acts
         } else {

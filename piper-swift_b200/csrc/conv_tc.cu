@@ -38,6 +38,11 @@ struct TcKernelParams {
   int split_kbc;                    // bf16x6 fp32 emulation: K blocks per operand plane (0 = off)
   int split2;                       // f16x3 fp32 emulation (two planes, two accumulators; uses split_kbc too)
   int sp1;                          // f16x3 in one pass: a stage holds A_hi, A_lo', B_hi, B_lo' of one K block
+  // persistent kernel, windowed activations: the A operand of a K block is ONE (128 + span)-row window of the
+  // group-planar tensor a_planar [cin / 8][a_rows][8] (row r at plane row a_pad + r), bulk-copied plane by plane into a
+  // no-swizzle K-major window; every tap is a descriptor row offset into it.  pwin = window rows (0 = off)
+  int pwin;
+  const uint16_t* a_planar; long long a_rows; int a_pad;
   TcEpi e[2];
   const float* uttbias; int ldub;
   const int* row_utt; int valid_div;
@@ -252,7 +257,7 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
               if (!((act_mask >> qq) & 1u)) continue;
               const int k = sl ^ (qq & (ppt - 1));
               const size_t orow_r = (size_t)(row_base + qq) * p.out_mul + ph0 + k;
-              *reinterpret_cast<uint4*>(plane + orow_r * 8) = lds128u(tbs + (uint32_t)(pl * pieces + i) * 16u);
+              if (!(p.dbg & 4)) *reinterpret_cast<uint4*>(plane + orow_r * 8) = lds128u(tbs + (uint32_t)(pl * pieces + i) * 16u);
             }
           }
         }
@@ -312,13 +317,16 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
       if (++c == cpg) { c = 0; ++g; }
       if (g != gc) { ec = p.e[g]; gc = g; }
       const TcEpi& e = ec;
-      const bool planar = e.out_act && e.act_planar;      // only used by plain convolutions (no residual)
+      const bool planar = e.out_act && e.act_planar;
       // Lean form for whole tiles of a plain convolution (every row of the warp's 32 inside the tensor, output row =
       // input row): no per-row predicates, strides hoisted, and the residual loads go out before the accumulator is
       // read so that their latency hides behind the TMEM load, bias add and staging.  The general form below runs
       // ~1100 warp instructions per 32 x 32 chunk at one issue per ~9 cycles (ncu), which made every epilogue with
       // fp32 / 16-bit outputs cost 5-14 us per row tile regardless of K.
-      const bool fast = !p.phase_cols && p.phases == 1 && p.out_mul == 1 && !planar && act_mask == 0xffffffffu;
+      // (a planar 16-bit copy is written from the final value there; the general form writes it before the residual,
+      // which only suits convolutions without one)
+      const bool fast = !p.phase_cols && p.phases == 1 && p.out_mul == 1 && act_mask == 0xffffffffu;
+      const bool planar_early = planar && !fast && !e.res && !e.accum;
       float4 rr[8];
       const size_t fcol = (size_t)e.col0 + (size_t)(ntile * p.nt + c * 32 + c4);
       const size_t frow = (size_t)(row_base + sub);
@@ -396,7 +404,7 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
 #pragma unroll
           for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
         }
-        if (planar && active) {   // group-planar operand of the fused MRF stage: 16 bytes per (row, plane)
+        if (planar_early && active) {   // group-planar operand of the fused MRF stage: 16 bytes per (row, plane)
           uint16_t* base = static_cast<uint16_t*>(e.out_act) + ((size_t)(ocol >> 3) * e.act_rows + e.act_pad + orow_c) * 8;
 #pragma unroll
           for (int pl = 0; pl < 4; ++pl) {
@@ -407,7 +415,7 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
             *reinterpret_cast<uint4*>(base + (size_t)pl * e.act_rows * 8) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
           }
         }
-        if (!e.out_f32 && !e.out_split && (planar || !e.out_act)) continue;
+        if (!e.out_f32 && !e.out_split && (planar_early || !e.out_act)) continue;
         if (p.dbg & 16) continue;
         __syncwarp();                                     // the previous chunk's readers are done with tbuf
 #pragma unroll
@@ -474,7 +482,16 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
               }
             }
           }
-          if (e.out_act && !(p.dbg & 4)) {
+          if (planar && !(p.dbg & 4)) {
+            // group-planar copy [C / 8][act_rows][8]: a lane holds half of a 16-byte (row, plane) piece, the four rows of
+            // an instruction are adjacent in the plane (64 contiguous bytes per plane and instruction)
+            uint16_t* oa = static_cast<uint16_t*>(e.out_act) + ((fcol >> 3) * (size_t)e.act_rows + e.act_pad + frow) * 8 + (fcol & 7);
+            const float sl = e.act_slope;
+#pragma unroll
+            for (int it = 0; it < 8; ++it)
+              *reinterpret_cast<uint2*>(oa + it * 32) = make_uint2(pack2(lrelu(x[it].x, sl), lrelu(x[it].y, sl), p.f16),
+                                                                   pack2(lrelu(x[it].z, sl), lrelu(x[it].w, sl), p.f16));
+          } else if (e.out_act && !(p.dbg & 4)) {
             uint16_t* oa = static_cast<uint16_t*>(e.out_act) + frow * e.ld_act + fcol;
             const size_t sa = (size_t)4 * e.ld_act;
             const float sl = e.act_slope;
@@ -525,6 +542,13 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
               *reinterpret_cast<uint2*>(sp + e.split_c) = t1;
               *reinterpret_cast<uint2*>(sp + 2 * e.split_c) = t2;
             }
+          }
+          if (planar && !planar_early) {
+            const size_t oc = ocol + c4;
+            *reinterpret_cast<uint2*>(static_cast<uint16_t*>(e.out_act) +
+                                      ((oc >> 3) * (size_t)e.act_rows + e.act_pad + orow0 + it * rstep) * 8 + (oc & 7)) =
+                make_uint2(pack2(lrelu(x.x, e.act_slope), lrelu(x.y, e.act_slope), p.f16),
+                           pack2(lrelu(x.z, e.act_slope), lrelu(x.w, e.act_slope), p.f16));
           }
           if (e.out_act && !planar && !(p.dbg & 4)) {
             const uint32_t lo = pack2(lrelu(x.x, e.act_slope), lrelu(x.y, e.act_slope), p.f16);
@@ -760,6 +784,7 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
 // tiles (up to 8 stages) and the accumulator is double-buffered in TMEM, so the epilogue of tile i (two
 // warpgroups, one per TMEM buffer) overlaps the TMA/MMA main loop of tile i+1 inside the same CTA.
 constexpr int TCP_MAX_STAGES = 8;
+constexpr int TCP_WIN_SLOTS = 3;               // activation windows in flight (window mode)
 constexpr int TCP_EG = 1;                      // epilogue warpgroups per TMEM buffer (column split); 2 starves registers
 // epilogue warpgroups taking tiles round robin.  The epilogues are latency-bound per warp, so a third group was tried
 // (-DPIPER_TC_NG=3): 14 warps put four on one SM sub-partition (16384 registers each), i.e. at most 128 registers per
@@ -778,20 +803,34 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
                                                                          const int total_tiles) {
   PDL_TRIGGER();   // the next kernel of the stream may be staged; this one waits for its predecessor after the set-up (PDL_WAIT below)
   auto TR = [&](int slot) { if (p.trace && blockIdx.x == 0) p.trace[slot] = clock64(); };
+  // wait accounting of the trace build (make trace: -DPIPER_TC_WAIT_TRACE): cycles the MMA warp / epilogue group 0 of
+  // CTA 0 spent waiting; compiled out of the product build (the counters cost registers in the epilogue)
+#ifdef PIPER_TC_WAIT_TRACE
+#define TCW_NOW() (p.trace ? clock64() : 0)
+#define TCW_ADD(acc, t0) do { if (p.trace) (acc) += clock64() - (t0); } while (0)
+#else
+#define TCW_NOW() 0
+#define TCW_ADD(acc, t0) do { (void)(t0); } while (0)
+#endif
   if (threadIdx.x == 0) TR(0);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int row_bytes = p.kb * 2;
   const int a_bytes = TC_BM * row_bytes;
   const int b_bytes = p.nt * row_bytes;
-  const int a_tiles = p.sp1 ? 2 : 1;
+  const int a_tiles = p.pwin ? 0 : (p.sp1 ? 2 : 1);
   const int stage_bytes = a_tiles * a_bytes + p.n_groups * b_bytes;
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)stages * stage_bytes);
+  const int win_bytes = p.pwin * 16 * (p.kb / 8);      // window mode: [kb / 8 planes][pwin rows][16 bytes]
+  const int a_ring_bytes = p.pwin ? TCP_WIN_SLOTS * win_bytes : 0;
+  uint8_t* stage_base = smem + a_ring_bytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(stage_base + (size_t)stages * stage_bytes);
   uint64_t* empty = full + TCP_MAX_STAGES;
   uint64_t* acc_full = empty + TCP_MAX_STAGES;
   uint64_t* acc_empty = acc_full + 4;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 4);
-  float* tbuf_base = reinterpret_cast<float*>(smem + (size_t)stages * stage_bytes + 512);   // one 32 x 36 float tile per epilogue warp
+  uint64_t* a_full = acc_empty + 4;
+  uint64_t* a_empty = a_full + TCP_WIN_SLOTS;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(a_empty + TCP_WIN_SLOTS);
+  float* tbuf_base = reinterpret_cast<float*>(stage_base + (size_t)stages * stage_bytes + 512);   // one 32 x 36 float tile per epilogue warp
   float* sbias = tbuf_base + TCP_NG * TCP_EG * 4 * 32 * 36;                                      // [2][TC_SBIAS] bias of both column groups
   const int bias_w = p.phase_cols ? p.phase_cols : n_tiles * p.nt;
   const bool bias_staged = bias_w <= TC_SBIAS;
@@ -812,6 +851,10 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
       mbar_init(&acc_full[s], 1);
       mbar_init(&acc_empty[s], 4 * TCP_EG);   // every warp of the warpgroups draining this buffer
     }
+    for (int s = 0; s < TCP_WIN_SLOTS; ++s) {
+      mbar_init(&a_full[s], 1);
+      mbar_init(&a_empty[s], 1);
+    }
     fence_barrier_init();
   } else if (warp == 1) {
     tmem_alloc(tmem_slot, p.tmem_cols);
@@ -827,10 +870,42 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
   if (threadIdx.x == 0) TR(2);
 
   if (warp == 0) {
-    // ===== TMA producer =====
+    // ===== TMA producer (one thread; a warp-uniform form with an elected issuer was neutral on the large launches and
+    // slower on the small ones) =====
     if (lane == 0) {
       int s = 0; uint32_t ph = 0;
+      int as = 0; uint32_t aph = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        if (p.pwin) {
+          // K block outermost: one window per K block, then the weight tiles of its taps
+          const int mt = t % m_tiles, ntile = t / m_tiles;
+          const int plane_bytes = p.pwin * 16;
+          for (int kbi = 0; kbi < p.kblocks; ++kbi) {
+            mbar_wait(&a_empty[as], aph ^ 1u);
+            uint8_t* aw = smem + (size_t)as * win_bytes;
+            const uint16_t* src = p.a_planar + ((size_t)(kbi * (p.kb / 8)) * p.a_rows + p.a_pad + mt * TC_BM + p.in_off) * 8;
+            if (p.dbg & 32) mbar_arrive(&a_full[as]);
+            else {
+              mbar_expect_tx(&a_full[as], (uint32_t)win_bytes);
+              for (int pl = 0; pl < p.kb / 8; ++pl)
+                bulk_load(aw + pl * plane_bytes, src + (size_t)pl * p.a_rows * 8, (uint32_t)plane_bytes, &a_full[as]);
+            }
+            if (++as == TCP_WIN_SLOTS) { as = 0; aph ^= 1u; }
+            for (int tap = 0; tap < p.taps; ++tap) {
+              mbar_wait(&empty[s], ph ^ 1u);
+              uint8_t* st = stage_base + (size_t)s * stage_bytes;
+              const int wrow = tap * p.cout_rows + ntile * p.nt;
+              if (p.dbg & 32) mbar_arrive(&full[s]);   // timing probe: no loads, stale operands
+              else {
+                mbar_expect_tx(&full[s], (uint32_t)stage_bytes);
+                for (int g = 0; g < p.n_groups; ++g)
+                  tma_load_2d(&tmap_b, &full[s], st + g * b_bytes, kbi * p.kb, wrow + p.e[g].row0);
+              }
+              if (++s == stages) { s = 0; ph ^= 1u; }
+            }
+          }
+          continue;
+        }
         // phase fastest: the polyphase outputs of one row tile interleave in memory (row = q * stride + phase), so
         // they are produced back to back and merge in L2 instead of rewriting every line `phases` times
         const int phase = t % p.phases, rest = t / p.phases;
@@ -852,24 +927,30 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
             const int wrow = (phase * p.taps + tap) * p.cout_rows + ntile * p.nt;
             for (int kbi = 0; kbi < kb_inner; ++kbi) {
               mbar_wait(&empty[s], ph ^ 1u);
-              uint8_t* st = smem + (size_t)s * stage_bytes;
+              uint8_t* st = stage_base + (size_t)s * stage_bytes;
               if (p.sp1) {
                 // one pass: both activation planes and both weight planes of this K block (A_hi, B_hi and B_lo' are
                 // fetched once instead of twice; the K chain of a tile is half as long)
-                mbar_expect_tx(&full[s], (uint32_t)(2 * a_bytes + 2 * b_bytes));
-                for (int h = 0; h < 2; ++h) {
-                  tma_load_2d(&tmap_a, &full[s], st + h * a_bytes, (h * kb_inner + kbi) * p.kb, arow);
-                  tma_load_2d(&tmap_b, &full[s], st + 2 * a_bytes + h * b_bytes, (h * kb_inner + kbi) * p.kb, wrow + p.e[0].row0);
+                if (p.dbg & 32) mbar_arrive(&full[s]);
+                else {
+                  mbar_expect_tx(&full[s], (uint32_t)(2 * a_bytes + 2 * b_bytes));
+                  for (int h = 0; h < 2; ++h) {
+                    tma_load_2d(&tmap_a, &full[s], st + h * a_bytes, (h * kb_inner + kbi) * p.kb, arow);
+                    tma_load_2d(&tmap_b, &full[s], st + 2 * a_bytes + h * b_bytes, (h * kb_inner + kbi) * p.kb, wrow + p.e[0].row0);
+                  }
                 }
                 if (++s == stages) { s = 0; ph ^= 1u; }
                 continue;
               }
               const int g0 = (p.split2 && pl == 1) ? 1 : 0;
-              mbar_expect_tx(&full[s], (uint32_t)(a_bytes + (p.n_groups - g0) * b_bytes));
-              tma_load_2d(&tmap_a, &full[s], st, (a_plane * kb_inner + kbi) * p.kb, arow);
-              for (int g = g0; g < p.n_groups; ++g) {
-                const int b_plane = p.split2 ? (pl == 0 ? g : 0) : pl;
-                tma_load_2d(&tmap_b, &full[s], st + a_bytes + g * b_bytes, (b_plane * kb_inner + kbi) * p.kb, wrow + p.e[g].row0);
+              if (p.dbg & 32) mbar_arrive(&full[s]);   // timing probe: no loads, stale operands
+              else {
+                mbar_expect_tx(&full[s], (uint32_t)(a_bytes + (p.n_groups - g0) * b_bytes));
+                tma_load_2d(&tmap_a, &full[s], st, (a_plane * kb_inner + kbi) * p.kb, arow);
+                for (int g = g0; g < p.n_groups; ++g) {
+                  const int b_plane = p.split2 ? (pl == 0 ? g : 0) : pl;
+                  tma_load_2d(&tmap_b, &full[s], st + a_bytes + g * b_bytes, (b_plane * kb_inner + kbi) * p.kb, wrow + p.e[g].row0);
+                }
               }
               if (++s == stages) { s = 0; ph ^= 1u; }
             }
@@ -884,9 +965,15 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
     const uint32_t idesc2 = make_idesc(2 * p.nt, p.f16);
     const int ksteps = p.kb / 16;
     const uint64_t d_hi = make_smem_desc(0, p.kb);
-    const uint32_t stage_lo = smem_u32(smem) >> 4;
+    const uint32_t stage_lo = smem_u32(stage_base) >> 4, ring_lo = smem_u32(smem) >> 4;
     const uint32_t stage16 = (uint32_t)stage_bytes >> 4, a16 = (uint32_t)a_bytes >> 4, b16 = (uint32_t)b_bytes >> 4;
+    const uint64_t a_ns = make_smem_desc_ns(0, (uint32_t)p.pwin * 16u, 128);   // planes pwin * 16 bytes apart, 8-row groups 128
+    const uint32_t win16 = (uint32_t)win_bytes >> 4, a_kstep_ns = 2u * (uint32_t)p.pwin;   // 16 channels = two planes
+    int as = 0; uint32_t aph = 0;
     int s = 0; uint32_t ph = 0, li = 0;
+#ifdef PIPER_TC_WAIT_TRACE
+    long long w_acc = 0, w_full = 0;   // trace: cycles this warp waited for a drained accumulator / for operands
+#endif
     const uint32_t nbuf = (uint32_t)p.nbuf;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++li) {
       const int ntile_m = (t / p.phases) / m_tiles;
@@ -895,20 +982,87 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
       // current one (with two, a group's MMA -> epilogue chain was serial, which small-K tiles cannot hide).
       const uint32_t buf = nbuf == 4 ? (li & 3u) : (li & 1u);
       const uint32_t use = nbuf == 4 ? (li >> 2) : (li >> 1);
+      const long long tw0 = TCW_NOW();
       mbar_wait(&acc_empty[buf], (use & 1u) ^ 1u);           // the epilogue drained this accumulator buffer
       tc_fence_after();
+      TCW_ADD(w_acc, tw0);
       const uint32_t acc = tmem_base + buf * acc_stride;
+      if (p.pwin) {
+        bool have_w = false;
+        for (int kbi = 0; kbi < p.kblocks; ++kbi) {
+          mbar_wait(&a_full[as], aph);
+          tc_fence_after();
+          const uint32_t a_lo = ring_lo + (uint32_t)as * win16;
+          for (int tap = 0; tap < p.taps; ++tap) {
+            if (!have_w) {
+              const long long tf0 = TCW_NOW();
+              mbar_wait(&full[s], ph);
+              tc_fence_after();
+              TCW_ADD(w_full, tf0);
+            }
+            if (li == 0 && kbi == 0 && tap == 0 && lane == 0) TR(3);
+            const uint32_t al = a_lo + (uint32_t)(tap * p.tap_step), bl = stage_lo + (uint32_t)s * stage16;
+            auto issue = [&](int k0, int k1) {
+              if (merge2) {
+                for (int k = k0; k < k1; ++k)
+                  umma_f16(acc, a_ns | (uint64_t)(al + a_kstep_ns * (uint32_t)k), d_hi | (uint64_t)(bl + 2u * (uint32_t)k), idesc2,
+                           (kbi == 0 && tap == 0 && k == 0) ? 0u : 1u);
+              } else {
+                for (int g = 0; g < p.n_groups; ++g)
+                  for (int k = k0; k < k1; ++k)
+                    umma_f16(acc + (uint32_t)(g * p.nt), a_ns | (uint64_t)(al + a_kstep_ns * (uint32_t)k),
+                             d_hi | (uint64_t)(bl + (uint32_t)g * b16 + 2u * (uint32_t)k), idesc,
+                             (kbi == 0 && tap == 0 && k == 0) ? 0u : 1u);
+              }
+            };
+#ifdef PIPER_TC_PREWAIT
+            const int k_split = ksteps - 1;
+#else
+            const int k_split = ksteps;
+#endif
+            if (elect_one()) issue(0, k_split);
+            int s1 = s + 1; uint32_t ph1 = ph;
+            if (s1 == stages) { s1 = 0; ph1 ^= 1u; }
+            have_w = false;
+            if (k_split < ksteps && !(kbi + 1 == p.kblocks && tap + 1 == p.taps)) {   // same pre-wait as the plain loop below
+              const long long tf0 = TCW_NOW();
+              mbar_wait(&full[s1], ph1);
+              tc_fence_after();
+              TCW_ADD(w_full, tf0);
+              have_w = true;
+            }
+            if (elect_one()) {
+              issue(k_split, ksteps);
+              umma_commit(&empty[s]);
+            }
+            s = s1; ph = ph1;
+          }
+          if (elect_one()) umma_commit(&a_empty[as]);   // the window is free when the MMAs of its last tap retire
+          if (++as == TCP_WIN_SLOTS) { as = 0; aph ^= 1u; }
+        }
+        if (elect_one()) umma_commit(&acc_full[buf]);
+        if (li == 0 && lane == 0) TR(4);
+        continue;
+      }
+      // PIPER_TC_PREWAIT (off): take the wait for stage i + 1 before the last K step of stage i is issued.  Tried to
+      // close the gap between the stages' MMA groups; it couples the release of slot s to the arrival of slot s + 1
+      // (one stage less in flight) and measured 4 % slower over the conv class.
+      bool have = false;
       for (int i = 0; i < n_it; ++i) {
-        mbar_wait(&full[s], ph);
-        tc_fence_after();
+        if (!have) {
+          const long long tf0 = TCW_NOW();
+          mbar_wait(&full[s], ph);
+          tc_fence_after();
+          TCW_ADD(w_full, tf0);
+        }
         if (li == 0 && i == 0 && lane == 0) TR(3);
         const uint32_t al = stage_lo + (uint32_t)s * stage16, bl = al + (p.sp1 ? 2u : 1u) * a16;
         const int g0 = (p.split2 && !p.sp1 && 2 * i >= n_it) ? 1 : 0;   // f16x3 in two passes: the A_lo' half of the K loop feeds D1 only
-        if (elect_one()) {
+        auto issue = [&](int k0, int k1) {
           if (p.sp1) {
             // A_hi x [B_hi ; B_lo'] -> D0 | D1 (adjacent weight tiles, adjacent accumulators: one N = 2 nt instruction),
             // then A_lo' x B_hi -> D1
-            for (int k = 0; k < ksteps; ++k) {
+            for (int k = k0; k < k1; ++k) {
               umma_f16(acc, d_hi | (uint64_t)(al + 2u * (uint32_t)k), d_hi | (uint64_t)(bl + 2u * (uint32_t)k), idesc2,
                        (i == 0 && k == 0) ? 0u : 1u);
               umma_f16(acc + (uint32_t)p.nt, d_hi | (uint64_t)(al + a16 + 2u * (uint32_t)k),
@@ -919,22 +1073,44 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
           if (merge2 && g0 == 0) {
             // Both groups read the same A tile, their B tiles are adjacent in the stage and their accumulators adjacent
             // in TMEM: one N = 2*nt instruction fetches A once instead of twice (an N=96 MMA is operand-fetch bound).
-            for (int k = 0; k < ksteps; ++k)
+            for (int k = k0; k < k1; ++k)
               umma_f16(acc, d_hi | (uint64_t)(al + 2u * (uint32_t)k), d_hi | (uint64_t)(bl + 2u * (uint32_t)k), idesc2,
                        (i == 0 && k == 0) ? 0u : 1u);
           } else
 #endif
           for (int g = g0; g < p.n_groups; ++g)
-            for (int k = 0; k < ksteps; ++k)
+            for (int k = k0; k < k1; ++k)
               umma_f16(acc + (uint32_t)(g * p.nt), d_hi | (uint64_t)(al + 2u * (uint32_t)k),
                        d_hi | (uint64_t)(bl + (uint32_t)g * b16 + 2u * (uint32_t)k), idesc, (i == 0 && k == 0) ? 0u : 1u);
+        };
+#ifdef PIPER_TC_PREWAIT
+        const int k_split = ksteps > 1 ? ksteps - 1 : ksteps;
+#else
+        const int k_split = ksteps;
+#endif
+        if (elect_one()) issue(0, k_split);
+        int s1 = s + 1; uint32_t ph1 = ph;
+        if (s1 == stages) { s1 = 0; ph1 ^= 1u; }
+        have = false;
+        if (k_split < ksteps && i + 1 < n_it) {
+          const long long tf0 = TCW_NOW();
+          mbar_wait(&full[s1], ph1);
+          tc_fence_after();
+          TCW_ADD(w_full, tf0);
+          have = true;
+        }
+        if (elect_one()) {
+          issue(k_split, ksteps);
           umma_commit(&empty[s]);                 // frees the smem slot when these MMAs retire
         }
-        if (++s == stages) { s = 0; ph ^= 1u; }
+        s = s1; ph = ph1;
       }
       if (elect_one()) umma_commit(&acc_full[buf]);
       if (li == 0 && lane == 0) TR(4);
     }
+#ifdef PIPER_TC_WAIT_TRACE
+    if (p.trace && blockIdx.x == 0 && lane == 0) { p.trace[8] = w_acc; p.trace[9] = w_full; }
+#endif
   } else {
     // ===== epilogue: four warpgroups = (TMEM buffer, i.e. every other tile) x (half of the column chunks) =====
     const uint32_t group = ((uint32_t)(warp - 2) >> 2) % (uint32_t)TCP_NG, half = (uint32_t)(warp - 2) / (4u * TCP_NG);
@@ -944,6 +1120,9 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
     // tile did (MMAs retire in issue order), so the wait is sound.
     const uint32_t ng_eff = p.nbuf == 4 ? (uint32_t)TCP_NG : 2u;
     uint32_t li = 0, turn = 0;
+#ifdef PIPER_TC_WAIT_TRACE
+    long long e_wait = 0, e_busy = 0;   // trace: cycles warp 2 waited for an accumulator / spent in its epilogues
+#endif
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++li) {
       const bool mine = turn == group;
       if (++turn == ng_eff) turn = 0;
@@ -952,13 +1131,27 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
       const int mt = rest % m_tiles, ntile = rest / m_tiles;
       const uint32_t buf = p.nbuf == 4 ? (li & 3u) : (li & 1u);
       const uint32_t use = p.nbuf == 4 ? (li >> 2) : (li >> 1);
+#ifdef PIPER_TC_WAIT_TRACE
+      long long te0 = 0, te1 = 0;
+      if (p.trace) {   // waits do not consume the phase: the one inside tc_epilogue passes at once
+        te0 = clock64();
+        mbar_wait(&acc_full[buf], use & 1u);
+        te1 = clock64();
+      }
+#endif
       tc_epilogue(p, tmem_base + buf * acc_stride, mt * TC_BM, ntile, phase, warp, lane, &acc_full[buf], use & 1u,
                   tbuf_base + (warp - 2) * (32 * 36), (int)half, TCP_EG, bias_staged ? sbias : nullptr);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
+#ifdef PIPER_TC_WAIT_TRACE
+      if (p.trace) { e_wait += te1 - te0; e_busy += clock64() - te1; }
+#endif
       if (li == 0 && warp == 2 && lane == 0) TR(5);
     }
+#ifdef PIPER_TC_WAIT_TRACE
+    if (p.trace && blockIdx.x == 0 && warp == 2 && lane == 0) { p.trace[10] = e_wait; p.trace[11] = e_busy; }
+#endif
   }
   tc_fence_before();
   __syncthreads();
@@ -1054,16 +1247,30 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
     uint32_t pc = 32;
     while ((int)pc < p.nbuf * n_groups * a.nt) pc <<= 1;
     p.tmem_cols = pc;
-    const int sb = (p.sp1 ? 2 : 1) * TC_BM * w.kb * 2 + n_groups * a.nt * w.kb * 2;
+    // windowed activations (see TcKernelParams::pwin): plain multi-tap convolutions whose input exists group-planar
+    static const int pwin_env = [] { const char* e = getenv("PIPER_B200_TC_PWIN"); return e ? atoi(e) : 1; }();
+    const int span = (w.taps - 1) * a.tap_step;
+    if (a.in_planar) {
+      if (!pwin_env || w.taps < 2 || w.split || w.phase_cols || w.phases != 1 || w.kb != 64 || w.cin != w.cin_pad || a.tap_step < 1 ||
+          span > 64 || a.in_pad + a.in_off < 0 || a.out_mul != 1)
+        throw std::runtime_error("conv_tc: a group-planar input needs a plain multi-tap convolution with whole 64-channel K blocks");
+      p.pwin = TC_BM + ((span + 7) & ~7);
+      p.a_planar = static_cast<const uint16_t*>(a.in_planar);
+      p.a_rows = a.in_rows; p.a_pad = a.in_pad;
+      if ((int64_t)a.in_pad + a.in_off + (int64_t)((a.Q + TC_BM - 1) / TC_BM) * TC_BM + (p.pwin - TC_BM) > a.in_rows)
+        throw std::runtime_error("conv_tc: group-planar input has too few pad rows behind the signal");
+    }
+    const int ring = p.pwin ? TCP_WIN_SLOTS * p.pwin * 16 * (w.kb / 8) : 0;
+    const int sb = (p.pwin ? 0 : (p.sp1 ? 2 : 1) * TC_BM * w.kb * 2) + n_groups * a.nt * w.kb * 2;
     constexpr int TBUF_BYTES = TCP_NG * TCP_EG * 4 * 32 * 36 * 4;
     constexpr int SBIAS_BYTES = 2 * TC_SBIAS * 4;
-    int st = (TC_SMEM_MAX - 3072 - TBUF_BYTES - SBIAS_BYTES) / sb;   // 1 KB static + alignment slack + barriers
+    int st = (TC_SMEM_MAX - 3072 - TBUF_BYTES - SBIAS_BYTES - ring) / sb;   // 1 KB static + alignment slack + barriers
     if (st > TCP_MAX_STAGES) st = TCP_MAX_STAGES;
     if (st < 2) throw std::runtime_error("conv_tc: tile does not fit in shared memory");
     const int m_tiles = (a.Q + TC_BM - 1) / TC_BM;
     const int total = m_tiles * a.n_tiles * w.phases;
     const int grid = total < num_sms ? total : num_sms;
-    const size_t smem = (size_t)st * sb + 1024 + 512 + TBUF_BYTES + SBIAS_BYTES;
+    const size_t smem = (size_t)ring + (size_t)st * sb + 1024 + 512 + TBUF_BYTES + SBIAS_BYTES;
     double flops = 2.0 * a.Q * w.phases * w.taps * w.cin * (double)(a.n_groups * a.nt * a.n_tiles);
     if (w.phase_cols) {   // algorithmic work only: the zero blocks of the merged weights do not count
       int used = 0;
@@ -1073,17 +1280,18 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
     ProfScope ps(ex, Prof::CONV_TC, flops);
     static const bool trace_env = [] { const char* e = getenv("PIPER_B200_TC_TRACE"); return e && atoi(e) != 0; }();
     if (trace_env) {
-      if (cudaMalloc(&p.trace, 8 * sizeof(long long)) != cudaSuccess) throw std::runtime_error("conv_tc: trace buffer");
-      cudaMemsetAsync(p.trace, 0, 8 * sizeof(long long), ex.st);
+      if (cudaMalloc(&p.trace, 12 * sizeof(long long)) != cudaSuccess) throw std::runtime_error("conv_tc: trace buffer");
+      cudaMemsetAsync(p.trace, 0, 12 * sizeof(long long), ex.st);
     }
     launch_pdl(conv_tc_persist_kernel, dim3(grid), dim3(TCP_THREADS), smem, ex.st, ta, tbp, p, st, m_tiles, a.n_tiles, total);
     if (trace_env) {   // debug only: CTA 0's phase boundaries in cycles since its start
-      long long h[8];
+      long long h[12];
       cudaStreamSynchronize(ex.st);
       cudaMemcpy(h, p.trace, sizeof(h), cudaMemcpyDeviceToHost);
       cudaFree(p.trace);
-      fprintf(stderr, "conv_tc trace Q %d cin %d nt %d tiles %d grid %d stages %d: setup %lld pdl_wait %lld first_full %lld mma_done %lld epi_done %lld exit %lld\n",
-              a.Q, w.cin, a.nt, total, grid, st, h[1] - h[0], h[2] - h[0], h[3] - h[0], h[4] - h[0], h[5] - h[0], h[6] - h[0]);
+      fprintf(stderr, "conv_tc trace Q %d cin %d nt %d tiles %d grid %d stages %d: setup %lld pdl_wait %lld first_full %lld mma_done %lld epi_done %lld exit %lld | mma warp waited: accumulator %lld operands %lld | epilogue group 0: waited %lld busy %lld\n",
+              a.Q, w.cin, a.nt, total, grid, st, h[1] - h[0], h[2] - h[0], h[3] - h[0], h[4] - h[0], h[5] - h[0], h[6] - h[0], h[8], h[9],
+              h[10], h[11]);
     }
     if (const cudaError_t le = cudaPeekAtLastError(); le != cudaSuccess) {
       cudaFuncAttributes fa{};
@@ -1096,6 +1304,7 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
     ++ex.launches;
     return;
   }
+  if (a.in_planar) throw std::runtime_error("conv_tc: a group-planar input needs the persistent kernel");
   const CUtensorMap tb = make_map(w.w, (uint64_t)w.cin_pad, (uint64_t)w.phases * w.taps * w.cout, (uint64_t)w.cin_pad,
                                   w.kb, a.nt, a.f16);
   const int span = (w.taps - 1) * (a.tap_step < 0 ? -a.tap_step : a.tap_step);

@@ -66,6 +66,10 @@ struct TcEpi {
 struct TcConvArgs {
   const void* in = nullptr;      // 16-bit activations [R_in][ldin], view of `cin` channels
   int ldin = 0, R_in = 0, cin = 0;
+  // optional: the same activations group-planar [cin / 8][in_rows][8], row r at plane row in_pad + r, zero rows around
+  // the signal (at least -in_off in front, 128 + the tap span behind).  Plain multi-tap convolutions then load each
+  // K block's rows ONCE as a window and realise the taps as descriptor row offsets (persistent kernel); `in` is unused.
+  const void* in_planar = nullptr; int64_t in_rows = 0; int in_pad = 0;
   const TcW* w = nullptr;
   int Q = 0;                     // output positions (per phase)
   int tap_step = 1, in_off = 0;  // input row of tap t for position q: q + in_off + t*tap_step

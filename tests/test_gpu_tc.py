@@ -188,3 +188,38 @@ def test_tc_long_form_high_voice(prec, min_snr):
     assert snr_db(ref.audio[0], out.audio[0]) >= min_snr
     again = r.synthesize_batch([ids], *S.FIXTURE_SCALES)
     assert np.array_equal(out.audio[0], again.audio[0])
+
+
+@pytest.mark.timeout(240)
+def test_flow_window_operand_path_against_oracle(tmp_path):
+    """PIPER_B200_FLOW_WINDOW=1 (off by default): the WN in_layer convolutions take their operand as a row window of the
+    group-planar residual copy (conv_tc.h, TcConvArgs::in_planar).  The switch is read once per process, so the run is a
+    child process; its audio is checked against the oracle with the f16 tolerance and against the default path."""
+    import os
+    import subprocess
+    import sys
+    ids = fixture_ids(8)
+    ns, ls, nw = S.FIXTURE_SCALES
+    out = tmp_path / "win.npy"
+    here = os.path.dirname(os.path.abspath(__file__))
+    root = os.path.dirname(here)
+    code = (
+        "import sys, numpy as np\n"
+        "sys.path[:0] = [%r, %r, %r]\n"
+        "from common import S, voice_files, fixture_ids\n"
+        "from piper_b200.runtime import PiperCUDARuntime, Options\n"
+        "mp, cp = voice_files('medium')\n"
+        "rt = PiperCUDARuntime(mp, cp, Options(precision='f16'))\n"
+        "r = rt.synthesize_batch([fixture_ids(8), fixture_ids(2)], *S.FIXTURE_SCALES)\n"
+        "np.save(%r, r.audio[0])\n"
+        "rt.close()\n" % (root, os.path.join(root, "piper-swift_b200"), here, str(out)))
+    env = dict(os.environ, PIPER_B200_FLOW_WINDOW="1")
+    subprocess.run([sys.executable, "-c", code], check=True, env=env, timeout=200)
+    a = np.load(out)
+    o = oracle("medium").infer(ids, ns, ls, nw, refrng.noise_dp(len(ids)), noise_main_fn=refrng.noise_main)
+    snr_min, abs_max = TOL["f16"]
+    assert a.shape == o["audio"].shape
+    assert snr_db(o["audio"], a) >= snr_min
+    assert np.abs(a - o["audio"]).max() <= abs_max
+    d = rt("medium", "f16").synthesize_batch([ids, fixture_ids(2)], ns, ls, nw).audio[0]
+    assert np.abs(a - d).max() <= 2e-3     # same arithmetic, K blocks and taps accumulated in the other order

@@ -226,7 +226,7 @@ int main() {
   cudaFuncSetAttribute(umma_bench, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   const int iters = 4096;
   printf("N a_mode shift16 kb_b per_tap f16 : issue_cycles/mma total_cycles/mma  (math cycles at 4096 FMA/clk)\n");
-  int Ns[] = {32, 64, 128, 256};
+  int Ns[] = {32, 64, 96, 128, 192, 256};
   for (int f16 = 1; f16 >= 0; --f16)
   for (int N : Ns)
     for (int a_mode = 0; a_mode < 2; ++a_mode)
