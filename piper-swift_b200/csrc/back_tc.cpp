@@ -347,6 +347,17 @@ TcConvArgs tc_args(const TcW& w, const void* in, int ldin, int R, const int* row
   return a;
 }
 
+// Small calls (one utterance): a launch with fewer tiles than SMs lasts as long as one CTA's chain, and two thirds of
+// that chain is the epilogue of its nt / 32 column chunks.  Narrower column tiles spread the chunks over more SMs; the
+// accumulation order of an output element does not depend on the tile width, so results are bit-identical (same rule as
+// split_args in synthesize.cpp).  `cout` = columns per group.
+void narrow_small(TcConvArgs& a, int cout) {
+  const int m_tiles = (a.Q + 127) / 128;
+  for (int nt : {64, 32})
+    if (nt < a.nt && m_tiles * (cout / a.nt) * 2 <= 148 && cout % nt == 0) a.nt = nt;
+  a.n_tiles = cout / a.nt;
+}
+
 }  // namespace
 
 size_t back_tc_bytes(const Context& ctx, int Rf, int batch) {
@@ -414,6 +425,7 @@ FlowOut run_flow_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep)
       TcConvArgs a = tc_args(t.pre, zb + c.in_off, H, Rf, in.frow_utt, 1, f16);
       a.e[0].out_f32 = h; a.e[0].ld_f32 = H;
       hb_out(a.e[0]);
+      narrow_small(a, t.pre.cout);
       launch_conv_tc(ex, a);
     }
     for (int l = 0; l < L; ++l) {
@@ -423,6 +435,7 @@ FlowOut run_flow_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep)
         a.gate = 1; a.n_groups = 2;
         a.nt = pick_nt(H);
         a.n_tiles = H / a.nt;
+        narrow_small(a, H);
         a.e[0].row0 = 0; a.e[0].bias = t.in_layers[l].bias;
         a.e[1].row0 = H; a.e[1].bias = t.in_layers[l].bias + H;
         a.e[0].out_act = actsb + (noskip ? l * H : 0); a.e[0].ld_act = H * LA;
@@ -437,6 +450,7 @@ FlowOut run_flow_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep)
           TcConvArgs a = tc_args(t.res[l], actsb + l * H, H * LA, Rf, in.frow_utt, 1, f16);
           a.e[0].out_f32 = h; a.e[0].ld_f32 = H; a.e[0].res = h; a.e[0].ld_res = H;
           hb_out(a.e[0]);
+          narrow_small(a, t.res[l].cout);
           launch_conv_tc(ex, a);
         }
       } else {   // res | skip
@@ -464,6 +478,7 @@ FlowOut run_flow_tc(Context& ctx, Exec& ex, const BackInputs& in, float* z_keep)
       a.e[0].out_f32 = z + c.out_off; a.e[0].ld_f32 = H;
       a.e[0].res = z + c.out_off; a.e[0].ld_res = H;
       a.e[0].out_act = zb + c.out_off; a.e[0].ld_act = H;
+      narrow_small(a, noskip ? t.post_fused.cout : t.post.cout);
       launch_conv_tc(ex, a);
     }
   }
@@ -507,6 +522,7 @@ float* run_decoder_tc(Context& ctx, Exec& ex, const DecoderIn& in) {
     TcConvArgs a = tc_args(tv.dec_pre, zb, H, Rf, in.frow_utt, 1, f16);
     a.uttbias = in.cond_dec; a.ldub = v.hp.dec_c0;
     a.e[0].out_act = act[cur]; a.e[0].ld_act = v.hp.dec_c0; a.e[0].act_slope = 0.1f;
+    narrow_small(a, tv.dec_pre.cout);
     launch_conv_tc(ex, a);
   }
   int R = Rf, U = 1;

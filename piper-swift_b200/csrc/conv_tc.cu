@@ -227,6 +227,8 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
             const float4 x = lds128(sbs + (uint32_t)(pp * 16 + 4 * i) * 4u);
             b2[2 * i] = f2pack(x.x, x.y); b2[2 * i + 1] = f2pack(x.z, x.w);
           }
+          // (tried: one phase per round with the next round's load in flight during the arithmetic - tcgen05.wait::ld waits
+          // for every load of the thread, so the lookahead is one round at most; 36 bytes of spills, ups launches 50 % slower)
           for (int k0 = 0; k0 < ppt; k0 += 2) {   // two phases per round trip (four would spill at 166 registers)
             uint32_t t[2][16];
             tmem_ld16_async(lane_base + (uint32_t)(k0 * Cp + pp * 16), t[0]);
