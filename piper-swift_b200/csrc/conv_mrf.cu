@@ -923,6 +923,8 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
         cudaFuncSetAttribute(mrf_tc_kernel<32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
         cudaFuncSetAttribute(mrf_tc_kernel<64, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
         cudaFuncSetAttribute(mrf_tc_kernel<128, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
+        cudaFuncSetAttribute(mrf_tc_kernel<128, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
+        cudaFuncSetAttribute(mrf_tc_kernel<128, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
         cudaFuncSetAttribute(mrf_tc_kernel<32, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
         cudaFuncSetAttribute(mrf_tc_kernel<64, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess ||
         cudaFuncSetAttribute(mrf_tc_kernel<128, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX) != cudaSuccess)
@@ -1031,7 +1033,9 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
     cudaMemsetAsync(p.trace, 0, trace_words * 4, ex.st);
   }
   static const int eg_env = [] { const char* e = getenv("PIPER_B200_MRF_EG"); return e ? atoi(e) : 0; }();
-  const int eg = eg_env >= 2 && eg_env <= 5 ? eg_env : 4;
+  // epilogue warpgroups: four, three at C = 64 (re-swept after the packed epilogue of round 2: 1.99 -> 1.93 ms for the
+  // C = 64 stage with three, C = 32 is slower with three or five, profiles/r02_mrf_sweep_eg.log)
+  const int eg = eg_env >= 2 && eg_env <= 5 ? eg_env : (a.C == 64 ? 3 : 4);
   const int threads = 160 + 128 * eg;
   // plain launch on request (no_pdl): the row-range launches of the last stage must not be staged early - their CTAs would
   // take the SMs the instant the previous range retires, ahead of the copy stream's gather kernel that waits for that range
@@ -1044,7 +1048,9 @@ void launch_mrf_tc(Exec& ex, const MrfArgs& a) {
     else if (a.C == 64) L(mrf_tc_kernel<64, 4, true>, 160 + 128 * 4);
     else L(mrf_tc_kernel<32, 4, true>, 160 + 128 * 4);
   } else if (a.C == 128) {
-    L(mrf_tc_kernel<128, 4>, 160 + 128 * 4);
+    if (eg == 2) L(mrf_tc_kernel<128, 2>, threads);
+    else if (eg == 3) L(mrf_tc_kernel<128, 3>, threads);
+    else L(mrf_tc_kernel<128, 4>, 160 + 128 * 4);
   } else if (a.C == 32) {
     if (eg == 2) L(mrf_tc_kernel<32, 2>, threads);
     else if (eg == 3) L(mrf_tc_kernel<32, 3>, threads);
