@@ -34,6 +34,7 @@ struct TcKernelParams {
   int phases, ct_pad, out_mul;
   int gate, f16, window, a_col0, relu;
   int phase_cols;                   // merged polyphase ConvTranspose: columns per phase (0 = off)
+  int ppt;                          // phases per column tile (nt / phase_cols; a power of two)
   uint32_t tap_mask[8];             // per column tile: taps to run (merged polyphase weights are zero elsewhere)
   int split_kbc;                    // bf16x6 fp32 emulation: K blocks per operand plane (0 = off)
   int split2;                       // f16x3 fp32 emulation (two planes, two accumulators; uses split_kbc too)
@@ -46,6 +47,7 @@ struct TcKernelParams {
   TcEpi e[2];
   const float* uttbias; int ldub;
   const int* row_utt; int valid_div;
+  int valid_shift;                  // log2(valid_div) when it is a power of two, else -1
   uint32_t tmem_cols;
   int nbuf;                         // accumulator buffers in TMEM (persistent kernel): 2, or 4 when 4 tiles fit in 512 columns
   long long* trace;                 // debug (PIPER_B200_TC_TRACE=1): clock64 of CTA 0 at its phase boundaries
@@ -109,6 +111,24 @@ __device__ __forceinline__ void sts128u(uint32_t a, const uint4& v) {
   asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
+// (row tile, column tile, phase) of tile t of the persistent kernel's list, phase fastest.  Every role decodes every tile; the
+// three 32-bit divisions of the plain form cost ~250 cycles per tile and warp, which shows where a tile's epilogue is a
+// few thousand cycles: one phase needs none, a handful of column tiles a compare-subtract loop.
+__device__ __forceinline__ void tile_coords(const TcKernelParams& p, int t, int m_tiles, int n_tiles, int& phase, int& mt,
+                                            int& ntile) {
+  int rest = t;
+  phase = 0;
+  if (p.phases > 1) { phase = t % p.phases; rest = t / p.phases; }
+  if (n_tiles <= 8) {
+    ntile = 0;
+    while (rest >= m_tiles) { rest -= m_tiles; ++ntile; }
+    mt = rest;
+  } else {
+    ntile = rest / m_tiles;
+    mt = rest - ntile * m_tiles;
+  }
+}
+
 // Epilogue of one 128-row x (n_groups * nt) accumulator tile, run by the four warps of a warpgroup (TMEM lane
 // quarter = warp % 4): waits for `bar`, then bias / utterance bias / residual / accumulate / mask and the
 // fp32 and 16-bit stores, or the tanh * sigmoid gate.
@@ -121,7 +141,7 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
   const bool active = q < p.Q;
   const int orow = active ? q * p.out_mul + (p.phases > 1 ? phase : 0) : 0;
   int utt = 0;
-  if (active && p.row_utt) utt = p.row_utt[orow / p.valid_div];
+  if (active && p.row_utt) utt = p.row_utt[p.valid_shift >= 0 ? (orow >> p.valid_shift) : (orow / p.valid_div)];
   const bool valid = utt >= 0;
   mbar_wait(bar, bar_parity);
   tc_fence_after();
@@ -211,8 +231,9 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
       // each input row q, i.e. ppt consecutive OUTPUT rows (16 bytes each per plane).  Two planes at a time are
       // assembled in the warp's buffer as [plane][q][phase] and written with every lane storing an adjacent
       // 16-byte piece (512 contiguous bytes per instruction); the lane = row form touched 32 lines per store.
-      const int Cp = p.phase_cols, ppt = p.nt / Cp, ph0 = ntile * ppt;
+      const int Cp = p.phase_cols, ppt = p.ppt, ph0 = ntile * ppt;
       const int pieces = 32 * ppt;                       // per plane
+      const int ppt_shift = __ffs(ppt) - 1;
 #ifndef PIPER_TC_UPS_SCALAR
       if (sbias && em.bias) {
         // batched form: the TMEM loads of all phases of a 16-column slice are issued back to back and waited for once
@@ -255,7 +276,7 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
             uint16_t* plane = static_cast<uint16_t*>(em.out_act) +
                               ((size_t)(em.col0 / 8 + pp * 2 + pl) * em.act_rows + em.act_pad) * 8;
             for (int i = lane; i < pieces; i += 32) {
-              const int qq = i / ppt, sl = i - qq * ppt;
+              const int qq = i >> ppt_shift, sl = i & (ppt - 1);   // ppt is a power of two (checked at launch)
               if (!((act_mask >> qq) & 1u)) continue;
               const int k = sl ^ (qq & (ppt - 1));
               const size_t orow_r = (size_t)(row_base + qq) * p.out_mul + ph0 + k;
@@ -298,7 +319,7 @@ __device__ __forceinline__ void tc_epilogue(const TcKernelParams& p, uint32_t tm
           uint16_t* plane = static_cast<uint16_t*>(em.out_act) +
                             ((size_t)(em.col0 / 8 + pp * 2 + pl) * em.act_rows + em.act_pad) * 8;
           for (int i = lane; i < pieces; i += 32) {
-            const int qq = i / ppt, sl = i - qq * ppt;
+            const int qq = i >> ppt_shift, sl = i & (ppt - 1);
             if (!((act_mask >> qq) & 1u)) continue;
             const int k = sl ^ (qq & (ppt - 1));
             const size_t orow_r = (size_t)(row_base + qq) * p.out_mul + ph0 + k;
@@ -877,10 +898,12 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
     if (lane == 0) {
       int s = 0; uint32_t ph = 0;
       int as = 0; uint32_t aph = 0;
+      bool first_issued = false;   // trace: when the first stage's loads were issued
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         if (p.pwin) {
           // K block outermost: one window per K block, then the weight tiles of its taps
-          const int mt = t % m_tiles, ntile = t / m_tiles;
+          int phase_, mt, ntile;
+          tile_coords(p, t, m_tiles, n_tiles, phase_, mt, ntile);
           const int plane_bytes = p.pwin * 16;
           for (int kbi = 0; kbi < p.kblocks; ++kbi) {
             mbar_wait(&a_empty[as], aph ^ 1u);
@@ -903,6 +926,7 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
                 for (int g = 0; g < p.n_groups; ++g)
                   tma_load_2d(&tmap_b, &full[s], st + g * b_bytes, kbi * p.kb, wrow + p.e[g].row0);
               }
+              if (!first_issued) { first_issued = true; TR(7); }
               if (++s == stages) { s = 0; ph ^= 1u; }
             }
           }
@@ -910,8 +934,8 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
         }
         // phase fastest: the polyphase outputs of one row tile interleave in memory (row = q * stride + phase), so
         // they are produced back to back and merge in L2 instead of rewriting every line `phases` times
-        const int phase = t % p.phases, rest = t / p.phases;
-        const int mt = rest % m_tiles, ntile = rest / m_tiles;
+        int phase, mt, ntile;
+        tile_coords(p, t, m_tiles, n_tiles, phase, mt, ntile);
         const int m0 = mt * TC_BM;
         const int in_off = p.phases > 1 ? (phase + p.ct_pad) / p.phases : p.in_off;
         // split (fp32-emulation) weights: operand plane outermost, so that every small term of every tap is
@@ -941,6 +965,7 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
                     tma_load_2d(&tmap_b, &full[s], st + 2 * a_bytes + h * b_bytes, (h * kb_inner + kbi) * p.kb, wrow + p.e[0].row0);
                   }
                 }
+                if (!first_issued) { first_issued = true; TR(7); }
                 if (++s == stages) { s = 0; ph ^= 1u; }
                 continue;
               }
@@ -954,6 +979,7 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
                   tma_load_2d(&tmap_b, &full[s], st + a_bytes + g * b_bytes, (b_plane * kb_inner + kbi) * p.kb, wrow + p.e[g].row0);
                 }
               }
+              if (!first_issued) { first_issued = true; TR(7); }
               if (++s == stages) { s = 0; ph ^= 1u; }
             }
           }
@@ -978,7 +1004,8 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
 #endif
     const uint32_t nbuf = (uint32_t)p.nbuf;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++li) {
-      const int ntile_m = (t / p.phases) / m_tiles;
+      int phase_m, mt_m, ntile_m;
+      tile_coords(p, t, m_tiles, n_tiles, phase_m, mt_m, ntile_m);
       const int n_it = __popc(p.tap_mask[ntile_m & 7]) * p.kblocks;
       // With four buffers each epilogue warpgroup owns two: the MMAs of its next tile run while it still drains the
       // current one (with two, a group's MMA -> epilogue chain was serial, which small-K tiles cannot hide).
@@ -1129,8 +1156,8 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
       const bool mine = turn == group;
       if (++turn == ng_eff) turn = 0;
       if (!mine) continue;
-      const int phase = t % p.phases, rest = t / p.phases;
-      const int mt = rest % m_tiles, ntile = rest / m_tiles;
+      int phase, mt, ntile;
+      tile_coords(p, t, m_tiles, n_tiles, phase, mt, ntile);
       const uint32_t buf = p.nbuf == 4 ? (li & 3u) : (li & 1u);
       const uint32_t use = p.nbuf == 4 ? (li >> 2) : (li >> 1);
 #ifdef PIPER_TC_WAIT_TRACE
@@ -1142,7 +1169,7 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) conv_tc_persist_kernel(const _
       }
 #endif
       tc_epilogue(p, tmem_base + buf * acc_stride, mt * TC_BM, ntile, phase, warp, lane, &acc_full[buf], use & 1u,
-                  tbuf_base + (warp - 2) * (32 * 36), (int)half, TCP_EG, bias_staged ? sbias : nullptr);
+                  tbuf_base + (warp - 2) * (32 * 36), TCP_EG == 1 ? 0 : (int)half, TCP_EG, bias_staged ? sbias : nullptr);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
@@ -1208,6 +1235,8 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
   p.e[0] = a.e[0]; p.e[1] = w.split == 2 ? a.e[0] : a.e[1];
   p.uttbias = a.uttbias; p.ldub = a.ldub;
   p.row_utt = a.row_utt; p.valid_div = a.valid_div < 1 ? 1 : a.valid_div;
+  p.valid_shift = -1;
+  if ((p.valid_div & (p.valid_div - 1)) == 0) { p.valid_shift = 0; while ((1 << p.valid_shift) < p.valid_div) ++p.valid_shift; }
   uint32_t cols = 32;
   while ((int)cols < a.n_groups * a.nt) cols <<= 1;
   p.tmem_cols = cols;
@@ -1219,6 +1248,7 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
         (ppt_ & (ppt_ - 1)) || ppt_ > 4)   // ppt: power of two, [2 planes][32][ppt] 16-byte pieces must fit the warp buffer
       throw std::runtime_error("conv_tc: bad tiling for merged polyphase weights");
     const int ppt = a.nt / w.phase_cols;   // phases per column tile
+    p.ppt = ppt;
     for (int t = 0; t < a.n_tiles; ++t) {
       uint32_t m = 0;
       for (int ph = t * ppt; ph < (t + 1) * ppt && ph < 16; ++ph) m |= w.phase_tapmask[ph];
@@ -1291,8 +1321,8 @@ void launch_conv_tc(Exec& ex, const TcConvArgs& a) {
       cudaStreamSynchronize(ex.st);
       cudaMemcpy(h, p.trace, sizeof(h), cudaMemcpyDeviceToHost);
       cudaFree(p.trace);
-      fprintf(stderr, "conv_tc trace Q %d cin %d nt %d tiles %d grid %d stages %d: setup %lld pdl_wait %lld first_full %lld mma_done %lld epi_done %lld exit %lld | mma warp waited: accumulator %lld operands %lld | epilogue group 0: waited %lld busy %lld\n",
-              a.Q, w.cin, a.nt, total, grid, st, h[1] - h[0], h[2] - h[0], h[3] - h[0], h[4] - h[0], h[5] - h[0], h[6] - h[0], h[8], h[9],
+      fprintf(stderr, "conv_tc trace Q %d cin %d nt %d tiles %d grid %d stages %d: setup %lld pdl_wait %lld first_issue %lld first_full %lld mma_done %lld epi_done %lld exit %lld | mma warp waited: accumulator %lld operands %lld | epilogue group 0: waited %lld busy %lld\n",
+              a.Q, w.cin, a.nt, total, grid, st, h[1] - h[0], h[2] - h[0], h[7] - h[0], h[3] - h[0], h[4] - h[0], h[5] - h[0], h[6] - h[0], h[8], h[9],
               h[10], h[11]);
     }
     if (const cudaError_t le = cudaPeekAtLastError(); le != cudaSuccess) {
