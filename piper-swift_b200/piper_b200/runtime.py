@@ -15,6 +15,7 @@ from __future__ import annotations
 import ctypes as C
 import math
 import os
+from collections.abc import Sequence as _SequenceABC
 from dataclasses import dataclass
 from typing import Iterator, List, Optional, Sequence
 
@@ -231,6 +232,30 @@ class PiperAudioChunk:           # PiperAudio.swift:13-25
     samples: np.ndarray
     is_final: bool
 
+
+
+class SliceViews(_SequenceABC):
+    """Per-utterance views of one flat result array, made on access.  A list of 256 numpy slices per field cost 0.2-0.4 ms
+    of host time inside every call - 3 % of the end-to-end step of the 256-utterance batch."""
+    __slots__ = ("flat", "offs")
+
+    def __init__(self, flat: np.ndarray, offs):
+        self.flat = flat
+        self.offs = offs.tolist() if isinstance(offs, np.ndarray) else list(offs)
+
+    def __len__(self) -> int:
+        return len(self.offs) - 1
+
+    def __getitem__(self, i):
+        n = len(self.offs) - 1
+        if isinstance(i, slice):
+            return [self[k] for k in range(*i.indices(n))]
+        i = int(i)
+        if i < 0:
+            i += n
+        if not 0 <= i < n:
+            raise IndexError("utterance index out of range")
+        return self.flat[self.offs[i]:self.offs[i + 1]]
 
 @dataclass
 class BatchResult:
@@ -478,7 +503,7 @@ class PiperCUDARuntime:
         n_ids = int(lengths.sum())
         dur_all = np.ctypeslib.as_array(rs.durations, shape=(n_ids,)).copy()
         id_off = np.concatenate([[0], np.cumsum(lengths)])
-        durs = [dur_all[id_off[b]:id_off[b + 1]] for b in range(B)]
+        durs = SliceViews(dur_all, id_off)
         out = BatchResult([], fl, durs, int(rs.total_samples), int(rs.total_frames))
         if keep_on_device:
             out.device_ptr = int(rs.audio)
@@ -491,15 +516,15 @@ class PiperCUDARuntime:
             p = np.ctypeslib.as_array(C.cast(rs.pcm16, C.POINTER(C.c_int16)), shape=(total,))
             if copy and own:
                 p = p.copy()
-            out.pcm16 = [p[offs[b]:offs[b + 1]] for b in range(B)]
+            out.pcm16 = SliceViews(p, offs)
             return out
         flat = np.ctypeslib.as_array(C.cast(rs.audio, C.POINTER(C.c_float)), shape=(total,))
         if copy and own:
             flat = flat.copy()
-        out.audio = [flat[offs[b]:offs[b + 1]] for b in range(B)]
+        out.audio = SliceViews(flat, offs)
         if pcm16:
             p = np.ctypeslib.as_array(C.cast(rs.pcm16, C.POINTER(C.c_int16)), shape=(total,)).copy()
-            out.pcm16 = [p[offs[b]:offs[b + 1]] for b in range(B)]
+            out.pcm16 = SliceViews(p, offs)
         return out
 
     # ---- parity hooks -------------------------------------------------------------------------------
