@@ -86,3 +86,20 @@ def test_ipa_to_ids_follows_the_reference_rule():
     rc = lib.piper_b200_config_ipa_to_ids(cfg.encode(), b"hello", buf, 4, C.byref(n))
     assert rc == 7 and n.value == 12 and list(buf) == [1, id_of["h"], 0, id_of["e"]]   # capacity: count still reported
     assert lib.piper_b200_config_ipa_to_ids(b"/nonexistent.json", b"a", buf, 4, C.byref(n)) == 2
+
+
+def test_slice_views_behave_like_the_list_they_replace():
+    """BatchResult.audio / .pcm16 / .durations are views made on access (runtime.SliceViews): same indexing, iteration,
+    slicing and emptiness rules as the list of per-utterance arrays, including empty utterances."""
+    import numpy as np
+    flat = np.arange(10, dtype=np.float32)
+    v = runtime.SliceViews(flat, np.array([0, 3, 3, 10], dtype=np.int64))
+    assert len(v) == 3 and bool(v)
+    assert v[0].tolist() == [0, 1, 2] and v[1].size == 0 and v[-1].tolist() == list(range(3, 10))
+    assert [a.size for a in v] == [3, 0, 7]
+    assert [a.tolist() for a in v[0:2]] == [[0, 1, 2], []]
+    assert np.array_equal(np.concatenate(v), flat)
+    assert v[2].base is flat or v[2].base is flat.base          # views, not copies
+    with pytest.raises(IndexError):
+        v[3]
+    assert len(runtime.SliceViews(flat[:0], [0])) == 0 and not runtime.SliceViews(flat[:0], [0])
