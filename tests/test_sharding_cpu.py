@@ -201,3 +201,30 @@ def test_pool_gathers_in_original_order():
         assert res.rank_of[i] == next(r for r, s in enumerate(pool.last_shards) if i in s)
     assert pool._bytes_per_id > HOP * 4          # the short first estimate was grown
     pool.close()
+
+
+def test_arena_views_layout_equals_the_per_utterance_walk():
+    """sharding.arena_views_layout (vectorised: rank-major arrays + one scatter) against the plain walk over every rank's
+    utterances, random shards including empty ranks and empty batches."""
+    import numpy as np
+    from piper_b200.sharding import arena_views_layout, shard_utterances, ArenaViews
+    rng = np.random.default_rng(7)
+    for _ in range(100):
+        world, n = int(rng.integers(1, 9)), int(rng.integers(0, 40))
+        lengths = [int(x) for x in rng.integers(1, 200, n)]
+        shards = shard_utterances(lengths, world)
+        table = np.zeros((world, max(len(s) for s in shards) + 1), np.int64)
+        for r, s in enumerate(shards):
+            table[r, 1:1 + len(s)] = rng.integers(0, 500, len(s))
+        offs = [int(x) * 4096 for x in np.cumsum(rng.integers(0, 10 ** 6, world))]
+        starts, nbytes, frames, rank_of = arena_views_layout(shards, table, offs, 1024)
+        for r, s in enumerate(shards):
+            at = offs[r]
+            for j, i in enumerate(s):
+                f = int(table[r, 1 + j])
+                assert (starts[i], nbytes[i], frames[i], rank_of[i]) == (at, f * 1024, f, r)
+                at += f * 1024
+    whole = np.arange(64, dtype=np.uint8)
+    v = ArenaViews(whole, np.array([8, 0, 16]), np.array([8, 4, 0]), np.float32)
+    assert len(v) == 3 and v[0].dtype == np.float32 and v[0].size == 2 and v[1].size == 1 and v[2].size == 0
+    assert v[0].tobytes() == whole[8:16].tobytes() and [a.size for a in v] == [2, 1, 0]
