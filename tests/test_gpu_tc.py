@@ -178,7 +178,10 @@ def test_tc_ragged_batch_leaves_in_row_ranges():
 def test_tc_long_form_high_voice(prec, min_snr):
     """BASELINE config 4 shape in the tensor-core modes: one long utterance of the ResBlock1 voice, so that every
     fused ResBlock1 unit launch walks several windows per CTA (the 28-id parity cases fit in one); against the fp32
-    CUDA path (durations exact, audio SNR), and twice (idempotence)."""
+    CUDA path (durations exact, audio SNR), and twice (idempotence).
+    This is also the regression case of the round-1 hang (tools/hang_repro.py: `high` voice, one
+    600-id utterance, seed 11): the ResBlock1 unit launches run in the streamed weight-ring order with ring = k = 11,
+    the geometry whose parity-aliased mbarrier wait hung before the fix - twice per precision, under the timeout."""
     ids = synthetic_utterances(1, 256, 600, 600, seed=11)[0]
     ref = rt("high", "fp32").synthesize_batch([ids], *S.FIXTURE_SCALES)
     r = rt("high", prec)
